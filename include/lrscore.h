@@ -1,0 +1,128 @@
+/*
+ * liblrscore -- C ABI of the B200 (sm_100a) logistic-regression scoring engine.
+ *
+ * This is the drop-in boundary for the hot path behind mlAPI's POST /predict.  The reference has
+ * no FFI layer of its own: `main.py` calls an unpickled scikit-learn estimator
+ * (REF/main.py:19-22).  Each entry point below names the reference call it replaces, so that a
+ * maintainer can bind it (ctypes stub in INTEGRATION.md) where `loaded_model.predict(...)` and
+ * `loaded_model.predict_proba(...)` are called today.
+ *
+ * Conventions
+ *   - plain C symbols, no exceptions; every call returns an int status (LR_OK == 0) and leaves a
+ *     message retrievable with lr_last_error() (thread-local) on failure;
+ *   - all matrices are row-major fp32 unless stated; "n_scores" is coef_.shape[0] (1 for a binary
+ *     model, C for a C-class multinomial one); a probability row has max(n_scores, 2) columns;
+ *   - `*_dev` pointers are device pointers on the model's device (a torch tensor's data_ptr()
+ *     works); `*_host` pointers are host pointers (pinned memory makes the copies asynchronous);
+ *   - a model is immutable after creation: concurrent lr_score calls on distinct streams are safe;
+ *     lr_score_host serialises on the model's own staging buffers;
+ *   - there is no CPU fallback: without a CUDA device every call fails with LR_ERR_CUDA.
+ */
+#ifndef LRSCORE_H_
+#define LRSCORE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LR_OK             0
+#define LR_ERR_INVALID    1   /* bad argument (shape, null pointer, alignment that no path accepts) */
+#define LR_ERR_CUDA       2   /* a CUDA runtime/driver call failed; lr_last_error() has the text   */
+#define LR_ERR_NONFINITE  3   /* at least one row scored to NaN/inf (non-finite X), see below      */
+#define LR_ERR_LIMIT      4   /* request exceeds a documented fixed capacity                         */
+
+/* Which kernel family serves a (model, n_rows) pair; see DESIGN.md "Kernels". */
+#define LR_PATH_AUTO     0
+#define LR_PATH_NARROW   1    /* fused row-dot + sigmoid/softmax, few lanes per row               */
+#define LR_PATH_WIDE     2    /* binary, large d: row-block streaming, W re-used across 8 rows    */
+#define LR_PATH_GEMM     3    /* multinomial: TMA-fed tcgen05 (3xTF32) GEMM + fused softmax       */
+#define LR_PATH_GENERIC  4    /* any shape: tiled SIMT GEMM + row softmax                         */
+
+typedef struct lr_model lr_model;
+
+/* Thread-local text of the last failure on this thread ("" if none). */
+const char* lr_last_error(void);
+
+/* Library ABI version (bumped on any signature change). */
+int lr_abi_version(void);
+
+/* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
+uint64_t lr_launch_count(void);
+
+/*
+ * Model loader.  Replaces `pickle.load(open('LRClassifier.pkl','rb'))` at REF/main.py:19 as far as
+ * the device is concerned: takes the estimator's float64 `coef_` (n_scores x n_features, row-major,
+ * contiguous -- note sklearn's lbfgs leaves it F-ordered, copy first) and `intercept_` (n_scores)
+ * and makes device-resident fp32 copies (plus the padded / TF32-split layouts the kernels want).
+ */
+int lr_model_create(const double* coef, const double* intercept, int32_t n_scores,
+                    int32_t n_features, int32_t device, lr_model** out);
+void lr_model_destroy(lr_model* m);
+
+int lr_model_info(const lr_model* m, int32_t* n_scores, int32_t* n_features, int32_t* device);
+
+/* Force a kernel family (tests / profiling); LR_PATH_AUTO restores the dispatcher.  A path that
+ * cannot serve the model's shape makes the next lr_score fail with LR_ERR_INVALID. */
+int lr_model_set_path(lr_model* m, int32_t path);
+/* The path lr_score would take for n_rows rows laid out with row pitch ldx at address X_dev. */
+int lr_model_select_path(const lr_model* m, const float* X_dev, int64_t n_rows, int64_t ldx,
+                         int32_t* path);
+
+/*
+ * The hot path.  One call replaces, for n_rows rows at once, the pair
+ *     loaded_model.predict(data_in)                 REF/main.py:21
+ *     loaded_model.predict_proba(data_in).max()     REF/main.py:22
+ * i.e. sklearn's decision_function (SK/linear_model/_base.py:366-396), predict (:398-427) and
+ * predict_proba (SK/linear_model/_logistic.py:1595-1625; sigmoid arm _base.py:429-440, softmax arm
+ * SK/utils/extmath.py:985-1024), fused so that X is read once.
+ *
+ *   X_dev        n_rows x n_features fp32, row pitch ldx elements (ldx >= n_features)
+ *   proba_dev    n_rows x max(n_scores,2) fp32, dense          or NULL
+ *   decision_dev n_rows (binary) / n_rows x n_scores fp32       or NULL
+ *   label_dev    n_rows int32 index into classes_ (binary: score > 0; else first argmax)  or NULL
+ *   maxprob_dev  n_rows fp32, the row's largest class probability                          or NULL
+ *   stream       cudaStream_t (NULL = legacy default stream)
+ *
+ * Asynchronous: returns once the work is enqueued.  n_rows == 0 is a no-op.  Rows whose score is
+ * not finite (NaN/inf in X -- sklearn raises ValueError for those, _base.py:385-389) are counted in
+ * a device-side status word, read with lr_model_take_nonfinite().
+ */
+int lr_score(lr_model* m, const float* X_dev, int64_t n_rows, int64_t ldx,
+             float* proba_dev, float* decision_dev, int32_t* label_dev, float* maxprob_dev,
+             void* stream);
+
+/* Synchronise `stream`, return the number of non-finite rows seen since the last call, and reset. */
+int lr_model_take_nonfinite(lr_model* m, void* stream, uint64_t* n_rows_nonfinite);
+
+/*
+ * Same contract as lr_score with HOST buffers: rows are streamed through device staging buffers in
+ * chunks (H2D copy, kernel, D2H copy overlapped on three streams) and the call returns when every
+ * output is in host memory.  This is the call the estimator wrapper and the /predict micro-batcher
+ * make, and the one bench.py's `e2e` figure times.  Returns LR_ERR_NONFINITE (outputs still
+ * written) when a row scored to NaN/inf.
+ */
+int lr_score_host(lr_model* m, const float* X_host, int64_t n_rows, int64_t ldx,
+                  float* proba_host, float* decision_host, int32_t* label_host,
+                  float* maxprob_host);
+
+/* Rows per staging chunk used by lr_score_host (0 = default: about 32 MiB of X per chunk). */
+int lr_model_set_host_chunk_rows(lr_model* m, int64_t rows);
+
+/*
+ * Page-locked host memory for the buffers handed to lr_score_host (the /predict micro-batcher's
+ * staging rows, bench.py's e2e inputs).  With pageable memory the copies still work but the driver
+ * stages them and the three-stream overlap is lost.  No reference counterpart: REF/main.py:20
+ * builds a Python list per request.
+ */
+int lr_host_alloc(void** ptr, uint64_t bytes);
+int lr_host_free(void* ptr);
+/* Pin / unpin an existing host range in place (e.g. a numpy array's buffer). */
+int lr_host_register(void* ptr, uint64_t bytes);
+int lr_host_unregister(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LRSCORE_H_ */

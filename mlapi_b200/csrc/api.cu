@@ -1,0 +1,319 @@
+// C ABI of liblrscore (see include/lrscore.h): model loader, path dispatch, device and host entry
+// points.  Everything here is host code; the kernels live in narrow.cu / wide.cu / generic.cu /
+// gemm_tcgen05.cu.
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+namespace lrs {
+
+static thread_local std::string t_last_error;
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const std::string& msg) { t_last_error = msg; }
+int fail(int code, const std::string& msg) {
+    t_last_error = msg;
+    return code;
+}
+
+// Keeps the caller's current device intact across a call.
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; }
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        int cur = -1;
+        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+    }
+};
+
+// Device staging for lr_score_host: kSlots chunks in flight, each on its own stream
+// (H2D copy -> kernel -> D2H copies), so the two copy engines and the SMs overlap.
+struct HostStage {
+    static constexpr int kSlots = 3;
+    std::mutex mu;
+    int64_t chunk_rows = 0;
+    int64_t pitch = 0;        // staged row pitch in elements (n_features rounded up to 4)
+    float* x[kSlots] = {};
+    float* proba[kSlots] = {};
+    float* decision[kSlots] = {};
+    int32_t* label[kSlots] = {};
+    float* maxprob[kSlots] = {};
+    cudaStream_t stream[kSlots] = {};
+    void release() {
+        for (int i = 0; i < kSlots; ++i) {
+            cudaFree(x[i]); cudaFree(proba[i]); cudaFree(decision[i]); cudaFree(label[i]); cudaFree(maxprob[i]);
+            if (stream[i]) cudaStreamDestroy(stream[i]);
+            x[i] = proba[i] = decision[i] = maxprob[i] = nullptr;
+            label[i] = nullptr;
+            stream[i] = nullptr;
+        }
+        chunk_rows = 0;
+    }
+};
+
+static int select_path(const Model& m, const ScoreArgs& a) {
+    if (m.forced_path != LR_PATH_AUTO) return m.forced_path;
+    if (m.n_scores == 1) {
+        if (m.Wn && m.n_features < 1024) return LR_PATH_NARROW;
+        if (wide_supports(m, a)) return LR_PATH_WIDE;
+        if (m.Wn) return LR_PATH_NARROW;
+        return LR_PATH_GENERIC;
+    }
+    if (m.Wn) return LR_PATH_NARROW;
+    if (gemm_supports(m, a)) return LR_PATH_GEMM;
+    return LR_PATH_GENERIC;
+}
+
+static int dispatch(const Model& m, const ScoreArgs& a) {
+    switch (select_path(m, a)) {
+        case LR_PATH_NARROW: return narrow_launch(m, a);
+        case LR_PATH_WIDE: return wide_launch(m, a);
+        case LR_PATH_GEMM: return gemm_launch(m, a);
+        case LR_PATH_GENERIC: return generic_launch(m, a);
+    }
+    return fail(LR_ERR_INVALID, "unknown path id");
+}
+
+static int check_args(const Model* m, const void* X, int64_t n_rows, int64_t ldx) {
+    if (!m) return fail(LR_ERR_INVALID, "model is NULL");
+    if (n_rows < 0) return fail(LR_ERR_INVALID, "n_rows is negative");
+    if (n_rows > 0 && !X) return fail(LR_ERR_INVALID, "X is NULL");
+    if (ldx < m->n_features)
+        return fail(LR_ERR_INVALID, "row pitch ldx (" + std::to_string(ldx) + ") is smaller than n_features (" +
+                                        std::to_string(m->n_features) + ")");
+    return LR_OK;
+}
+
+}  // namespace lrs
+
+using namespace lrs;
+
+extern "C" {
+
+const char* lr_last_error(void) { return t_last_error.c_str(); }
+int lr_abi_version(void) { return 1; }
+uint64_t lr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int lr_model_create(const double* coef, const double* intercept, int32_t n_scores,
+                    int32_t n_features, int32_t device, lr_model** out) {
+    if (!out) return fail(LR_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    if (!coef || !intercept) return fail(LR_ERR_INVALID, "coef / intercept is NULL");
+    if (n_scores < 1 || n_features < 1) return fail(LR_ERR_INVALID, "n_scores and n_features must be >= 1");
+    int count = 0;
+    LRS_CUDA(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count)
+        return fail(LR_ERR_INVALID, "device " + std::to_string(device) + " out of range (" + std::to_string(count) + " visible)");
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(LR_ERR_CUDA, "cudaSetDevice failed");
+    cudaDeviceProp prop;
+    LRS_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(LR_ERR_CUDA, std::string("liblrscore is built for sm_100a only; device is ") + prop.name +
+                                     " (sm_" + std::to_string(prop.major) + std::to_string(prop.minor) + ")");
+
+    Model* m = new Model();
+    m->device = device;
+    m->n_scores = n_scores;
+    m->n_features = n_features;
+    m->n_out = n_scores < 2 ? 2 : n_scores;
+    m->num_sms = prop.multiProcessorCount;
+
+    const size_t nw = (size_t)n_scores * n_features;
+    std::vector<float> w32(nw), b32(n_scores);
+    for (size_t i = 0; i < nw; ++i) w32[i] = (float)coef[i];
+    for (int i = 0; i < n_scores; ++i) b32[i] = (float)intercept[i];
+
+    int rc = LR_OK;
+    auto bail = [&](int code) { lr_model_destroy(reinterpret_cast<lr_model*>(m)); return code; };
+    if (cudaMalloc(&m->W, nw * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&m->b, n_scores * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&m->status, 4 * sizeof(unsigned long long)) != cudaSuccess)
+        return bail(fail(LR_ERR_CUDA, std::string("cudaMalloc(model): ") + cudaGetErrorString(cudaGetLastError())));
+    if (cudaMemcpy(m->W, w32.data(), nw * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(m->b, b32.data(), n_scores * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemset(m->status, 0, 4 * sizeof(unsigned long long)) != cudaSuccess)
+        return bail(fail(LR_ERR_CUDA, std::string("upload(model): ") + cudaGetErrorString(cudaGetLastError())));
+    if ((rc = narrow_prepare(*m, w32.data(), b32.data())) != LR_OK) return bail(rc);
+    if ((rc = gemm_prepare(*m, coef, intercept)) != LR_OK) return bail(rc);
+    m->stage = new HostStage();
+    *out = reinterpret_cast<lr_model*>(m);
+    return LR_OK;
+}
+
+void lr_model_destroy(lr_model* h) {
+    if (!h) return;
+    Model* m = reinterpret_cast<Model*>(h);
+    DeviceGuard guard(m->device);
+    cudaDeviceSynchronize();
+    if (m->stage) { m->stage->release(); delete m->stage; }
+    gemm_destroy(*m);
+    cudaFree(m->W); cudaFree(m->b); cudaFree(m->Wn); cudaFree(m->bn); cudaFree(m->status);
+    delete m;
+}
+
+int lr_model_info(const lr_model* h, int32_t* n_scores, int32_t* n_features, int32_t* device) {
+    if (!h) return fail(LR_ERR_INVALID, "model is NULL");
+    const Model* m = reinterpret_cast<const Model*>(h);
+    if (n_scores) *n_scores = m->n_scores;
+    if (n_features) *n_features = m->n_features;
+    if (device) *device = m->device;
+    return LR_OK;
+}
+
+int lr_model_set_path(lr_model* h, int32_t path) {
+    if (!h) return fail(LR_ERR_INVALID, "model is NULL");
+    if (path < LR_PATH_AUTO || path > LR_PATH_GENERIC) return fail(LR_ERR_INVALID, "unknown path id");
+    reinterpret_cast<Model*>(h)->forced_path = path;
+    return LR_OK;
+}
+
+int lr_model_select_path(const lr_model* h, const float* X_dev, int64_t n_rows, int64_t ldx, int32_t* path) {
+    if (!h || !path) return fail(LR_ERR_INVALID, "model / path is NULL");
+    const Model* m = reinterpret_cast<const Model*>(h);
+    ScoreArgs a{X_dev, n_rows, ldx, nullptr, nullptr, nullptr, nullptr, nullptr};
+    *path = select_path(*m, a);
+    return LR_OK;
+}
+
+int lr_score(lr_model* h, const float* X_dev, int64_t n_rows, int64_t ldx, float* proba_dev,
+             float* decision_dev, int32_t* label_dev, float* maxprob_dev, void* stream) {
+    Model* m = reinterpret_cast<Model*>(h);
+    int rc = check_args(m, X_dev, n_rows, ldx);
+    if (rc != LR_OK) return rc;
+    if (n_rows == 0) return LR_OK;
+    DeviceGuard guard(m->device);
+    if (!guard.ok) return fail(LR_ERR_CUDA, "cudaSetDevice failed");
+    ScoreArgs a{X_dev, n_rows, ldx, proba_dev, decision_dev, label_dev, maxprob_dev,
+                reinterpret_cast<cudaStream_t>(stream)};
+    return dispatch(*m, a);
+}
+
+int lr_model_take_nonfinite(lr_model* h, void* stream, uint64_t* out) {
+    if (!h || !out) return fail(LR_ERR_INVALID, "model / out is NULL");
+    Model* m = reinterpret_cast<Model*>(h);
+    DeviceGuard guard(m->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    unsigned long long v = 0;
+    LRS_CUDA(cudaMemcpyAsync(&v, m->status, sizeof(v), cudaMemcpyDeviceToHost, s));
+    LRS_CUDA(cudaMemsetAsync(m->status, 0, sizeof(v), s));
+    LRS_CUDA(cudaStreamSynchronize(s));
+    *out = v;
+    return LR_OK;
+}
+
+int lr_model_set_host_chunk_rows(lr_model* h, int64_t rows) {
+    if (!h) return fail(LR_ERR_INVALID, "model is NULL");
+    if (rows < 0) return fail(LR_ERR_INVALID, "rows is negative");
+    Model* m = reinterpret_cast<Model*>(h);
+    std::lock_guard<std::mutex> lock(m->stage->mu);
+    DeviceGuard guard(m->device);
+    cudaDeviceSynchronize();
+    m->stage->release();
+    m->host_chunk_rows = rows;
+    return LR_OK;
+}
+
+static int stage_prepare(Model& m, HostStage& st) {
+    if (st.chunk_rows) return LR_OK;
+    const int64_t pitch = ((int64_t)m.n_features + 3) / 4 * 4;
+    int64_t rows = m.host_chunk_rows;
+    if (rows <= 0) {
+        // ~32 MiB of X per chunk: large enough to run PCIe at full rate, small enough that the
+        // first kernel starts early; at least 8 rows so that wide models still batch.
+        rows = (32ll << 20) / (pitch * (int64_t)sizeof(float));
+        if (rows < 8) rows = 8;
+    }
+    for (int i = 0; i < HostStage::kSlots; ++i) {
+        LRS_CUDA(cudaMalloc(&st.x[i], rows * pitch * sizeof(float)));
+        LRS_CUDA(cudaMalloc(&st.proba[i], rows * m.n_out * sizeof(float)));
+        LRS_CUDA(cudaMalloc(&st.decision[i], rows * m.n_scores * sizeof(float)));
+        LRS_CUDA(cudaMalloc(&st.label[i], rows * sizeof(int32_t)));
+        LRS_CUDA(cudaMalloc(&st.maxprob[i], rows * sizeof(float)));
+        LRS_CUDA(cudaStreamCreateWithFlags(&st.stream[i], cudaStreamNonBlocking));
+    }
+    st.pitch = pitch;
+    st.chunk_rows = rows;
+    return LR_OK;
+}
+
+int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
+                  float* decision_host, int32_t* label_host, float* maxprob_host) {
+    Model* m = reinterpret_cast<Model*>(h);
+    int rc = check_args(m, X_host, n_rows, ldx);
+    if (rc != LR_OK) return rc;
+    if (n_rows == 0) return LR_OK;
+    DeviceGuard guard(m->device);
+    if (!guard.ok) return fail(LR_ERR_CUDA, "cudaSetDevice failed");
+    HostStage& st = *m->stage;
+    std::lock_guard<std::mutex> lock(st.mu);
+    if ((rc = stage_prepare(*m, st)) != LR_OK) { st.release(); return rc; }
+
+    const int64_t d = m->n_features;
+    int slot = 0;
+    for (int64_t r0 = 0; r0 < n_rows; r0 += st.chunk_rows, slot = (slot + 1) % HostStage::kSlots) {
+        const int64_t rows = (n_rows - r0 < st.chunk_rows) ? (n_rows - r0) : st.chunk_rows;
+        cudaStream_t s = st.stream[slot];
+        const float* src = X_host + r0 * ldx;
+        if (ldx == st.pitch) {
+            LRS_CUDA(cudaMemcpyAsync(st.x[slot], src, rows * ldx * sizeof(float), cudaMemcpyHostToDevice, s));
+        } else {
+            LRS_CUDA(cudaMemcpy2DAsync(st.x[slot], st.pitch * sizeof(float), src, ldx * sizeof(float),
+                                       d * sizeof(float), rows, cudaMemcpyHostToDevice, s));
+        }
+        ScoreArgs a{st.x[slot], rows, st.pitch,
+                    proba_host ? st.proba[slot] : nullptr, decision_host ? st.decision[slot] : nullptr,
+                    label_host ? st.label[slot] : nullptr, maxprob_host ? st.maxprob[slot] : nullptr, s};
+        if ((rc = dispatch(*m, a)) != LR_OK) { cudaDeviceSynchronize(); return rc; }
+        if (proba_host)
+            LRS_CUDA(cudaMemcpyAsync(proba_host + r0 * m->n_out, st.proba[slot], rows * m->n_out * sizeof(float),
+                                     cudaMemcpyDeviceToHost, s));
+        if (decision_host)
+            LRS_CUDA(cudaMemcpyAsync(decision_host + r0 * m->n_scores, st.decision[slot],
+                                     rows * m->n_scores * sizeof(float), cudaMemcpyDeviceToHost, s));
+        if (label_host)
+            LRS_CUDA(cudaMemcpyAsync(label_host + r0, st.label[slot], rows * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+        if (maxprob_host)
+            LRS_CUDA(cudaMemcpyAsync(maxprob_host + r0, st.maxprob[slot], rows * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    for (int i = 0; i < HostStage::kSlots; ++i) LRS_CUDA(cudaStreamSynchronize(st.stream[i]));
+    unsigned long long bad = 0;
+    LRS_CUDA(cudaMemcpy(&bad, m->status, sizeof(bad), cudaMemcpyDeviceToHost));
+    if (bad) {
+        LRS_CUDA(cudaMemset(m->status, 0, sizeof(bad)));
+        return fail(LR_ERR_NONFINITE, std::to_string(bad) + " row(s) scored to NaN or infinity (non-finite input)");
+    }
+    return LR_OK;
+}
+
+int lr_host_alloc(void** ptr, uint64_t bytes) {
+    if (!ptr) return fail(LR_ERR_INVALID, "ptr is NULL");
+    *ptr = nullptr;
+    if (bytes == 0) return LR_OK;
+    LRS_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+    return LR_OK;
+}
+
+int lr_host_free(void* ptr) {
+    if (ptr) LRS_CUDA(cudaFreeHost(ptr));
+    return LR_OK;
+}
+
+int lr_host_register(void* ptr, uint64_t bytes) {
+    if (!ptr || bytes == 0) return fail(LR_ERR_INVALID, "empty range");
+    LRS_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return LR_OK;
+}
+
+int lr_host_unregister(void* ptr) {
+    if (!ptr) return fail(LR_ERR_INVALID, "ptr is NULL");
+    LRS_CUDA(cudaHostUnregister(ptr));
+    return LR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// Shared host/device helpers for liblrscore (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <string>
+
+#include "../../include/lrscore.h"
+
+namespace lrs {
+
+// ---- error plumbing ------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+
+#define LRS_CUDA(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return ::lrs::fail(LR_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+extern std::atomic<uint64_t> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+// ---- model -----------------------------------------------------------------------------------
+struct HostStage;   // api.cu
+struct GemmPlan;    // gemm_tcgen05.cu
+
+struct Model {
+    int device = 0;
+    int n_scores = 0;     // coef_.shape[0]
+    int n_features = 0;
+    int n_out = 0;        // max(n_scores, 2): columns of a probability row
+    int num_sms = 148;
+    int forced_path = LR_PATH_AUTO;
+
+    float* W = nullptr;   // n_scores x n_features fp32 (device)
+    float* b = nullptr;   // n_scores
+    // narrow path: W zero-padded to [ns_pad][d_pad], intercept padded with -inf
+    float* Wn = nullptr;
+    float* bn = nullptr;
+    int narrow_ns = 0, narrow_dpad = 0, narrow_lanes = 0;
+    // status word(s): [0] = rows that scored to a non-finite value
+    unsigned long long* status = nullptr;
+
+    GemmPlan* gemm = nullptr;
+    HostStage* stage = nullptr;
+    int64_t host_chunk_rows = 0;
+};
+
+struct ScoreArgs {
+    const float* X;
+    int64_t n_rows;
+    int64_t ldx;
+    float* proba;
+    float* decision;
+    int32_t* label;
+    float* maxprob;
+    cudaStream_t stream;
+};
+
+// per-family entry points (each returns LR_OK / error code, sets last error)
+bool narrow_supports(const Model& m);
+int narrow_prepare(Model& m, const float* W_host, const float* b_host);
+int narrow_launch(const Model& m, const ScoreArgs& a);
+
+bool wide_supports(const Model& m, const ScoreArgs& a);
+int wide_launch(const Model& m, const ScoreArgs& a);
+
+int generic_launch(const Model& m, const ScoreArgs& a);
+
+bool gemm_supports(const Model& m, const ScoreArgs& a);
+int gemm_prepare(Model& m, const double* coef, const double* intercept);
+void gemm_destroy(Model& m);
+int gemm_launch(const Model& m, const ScoreArgs& a);
+
+// ---- device helpers ----------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float4 ldg_stream4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ldg_stream1(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+// Binary arm of predict_proba (SK/linear_model/_base.py:437-440): returns (1-p, p) with
+// p = expit(z), evaluated from e = exp(-|z|) so that both columns keep full relative accuracy and
+// saturate to exactly 0/1 like scipy's expit does in float64.
+__device__ __forceinline__ float2 sigmoid_pair(float z) {
+    float e = expf(-fabsf(z));
+    float big = __frcp_rn(1.0f + e);   // probability of the predicted side, >= 0.5
+    float small = e * big;
+    return z > 0.0f ? make_float2(small, big) : make_float2(big, small);
+}
+
+__device__ __forceinline__ bool finite_f(float z) { return fabsf(z) <= 3.402823466e38f; }
+
+#endif  // __CUDACC__
+
+}  // namespace lrs

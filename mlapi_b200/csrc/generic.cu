@@ -1,0 +1,108 @@
+// Generic path: any (n_scores, n_features), any alignment or row pitch.  One warp per row, score
+// columns in groups of four, scalar coalesced loads; softmax by an online (running max / running
+// sum) pass followed by an in-place normalisation of the row the warp has just written.  It is the
+// shape-complete safety net under the tuned paths (narrow / wide / gemm), not a roofline kernel:
+// X is re-read from L1/L2 once per group of four score columns.
+//
+// Same reference arithmetic as the other paths: SK/linear_model/_base.py:390-391 (scores),
+// :415-418 (labels), :437-440 (sigmoid arm), SK/utils/extmath.py:1012-1024 (softmax arm).
+#include "common.cuh"
+
+namespace lrs {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int CC = 4;
+
+__global__ void __launch_bounds__(kThreads)
+generic_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
+               const float* __restrict__ W, const float* __restrict__ b,
+               float* __restrict__ proba, float* __restrict__ decision,
+               int32_t* __restrict__ label, float* __restrict__ maxprob,
+               unsigned long long* status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps_total = (int64_t)gridDim.x * (kThreads / 32);
+    for (int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5); row < n_rows;
+         row += warps_total) {
+        const float* x = X + row * ldx;
+        float run_max = -CUDART_INF_F, run_sum = 0.0f;
+        int arg = 0;
+        bool ok = true;
+        for (int c0 = 0; c0 < C; c0 += CC) {
+            float acc[CC];
+#pragma unroll
+            for (int i = 0; i < CC; ++i) acc[i] = 0.0f;
+            for (int k = lane; k < d; k += 32) {
+                const float xv = __ldg(x + k);
+#pragma unroll
+                for (int i = 0; i < CC; ++i)
+                    if (c0 + i < C) acc[i] = fmaf(xv, __ldg(W + (int64_t)(c0 + i) * d + k), acc[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < CC; ++i)
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1)
+                    acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], off);
+#pragma unroll
+            for (int i = 0; i < CC; ++i) {
+                const int c = c0 + i;
+                if (c < C) {
+                    const float z = acc[i] + __ldg(b + c);
+                    ok = ok && finite_f(z);
+                    if (C == 1) {
+                        if (lane == 0) {
+                            const float2 p = sigmoid_pair(z);
+                            if (proba) reinterpret_cast<float2*>(proba)[row] = p;
+                            if (decision) decision[row] = z;
+                            if (label) label[row] = z > 0.0f ? 1 : 0;
+                            if (maxprob) maxprob[row] = fmaxf(p.x, p.y);
+                        }
+                    } else {
+                        if (lane == 0) {
+                            if (decision) decision[row * C + c] = z;
+                            if (proba) proba[row * C + c] = z;     // normalised below
+                        }
+                        if (z > run_max) {                          // strict: first maximum wins
+                            run_sum = run_sum * expf(run_max - z) + 1.0f;
+                            run_max = z;
+                            arg = c;
+                        } else {
+                            run_sum += expf(z - run_max);
+                        }
+                    }
+                }
+            }
+        }
+        if (!ok && lane == 0) atomicAdd(status, 1ull);
+        if (C > 1) {
+            const float inv = __frcp_rn(run_sum);
+            if (lane == 0) {
+                if (label) label[row] = arg;
+                if (maxprob) maxprob[row] = inv;
+            }
+            if (proba) {
+                __syncwarp();
+                for (int c = lane; c < C; c += 32) {
+                    const float z = proba[row * C + c];
+                    proba[row * C + c] = expf(z - run_max) * inv;
+                }
+            }
+        }
+    }
+}
+
+}  // namespace
+
+int generic_launch(const Model& m, const ScoreArgs& a) {
+    const int64_t need = (a.n_rows + (kThreads / 32) - 1) / (kThreads / 32);
+    const int64_t cap = (int64_t)m.num_sms * 8;
+    const int grid = (int)(need < cap ? need : cap);
+    generic_kernel<<<grid, kThreads, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.n_scores,
+                                                    m.W, m.b, a.proba, a.decision, a.label,
+                                                    a.maxprob, m.status);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
+}  // namespace lrs

@@ -1,0 +1,341 @@
+// Narrow path: one fused kernel for models whose whole coefficient matrix fits in shared memory
+// (the notebook's iris model d=4,C=3 and the d=32 binary north-star config).
+//
+// Replaces, per row, sklearn's decision_function (SK/linear_model/_base.py:390-391),
+// _predict_proba_lr / softmax (SK/linear_model/_base.py:437-440, SK/utils/extmath.py:1012-1024),
+// the label rule of predict (SK/linear_model/_base.py:415-418) and the `.max()` of REF/main.py:22
+// in a single pass over X.
+//
+// Mapping.  LANES lanes (a power of two, <= 32) share a row; each lane owns V-float chunks of it
+// (V = 4 -> one 128-bit load per chunk).  A warp covers G = 32/LANES rows per load instruction and
+// keeps U such instructions in flight, so one warp iteration consumes G*U consecutive rows --
+// a contiguous, fully coalesced span of X.  The partial dot products are then summed across the
+// LANES lanes with a halving exchange ("transpose reduce"): instead of every lane ending up with
+// every sum, each lane ends up owning complete sums of distinct rows, so the sigmoid/softmax
+// epilogue and the output stores are spread over all 32 lanes and the P rows a warp writes are
+// again one contiguous span.
+//
+// HBM roofline: algorithmic bytes per row = 4*d read + 4*max(C,2) written (+4 per optional
+// label / maxprob / decision column); W and b are read once per CTA and excluded.
+#include <cmath>
+
+#include "common.cuh"
+
+namespace lrs {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+template <int OFF, int ROWS, int NS, int U>
+__device__ __forceinline__ void lane_reduce(float (&acc)[U][NS], int s) {
+    if constexpr (OFF >= 1) {
+        if constexpr (ROWS > 1) {
+            constexpr int H = ROWS / 2;
+            const bool upper = (s & OFF) != 0;
+#pragma unroll
+            for (int r = 0; r < H; ++r) {
+#pragma unroll
+                for (int c = 0; c < NS; ++c) {
+                    const float keep = upper ? acc[r + H][c] : acc[r][c];
+                    const float send = upper ? acc[r][c] : acc[r + H][c];
+                    acc[r][c] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
+                }
+            }
+            lane_reduce<OFF / 2, H, NS, U>(acc, s);
+        } else {
+#pragma unroll
+            for (int c = 0; c < NS; ++c) acc[0][c] += __shfl_xor_sync(0xffffffffu, acc[0][c], OFF);
+            lane_reduce<OFF / 2, 1, NS, U>(acc, s);
+        }
+    }
+}
+
+template <int V>
+struct Vec;
+template <>
+struct Vec<4> {
+    float v[4];
+    __device__ __forceinline__ void load(const float* p) {
+        float4 t = ldg_stream4(p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+};
+template <>
+struct Vec<1> {
+    float v[1];
+    __device__ __forceinline__ void load(const float* p) { v[0] = ldg_stream1(p); }
+};
+
+struct Outs {
+    float* proba;
+    float* decision;
+    int32_t* label;
+    float* maxprob;
+    unsigned long long* status;
+    int n_scores;   // real score columns (<= NS)
+};
+
+// Epilogue for one complete row whose NS scores (intercept added) sit in z[].
+template <int NS>
+__device__ __forceinline__ void finish_row(const float (&z)[NS], int64_t row, const Outs& o) {
+    if constexpr (NS == 1) {
+        const float zz = z[0];
+        if (!finite_f(zz)) atomicAdd(o.status, 1ull);
+        const float2 p = sigmoid_pair(zz);
+        if (o.proba) __stcs(reinterpret_cast<float2*>(o.proba) + row, p);
+        if (o.decision) __stcs(o.decision + row, zz);
+        if (o.label) __stcs(o.label + row, zz > 0.0f ? 1 : 0);
+        if (o.maxprob) __stcs(o.maxprob + row, fmaxf(p.x, p.y));
+    } else {
+        float zmax = z[0];
+        int arg = 0;
+        bool ok = true;
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {
+            if (c < o.n_scores) ok = ok && finite_f(z[c]);
+            if (c > 0 && z[c] > zmax) { zmax = z[c]; arg = c; }   // strict: first maximum wins
+        }
+        if (!ok) atomicAdd(o.status, 1ull);
+        float e[NS];
+        float sum = 0.0f;
+#pragma unroll
+        for (int c = 0; c < NS; ++c) { e[c] = expf(z[c] - zmax); sum += e[c]; }
+        const float inv = __frcp_rn(sum);
+        if (o.proba) {
+            float* p = o.proba + row * o.n_scores;
+#pragma unroll
+            for (int c = 0; c < NS; ++c)
+                if (c < o.n_scores) __stcs(p + c, e[c] * inv);
+        }
+        if (o.decision) {
+            float* q = o.decision + row * o.n_scores;
+#pragma unroll
+            for (int c = 0; c < NS; ++c)
+                if (c < o.n_scores) __stcs(q + c, z[c]);
+        }
+        if (o.label) __stcs(o.label + row, arg);
+        if (o.maxprob) __stcs(o.maxprob + row, inv);   // exp(zmax - zmax) == 1
+    }
+}
+
+// SINGLE: every lane owns exactly one chunk of the row, so its NS*V coefficients live in registers.
+template <int V, int LANES, int NS, int U, bool SINGLE>
+__global__ void __launch_bounds__(kThreads)
+narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad,
+              const float* __restrict__ Wn, const float* __restrict__ bn, Outs o) {
+    constexpr int G = 32 / LANES;                 // rows per load instruction per warp
+    constexpr int M = (U < LANES) ? U : LANES;    // lanes that end up owning distinct rows
+    constexpr int ROWS_OWNED = U / M;
+    constexpr int ROWS_PER_ITER = G * U;
+
+    extern __shared__ __align__(16) float w_s[];  // [NS][dpad]
+    if constexpr (!SINGLE) {
+        for (int i = threadIdx.x; i < NS * dpad; i += kThreads) w_s[i] = Wn[i];
+        __syncthreads();
+    }
+
+    const int lane = threadIdx.x & 31;
+    const int g = lane / LANES;
+    const int s = lane % LANES;
+    const int k0 = s * V;
+
+    float wreg[NS][V];
+    if constexpr (SINGLE) {
+#pragma unroll
+        for (int c = 0; c < NS; ++c)
+#pragma unroll
+            for (int v = 0; v < V; ++v) wreg[c][v] = Wn[c * dpad + k0 + v];
+    }
+    float bias[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) bias[c] = bn[c];
+
+    const int64_t warps_total = (int64_t)gridDim.x * (kThreads / 32);
+    const int64_t warp_id = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    const int64_t n_tiles = (n_rows + ROWS_PER_ITER - 1) / ROWS_PER_ITER;
+
+    for (int64_t tile = warp_id; tile < n_tiles; tile += warps_total) {
+        const int64_t base = tile * ROWS_PER_ITER;
+        float acc[U][NS];
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+#pragma unroll
+            for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
+
+        if constexpr (SINGLE) {
+            Vec<V> x[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int64_t row = base + j * G + g;
+                if (row < n_rows && k0 < d) {
+                    x[j].load(X + row * ldx + k0);
+                } else {
+#pragma unroll
+                    for (int v = 0; v < V; ++v) x[j].v[v] = 0.0f;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j)
+#pragma unroll
+                for (int c = 0; c < NS; ++c)
+#pragma unroll
+                    for (int v = 0; v < V; ++v) acc[j][c] = fmaf(x[j].v[v], wreg[c][v], acc[j][c]);
+        } else {
+            const int dloop = (d + LANES * V - 1) / (LANES * V) * (LANES * V);   // <= dpad
+            for (int k = k0; k < dloop; k += LANES * V) {
+                Vec<V> x[U];
+#pragma unroll
+                for (int j = 0; j < U; ++j) {
+                    const int64_t row = base + j * G + g;
+                    if (row < n_rows && k < d) {
+                        x[j].load(X + row * ldx + k);
+                    } else {
+#pragma unroll
+                        for (int v = 0; v < V; ++v) x[j].v[v] = 0.0f;
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < NS; ++c) {
+                    float w[V];
+                    if constexpr (V == 4) {
+                        const float4 t = *reinterpret_cast<const float4*>(w_s + c * dpad + k);
+                        w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
+                    } else {
+                        w[0] = w_s[c * dpad + k];
+                    }
+#pragma unroll
+                    for (int j = 0; j < U; ++j)
+#pragma unroll
+                        for (int v = 0; v < V; ++v) acc[j][c] = fmaf(x[j].v[v], w[v], acc[j][c]);
+                }
+            }
+        }
+
+        lane_reduce<LANES / 2, U, NS, U>(acc, s);
+
+        // lane s now owns rows u = sel*ROWS_OWNED + r (r < ROWS_OWNED) of its group, complete.
+        const int sel = s / (LANES / M);
+        const bool owner = (s % (LANES / M)) == 0;
+        if (owner) {
+#pragma unroll
+            for (int r = 0; r < ROWS_OWNED; ++r) {
+                const int u = sel * ROWS_OWNED + r;
+                const int64_t row = base + u * G + g;
+                if (row < n_rows) {
+                    float z[NS];
+#pragma unroll
+                    for (int c = 0; c < NS; ++c) z[c] = acc[r][c] + bias[c];
+                    finish_row<NS>(z, row, o);
+                }
+            }
+        }
+    }
+}
+
+template <int NS>
+constexpr int unroll_for() { return NS == 1 ? 8 : (NS <= 4 ? 4 : (NS <= 8 ? 2 : 1)); }
+
+template <int V, int LANES, int NS, bool SINGLE>
+int launch_inst(const Model& m, const ScoreArgs& a) {
+    constexpr int U = unroll_for<NS>();
+    auto kern = narrow_kernel<V, LANES, NS, U, SINGLE>;
+    const size_t smem = SINGLE ? 0 : (size_t)NS * m.narrow_dpad * sizeof(float);
+    static int blocks_per_sm[64] = {0};   // per device, per instantiation
+    int dev = m.device & 63;
+    if (blocks_per_sm[dev] == 0) {
+        if (smem > 48 * 1024)
+            LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        int occ = 0;
+        LRS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
+        blocks_per_sm[dev] = occ > 0 ? occ : 1;
+    }
+    constexpr int rows_per_iter = (32 / LANES) * U;
+    const int64_t tiles = (a.n_rows + rows_per_iter - 1) / rows_per_iter;
+    const int64_t need = (tiles + (kThreads / 32) - 1) / (kThreads / 32);
+    const int64_t cap = (int64_t)m.num_sms * blocks_per_sm[dev];
+    const int grid = (int)(need < cap ? need : cap);
+    Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
+    kern<<<grid, kThreads, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad,
+                                             m.Wn, m.bn, o);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
+template <int V, int LANES, int NS>
+int launch_ns(const Model& m, const ScoreArgs& a, bool single) {
+    if constexpr (V == 4 && NS <= 4) {
+        if (single) return launch_inst<V, LANES, NS, true>(m, a);
+    }
+    return launch_inst<V, LANES, NS, false>(m, a);
+}
+
+template <int V, int LANES>
+int launch_lanes(const Model& m, const ScoreArgs& a, bool single) {
+    switch (m.narrow_ns) {
+        case 1: return launch_ns<V, LANES, 1>(m, a, single);
+        case 3: return launch_ns<V, LANES, 3>(m, a, single);
+        case 4: return launch_ns<V, LANES, 4>(m, a, single);
+        case 8: return launch_ns<V, LANES, 8>(m, a, single);
+        case 16: return launch_ns<V, LANES, 16>(m, a, single);
+    }
+    return fail(LR_ERR_INVALID, "narrow path: unsupported score count");
+}
+
+template <int V>
+int launch_v(const Model& m, const ScoreArgs& a) {
+    int chunks = (m.n_features + V - 1) / V;
+    int lanes = 1;
+    while (lanes < chunks && lanes < 32) lanes <<= 1;
+    const bool single = chunks <= lanes;
+    switch (lanes) {
+        case 1: return launch_lanes<V, 1>(m, a, single);
+        case 2: return launch_lanes<V, 2>(m, a, single);
+        case 4: return launch_lanes<V, 4>(m, a, single);
+        case 8: return launch_lanes<V, 8>(m, a, single);
+        case 16: return launch_lanes<V, 16>(m, a, single);
+        default: return launch_lanes<V, 32>(m, a, single);
+    }
+}
+
+}  // namespace
+
+// Shapes the narrow path serves: <= 16 score columns and a padded W of at most 96 KB.
+bool narrow_supports(const Model& m) {
+    if (m.n_scores > 16) return false;
+    int ns = m.n_scores == 1 ? 1 : (m.n_scores <= 3 ? 3 : (m.n_scores <= 4 ? 4 : (m.n_scores <= 8 ? 8 : 16)));
+    int dpad = (m.n_features + 127) / 128 * 128;
+    return (size_t)ns * dpad * sizeof(float) <= 96 * 1024 && m.n_features <= 4096;
+}
+
+int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
+    if (!narrow_supports(m)) return LR_OK;
+    const int ns = m.n_scores == 1 ? 1 : (m.n_scores <= 3 ? 3 : (m.n_scores <= 4 ? 4 : (m.n_scores <= 8 ? 8 : 16)));
+    // dpad covers whole lane-chunk sweeps for both V=4 and V=1 mappings (a multiple of 32*4).
+    const int dpad = (m.n_features + 127) / 128 * 128;
+    std::string w((size_t)ns * dpad * sizeof(float), '\0');
+    float* wp = reinterpret_cast<float*>(&w[0]);
+    float bp[16];
+    for (int c = 0; c < ns; ++c) {
+        bp[c] = c < m.n_scores ? b_host[c] : -INFINITY;   // padded classes never win, exp -> 0
+        if (c < m.n_scores)
+            for (int k = 0; k < m.n_features; ++k) wp[(size_t)c * dpad + k] = W_host[(size_t)c * m.n_features + k];
+    }
+    LRS_CUDA(cudaMalloc(&m.Wn, w.size()));
+    LRS_CUDA(cudaMalloc(&m.bn, ns * sizeof(float)));
+    LRS_CUDA(cudaMemcpy(m.Wn, wp, w.size(), cudaMemcpyHostToDevice));
+    LRS_CUDA(cudaMemcpy(m.bn, bp, ns * sizeof(float), cudaMemcpyHostToDevice));
+    m.narrow_ns = ns;
+    m.narrow_dpad = dpad;
+    return LR_OK;
+}
+
+int narrow_launch(const Model& m, const ScoreArgs& a) {
+    if (!m.Wn) return fail(LR_ERR_INVALID, "narrow path does not serve this model shape");
+    const bool vec = (m.n_features % 4 == 0) && (a.ldx % 4 == 0) &&
+                     ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0);
+    return vec ? launch_v<4>(m, a) : launch_v<1>(m, a);
+}
+
+}  // namespace lrs

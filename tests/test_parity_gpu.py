@@ -1,0 +1,266 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes -> liblrscore.so), against
+the numpy oracle on seeded inputs and against the committed sklearn golden vectors."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import parity
+import synth
+from oracle import lr_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+ALL = dict(proba=True, decision=True, label=True, maxprob=True)
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import __graft_entry__
+    __graft_entry__.build()
+    import mlapi_b200
+    from mlapi_b200 import _lib
+    return mlapi_b200, _lib
+
+
+def _model(eng, W, b, classes=None, **kw):
+    mlapi, _ = eng
+    W = np.atleast_2d(W)
+    n_classes = max(W.shape[0], 2)
+    return mlapi.B200LogisticRegression(W, b, np.arange(n_classes) if classes is None else classes, **kw)
+
+
+def _check(clf, X, W, b, what, **sel):
+    out = clf.score_rows(X, **(sel or ALL))
+    parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                         orc.predict_index(X, W, b), what)
+    return out
+
+
+# ---- cfg 0: the notebook's model -----------------------------------------------------------------
+def test_iris_against_golden(eng, golden):
+    g = golden("iris_model.npz")
+    clf = _model(eng, g["coef"], g["intercept"], g["classes"])
+    out = clf.score_rows(g["X"], **ALL)
+    parity.assert_parity(out, g["decision"], g["proba"], g["label_idx"], "iris/golden")
+    assert list(clf.predict(g["X"][:3])) == ["Iris-setosa"] * 3
+    # the two requests of SURVEY.md 8c
+    lab, p = clf.predict_with_max_proba([[5.1, 3.5, 1.4, 0.2], [6.0, 2.9, 4.5, 1.5]])
+    assert list(lab) == ["Iris-setosa", "Iris-versicolor"]
+    np.testing.assert_allclose(p, [0.9793734699646953, 0.7493304124804981], atol=1e-5)
+    # notebook accuracy (REF/Logistic Regression.ipynb:13) through the engine
+    _, (Xtr, Xte, ytr, yte) = synth.fit_notebook_model()
+    assert clf.score(Xte.astype(np.float64), yte) == 0.9666666666666667
+
+
+def test_iris_batch10k_against_golden(eng, golden):
+    g, m = golden("iris_batch10k.npz"), golden("iris_model.npz")
+    rng = np.random.default_rng(0)
+    X = (rng.random((10_000, 4), dtype=np.float32) * 8.0).astype(np.float32)
+    assert synth.sha(X) == str(g["x_sha"])
+    clf = _model(eng, m["coef"], m["intercept"], m["classes"])
+    out = clf.score_rows(X, **ALL)
+    parity.assert_parity(out, g["decision"], g["proba"], g["label_idx"], "iris10k/golden")
+
+
+# ---- cfg 1..3 at oracle size, against golden and oracle ------------------------------------------
+@pytest.mark.parametrize("name", list(synth.CONFIGS))
+def test_synthetic_configs_against_golden(eng, golden, name):
+    g = golden(name + ".npz")
+    X, W, b = synth.make_config(name, int(g["n"]))
+    assert synth.sha(X) == str(g["x_sha"])
+    clf = _model(eng, W, b)
+    out = clf.score_rows(X, **ALL)
+    parity.assert_parity(out, g["decision"], g["proba"], g["label_idx"], name + "/golden")
+
+
+def test_adversarial_rows(eng, golden):
+    g = golden("adversarial.npz")
+    for pre in ("bin_", "mul_"):
+        clf = _model(eng, g[pre + "W"], g[pre + "b"])
+        out = clf.score_rows(g[pre + "X"], **ALL)
+        parity.assert_parity(out, g[pre + "decision"], g[pre + "proba"], g[pre + "label_idx"], pre)
+        if pre == "bin_":
+            # exact ties -> classes_[0]; saturation -> exactly 0 / 1
+            assert list(out["label"][:2]) == [0, 0]
+            assert out["proba"][2, 1] == 1.0 and out["proba"][2, 0] == 0.0
+            assert out["proba"][3, 0] == 1.0 and out["proba"][3, 1] == 0.0
+        else:
+            assert list(out["label"][:3]) == [0, 0, 2]            # first maximum wins
+
+
+# ---- shape sweep: every narrow lane mapping, ragged n, every path -----------------------------------
+@pytest.mark.parametrize("d", [1, 2, 3, 4, 5, 7, 8, 12, 16, 20, 31, 32, 33, 64, 100, 128, 200, 256, 700])
+@pytest.mark.parametrize("ns", [1, 3])
+def test_narrow_shapes(eng, d, ns):
+    _, lib = eng
+    rng = np.random.default_rng(1000 + d * 7 + ns)
+    W, b = synth.make_model(d, ns, 2000 + d)
+    clf = _model(eng, W, b)
+    clf.set_path(lib.PATH_NARROW)
+    for n in (1, 31, 257, 4099):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        _check(clf, X, W, b, f"narrow d={d} ns={ns} n={n}")
+
+
+@pytest.mark.parametrize("ns", [2, 4, 5, 8, 9, 16])
+def test_narrow_class_buckets(eng, ns):
+    _, lib = eng
+    rng = np.random.default_rng(ns)
+    for d in (4, 24, 96):
+        W, b = synth.make_model(d, ns, 77 + ns)
+        clf = _model(eng, W, b)
+        clf.set_path(lib.PATH_NARROW)
+        X = rng.standard_normal((1037, d), dtype=np.float32)
+        _check(clf, X, W, b, f"narrow ns={ns} d={d}")
+
+
+@pytest.mark.parametrize("d", [4, 5, 1000, 1024, 4097, 10_000, 100_000])
+def test_wide_shapes(eng, d):
+    _, lib = eng
+    rng = np.random.default_rng(d)
+    W, b = synth.make_model(d, 1, 31 + d)
+    clf = _model(eng, W, b)
+    clf.set_path(lib.PATH_WIDE)
+    for n in (1, 7, 301, 2500):
+        if n * d > 40_000_000:
+            continue
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        _check(clf, X, W, b, f"wide d={d} n={n}")
+
+
+@pytest.mark.parametrize("d,ns", [(1, 1), (7, 1), (33, 2), (50, 20), (130, 37), (1024, 100), (3000, 1)])
+def test_generic_shapes(eng, d, ns):
+    _, lib = eng
+    rng = np.random.default_rng(d * 31 + ns)
+    W, b = synth.make_model(d, ns, 5 + d)
+    clf = _model(eng, W, b)
+    clf.set_path(lib.PATH_GENERIC)
+    for n in (1, 33, 1001):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        _check(clf, X, W, b, f"generic d={d} ns={ns} n={n}")
+
+
+def test_auto_dispatch_and_output_subsets(eng):
+    _, lib = eng
+    rng = np.random.default_rng(3)
+    for d, ns in ((32, 1), (4, 3), (2048, 1), (64, 40)):
+        W, b = synth.make_model(d, ns, d + ns)
+        clf = _model(eng, W, b)
+        X = rng.standard_normal((777, d), dtype=np.float32)
+        for sel in (dict(proba=True), dict(label=True), dict(maxprob=True), dict(decision=True),
+                    dict(label=True, maxprob=True)):
+            out = _check(clf, X, W, b, f"auto d={d} ns={ns} {sel}", **sel)
+            assert all((out[k] is not None) == bool(sel.get(k)) for k in out)
+
+
+# ---- sklearn surface and error behaviour --------------------------------------
+def test_estimator_surface_matches_sklearn(eng):
+    X, W, b = synth.make_config("cfg1_d32_binary", 500)
+    sk = synth.sklearn_model(W, b, classes=np.array(["neg", "pos"]))
+    clf = eng[0].B200LogisticRegression.from_sklearn(sk)
+    assert clf.predict_proba(X).dtype == np.float64 and clf.predict_proba(X).shape == (500, 2)
+    assert clf.decision_function(X).shape == (500,)
+    safe = np.abs(sk.decision_function(X)) > 1e-5
+    assert np.array_equal(clf.predict(X)[safe], sk.predict(X)[safe])
+    np.testing.assert_allclose(clf.predict_proba(X), sk.predict_proba(X), atol=1e-5, rtol=1e-5)
+    np.testing.assert_allclose(clf.predict_log_proba(X), sk.predict_log_proba(X), atol=2e-5, rtol=1e-4)
+    assert abs(clf.score(X, sk.predict(X)) - 1.0) < 0.01
+    # list-of-lists, ints, float64, F-order are all accepted like sklearn does
+    Xi = np.asfortranarray((X[:9] * 3).astype(np.int64))
+    np.testing.assert_allclose(clf.predict_proba(Xi.tolist()), sk.predict_proba(Xi), atol=1e-5)
+    np.testing.assert_allclose(clf.predict_proba(Xi), sk.predict_proba(Xi), atol=1e-5)
+
+
+def test_estimator_errors_match_sklearn(eng):
+    X, W, b = synth.make_config("cfg1_d32_binary", 8)
+    clf = _model(eng, W, b)
+    with pytest.raises(ValueError, match="X has 5 features, but LogisticRegression is expecting 32"):
+        clf.predict(np.zeros((3, 5)))
+    with pytest.raises(ValueError, match="Expected 2D array"):
+        clf.predict(np.zeros(32))
+    with pytest.raises(ValueError, match="0 sample"):
+        clf.predict(np.zeros((0, 32)))
+    for bad in (np.nan, np.inf, -np.inf):
+        Xb = X.copy()
+        Xb[5, 7] = bad
+        with pytest.raises(ValueError, match="NaN or infinity"):
+            clf.predict_proba(Xb)
+    clf.predict_proba(X)   # the status word was reset: a clean batch passes again
+    from sklearn.exceptions import NotFittedError
+    from sklearn.linear_model import LogisticRegression
+    with pytest.raises(NotFittedError):
+        eng[0].B200LogisticRegression.from_sklearn(LogisticRegression())
+
+
+# ---- device-resident path (torch tensors), row pitch, misalignment ---------------------------------
+def test_device_path_pitch_and_alignment(eng):
+    import torch
+    _, lib = eng
+    rng = np.random.default_rng(9)
+    for d, ns in ((32, 1), (4, 3), (2000, 1), (12, 5)):
+        W, b = synth.make_model(d, ns, 90 + d)
+        clf = _model(eng, W, b)
+        n = 1237
+        buf = rng.standard_normal((n, d + 9), dtype=np.float32)
+        for off, pitch_pad in ((0, 0), (0, 4), (1, 3), (3, 9 - 3)):
+            Xh = buf[:, off:off + d]
+            t_full = torch.from_numpy(buf).cuda()
+            Xt = t_full[:, off:off + d]                          # row pitch d+9, base offset `off` floats
+            out = clf.score_rows(Xt, **ALL)
+            torch.cuda.synchronize()
+            host = {k: v.cpu().numpy() for k, v in out.items()}
+            parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
+                                 orc.predict_index(Xh, W, b), f"device d={d} ns={ns} off={off}")
+            assert clf.take_nonfinite() == 0
+    # non-finite rows are counted on the device path
+    X = torch.randn(100, 32, device="cuda")
+    X[3, 3] = float("nan")
+    X[50, 0] = float("inf")
+    W, b = synth.make_model(32, 1, 1)
+    clf = _model(eng, W, b)
+    clf.score_rows(X, proba=True)
+    assert clf.take_nonfinite() == 2 and clf.take_nonfinite() == 0
+
+
+def test_host_chunking_is_bit_identical(eng):
+    """lr_score_host streams chunks; chunk boundaries must not change a single bit."""
+    _, lib = eng
+    X, W, b = synth.make_config("cfg1_d32_binary", 50_000)
+    clf = _model(eng, W, b)
+    ref = clf.score_rows(X, **ALL)
+    rep = clf._replicas[0]
+    lib.check(rep.lib.lr_model_set_host_chunk_rows(rep.handle, 999))
+    got = clf.score_rows(X, **ALL)
+    for k in ref:
+        assert np.array_equal(ref[k], got[k]), k
+    # pinned input/outputs take the same route
+    from mlapi_b200.estimator import PinnedArray
+    px = PinnedArray(X.shape)
+    px.array[...] = X
+    got = clf.score_rows(px.array, **ALL)
+    for k in ref:
+        assert np.array_equal(ref[k], got[k]), k
+    px.free()
+
+
+def test_c_abi_direct_call(eng):
+    """Straight ctypes, no wrapper: what INTEGRATION.md's stub does."""
+    _, lib = eng
+    L = lib.load()
+    g = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "iris_model.npz"))
+    coef = np.ascontiguousarray(g["coef"])
+    h = C.c_void_p()
+    assert L.lr_model_create(coef.ctypes.data_as(C.c_void_p), g["intercept"].ctypes.data_as(C.c_void_p),
+                             3, 4, 0, C.byref(h)) == 0
+    X = np.array([[5.1, 3.5, 1.4, 0.2]], dtype=np.float32)
+    label = np.zeros(1, np.int32)
+    maxp = np.zeros(1, np.float32)
+    before = L.lr_launch_count()
+    assert L.lr_score_host(h, X.ctypes.data_as(C.c_void_p), 1, 4, None, None,
+                           label.ctypes.data_as(C.c_void_p), maxp.ctypes.data_as(C.c_void_p)) == 0
+    assert L.lr_launch_count() == before + 1
+    assert label[0] == 0 and abs(maxp[0] - 0.9793734699646953) < 1e-5
+    assert L.lr_score_host(h, X.ctypes.data_as(C.c_void_p), 1, 3, None, None, None, None) == lib.LR_ERR_INVALID
+    assert "ldx" in lib.last_error()
+    L.lr_model_destroy(h)
