@@ -44,6 +44,8 @@ struct Model {
     float* Wn = nullptr;
     float* bn = nullptr;
     int narrow_ns = 0, narrow_dpad = 0, narrow_lanes = 0;
+    bool narrow_bulk = false;             // opt-in (LRS_NARROW_BULK=1): cp.async.bulk ring, measured 4% slower than plain loads
+    int64_t narrow_bulk_min_rows = 65536;
     // status word(s): [0] = rows that scored to a non-finite value
     unsigned long long* status = nullptr;
 
@@ -102,6 +104,49 @@ __device__ __forceinline__ float2 sigmoid_pair(float z) {
     float big = __frcp_rn(1.0f + e);   // probability of the predicted side, >= 0.5
     float small = e * big;
     return z > 0.0f ? make_float2(small, big) : make_float2(big, small);
+}
+
+// ---- mbarrier + bulk-copy (TMA engine) primitives -----------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// Bounded wait: a pipeline bug traps (-> cudaErrorLaunchFailure) after ~2 s instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+// 1-D bulk copy global -> shared, completion counted in bytes on `bar`.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
 }
 
 __device__ __forceinline__ bool finite_f(float z) { return fabsf(z) <= 3.402823466e38f; }

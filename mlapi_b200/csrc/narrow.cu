@@ -18,6 +18,7 @@
 // HBM roofline: algorithmic bytes per row = 4*d read + 4*max(C,2) written (+4 per optional
 // label / maxprob / decision column); W and b are read once per CTA and excluded.
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -163,16 +164,25 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
 #pragma unroll
             for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
 
+        // All U loads of a chunk are issued back to back and unpredicated.  Full tiles (all but the
+        // last) step a single pointer by a fixed stride; the last tile clamps row indices to the
+        // final row (those results are never stored).  Lanes past the end of a row re-read column 0
+        // against zero weights, so nothing here can fault or branch.
+        const bool full_tile = base + ROWS_PER_ITER <= n_rows;
+        const int64_t jstride = (int64_t)G * ldx;
         if constexpr (SINGLE) {
             Vec<V> x[U];
+            const int kc = k0 < d ? k0 : 0;
+            if (full_tile) {
+                const float* p = X + (base + g) * ldx + kc;
 #pragma unroll
-            for (int j = 0; j < U; ++j) {
-                const int64_t row = base + j * G + g;
-                if (row < n_rows && k0 < d) {
-                    x[j].load(X + row * ldx + k0);
-                } else {
+                for (int j = 0; j < U; ++j) x[j].load(p + j * jstride);
+            } else {
 #pragma unroll
-                    for (int v = 0; v < V; ++v) x[j].v[v] = 0.0f;
+                for (int j = 0; j < U; ++j) {
+                    int64_t row = base + j * G + g;
+                    row = row < n_rows ? row : n_rows - 1;
+                    x[j].load(X + row * ldx + kc);
                 }
             }
 #pragma unroll
@@ -183,18 +193,18 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
                     for (int v = 0; v < V; ++v) acc[j][c] = fmaf(x[j].v[v], wreg[c][v], acc[j][c]);
         } else {
             const int dloop = (d + LANES * V - 1) / (LANES * V) * (LANES * V);   // <= dpad
+            const float* rowp[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                int64_t row = base + j * G + g;
+                row = row < n_rows ? row : n_rows - 1;
+                rowp[j] = X + row * ldx;
+            }
             for (int k = k0; k < dloop; k += LANES * V) {
                 Vec<V> x[U];
+                const int kc = k < d ? k : 0;      // past-the-end chunks meet zero weights
 #pragma unroll
-                for (int j = 0; j < U; ++j) {
-                    const int64_t row = base + j * G + g;
-                    if (row < n_rows && k < d) {
-                        x[j].load(X + row * ldx + k);
-                    } else {
-#pragma unroll
-                        for (int v = 0; v < V; ++v) x[j].v[v] = 0.0f;
-                    }
-                }
+                for (int j = 0; j < U; ++j) x[j].load(rowp[j] + kc);
 #pragma unroll
                 for (int c = 0; c < NS; ++c) {
                     float w[V];
@@ -217,6 +227,126 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
         // lane s now owns rows u = sel*ROWS_OWNED + r (r < ROWS_OWNED) of its group, complete.
         const int sel = s / (LANES / M);
         const bool owner = (s % (LANES / M)) == 0;
+        if (owner) {
+#pragma unroll
+            for (int r = 0; r < ROWS_OWNED; ++r) {
+                const int u = sel * ROWS_OWNED + r;
+                const int64_t row = base + u * G + g;
+                if (row < n_rows) {
+                    float z[NS];
+#pragma unroll
+                    for (int c = 0; c < NS; ++c) z[c] = acc[r][c] + bias[c];
+                    finish_row<NS>(z, row, o);
+                }
+            }
+        }
+    }
+}
+
+// ---- bulk-copy ring variant ------------------------------------------------------------------------
+// Same arithmetic as narrow_kernel<4, LANES, NS, U, true>, but X reaches the SM through the TMA
+// engine: one producer lane streams contiguous row tiles (kConsumerWarps * G * U rows) into a ring of
+// shared-memory stages with cp.async.bulk, completion counted on an mbarrier per stage; the eight
+// consumer warps read their rows with conflict-free 128-bit shared loads and release the stage
+// through a second mbarrier.  Bytes in flight per SM = stages x tile bytes (~190 KB), independent of
+// register allocation and occupancy.  Measured on B200 (profiles/r01_narrow.md): 6553 GB/s against
+// 6837 GB/s for the plain-load kernel once its eight loads are issued back to back, so this variant
+// is opt-in (LRS_NARROW_BULK=1) and kept as the measured alternative.
+// Needs dense rows (ldx == d), d % 4 == 0 and a 16-byte aligned X.
+constexpr int kConsumerWarps = 8;
+constexpr int kBulkThreads = (kConsumerWarps + 1) * 32;
+constexpr int kBulkSmemBudget = 200 * 1024;
+
+template <int LANES, int NS, int U>
+__global__ void __launch_bounds__(kBulkThreads, 1)
+narrow_bulk_kernel(const float* __restrict__ X, int64_t n_rows, int d, int dpad, int stages,
+                   const float* __restrict__ Wn, const float* __restrict__ bn, Outs o) {
+    constexpr int V = 4;
+    constexpr int G = 32 / LANES;
+    constexpr int M = (U < LANES) ? U : LANES;
+    constexpr int ROWS_OWNED = U / M;
+    constexpr int ROWS_PER_WARP = G * U;
+    constexpr int TILE_ROWS = ROWS_PER_WARP * kConsumerWarps;
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t stage_bytes = (uint32_t)TILE_ROWS * d * sizeof(float);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);          // [stages]
+    uint64_t* empty = full + stages;                                  // [stages]
+    unsigned char* ring = smem_raw + 128 * ((2 * stages * 8 + 127) / 128);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(full + i, 1);
+            mbar_init(empty + i, kConsumerWarps);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int64_t n_tiles = (n_rows + TILE_ROWS - 1) / TILE_ROWS;
+
+    if (warp == kConsumerWarps) {
+        // ===== producer: one lane feeds the ring =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                mbar_wait(empty + stage, phase ^ 1);
+                const int64_t row0 = tile * TILE_ROWS;
+                const int64_t rows = (n_rows - row0 < TILE_ROWS) ? (n_rows - row0) : TILE_ROWS;
+                const uint32_t bytes = (uint32_t)(rows * d * sizeof(float));
+                mbar_expect_tx(full + stage, bytes);
+                bulk_g2s(ring + (size_t)stage * stage_bytes, X + row0 * d, bytes, full + stage);
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers =====
+    const int g = lane / LANES;
+    const int s = lane % LANES;
+    const int k0 = s * V;
+    const int kc = k0 < d ? k0 : 0;
+    float wreg[NS][V];
+#pragma unroll
+    for (int c = 0; c < NS; ++c)
+#pragma unroll
+        for (int v = 0; v < V; ++v) wreg[c][v] = Wn[c * dpad + k0 + v];
+    float bias[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) bias[c] = bn[c];
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        mbar_wait(full + stage, phase);
+        const float* xs = reinterpret_cast<const float*>(ring + (size_t)stage * stage_bytes) +
+                          (size_t)(warp * ROWS_PER_WARP + g) * d + kc;
+        float4 x[U];
+#pragma unroll
+        for (int j = 0; j < U; ++j) x[j] = *reinterpret_cast<const float4*>(xs + (size_t)j * G * d);
+        float acc[U][NS];
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+#pragma unroll
+            for (int c = 0; c < NS; ++c) {
+                float a = x[j].x * wreg[c][0];
+                a = fmaf(x[j].y, wreg[c][1], a);
+                a = fmaf(x[j].z, wreg[c][2], a);
+                acc[j][c] = fmaf(x[j].w, wreg[c][3], a);
+            }
+        // the stage is free as soon as every lane of this warp holds its data in registers
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + stage);
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+
+        lane_reduce<LANES / 2, U, NS, U>(acc, s);
+        const int sel = s / (LANES / M);
+        const bool owner = (s % (LANES / M)) == 0;
+        const int64_t base = tile * TILE_ROWS + warp * ROWS_PER_WARP;
         if (owner) {
 #pragma unroll
             for (int r = 0; r < ROWS_OWNED; ++r) {
@@ -299,6 +429,58 @@ int launch_v(const Model& m, const ScoreArgs& a) {
     }
 }
 
+template <int LANES, int NS>
+int launch_bulk_inst(const Model& m, const ScoreArgs& a) {
+    constexpr int U = unroll_for<NS>();
+    constexpr int tile_rows = (32 / LANES) * U * kConsumerWarps;
+    auto kern = narrow_bulk_kernel<LANES, NS, U>;
+    const size_t stage_bytes = (size_t)tile_rows * m.n_features * sizeof(float);
+    int stages = (int)((kBulkSmemBudget - 256) / stage_bytes);
+    if (stages > 12) stages = 12;
+    if (stages < 2) return -1;
+    const size_t smem = 128 * ((2 * stages * 8 + 127) / 128) + stages * stage_bytes;
+    static bool configured[64] = {false};
+    const int dev = m.device & 63;
+    if (!configured[dev]) {
+        LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkSmemBudget));
+        configured[dev] = true;
+    }
+    const int64_t tiles = (a.n_rows + tile_rows - 1) / tile_rows;
+    const int grid = (int)(tiles < m.num_sms ? tiles : m.num_sms);
+    Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
+    kern<<<grid, kBulkThreads, smem, a.stream>>>(a.X, a.n_rows, m.n_features, m.narrow_dpad, stages,
+                                                 m.Wn, m.bn, o);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
+template <int LANES>
+int launch_bulk_lanes(const Model& m, const ScoreArgs& a) {
+    switch (m.narrow_ns) {
+        case 1: return launch_bulk_inst<LANES, 1>(m, a);
+        case 3: return launch_bulk_inst<LANES, 3>(m, a);
+        case 4: return launch_bulk_inst<LANES, 4>(m, a);
+    }
+    return -1;
+}
+
+// Returns -1 when the bulk variant does not apply (caller falls through to the plain-load kernel).
+int launch_bulk(const Model& m, const ScoreArgs& a) {
+    const int chunks = m.n_features / 4;
+    int lanes = 1;
+    while (lanes < chunks) lanes <<= 1;
+    switch (lanes) {
+        case 1: return launch_bulk_lanes<1>(m, a);
+        case 2: return launch_bulk_lanes<2>(m, a);
+        case 4: return launch_bulk_lanes<4>(m, a);
+        case 8: return launch_bulk_lanes<8>(m, a);
+        case 16: return launch_bulk_lanes<16>(m, a);
+        case 32: return launch_bulk_lanes<32>(m, a);
+    }
+    return -1;
+}
+
 }  // namespace
 
 // Shapes the narrow path serves: <= 16 score columns and a padded W of at most 96 KB.
@@ -328,6 +510,8 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
     LRS_CUDA(cudaMemcpy(m.bn, bp, ns * sizeof(float), cudaMemcpyHostToDevice));
     m.narrow_ns = ns;
     m.narrow_dpad = dpad;
+    if (const char* e = getenv("LRS_NARROW_BULK")) m.narrow_bulk = atoi(e) != 0;
+    if (const char* e = getenv("LRS_NARROW_BULK_MIN_ROWS")) m.narrow_bulk_min_rows = atoll(e);
     return LR_OK;
 }
 
@@ -335,6 +519,11 @@ int narrow_launch(const Model& m, const ScoreArgs& a) {
     if (!m.Wn) return fail(LR_ERR_INVALID, "narrow path does not serve this model shape");
     const bool vec = (m.n_features % 4 == 0) && (a.ldx % 4 == 0) &&
                      ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0);
+    // Opt-in: large dense batches through the bulk-copy ring (see narrow_bulk_kernel).
+    if (vec && m.narrow_bulk && a.ldx == m.n_features && m.n_features <= 128 && a.n_rows >= m.narrow_bulk_min_rows) {
+        const int rc = launch_bulk(m, a);
+        if (rc >= 0) return rc;
+    }
     return vec ? launch_v<4>(m, a) : launch_v<1>(m, a);
 }
 

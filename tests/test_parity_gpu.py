@@ -103,6 +103,27 @@ def test_narrow_shapes(eng, d, ns):
         _check(clf, X, W, b, f"narrow d={d} ns={ns} n={n}")
 
 
+@pytest.mark.parametrize("d", [4, 8, 12, 32, 36, 64, 128])
+@pytest.mark.parametrize("ns", [1, 3, 4])
+def test_narrow_bulk_ring_matches_plain_loads(eng, d, ns, monkeypatch):
+    """The cp.async.bulk ring variant (large dense batches) against the oracle, and bit-for-bit
+    against the plain-load kernel: both sum each row in the same order."""
+    _, lib = eng
+    rng = np.random.default_rng(d * 13 + ns)
+    W, b = synth.make_model(d, ns, 400 + d)
+    monkeypatch.setenv("LRS_NARROW_BULK", "0")
+    plain = _model(eng, W, b)
+    monkeypatch.setenv("LRS_NARROW_BULK", "1")
+    monkeypatch.setenv("LRS_NARROW_BULK_MIN_ROWS", "1")
+    bulk = _model(eng, W, b)
+    for n in (1, 255, 256, 257, 70_001):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        got = _check(bulk, X, W, b, f"bulk d={d} ns={ns} n={n}")
+        ref = plain.score_rows(X, **ALL)
+        for k in ref:
+            assert np.array_equal(ref[k], got[k]), (k, d, ns, n)
+
+
 @pytest.mark.parametrize("ns", [2, 4, 5, 8, 9, 16])
 def test_narrow_class_buckets(eng, ns):
     _, lib = eng
