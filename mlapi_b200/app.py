@@ -1,0 +1,105 @@
+"""FastAPI application with the reference's surface (REF/main.py:8-39), served by the B200 engine.
+
+    uvicorn mlapi_b200.app:app            # the reference's run line is `uvicorn main:app` (REF/README.md:16)
+
+Same routes, same request/response schema:
+  POST /predict  body {"sepal_length": float, "sepal_width": float, "petal_length": float,
+                       "petal_width": float}  ->  {"prediction": <label>, "probability": <max proba>}
+  POST /files/   multipart `file` + form `token` (CSV echo; not on the scoring path, unaccelerated)
+What changes underneath: the pickle is loaded ONCE at start-up into device-resident fp32 buffers
+(the reference unpickles on every request, REF/main.py:19), and requests are coalesced by
+`MicroBatcher` into device batches instead of being scored one by one on the event loop.
+
+Environment: LR_MODEL_PATH (default 'LRClassifier.pkl', the reference's hard-coded path),
+LR_DEVICES (comma list, default '0'), LR_MAX_BATCH (4096), LR_MAX_WAIT_US (200).
+"""
+from __future__ import annotations
+
+import math
+import os
+from contextlib import asynccontextmanager
+from io import StringIO
+from typing import Optional
+
+from fastapi import FastAPI, File, Form
+from pydantic import BaseModel
+
+from .batcher import MicroBatcher, engine_score_fns
+
+
+class IrisSpecies(BaseModel):
+    """Request schema, field for field as REF/main.py:10-14."""
+    sepal_length: float
+    sepal_width: float
+    petal_length: float
+    petal_width: float
+
+
+def create_app(model=None, model_path: Optional[str] = None, devices=None, max_batch: Optional[int] = None,
+               max_wait_us: Optional[float] = None, score_fns=None, classes=None) -> FastAPI:
+    """Build the app.  `model` may be a ready `B200LogisticRegression` (tests); otherwise the pickle
+    at `model_path` is loaded at start-up.  `score_fns` (+ `classes`) lets host-logic tests inject a scorer."""
+    state = {}
+
+    @asynccontextmanager
+    async def lifespan(app: FastAPI):
+        clf = model
+        if clf is None and score_fns is None:
+            from .estimator import load_model
+            path = model_path or os.environ.get("LR_MODEL_PATH", "LRClassifier.pkl")
+            devs = devices if devices is not None else [int(x) for x in os.environ.get("LR_DEVICES", "0").split(",")]
+            clf = load_model(path, devices=devs)
+        fns = score_fns if score_fns is not None else engine_score_fns(clf)
+        alloc = None
+        if score_fns is None:
+            from .estimator import PinnedArray
+            pins = []
+
+            def alloc(shape, dtype):           # pinned staging rows: the H2D copy is a plain DMA
+                pa = PinnedArray(shape, dtype)
+                pins.append(pa)
+                return pa.array
+            state["pins"] = pins
+        state["classes"] = list(clf.classes_) if clf is not None else list(classes)
+        state["batcher"] = MicroBatcher(
+            fns, n_features=4,
+            max_batch=max_batch or int(os.environ.get("LR_MAX_BATCH", "4096")),
+            max_wait_us=max_wait_us if max_wait_us is not None else float(os.environ.get("LR_MAX_WAIT_US", "200")),
+            alloc=alloc)
+        app.state.batcher = state["batcher"]
+        yield
+        state["batcher"].close()
+
+    app = FastAPI(lifespan=lifespan)
+
+    @app.post("/predict")
+    async def predict_species(iris: IrisSpecies):
+        # REF/main.py:18-22: dict -> [[sl, sw, pl, pw]] -> predict + predict_proba.max()
+        row = (iris.sepal_length, iris.sepal_width, iris.petal_length, iris.petal_width)
+        if not all(math.isfinite(v) for v in row):
+            # sklearn raises ValueError here (SK/linear_model/_base.py:385-389) -> HTTP 500, as in the reference
+            raise ValueError("Input X contains NaN or infinity.")
+        label_idx, prob = await state["batcher"].submit(row)
+        cls = state["classes"][label_idx]
+        return {"prediction": cls.item() if hasattr(cls, "item") else cls, "probability": prob}
+
+    @app.post("/files/")
+    async def create_file(file: bytes = File(...), token: str = Form(...)):
+        # REF/main.py:29-39.  Not on the scoring path.  The reference returns the DataFrame object
+        # itself, which current FastAPI cannot serialise (HTTP 500); the frame is returned as columns.
+        import pandas as pd
+        df = pd.read_csv(StringIO(str(file, "utf-8")))
+        return {"file": df.to_dict(orient="list"), "token": token}
+
+    @app.get("/batcher_stats")
+    async def batcher_stats():
+        return state["batcher"].stats()
+
+    return app
+
+
+def __getattr__(name):
+    # `uvicorn mlapi_b200.app:app` builds the default app lazily (needs the pickle and a GPU)
+    if name == "app":
+        return create_app()
+    raise AttributeError(name)

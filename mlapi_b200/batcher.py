@@ -1,0 +1,173 @@
+"""Request micro-batcher: coalesces single-row /predict calls into device batches.
+
+The reference scores one row per request on the event loop, re-loading the pickle each time
+(REF/main.py:17-22).  Here requests are queued; one worker thread per model replica (= per GPU)
+drains the queue into a pinned staging matrix and makes ONE `lr_score_host` call per batch (label +
+max probability in a single pass, i.e. REF/main.py:21-22 fused), then resolves the waiting futures.
+A batch closes when it reaches `max_batch` rows or when its oldest request has waited
+`max_wait_us`.  Replicas pull from the same queue, so multi-GPU serving is "replicas only": no
+collective, natural load balance.
+"""
+from __future__ import annotations
+
+import asyncio
+import queue
+import threading
+import time
+from collections import Counter
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+ScoreFn = Callable[[np.ndarray, int], Tuple[np.ndarray, np.ndarray]]
+"""(staging rows [max_batch, d] float32, n valid rows) -> (label index [n] int, max proba [n] float)"""
+
+
+class MicroBatcher:
+    def __init__(self, score_fns: Sequence[ScoreFn], n_features: int, max_batch: int = 4096,
+                 max_wait_us: float = 200.0, alloc: Optional[Callable] = None):
+        if max_batch < 1:
+            raise ValueError("max_batch must be >= 1")
+        self.n_features = int(n_features)
+        self.max_batch = int(max_batch)
+        self.max_wait = float(max_wait_us) * 1e-6
+        self._q: "queue.SimpleQueue" = queue.SimpleQueue()
+        self._stop = threading.Event()
+        self.batch_sizes: Counter = Counter()
+        self.requests = 0
+        self._alloc = alloc or (lambda shape, dtype: np.empty(shape, dtype))
+        self._threads: List[threading.Thread] = []
+        for i, fn in enumerate(score_fns):
+            t = threading.Thread(target=self._worker, args=(fn,), name=f"lr-batcher-{i}", daemon=True)
+            t.start()
+            self._threads.append(t)
+
+    # ---- producer side (event loop) ----------------------------------------------------------------
+    async def submit(self, row: Sequence[float]) -> Tuple[int, float]:
+        """Queue one row; resolves to (label index, max class probability)."""
+        if len(row) != self.n_features:
+            raise ValueError(f"X has {len(row)} features, but LogisticRegression is expecting "
+                             f"{self.n_features} features as input.")
+        loop = asyncio.get_running_loop()
+        fut = loop.create_future()
+        self._q.put((row, fut, loop))
+        return await fut
+
+    def submit_blocking(self, row: Sequence[float], timeout: float = 30.0) -> Tuple[int, float]:
+        """Thread-side variant for callers without an event loop."""
+        done = threading.Event()
+        box = {}
+
+        class _Fut:
+            def set_result(self, v):
+                box["v"] = v
+                done.set()
+
+            def set_exception(self, e):
+                box["e"] = e
+                done.set()
+
+            def done(self):
+                return done.is_set()
+
+        self._q.put((row, _Fut(), None))
+        if not done.wait(timeout):
+            raise TimeoutError("micro-batcher did not answer")
+        if "e" in box:
+            raise box["e"]
+        return box["v"]
+
+    # ---- consumer side (one thread per replica) ----------------------------------------------------
+    def _worker(self, score_fn: ScoreFn):
+        stage = self._alloc((self.max_batch, self.n_features), np.float32)
+        while not self._stop.is_set():
+            try:
+                first = self._q.get(timeout=0.05)
+            except queue.Empty:
+                continue
+            items = [first]
+            deadline = time.perf_counter() + self.max_wait
+            while len(items) < self.max_batch:
+                remaining = deadline - time.perf_counter()
+                try:
+                    items.append(self._q.get_nowait() if remaining <= 0 else self._q.get(timeout=remaining))
+                except queue.Empty:
+                    break
+                if remaining <= 0 and self._q.empty():
+                    break
+            n = len(items)
+            try:
+                for i, (row, _, _) in enumerate(items):
+                    stage[i] = row
+                labels, probs = score_fn(stage, n)
+                results = [(int(labels[i]), float(probs[i])) for i in range(n)]
+                err = None
+            except Exception as e:  # noqa: BLE001 - forwarded to every waiter
+                results, err = None, e
+            self.batch_sizes[n] += 1
+            self.requests += n
+            self._resolve(items, results, err)
+
+    @staticmethod
+    def _resolve(items, results, err):
+        by_loop = {}
+        for i, (_, fut, loop) in enumerate(items):
+            by_loop.setdefault(loop, []).append((fut, None if results is None else results[i]))
+
+        def finish(pairs):
+            for fut, res in pairs:
+                if fut.done():
+                    continue
+                if err is not None:
+                    fut.set_exception(err)
+                else:
+                    fut.set_result(res)
+
+        for loop, pairs in by_loop.items():
+            if loop is None:
+                finish(pairs)
+            else:
+                loop.call_soon_threadsafe(finish, pairs)     # one wake-up per batch, not per request
+
+    def close(self):
+        self._stop.set()
+        for t in self._threads:
+            t.join(timeout=2.0)
+
+    def stats(self) -> dict:
+        sizes = sorted(self.batch_sizes.items())
+        total = sum(c for _, c in sizes)
+        return {"requests": self.requests, "batches": total,
+                "mean_batch": (self.requests / total) if total else 0.0,
+                "max_batch_seen": sizes[-1][0] if sizes else 0}
+
+
+def engine_score_fns(clf) -> List[ScoreFn]:
+    """One scoring closure per replica of a `B200LogisticRegression`: label + max proba through
+    `lr_score_host`, outputs in preallocated arrays."""
+    import ctypes as C
+
+    from . import _lib
+
+    fns = []
+    for rep in clf._replicas:
+        def make(rep=rep):
+            labels = None
+            probs = None
+
+            def fn(stage: np.ndarray, n: int):
+                nonlocal labels, probs
+                if labels is None or labels.shape[0] < stage.shape[0]:
+                    labels = np.empty(stage.shape[0], np.int32)
+                    probs = np.empty(stage.shape[0], np.float32)
+                code = rep.lib.lr_score_host(rep.handle, stage.ctypes.data_as(C.c_void_p), n, stage.shape[1],
+                                             None, None, labels.ctypes.data_as(C.c_void_p),
+                                             probs.ctypes.data_as(C.c_void_p))
+                if code == _lib.LR_ERR_NONFINITE:
+                    raise ValueError("Input X contains NaN or infinity.")
+                _lib.check(code)
+                return labels, probs
+
+            return fn
+        fns.append(make())
+    return fns

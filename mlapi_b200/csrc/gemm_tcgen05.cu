@@ -47,7 +47,7 @@ constexpr int B_STAGES = 4;
 constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB (x2: hi, lo)
 constexpr int B_TILE_BYTES = BN * BK * 4;     // 32 KB
 constexpr int kThreads = 320;                 // 10 warps
-constexpr int kMaxCluster = 8;
+constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 
 struct SmemLayout {
     // offsets from the 1024-byte aligned base
@@ -340,6 +340,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int r_in_tile = q * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        int n_real = p.n_classes - col0;             // real (unpadded) classes held by this CTA
+        n_real = n_real < 0 ? 0 : (n_real > n_cols_cta ? n_cols_cta : n_real);
         uint32_t accph = 0;
         uint32_t it = 0;
         for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters, ++it) {
@@ -348,41 +350,102 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             accph ^= 1;
             tc_fence_after();
 
-            // pass 1: running max / argmax / sum of exp over this CTA's classes
+            // pass 1: running max / first argmax / sum of exp over this CTA's classes
             float m = -INFINITY, ssum = 0.0f;
             int arg = col0;
             bool ok = true;
-            for (int cb = 0; cb < n_cols_cta; cb += 32) {
-                if (col0 + cb >= p.n_classes) break;          // only padding from here on
+            for (int cb = 0; cb < n_real; cb += 32) {
                 float v[32];
                 tmem_ld32(t_lane + (uint32_t)cb, v);
-                float cm = -INFINITY;
+                const float m_old = m;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    v[i] += bias_s[cb + i];
-                    if (col0 + cb + i < p.n_classes) ok = ok && finite_f(v[i]);
-                    if (v[i] > cm) cm = v[i];
-                    if (v[i] > m) { m = v[i]; arg = col0 + cb + i; }      // strict: first maximum wins
+                    v[i] += bias_s[cb + i];                       // padding carries -inf
+                    if (cb + i < n_real) ok = ok && finite_f(v[i]);
+                    if (v[i] > m) { m = v[i]; arg = col0 + cb + i; }   // strict: first maximum wins
                 }
-                // m already includes this chunk's maximum
+                if (m > m_old) ssum *= ex2((m_old - m) * kLog2e);  // re-base the sum on the new max
                 const float ml = m * kLog2e;
                 float add = 0.0f;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) add += ex2(fmaf(v[i], kLog2e, -ml));
-                (void)cm;
-                ssum = ssum * 1.0f + add;             // rescaled below when m moved
-                // rescale: sum so far was relative to the previous maximum
-                // (handled by keeping prev max)
-                // see note: implemented via m_prev
-                // -- replaced by explicit form just below --
-                ssum = ssum;
-                (void)ssum;
-                // explicit running form
-                // (kept simple: recompute with m_prev tracked outside)
-                // NOTE: this block is rewritten in finalize_stats()
-                break;
+                ssum += add;
             }
-            (void)m; (void)arg; (void)ok; (void)row; (void)xchg; (void)xchg_bar; (void)it;
+
+            // combine with the other class slices of the same rows (distributed shared memory)
+            float gm = m, gs = ssum;
+            int garg = arg;
+            bool gok = ok;
+            if (p.ncc > 1) {
+                const uint32_t buf = it & 1;
+                const uint32_t slot = smem_u32(xchg + (buf * kMaxCluster + rank) * BM + r_in_tile);
+                const uint32_t bar = smem_u32(xchg_bar + buf);
+                for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
+                    st_cluster_v4(map_to_cta(slot, dst), m, ssum, __int_as_float(arg), ok ? 1.0f : 0.0f);
+                    mbar_arrive_cluster(map_to_cta(bar, dst));
+                }
+                mbar_wait_cluster(xchg_bar + buf, (it >> 1) & 1);
+                gm = -INFINITY;
+                for (int src = 0; src < p.ncc; ++src) {
+                    const float4 e = xchg[(buf * kMaxCluster + src) * BM + r_in_tile];
+                    if (e.x > gm) { gm = e.x; garg = __float_as_int(e.z); }   // lower slice wins ties
+                    gok = gok && (e.w != 0.0f);
+                }
+                gs = 0.0f;
+                for (int src = 0; src < p.ncc; ++src) {
+                    const float4 e = xchg[(buf * kMaxCluster + src) * BM + r_in_tile];
+                    gs += e.y * ex2((e.x - gm) * kLog2e);
+                }
+            }
+            const float inv = __frcp_rn(gs);
+            const float gml = gm * kLog2e;
+            const bool live = row < p.n_rows;
+
+            // pass 2: normalise and store this CTA's slice of the row
+            for (int cb = 0; cb < n_real; cb += 32) {
+                float v[32];
+                tmem_ld32(t_lane + (uint32_t)cb, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += bias_s[cb + i];
+                if (live) {
+                    const int64_t off = row * p.n_classes + col0 + cb;
+                    const bool whole = cb + 32 <= n_real;
+                    if (p.decision) {
+                        if (whole && p.vec_store) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4)
+                                __stcs(reinterpret_cast<float4*>(p.decision + off + i),
+                                       make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (cb + i < n_real) __stcs(p.decision + off + i, v[i]);
+                        }
+                    }
+                    if (p.proba) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] = ex2(fmaf(v[i], kLog2e, -gml)) * inv;
+                        if (whole && p.vec_store) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4)
+                                __stcs(reinterpret_cast<float4*>(p.proba + off + i),
+                                       make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (cb + i < n_real) __stcs(p.proba + off + i, v[i]);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(acc_empty);                   // TMEM may be overwritten by the next tile
+
+            if (live && rank == 0) {
+                if (p.label) __stcs(p.label + row, garg);
+                if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
+                if (!gok) atomicAdd(p.status, 1ull);
+            }
         }
     }
 
@@ -397,9 +460,157 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
 }  // namespace
 
-bool gemm_supports(const Model&, const ScoreArgs&) { return false; }
-int gemm_prepare(Model&, const double*, const double*) { return LR_OK; }
-void gemm_destroy(Model&) {}
-int gemm_launch(const Model&, const ScoreArgs&) { return fail(LR_ERR_INVALID, "gemm path not built"); }
+struct GemmPlan {
+    float* w_hi = nullptr;      // [c_pad][d] TF32 (round-to-nearest) part of coef_
+    float* w_lo = nullptr;      // [c_pad][d] TF32 of the residual
+    float* bias = nullptr;      // [c_pad], -inf beyond n_classes
+    CUtensorMap map_whi, map_wlo;
+    int nb = 0, ncc = 0, c_pad = 0;
+    bool configured[64] = {false};
+};
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D fp32 row-major [rows][cols] with row pitch `ld` elements; box = box_rows x 32 columns, 128B swizzle.
+int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_tiled();
+    if (!fn) return fail(LR_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * sizeof(float)};
+    cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(LR_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return LR_OK;
+}
+
+// cvt.rna.tf32.f32 on the host: round to nearest (ties away), keep 10 mantissa bits.
+float tf32_rna_host(float x) {
+    uint32_t u;
+    std::memcpy(&u, &x, 4);
+    if ((u & 0x7f800000u) != 0x7f800000u) u += 0x1000u;
+    u &= 0xffffe000u;
+    std::memcpy(&x, &u, 4);
+    return x;
+}
+
+}  // namespace
+
+// Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048;
+// rows of X and W must be 16-byte aligned (TMA).
+bool gemm_supports(const Model& m, const ScoreArgs& a) {
+    return m.gemm != nullptr && (a.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0) &&
+           a.n_rows < (int64_t)1 << 31;
+}
+
+int gemm_prepare(Model& m, const double* coef, const double* intercept) {
+    if (m.n_scores <= 16 || m.n_scores > kMaxCluster * 2 * BN || m.n_features % 4 != 0) return LR_OK;
+    if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
+    GemmPlan* g = new GemmPlan();
+    const int C = m.n_scores, d = m.n_features;
+    if (C <= BN) { g->nb = 1; g->ncc = 1; }
+    else if (C <= 2 * BN) { g->nb = 2; g->ncc = 1; }
+    else { g->nb = 2; g->ncc = (C + 2 * BN - 1) / (2 * BN); if (g->ncc == 3) g->ncc = 4; }
+    g->c_pad = g->ncc * g->nb * BN;
+    std::vector<float> hi((size_t)g->c_pad * d, 0.0f), lo((size_t)g->c_pad * d, 0.0f), bias(g->c_pad, -INFINITY);
+    for (int c = 0; c < C; ++c) {
+        bias[c] = (float)intercept[c];
+        for (int k = 0; k < d; ++k) {
+            const double w = coef[(size_t)c * d + k];
+            const float h = tf32_rna_host((float)w);
+            hi[(size_t)c * d + k] = h;
+            lo[(size_t)c * d + k] = tf32_rna_host((float)(w - (double)h));
+        }
+    }
+    m.gemm = g;
+    const size_t bytes = hi.size() * sizeof(float);
+    LRS_CUDA(cudaMalloc(&g->w_hi, bytes));
+    LRS_CUDA(cudaMalloc(&g->w_lo, bytes));
+    LRS_CUDA(cudaMalloc(&g->bias, bias.size() * sizeof(float)));
+    LRS_CUDA(cudaMemcpy(g->w_hi, hi.data(), bytes, cudaMemcpyHostToDevice));
+    LRS_CUDA(cudaMemcpy(g->w_lo, lo.data(), bytes, cudaMemcpyHostToDevice));
+    LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+    int rc;
+    if ((rc = make_map(&g->map_whi, g->w_hi, g->c_pad, d, d, BN)) != LR_OK) return rc;
+    if ((rc = make_map(&g->map_wlo, g->w_lo, g->c_pad, d, d, BN)) != LR_OK) return rc;
+    return LR_OK;
+}
+
+void gemm_destroy(Model& m) {
+    if (!m.gemm) return;
+    cudaFree(m.gemm->w_hi);
+    cudaFree(m.gemm->w_lo);
+    cudaFree(m.gemm->bias);
+    delete m.gemm;
+    m.gemm = nullptr;
+}
+
+int gemm_launch(const Model& m, const ScoreArgs& a) {
+    if (!gemm_supports(m, a))
+        return fail(LR_ERR_INVALID, "gemm path needs 17..2048 classes, n_features % 4 == 0 and 16-byte aligned rows of X");
+    GemmPlan* g = m.gemm;
+    CUtensorMap map_x;
+    int rc = make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM);
+    if (rc != LR_OK) return rc;
+    const size_t smem = SmemLayout::total + 1024;
+    const int dev = m.device & 63;
+    if (!g->configured[dev]) {
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        g->configured[dev] = true;
+    }
+    GemmParams p;
+    p.n_rows = a.n_rows;
+    p.n_features = m.n_features;
+    p.n_classes = m.n_scores;
+    p.nb = g->nb;
+    p.ncc = g->ncc;
+    p.num_k_chunks = (m.n_features + BK - 1) / BK;
+    p.bias = g->bias;
+    p.proba = a.proba;
+    p.decision = a.decision;
+    p.label = a.label;
+    p.maxprob = a.maxprob;
+    p.status = m.status;
+    const bool al = (m.n_scores % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(a.decision) & 15u) == 0);
+    p.vec_store = al ? 1 : 0;
+
+    const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
+    int64_t clusters = m.num_sms / g->ncc;
+    if (clusters > n_tiles) clusters = n_tiles;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * g->ncc));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = a.stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)g->ncc;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel, map_x, g->map_whi, g->map_wlo, p));
+    count_launch();
+    return LR_OK;
+}
 
 }  // namespace lrs

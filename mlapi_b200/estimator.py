@@ -22,6 +22,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
+from .sharding import shard_bounds
 
 
 def _is_torch_tensor(x) -> bool:
@@ -181,9 +182,8 @@ class B200LogisticRegression:
             if G == 1 or n < 2 * G:
                 results = [run(self._replicas[0], 0, n)]
             else:
-                bounds = [n * g // G for g in range(G + 1)]     # contiguous row blocks
-                results = list(self._pool.map(lambda g: run(self._replicas[g], bounds[g], bounds[g + 1]),
-                                              range(G)))
+                bounds = shard_bounds(n, G)                     # contiguous row blocks, no collective
+                results = list(self._pool.map(lambda g: run(self._replicas[g], *bounds[g]), range(G)))
         for code, msg in results:
             if code == _lib.LR_ERR_NONFINITE:
                 raise ValueError("Input X contains NaN or infinity (or a value too large for float32).")

