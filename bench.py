@@ -116,14 +116,16 @@ def cpu_reference(workload, threads=None, reps=None, budget_s=20.0):
     W, b = make_model(d, ns, 2)
     clf = synth.sklearn_model(W, b)
     X = np.random.default_rng(1).standard_normal((n, d), dtype=np.float32)
-    clf.predict_proba(X[: max(1, n // 8)])
-    times = []
-    t_end = time.perf_counter() + budget_s
-    while len(times) < (reps or 3) or (reps is None and time.perf_counter() < t_end and len(times) < 10):
-        t0 = time.perf_counter()
-        clf.predict_proba(X)
-        times.append(time.perf_counter() - t0)
     cores = len(os.sched_getaffinity(0))
+    times = []
+    from threadpoolctl import threadpool_limits
+    with threadpool_limits(limits=cores):        # torchrun exports OMP_NUM_THREADS=1: undo it here
+        clf.predict_proba(X[: max(1, n // 8)])
+        t_end = time.perf_counter() + budget_s
+        while len(times) < (reps or 3) or (reps is None and time.perf_counter() < t_end and len(times) < 10):
+            t0 = time.perf_counter()
+            clf.predict_proba(X)
+            times.append(time.perf_counter() - t0)
     blas = [f"{i.get('internal_api')}:{i.get('num_threads')}" for i in threadpool_info()]
     return dict(rows=n, times=times, best=min(times), median=float(np.median(times)), cores=cores,
                 sample=f"{n} rows x d={d} fp32 (same distribution as the GPU batch), sklearn "
@@ -142,13 +144,15 @@ def run_reference(args):
     W, b = make_model(d, ns, 2)
     clf = synth.sklearn_model(W, b)
     X = np.random.default_rng(1).standard_normal((rows, d), dtype=np.float32)
-    for _ in range(args.warmup):
-        clf.predict_proba(X)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        clf.predict_proba(X)
-    dt = (time.perf_counter() - t0) / args.steps
     cores = len(os.sched_getaffinity(0))
+    from threadpoolctl import threadpool_limits
+    with threadpool_limits(limits=cores):        # all host threads, whatever the launcher exported
+        for _ in range(args.warmup):
+            clf.predict_proba(X)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            clf.predict_proba(X)
+        dt = (time.perf_counter() - t0) / args.steps
     value = rows / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,

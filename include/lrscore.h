@@ -111,6 +111,27 @@ int lr_score_host(lr_model* m, const float* X_host, int64_t n_rows, int64_t ldx,
 int lr_model_set_host_chunk_rows(lr_model* m, int64_t rows);
 
 /*
+ * Refit row: loss and gradient of the log-loss over n_rows rows in ONE fused pass over X -- what
+ * `LogisticRegression().fit` (REF/Logistic Regression.ipynb:33-34) evaluates per lbfgs iteration
+ * through LinearModelLoss.loss_gradient (SK/linear_model/_linear_loss.py:291-378; pointwise terms
+ * SK/_loss/_loss.pyx.tp:728-751 binary, :269/:1202 multinomial).
+ *
+ *   y_dev    n_rows int32 class indices (binary: 0 / 1)
+ *   W_dev    n_scores x n_features fp32 (current iterate), b_dev n_scores fp32
+ *   out_dev  float64 [1 + n_scores*n_features + n_scores] = [ sum_i loss_i | sum_i r_i x_i^T | sum_i r_i ]
+ *
+ * The sums are UNNORMALISED and cover only the rows given: ranks all-reduce `out_dev` (the single
+ * collective of the design), then divide by n and add the L2 term on the host (intercept
+ * unpenalised).  Serves n_scores <= 8 and n_features <= 128 (16-byte aligned rows) or <= 32
+ * (any rows); larger shapes return LR_ERR_LIMIT.  Per-CTA partial vectors go through device scratch
+ * owned by the library (allocated on first use per device); calls on one device must be
+ * stream-ordered with respect to each other.  Uses the current device unless X_dev says otherwise.
+ */
+int lr_loss_grad(const float* X_dev, const int32_t* y_dev, int64_t n_rows, int64_t ldx,
+                 const float* W_dev, const float* b_dev, int32_t n_scores, int32_t n_features,
+                 double* out_dev, void* stream);
+
+/*
  * Page-locked host memory for the buffers handed to lr_score_host (the /predict micro-batcher's
  * staging rows, bench.py's e2e inputs).  With pageable memory the copies still work but the driver
  * stages them and the three-stream overlap is lost.  No reference counterpart: REF/main.py:20

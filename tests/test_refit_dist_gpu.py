@@ -1,0 +1,61 @@
+"""Two-rank NCCL refit: each rank holds half the rows, the only exchange is the all-reduce of the
+[loss | grad] vector, and both ranks must land on the single-rank model.  Needs 2 GPUs (skipped on
+a 1-GPU box; run with `gpurun --gpus 2`)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from mlapi_b200 import refit, sharding
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    rng = np.random.default_rng(4)
+    n, d = 40_001, 32
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    y = (X[:, 0] * 1.5 - X[:, 3] + 0.3 * rng.standard_normal(n) > 0.2).astype(np.int64)
+    lo, hi = sharding.my_rows(n, rank, world)
+    res = refit.fit(X[lo:hi], y[lo:hi], classes=np.array([0, 1]))
+    q.put((rank, res.coef_, res.intercept_, res.n_iter_[0], res.world_))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_refit_matches_single_rank():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import __graft_entry__
+    __graft_entry__.build()
+    import torch.multiprocessing as mp
+    from mlapi_b200 import refit
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    results = sorted((q.get(timeout=300) for _ in procs), key=lambda t: t[0])
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    rng = np.random.default_rng(4)
+    n, d = 40_001, 32
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    y = (X[:, 0] * 1.5 - X[:, 3] + 0.3 * rng.standard_normal(n) > 0.2).astype(np.int64)
+    single = refit.fit(X, y)
+    assert results[0][4] == 2
+    np.testing.assert_array_equal(results[0][1], results[1][1])          # identical steps on both ranks
+    np.testing.assert_allclose(results[0][1], single.coef_, atol=2e-3)
+    np.testing.assert_allclose(results[0][2], single.intercept_, atol=2e-3)
