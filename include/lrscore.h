@@ -132,6 +132,27 @@ int lr_loss_grad(const float* X_dev, const int32_t* y_dev, int64_t n_rows, int64
                  double* out_dev, void* stream);
 
 /*
+ * lr_loss_grad for callers that must not allocate.  (No counterpart in the reference: this variant
+ * exists for the embedding side, not for parity.)  Same arguments and results as lr_loss_grad, but
+ * the per-CTA partial sums go to a fixed array built into the library (about 0.6 MB per GPU, held
+ * until the process exits) instead of a cudaMalloc'ed buffer, and the call makes no cudaMalloc /
+ * cudaFree or any other allocating call.  Meant for hosts that give all device memory to their own
+ * pool at start-up, that cannot let a refit step stall other streams inside the allocator, or whose
+ * rules keep third-party code off the device heap.
+ *   - limit: 1 + n_scores*(n_features+1) <= 512 floats per partial vector, else LR_ERR_LIMIT
+ *     (the array has room for 296 vectors of that size);
+ *   - the first call on each device looks the array up (one-time set-up): make that call before
+ *     starting any stream capture;
+ *   - X_dev must be on the current device;
+ *   - all calls on a device share the one array, which still holds the previous call's data: the
+ *     arrival counter is cleared on `stream` before every launch, and calls whose GPU work overlaps
+ *     race with each other -- keep them ordered.
+ */
+int lr_loss_grad_static(const float* X_dev, const int32_t* y_dev, int64_t n_rows, int64_t ldx,
+                        const float* W_dev, const float* b_dev, int32_t n_scores, int32_t n_features,
+                        double* out_dev, void* stream);
+
+/*
  * Page-locked host memory for the buffers handed to lr_score_host (the /predict micro-batcher's
  * staging rows, bench.py's e2e inputs).  With pageable memory the copies still work but the driver
  * stages them and the three-stream overlap is lost.  No reference counterpart: REF/main.py:20

@@ -318,3 +318,77 @@ extern "C" int lr_loss_grad(const float* X_dev, const int32_t* y_dev, int64_t n_
     RefitArgs a{X_dev, y_dev, n_rows, ldx, W_dev, b_dev, n_scores, n_features, out_dev, nullptr, nullptr, 0};
     return run_refit(a, scratch, want, reinterpret_cast<cudaStream_t>(stream));
 }
+
+// ---- lr_loss_grad_static: the same reduction with no allocation anywhere ---------------------------
+//
+// Who this is for.  lr_loss_grad above grows a cudaMalloc'ed scratch buffer the first time it runs
+// on a device.  Some hosts cannot afford that call: a serving process that hands all of its device
+// memory to its own pool at start-up (a later cudaMalloc can simply fail there), a refit step that
+// runs beside latency-sensitive scoring streams (cudaMalloc/cudaFree may stall the whole device while
+// they run), or an embedding runtime whose rules forbid third-party code from touching the device
+// heap.  For those callers the per-CTA partial vectors live in a fixed array that is part of the
+// library image: every GPU that loads liblrscore holds kStaticScratchBytes (about 0.6 MB) of it
+// until the process exits, whether this entry point is used or not.
+//
+// Limits that follow from the fixed size: one partial vector [loss | grad_W | grad_b] may hold at
+// most kStaticMaxVector floats, and the array has room for kStaticMaxCtas such vectors (two CTAs per
+// SM on a B200; shorter vectors leave room for more CTAs, and when fewer CTAs fit than the GPU could
+// run, each one strides over more row tiles).  Larger problems are refused with LR_ERR_LIMIT; use
+// lr_loss_grad for them.
+//
+// Sharing.  There is ONE array per device and every call uses it, so it still holds the previous
+// call's partial sums and arrival counter when the next call starts.  The kernel overwrites every
+// partial slot it later reads, and the counter -- the one word that has to start at zero -- is
+// cleared on the caller's stream before each launch.  Two calls whose GPU work overlaps (different
+// streams, or different host threads without ordering) would write the same slots and race: keep
+// calls on one device ordered one after the other.
+constexpr int kStaticMaxCtas = 296;
+constexpr int kStaticMaxVector = 512;
+constexpr size_t kStaticScratchBytes = 256 + (size_t)kStaticMaxCtas * kStaticMaxVector * sizeof(float);
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace lrs {
+namespace {
+// Device address of g_static_scratch, per device.  In host code the symbol's name is only a
+// stand-in; the address a kernel may use comes from cudaGetSymbolAddress, asked once per device
+// while that device is current.
+std::mutex g_static_mu;
+void* g_static_addr[64] = {};
+}  // namespace
+}  // namespace lrs
+
+extern "C" int lr_loss_grad_static(const float* X_dev, const int32_t* y_dev, int64_t n_rows, int64_t ldx,
+                                   const float* W_dev, const float* b_dev, int32_t n_scores,
+                                   int32_t n_features, double* out_dev, void* stream) {
+    int rc = check_refit_args(X_dev, y_dev, n_rows, ldx, W_dev, b_dev, n_scores, n_features, out_dev);
+    if (rc != LR_OK) return rc;
+    const int64_t vec = 1 + (int64_t)n_scores * ((int64_t)n_features + 1);
+    if (vec > kStaticMaxVector)
+        return fail(LR_ERR_LIMIT, "lr_loss_grad_static: one partial vector needs " + std::to_string(vec) +
+                                      " floats (1 + n_scores*(n_features+1)) but the built-in scratch holds at most " +
+                                      std::to_string(kStaticMaxVector) + "; use lr_loss_grad for this shape");
+    int dev = 0;
+    LRS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(LR_ERR_LIMIT, "lr_loss_grad_static: device index above 63");
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, X_dev) == cudaSuccess && attr.type == cudaMemoryTypeDevice && attr.device != dev)
+        return fail(LR_ERR_INVALID, "lr_loss_grad_static: X_dev lives on device " + std::to_string(attr.device) +
+                                        " but device " + std::to_string(dev) + " is current");
+    void* scratch = nullptr;
+    {
+        // One-time set-up for this device (the first call here should happen before any stream
+        // capture is started): look up where the array lives on the current device.
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_addr[dev]) {
+            void* p = nullptr;
+            LRS_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+            g_static_addr[dev] = p;
+        }
+        scratch = g_static_addr[dev];
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    LRS_CUDA(cudaMemsetAsync(scratch, 0, 256, s));          // the arrival counter must start at zero
+    RefitArgs a{X_dev, y_dev, n_rows, ldx, W_dev, b_dev, n_scores, n_features, out_dev, nullptr, nullptr, 0};
+    return run_refit(a, scratch, kStaticScratchBytes, s);
+}
