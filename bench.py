@@ -182,6 +182,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--outputs", default="proba", help="comma list of proba,decision,label,maxprob")
+    ap.add_argument("--logit-scale", type=float, default=1.0,
+                    help="multiply W by this (confident models stress the tensor path's re-scoring pass)")
     args = ap.parse_args()
     if args.impl == "b200":
         args.warmup = max(args.warmup, 3)          # timing rule: at least 3 untimed steps
@@ -214,6 +216,7 @@ def main():
         n = args.rows
     n_out = max(ns, 2)
     W, b = make_model(d, ns, 2)
+    W = W * args.logit_scale
     clf = B200LogisticRegression(W, b, np.arange(n_out), devices=[local])
     rep = clf._replicas[0]
     dev = torch.device("cuda", local)
@@ -343,7 +346,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
             "config": {"workload": desc, "rows_per_gpu": n, "n_features": d, "n_scores": ns,
-                       "outputs": sorted(want), "kernel_path": _lib.PATH_NAMES.get(path.value, "?"),
+                       "outputs": sorted(want), "logit_scale": args.logit_scale, "kernel_path": _lib.PATH_NAMES.get(path.value, "?"),
                        "parallelism": f"row-shard x{world}, no collective",
                        "l2": "inputs larger than L2 (no flush needed)" if n * d * 4 > (512 << 20)
                        else "inputs fit in L2: latency figure, not a bandwidth figure"},

@@ -96,6 +96,12 @@ int lr_score(lr_model* m, const float* X_dev, int64_t n_rows, int64_t ldx,
 /* Synchronise `stream`, return the number of non-finite rows seen since the last call, and reset. */
 int lr_model_take_nonfinite(lr_model* m, void* stream, uint64_t* n_rows_nonfinite);
 
+/* Synchronise `stream` and return (then reset) how many rows the tensor-core path handed to its fp32
+ * re-scoring pass since the last call: rows whose runner-up class sits inside the accumulation error
+ * of the maximum, or whose probabilities that error could move by more than the parity bar.
+ * Diagnostic; 0 on the other paths. */
+int lr_model_take_rescored(lr_model* m, void* stream, uint64_t* n_rows_rescored);
+
 /*
  * Same contract as lr_score with HOST buffers: rows are streamed through device staging buffers in
  * chunks (H2D copy, kernel, D2H copy overlapped on three streams) and the call returns when every

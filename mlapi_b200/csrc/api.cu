@@ -207,6 +207,19 @@ int lr_model_take_nonfinite(lr_model* h, void* stream, uint64_t* out) {
     return LR_OK;
 }
 
+int lr_model_take_rescored(lr_model* h, void* stream, uint64_t* out) {
+    if (!h || !out) return fail(LR_ERR_INVALID, "model / out is NULL");
+    Model* m = reinterpret_cast<Model*>(h);
+    DeviceGuard guard(m->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    unsigned long long v = 0;
+    LRS_CUDA(cudaMemcpyAsync(&v, m->status + 1, sizeof(v), cudaMemcpyDeviceToHost, s));
+    LRS_CUDA(cudaMemsetAsync(m->status + 1, 0, sizeof(v), s));
+    LRS_CUDA(cudaStreamSynchronize(s));
+    *out = v;
+    return LR_OK;
+}
+
 int lr_model_set_host_chunk_rows(lr_model* h, int64_t rows) {
     if (!h) return fail(LR_ERR_INVALID, "model is NULL");
     if (rows < 0) return fail(LR_ERR_INVALID, "rows is negative");

@@ -30,10 +30,12 @@
 #include <cuda.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
 #include "common.cuh"
+#include "generic_row.cuh"
 
 namespace lrs {
 
@@ -46,7 +48,8 @@ constexpr int A_STAGES = 2;
 constexpr int B_STAGES = 4;
 constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB (x2: hi, lo)
 constexpr int B_TILE_BYTES = BN * BK * 4;     // 32 KB
-constexpr int kThreads = 320;                 // 10 warps
+constexpr int kThreads = 448;                 // 14 warps: TMA, MMA, 4 converters, 8 epilogue
+constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 
 struct SmemLayout {
@@ -55,9 +58,11 @@ struct SmemLayout {
     static constexpr int a_lo = a_hi + A_STAGES * A_TILE_BYTES;      // [A_STAGES][16 KB]
     static constexpr int b = a_lo + A_STAGES * A_TILE_BYTES;         // [B_STAGES][32 KB]
     static constexpr int bias = b + B_STAGES * B_TILE_BYTES;         // [512] floats
-    static constexpr int xchg = bias + 512 * 4;                      // [2][kMaxCluster][BM] float4 (m, s, arg, -)
-    static constexpr int bars = xchg + 2 * kMaxCluster * BM * 16;    // mbarriers
-    static constexpr int n_bars = 3 * A_STAGES + 2 * B_STAGES + 2 + 2;
+    static constexpr int xchg = bias + 512 * 4;                      // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
+    static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
+    static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
+    static constexpr int bars = glob + BM * 8;                       // mbarriers
+    static constexpr int n_bars = 3 * A_STAGES + 2 * B_STAGES + 2 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
 };
@@ -68,6 +73,7 @@ struct GemmParams {
     int n_features;
     int n_classes;
     int nb;                 // 256-class blocks per CTA (1 or 2)
+    int split;              // 1: nb == 1 and the correction products accumulate in TMEM columns 256..511
     int ncc;                // CTAs per cluster (class split)
     int num_k_chunks;
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
@@ -76,6 +82,8 @@ struct GemmParams {
     int32_t* label;
     float* maxprob;
     unsigned long long* status;
+    unsigned char* flags;   // [n_rows] set for rows to re-score in fp32 (near-ties, risky probabilities)
+    float* lse;             // [n_rows] log-sum-exp of the row as the tensor path saw it (for the re-scoring pass)
     int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned)
 };
 
@@ -155,6 +163,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+        "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+        "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+        "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+        "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+        "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+        "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+        "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void st_cluster_v2(uint32_t addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -193,7 +221,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     unsigned char* a_lo = smem + SmemLayout::a_lo;
     unsigned char* b_t = smem + SmemLayout::b;
     float* bias_s = reinterpret_cast<float*>(smem + SmemLayout::bias);
-    float4* xchg = reinterpret_cast<float4*>(smem + SmemLayout::xchg);
+    float2* xchg = reinterpret_cast<float2*>(smem + SmemLayout::xchg);
+    float2* halves = reinterpret_cast<float2*>(smem + SmemLayout::halves);
+    float2* glob = reinterpret_cast<float2*>(smem + SmemLayout::glob);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SmemLayout::bars);
     uint64_t* x_full = bars;                       // [A_STAGES] TMA -> converters
     uint64_t* a_ready = x_full + A_STAGES;         // [A_STAGES] converters -> MMA
@@ -202,7 +232,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* b_empty = b_full + B_STAGES;         // [B_STAGES] MMA -> TMA
     uint64_t* acc_full = b_empty + B_STAGES;       // MMA -> epilogue
     uint64_t* acc_empty = acc_full + 1;            // epilogue -> MMA
-    uint64_t* xchg_bar = acc_empty + 1;            // [2] softmax statistics from every CTA of the cluster
+    uint64_t* xchg_bar = acc_empty + 1;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SmemLayout::tmem_slot);
 
     const int warp = threadIdx.x >> 5;
@@ -222,9 +252,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_init(b_empty + i, 1);
         }
         mbar_init(acc_full, 1);
-        mbar_init(acc_empty, 128);
-        mbar_init(xchg_bar + 0, 128 * p.ncc);
-        mbar_init(xchg_bar + 1, 128 * p.ncc);
+        mbar_init(acc_empty, kEpiThreads);
+        for (int i = 0; i < 4; ++i) mbar_init(xchg_bar + i, 128 * p.ncc);
         mbar_fence_init();
     }
     for (int i = threadIdx.x; i < n_cols_cta; i += kThreads) bias_s[i] = p.bias[col0 + i];
@@ -288,14 +317,20 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             tc_fence_after();
                             const uint64_t bd = make_smem_desc(smem_u32(b_t + bs * B_TILE_BYTES));
                             const uint32_t d_tmem = tmem_base + (uint32_t)(nbk * BN);
-#pragma unroll
-                            for (int k = 0; k < BK / 8; ++k) {        // 32-byte steps inside the swizzled row
-                                const uint32_t acc = (kc > 0 || part > 0 || k > 0) ? 1u : 0u;
-                                tc_mma_tf32(d_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, acc);
-                            }
+                            // split mode: the small products (x_lo.w_hi, x_hi.w_lo) get their own
+                            // accumulator, so only the 128 x_hi.w_hi steps are added at full magnitude
+                            const uint32_t c_tmem = p.split ? tmem_base + (uint32_t)BN : d_tmem;
                             if (part == 0) {
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k) tc_mma_tf32(d_tmem, alo + 2 * k, bd + 2 * k, kIdesc, 1u);
+                                for (int k = 0; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
+                                    tc_mma_tf32(d_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, (kc > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+                                for (int k = 0; k < BK / 8; ++k)
+                                    tc_mma_tf32(c_tmem, alo + 2 * k, bd + 2 * k, kIdesc,
+                                                (!p.split || kc > 0 || k > 0) ? 1u : 0u);
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < BK / 8; ++k) tc_mma_tf32(c_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, 1u);
                             }
                             tc_commit(b_empty + bs);
                             if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
@@ -336,96 +371,190 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             }
         }
     } else {
-        // ===================== epilogue =====================
+        // ===================== epilogue (8 warps) =====================
+        // Warp w may read TMEM lanes 32*(w%4)..+31 only, so the eight warps form two groups of four:
+        // group h covers half of this CTA's class columns for all 128 rows.  Three passes over TMEM:
+        //   1. row max and first argmax                       -> combine halves, then CTAs (DSMEM)
+        //   2. e = exp(z - max), sum, near-tie count; e is written back over the accumulator
+        //                                                      -> combine halves, then CTAs
+        //   3. p = e / sum -> global memory
+        // so each class costs one exp, and the statistics of a row meet through shared memory.
+        const int ew = warp - 6;                     // 0..7
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
+        const int h = ew >> 2;                       // column half
         const int r_in_tile = q * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         int n_real = p.n_classes - col0;             // real (unpadded) classes held by this CTA
         n_real = n_real < 0 ? 0 : (n_real > n_cols_cta ? n_cols_cta : n_real);
+        const int n_chunks = (n_real + 31) / 32;
+        const int cb_lo = h == 0 ? 0 : ((n_chunks + 1) / 2) * 32;
+        const int cb_hi = h == 0 ? ((n_chunks + 1) / 2) * 32 : n_chunks * 32;
         uint32_t accph = 0;
         uint32_t it = 0;
         for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters, ++it) {
             const int64_t row = tile * BM + r_in_tile;
+            const bool live = row < p.n_rows;
+            const uint32_t par = it & 1;
             mbar_wait(acc_full, accph);
             accph ^= 1;
             tc_fence_after();
 
-            // pass 1: running max / first argmax / sum of exp over this CTA's classes
-            float m = -INFINITY, ssum = 0.0f;
-            int arg = col0;
-            bool ok = true;
-            for (int cb = 0; cb < n_real; cb += 32) {
+            // ---- pass 1: max and first argmax over my columns
+            float m = -INFINITY;
+            int arg = col0 + cb_lo;
+            for (int cb = cb_lo; cb < cb_hi; cb += 32) {
                 float v[32];
                 tmem_ld32(t_lane + (uint32_t)cb, v);
-                const float m_old = m;
+                if (p.split) {
+                    float u[32];
+                    tmem_ld32(t_lane + (uint32_t)(BN + cb), u);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] += u[i];
+                }
+                float cm = -INFINITY;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     v[i] += bias_s[cb + i];                       // padding carries -inf
-                    if (cb + i < n_real) ok = ok && finite_f(v[i]);
-                    if (v[i] > m) { m = v[i]; arg = col0 + cb + i; }   // strict: first maximum wins
+                    cm = fmaxf(cm, v[i]);
                 }
-                if (m > m_old) ssum *= ex2((m_old - m) * kLog2e);  // re-base the sum on the new max
-                const float ml = m * kLog2e;
-                float add = 0.0f;
+                if (cm > m) {                                     // strict: an earlier chunk keeps a tie
+                    m = cm;
+                    int idx = 31;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) add += ex2(fmaf(v[i], kLog2e, -ml));
-                ssum += add;
-            }
-
-            // combine with the other class slices of the same rows (distributed shared memory)
-            float gm = m, gs = ssum;
-            int garg = arg;
-            bool gok = ok;
-            if (p.ncc > 1) {
-                const uint32_t buf = it & 1;
-                const uint32_t slot = smem_u32(xchg + (buf * kMaxCluster + rank) * BM + r_in_tile);
-                const uint32_t bar = smem_u32(xchg_bar + buf);
-                for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                    st_cluster_v4(map_to_cta(slot, dst), m, ssum, __int_as_float(arg), ok ? 1.0f : 0.0f);
-                    mbar_arrive_cluster(map_to_cta(bar, dst));
-                }
-                mbar_wait_cluster(xchg_bar + buf, (it >> 1) & 1);
-                gm = -INFINITY;
-                for (int src = 0; src < p.ncc; ++src) {
-                    const float4 e = xchg[(buf * kMaxCluster + src) * BM + r_in_tile];
-                    if (e.x > gm) { gm = e.x; garg = __float_as_int(e.z); }   // lower slice wins ties
-                    gok = gok && (e.w != 0.0f);
-                }
-                gs = 0.0f;
-                for (int src = 0; src < p.ncc; ++src) {
-                    const float4 e = xchg[(buf * kMaxCluster + src) * BM + r_in_tile];
-                    gs += e.y * ex2((e.x - gm) * kLog2e);
+                    for (int i = 30; i >= 0; --i) idx = (v[i] == cm) ? i : idx;   // first index wins
+                    arg = col0 + cb + idx;
                 }
             }
-            const float inv = __frcp_rn(gs);
-            const float gml = gm * kLog2e;
-            const bool live = row < p.n_rows;
-
-            // pass 2: normalise and store this CTA's slice of the row
-            for (int cb = 0; cb < n_real; cb += 32) {
-                float v[32];
-                tmem_ld32(t_lane + (uint32_t)cb, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] += bias_s[cb + i];
-                if (live) {
-                    const int64_t off = row * p.n_classes + col0 + cb;
-                    const bool whole = cb + 32 <= n_real;
-                    if (p.decision) {
-                        if (whole && p.vec_store) {
-#pragma unroll
-                            for (int i = 0; i < 32; i += 4)
-                                __stcs(reinterpret_cast<float4*>(p.decision + off + i),
-                                       make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (cb + i < n_real) __stcs(p.decision + off + i, v[i]);
+            // combine the two column halves of this CTA, then the class slices of the cluster
+            float gm;
+            int garg;
+            {
+                if (h == 1) halves[BM + r_in_tile] = make_float2(m, __int_as_float(arg));
+                epi_bar_sync();
+                if (h == 0) {
+                    const float2 o = halves[BM + r_in_tile];
+                    if (o.x > m) { m = o.x; arg = __float_as_int(o.y); }          // lower columns keep a tie
+                    gm = m;
+                    garg = arg;
+                    if (p.ncc > 1) {
+                        float2* buf = xchg + (size_t)((par * 2 + 0) * kMaxCluster) * BM;
+                        const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
+                        const uint32_t bar = smem_u32(xchg_bar + par * 2 + 0);
+                        for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
+                            st_cluster_v2(map_to_cta(slot, dst), m, __int_as_float(arg));
+                            mbar_arrive_cluster(map_to_cta(bar, dst));
+                        }
+                        mbar_wait_cluster(xchg_bar + par * 2 + 0, (it >> 1) & 1);
+                        gm = -INFINITY;
+                        for (int src = 0; src < p.ncc; ++src) {
+                            const float2 e = buf[src * BM + r_in_tile];
+                            if (e.x > gm) { gm = e.x; garg = __float_as_int(e.y); }  // lower slice keeps a tie
                         }
                     }
-                    if (p.proba) {
+                    glob[r_in_tile] = make_float2(gm, __int_as_float(garg));
+                }
+                epi_bar_sync();
+                const float2 gsv = glob[r_in_tile];
+                gm = gsv.x;
+                garg = __float_as_int(gsv.y);
+            }
+
+            // ---- pass 2: e = exp(z - max) written back to TMEM, sum, near-tie count, decision out
+            const float gml = gm * kLog2e;
+            // A runner-up this close to the maximum may be the true winner: measured logit error of the
+            // truncating TMEM accumulation is <= 3.2e-6 |z| with the split accumulator and 3x that
+            // without; the band is twice that, with margin.
+            const float kappa = p.split ? 3.5e-6f : 1.1e-5f;
+            const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
+            float ssum = 0.0f;
+            int near = 0;
+            for (int cb = cb_lo; cb < cb_hi; cb += 32) {
+                float v[32];
+                tmem_ld32(t_lane + (uint32_t)cb, v);
+                if (p.split) {
+                    float u[32];
+                    tmem_ld32(t_lane + (uint32_t)(BN + cb), u);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] = ex2(fmaf(v[i], kLog2e, -gml)) * inv;
-                        if (whole && p.vec_store) {
+                    for (int i = 0; i < 32; ++i) v[i] += u[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += bias_s[cb + i];
+                if (p.decision && live) {
+                    const int64_t off = row * p.n_classes + col0 + cb;
+                    if (cb + 32 <= n_real && p.vec_store) {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4)
+                            __stcs(reinterpret_cast<float4*>(p.decision + off + i),
+                                   make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (cb + i < n_real) __stcs(p.decision + off + i, v[i]);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    near += v[i] > tau ? 1 : 0;
+                    v[i] = ex2(fmaf(v[i], kLog2e, -gml));
+                    ssum += v[i];
+                }
+                tmem_st32(t_lane + (uint32_t)cb, v);
+            }
+            tmem_wait_st();
+            float gs;
+            int gnear;
+            {
+                if (h == 1) halves[BM + r_in_tile] = make_float2(ssum, __int_as_float(near));
+                epi_bar_sync();
+                if (h == 0) {
+                    const float2 o = halves[BM + r_in_tile];
+                    ssum += o.x;
+                    near += __float_as_int(o.y);
+                    gs = ssum;
+                    gnear = near;
+                    if (p.ncc > 1) {
+                        float2* buf = xchg + (size_t)((par * 2 + 1) * kMaxCluster) * BM;
+                        const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
+                        const uint32_t bar = smem_u32(xchg_bar + par * 2 + 1);
+                        for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
+                            st_cluster_v2(map_to_cta(slot, dst), ssum, __int_as_float(near));
+                            mbar_arrive_cluster(map_to_cta(bar, dst));
+                        }
+                        mbar_wait_cluster(xchg_bar + par * 2 + 1, (it >> 1) & 1);
+                        gs = 0.0f;
+                        gnear = 0;
+                        for (int src = 0; src < p.ncc; ++src) {      // fixed order: every CTA gets the same sum
+                            const float2 e = buf[src * BM + r_in_tile];
+                            gs += e.x;
+                            gnear += __float_as_int(e.y);
+                        }
+                    }
+                    glob[r_in_tile] = make_float2(gs, __int_as_float(gnear));
+                }
+                epi_bar_sync();
+                const float2 gsv = glob[r_in_tile];
+                gs = gsv.x;
+                gnear = __float_as_int(gsv.y);
+            }
+            const float inv = __frcp_rn(gs);
+
+            // ---- pass 3: normalise and store this warp's slice of the row
+            // |dp| ~ p(1-p)|dz| with |dz| <= kappa |z|: flag the row when that could pass ~6e-6, which
+            // needs a large maximum AND a class of middling probability
+            const float risk_thr = 8e-6f / (kappa * fmaxf(fabsf(gm), 1.0f));
+            bool risk = false;
+            if (p.proba) {
+                for (int cb = cb_lo; cb < cb_hi; cb += 32) {
+                    float v[32];
+                    tmem_ld32(t_lane + (uint32_t)cb, v);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        v[i] *= inv;
+                        risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
+                    }
+                    if (live) {
+                        const int64_t off = row * p.n_classes + col0 + cb;
+                        if (cb + 32 <= n_real && p.vec_store) {
 #pragma unroll
                             for (int i = 0; i < 32; i += 4)
                                 __stcs(reinterpret_cast<float4*>(p.proba + off + i),
@@ -441,10 +570,18 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             tc_fence_before();
             mbar_arrive(acc_empty);                   // TMEM may be overwritten by the next tile
 
-            if (live && rank == 0) {
-                if (p.label) __stcs(p.label + row, garg);
-                if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
-                if (!gok) atomicAdd(p.status, 1ull);
+            if (live) {
+                if (risk && p.flags) p.flags[row] = 1;
+                if (rank == 0 && h == 0) {
+                    if (p.label) __stcs(p.label + row, garg);
+                    if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
+                    if (!(finite_f(gm) && finite_f(gs))) atomicAdd(p.status, 1ull);
+                    if (p.flags) {
+                        p.lse[row] = gm + logf(gs);
+                        // a runner-up inside the error band, or a top probability the error could move
+                        if (gnear >= 2 || inv * (1.0f - inv) > risk_thr) p.flags[row] = 1;
+                    }
+                }
             }
         }
     }
@@ -458,6 +595,122 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     }
 }
 
+// ---- fp32 re-scoring of the rows flagged by the epilogue ------------------------------------------
+// A flagged row has a runner-up inside the accumulation error band of its maximum, or a class whose
+// probability that error could move by more than the parity bar.  Only the classes that carry
+// weight matter for either, so the pass re-computes the logits of those classes in fp32 FMA
+// arithmetic (error ~1e-6) and patches the row: one warp per flagged row, traffic = the row of X,
+// the row of P and a few rows of W instead of all of W.
+__device__ __forceinline__ float warp_dot(const float* __restrict__ x, const float* __restrict__ w, int d, int lane) {
+    float acc = 0.0f;
+    for (int k = lane; k < d; k += 32) acc = fmaf(__ldg(x + k), __ldg(w + k), acc);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    return acc;
+}
+
+__global__ void __launch_bounds__(256)
+gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
+                      const float* __restrict__ W, const float* __restrict__ b,
+                      const unsigned char* __restrict__ flags, const float* __restrict__ lse, float* proba,
+                      float* decision, int32_t* label, float* maxprob, unsigned long long* rescored) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps_total = (int64_t)gridDim.x * 8;
+    for (int64_t base = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 32; base < n_rows; base += warps_total * 32) {
+        const int64_t mine = base + lane;
+        unsigned todo = __ballot_sync(0xffffffffu, mine < n_rows && flags[mine] != 0);
+        while (todo) {
+            const int64_t row = base + (__ffs(todo) - 1);
+            todo &= todo - 1;
+            const float* x = X + row * ldx;
+            float* pr = proba + row * C;
+            const float L = lse[row];
+            float pmax = 0.0f;
+            for (int c = lane; c < C; c += 32) pmax = fmaxf(pmax, pr[c]);
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
+            const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
+            float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
+            int best = 0;
+            for (int c0 = 0; c0 < C; c0 += 32) {
+                const int c = c0 + lane;
+                const float pc = c < C ? pr[c] : 0.0f;
+                unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
+                float q_mine = pc;
+                while (sel) {
+                    const int j = __ffs(sel) - 1;
+                    sel &= sel - 1;
+                    const int cj = c0 + j;
+                    const float z = warp_dot(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
+                    const float q = expf(z - L);                    // in units of the old row sum
+                    old_mass += __shfl_sync(0xffffffffu, pc, j);
+                    new_mass += q;
+                    if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+                    if (lane == j) q_mine = q;
+                    if (decision && lane == 0) decision[row * C + cj] = z;
+                }
+                if (c < C && q_mine != pc) pr[c] = q_mine;
+            }
+            const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+            const float invT = __frcp_rn(T);
+            __syncwarp();
+            if (fabsf(T - 1.0f) > 1e-7f)
+                for (int c = lane; c < C; c += 32) pr[c] *= invT;
+            if (lane == 0) {
+                if (label) label[row] = best;
+                if (maxprob) maxprob[row] = best_q * invT;
+                atomicAdd(rescored, 1ull);
+            }
+        }
+    }
+}
+
+// Same purpose when the caller asked for no probability matrix (labels / max probability only, the
+// /predict pattern): there is no row of P to pick classes from, so a whole CTA re-scores every class
+// of the flagged row, eight warps splitting the classes.
+__global__ void __launch_bounds__(256)
+gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
+                       const float* __restrict__ W, const float* __restrict__ b,
+                       const unsigned char* __restrict__ flags, float* decision, int32_t* label, float* maxprob,
+                       unsigned long long* rescored) {
+    __shared__ float s_m[8], s_s[8];
+    __shared__ int s_a[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = (int64_t)blockIdx.x * 256; base < n_rows; base += (int64_t)gridDim.x * 256) {
+        const int64_t mine = base + threadIdx.x;
+        const int any = __syncthreads_or(mine < n_rows && flags[mine] != 0);
+        if (!any) continue;
+        for (int j = 0; j < 256 && base + j < n_rows; ++j) {
+            if (!flags[base + j]) continue;                         // uniform across the CTA
+            const int64_t row = base + j;
+            const float* x = X + row * ldx;
+            float m = -CUDART_INF_F, ssum = 0.0f;
+            int arg = 0;
+            const int per = (C + 7) / 8;
+            const int c_hi = min(C, (warp + 1) * per);
+            for (int c = warp * per; c < c_hi; ++c) {
+                const float z = warp_dot(x, W + (int64_t)c * d, d, lane) + __ldg(b + c);
+                if (decision && lane == 0) decision[row * C + c] = z;
+                if (z > m) { ssum = ssum * expf(m - z) + 1.0f; m = z; arg = c; }
+                else ssum += expf(z - m);
+            }
+            if (lane == 0) { s_m[warp] = m; s_s[warp] = ssum; s_a[warp] = arg; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                float gm = -CUDART_INF_F;
+                int ga = 0;
+                for (int w = 0; w < 8; ++w) if (s_m[w] > gm) { gm = s_m[w]; ga = s_a[w]; }
+                float gs = 0.0f;
+                for (int w = 0; w < 8; ++w) if (s_s[w] > 0.0f) gs += s_s[w] * expf(s_m[w] - gm);
+                if (label) label[row] = ga;
+                if (maxprob) maxprob[row] = __frcp_rn(gs);
+                atomicAdd(rescored, 1ull);
+            }
+            __syncthreads();
+        }
+    }
+}
+
 }  // namespace
 
 struct GemmPlan {
@@ -466,7 +719,10 @@ struct GemmPlan {
     float* bias = nullptr;      // [c_pad], -inf beyond n_classes
     CUtensorMap map_whi, map_wlo;
     int nb = 0, ncc = 0, c_pad = 0;
+    bool split = false;
     bool configured[64] = {false};
+    int max_clusters[64] = {0};
+    bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
 
 namespace {
@@ -526,10 +782,18 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
     GemmPlan* g = new GemmPlan();
     const int C = m.n_scores, d = m.n_features;
-    if (C <= BN) { g->nb = 1; g->ncc = 1; }
+    // Up to 1024 classes: 256 classes per CTA and a separate TMEM accumulator for the correction
+    // products (3x smaller accumulation error).  Above that, 512 classes per CTA with
+    // one shared accumulator.
+    bool split = C <= kMaxCluster * BN;
+    if (const char* e = getenv("LRS_GEMM_SPLIT")) split = split && atoi(e) != 0;
+    if (split) { g->nb = 1; g->ncc = (C + BN - 1) / BN; }
     else if (C <= 2 * BN) { g->nb = 2; g->ncc = 1; }
-    else { g->nb = 2; g->ncc = (C + 2 * BN - 1) / (2 * BN); if (g->ncc == 3) g->ncc = 4; }
+    else { g->nb = 2; g->ncc = (C + 2 * BN - 1) / (2 * BN); }
+    if (g->ncc == 3) g->ncc = 4;
+    g->split = split;
     g->c_pad = g->ncc * g->nb * BN;
+    if (const char* e = getenv("LRS_GEMM_FIXUP")) g->fixup = atoi(e) != 0;
     std::vector<float> hi((size_t)g->c_pad * d, 0.0f), lo((size_t)g->c_pad * d, 0.0f), bias(g->c_pad, -INFINITY);
     for (int c = 0; c < C; ++c) {
         bias[c] = (float)intercept[c];
@@ -576,11 +840,28 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         g->configured[dev] = true;
     }
+    // Scratch of the fp32 re-scoring pass: per row the log-sum-exp the tensor path saw and one flag
+    // byte (near-ties, risky probabilities).  Per call and stream-ordered (cudaMallocAsync), so
+    // concurrent lr_score calls on one model stay independent.
+    const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
+    unsigned char* flags = nullptr;
+    float* lse = nullptr;
+    if (fixup) {
+        void* ptr = nullptr;
+        const size_t lse_bytes = ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256;
+        LRS_CUDA(cudaMallocAsync(&ptr, lse_bytes + (size_t)a.n_rows, a.stream));
+        lse = reinterpret_cast<float*>(ptr);
+        flags = reinterpret_cast<unsigned char*>(ptr) + lse_bytes;
+        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
+    }
     GemmParams p;
+    p.flags = flags;
+    p.lse = lse;
     p.n_rows = a.n_rows;
     p.n_features = m.n_features;
     p.n_classes = m.n_scores;
     p.nb = g->nb;
+    p.split = g->split ? 1 : 0;
     p.ncc = g->ncc;
     p.num_k_chunks = (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
@@ -594,10 +875,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.vec_store = al ? 1 : 0;
 
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
-    int64_t clusters = m.num_sms / g->ncc;
-    if (clusters > n_tiles) clusters = n_tiles;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(clusters * g->ncc));
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = a.stream;
@@ -608,8 +886,36 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    // Persistent grid = as many clusters as can be co-resident.  A cluster must sit inside one GPC and
+    // GPCs hold 16/18/20 SMs, so clusters of 4 do not tile all 148 SMs: asking for floor(148/ncc)
+    // clusters would leave the last one waiting for a whole wave (measured: 2x slower).
+    if (g->max_clusters[dev] == 0) {
+        cfg.gridDim = dim3((unsigned)(m.num_sms / g->ncc * g->ncc));
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel, &cfg) != cudaSuccess || nc < 1) {
+            cudaGetLastError();
+            nc = m.num_sms / g->ncc / 2 > 0 ? m.num_sms / g->ncc / 2 : 1;
+        }
+        g->max_clusters[dev] = nc;
+    }
+    int64_t clusters = g->max_clusters[dev];
+    if (clusters > n_tiles) clusters = n_tiles;
+    cfg.gridDim = dim3((unsigned)(clusters * g->ncc));
     LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel, map_x, g->map_whi, g->map_wlo, p));
     count_launch();
+    if (fixup) {
+        if (a.proba)
+            gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.n_scores,
+                                                                      m.W, m.b, flags, lse, a.proba, a.decision,
+                                                                      a.label, a.maxprob, m.status + 1);
+        else
+            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features,
+                                                                       m.n_scores, m.W, m.b, flags, a.decision,
+                                                                       a.label, a.maxprob, m.status + 1);
+        count_launch();
+        LRS_CUDA(cudaGetLastError());
+        LRS_CUDA(cudaFreeAsync(lse, a.stream));
+    }
     return LR_OK;
 }
 

@@ -232,6 +232,13 @@ class B200LogisticRegression:
         _lib.check(rep.lib.lr_model_take_nonfinite(rep.handle, None, C.byref(v)))
         return int(v.value)
 
+    def take_rescored(self, device_index: int = 0) -> int:
+        """Rows the tensor-core path re-scored in fp32 since the last call (diagnostic; syncs)."""
+        rep = self._replicas[device_index]
+        v = C.c_uint64()
+        _lib.check(rep.lib.lr_model_take_rescored(rep.handle, None, C.byref(v)))
+        return int(v.value)
+
     # ---- sklearn surface -----------------------------------------------------------------------
     def _cast(self, a):
         return a if _is_torch_tensor(a) or a.dtype == self.out_dtype else a.astype(self.out_dtype)

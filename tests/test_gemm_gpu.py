@@ -81,6 +81,30 @@ def test_gemm_matches_generic_path_and_counts_nonfinite(eng):
     clf.close()
 
 
+@pytest.mark.parametrize("scale", [1.0, 4.0, 10.0])
+def test_gemm_confident_models_meet_the_bar(eng, scale):
+    """Large logits amplify the tensor core's truncating accumulation; the fp32 re-scoring pass must
+    bring probabilities and labels back inside the parity bar, with and without a P matrix."""
+    mlapi, lib = eng
+    d, c, n = 1024, 1000, 20_000
+    W, b = synth.make_model(d, c, 6)
+    W = W * scale
+    X = synth.make_X(n, d, 5)
+    z = orc.decision_function(X, W, b)
+    P = orc.softmax(z)
+    idx = z.argmax(1)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    out = clf.score_rows(X, **ALL)
+    rescored = clf.take_rescored()
+    # logits of classes that carry no weight stay at tensor-core accuracy (~3.5e-6 |z|)
+    parity.assert_parity(out, z, P, idx, f"gemm confident x{scale}", z_atol=4e-6 * np.abs(z).max() + 2e-5)
+    out2 = clf.score_rows(X, label=True, maxprob=True)          # the /predict pattern: no P matrix
+    parity.assert_parity(out2, z, P, idx, f"gemm confident x{scale} (label+maxprob)")
+    if scale >= 4.0:
+        assert rescored > 0
+    clf.close()
+
+
 def test_gemm_device_pitch(eng):
     import torch
     mlapi, lib = eng
