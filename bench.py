@@ -133,6 +133,26 @@ def cpu_reference(workload, threads=None, reps=None, budget_s=20.0):
                        f"BLAS threads {','.join(blas) or 'n/a'}; os.cpu_count={os.cpu_count()}")
 
 
+def bind_to_gpu_numa_node(gpu_index):
+    """Pin this rank's host threads to the CPUs next to its GPU before any pinned allocation, so the
+    e2e staging buffers are placed on the local NUMA node and every rank uses its own memory
+    controller / PCIe root (with 8 ranks on one socket's memory the H2D copies contend)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = {w * 64 + b for w, word in enumerate(mask) for b in range(64) if (word >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return 0
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -201,6 +221,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_cpus = bind_to_gpu_numa_node(local) if world > 1 else 0
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if rank == 0:
@@ -302,6 +324,7 @@ def main():
                "d2h_bytes_per_step": int(n_e * n_out * 4), "rows_per_step_per_gpu": n_e,
                "steps": args.e2e_steps, "ms_per_step": dt * 1e3,
                "api": "lr_score_host (C ABI), pinned host X and P, 3-stream chunked H2D/kernel/D2H",
+               "host_cpus_bound_per_rank": numa_cpus,
                "matches_device_result": same}
         xh.free(); ph.free()
 
