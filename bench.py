@@ -342,6 +342,9 @@ def main():
                     "frac": achieved / peak, "traffic": None,
                     "peak_source": f"half of {peaks['src']} bf16 burst peak (TF32 rate); algorithmic flops "
                                    "2*d*C per row counted once (the kernel issues 3 TF32 MMAs per product)",
+                    "frac_of_sustained": achieved / (peaks["bf16_sustained"] / 2.0),
+                    "sustained_note": "steps are 40+ ms of tensor work under the 1 kW cap (sw_power_cap active): "
+                                      "half the sustained bf16 figure is the applicable ceiling",
                     "hbm_gbs": alg_bytes / (ms * 1e-3) / 1e9}
         else:
             achieved = alg_bytes / (ms * 1e-3) / 1e9

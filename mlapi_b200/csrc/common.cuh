@@ -123,22 +123,27 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// Bounded wait: a pipeline bug traps (-> cudaErrorLaunchFailure) after ~2 s instead of hanging the GPU.
+// Bounded wait: a pipeline bug traps (-> cudaErrorLaunchFailure) after a few seconds instead of hanging
+// the GPU.  The retry loop lives inside the asm block on purpose: a C++ loop with a per-lane exit
+// would make the surrounding control flow divergent in the compiler's eyes, and every value computed
+// after it (stage indices, shared-memory descriptors) would lose its place in uniform registers.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (done) break;
-        if (clock64() - t0 > 4000000000ll) __trap();
-    }
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .u32 n;\n\t"
+        "mov.u32 n, 0;\n"
+        "LRS_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra LRS_DONE;\n\t"
+        "add.u32 n, n, 1;\n\t"
+        "setp.lt.u32 p, n, 50000000;\n\t"
+        "@p bra LRS_WAIT;\n\t"
+        "trap;\n"
+        "LRS_DONE:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on `bar`.
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {

@@ -109,20 +109,22 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t remote_bar_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar_addr) : "memory");
 }
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (done) break;
-        if (clock64() - t0 > 4000000000ll) __trap();
-    }
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .u32 n;\n\t"
+        "mov.u32 n, 0;\n"
+        "LRS_CWAIT:\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra LRS_CDONE;\n\t"
+        "add.u32 n, n, 1;\n\t"
+        "setp.lt.u32 p, n, 50000000;\n\t"
+        "@p bra LRS_CWAIT;\n\t"
+        "trap;\n"
+        "LRS_CDONE:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
 }
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
     asm volatile(
@@ -130,6 +132,11 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
             smem_u32(dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -275,75 +282,94 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            int as = 0, bs = 0;
-            uint32_t aph = 0, bph = 0;
-            for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-                const int row0 = (int)(tile * BM);
-                for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                    mbar_wait(a_empty + as, aph ^ 1);
+        // (whole warp walks the loop, one elected lane issues: see the MMA issuer for why)
+        const bool leader = elect_one();
+        int as = 0, bs = 0;
+        uint32_t aph = 0, bph = 0;
+        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+            const int row0 = (int)(tile * BM);
+            for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                mbar_wait(a_empty + as, aph ^ 1);
+                if (leader) {
                     mbar_expect_tx(x_full + as, A_TILE_BYTES);
                     tma_load_2d(a_hi + as * A_TILE_BYTES, &map_x, kc * BK, row0, x_full + as);
-                    if (++as == A_STAGES) { as = 0; aph ^= 1; }
-                    for (int part = 0; part < 2; ++part) {            // 0: w_hi, 1: w_lo
-                        for (int nbk = 0; nbk < p.nb; ++nbk) {
-                            mbar_wait(b_empty + bs, bph ^ 1);
+                }
+                __syncwarp();
+                if (++as == A_STAGES) { as = 0; aph ^= 1; }
+                for (int part = 0; part < 2; ++part) {            // 0: w_hi, 1: w_lo
+                    for (int nbk = 0; nbk < p.nb; ++nbk) {
+                        mbar_wait(b_empty + bs, bph ^ 1);
+                        if (leader) {
                             mbar_expect_tx(b_full + bs, B_TILE_BYTES);
                             tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BK,
                                         col0 + nbk * BN, b_full + bs);
-                            if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                         }
+                        __syncwarp();
+                        if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
                 }
             }
         }
-        __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            int as = 0, bs = 0;
-            uint32_t aph = 0, bph = 0, accph = 0;
-            for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-                mbar_wait(acc_empty, accph ^ 1);
-                tc_fence_after();
-                for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                    mbar_wait(a_ready + as, aph);
-                    tc_fence_after();
-                    const uint64_t ahi = make_smem_desc(smem_u32(a_hi + as * A_TILE_BYTES));
-                    const uint64_t alo = make_smem_desc(smem_u32(a_lo + as * A_TILE_BYTES));
-                    for (int part = 0; part < 2; ++part) {
-                        for (int nbk = 0; nbk < p.nb; ++nbk) {
-                            mbar_wait(b_full + bs, bph);
-                            tc_fence_after();
-                            const uint64_t bd = make_smem_desc(smem_u32(b_t + bs * B_TILE_BYTES));
-                            const uint32_t d_tmem = tmem_base + (uint32_t)(nbk * BN);
-                            // split mode: the small products (x_lo.w_hi, x_hi.w_lo) get their own
-                            // accumulator, so only the 128 x_hi.w_hi steps are added at full magnitude
-                            const uint32_t c_tmem = p.split ? tmem_base + (uint32_t)BN : d_tmem;
+        // The whole warp walks the pipeline (waits included) and only lane 0 issues: with warp-uniform
+        // control flow the compiler keeps stage indices, shared-memory descriptors and TMEM addresses
+        // in uniform registers, which is what UTCHMMA takes.  Under `if (lane == 0) { loop }` every
+        // operand was re-broadcast (R2UR) per instruction, ~14 instructions per MMA, and the issuing
+        // lane -- not the tensor pipe -- set the pace (ncu: tensor pipe 61 % active).
+        const bool leader = elect_one();
+        const uint64_t desc0 = make_smem_desc(0);                    // every field but the address
+        const uint64_t ahi0 = desc0 | (uint64_t)((smem_u32(a_hi) & 0x3FFFF) >> 4);
+        const uint64_t alo0 = desc0 | (uint64_t)((smem_u32(a_lo) & 0x3FFFF) >> 4);
+        const uint64_t b0 = desc0 | (uint64_t)((smem_u32(b_t) & 0x3FFFF) >> 4);
+        const uint32_t c_off = p.split ? (uint32_t)BN : 0u;          // split: corrections -> columns 256..511
+        const uint32_t corr_first = p.split ? 0u : 1u;               // accumulate flag of the first correction MMA
+        int as = 0, bs = 0;
+        uint32_t aph = 0, bph = 0, accph = 0;
+        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+            mbar_wait(acc_empty, accph ^ 1);
+            tc_fence_after();
+            for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                mbar_wait(a_ready + as, aph);
+                const uint64_t ahi = ahi0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
+                const uint64_t alo = alo0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
+                const uint32_t first = kc > 0 ? 1u : 0u;
+                for (int part = 0; part < 2; ++part) {
+                    for (int nbk = 0; nbk < p.nb; ++nbk) {
+                        mbar_wait(b_full + bs, bph);
+                        tc_fence_after();
+                        const uint64_t bd = b0 + (uint64_t)(bs * (B_TILE_BYTES >> 4));
+                        const uint32_t d_tmem = tmem_base + (uint32_t)(nbk * BN);
+                        const uint32_t c_tmem = d_tmem + c_off;
+                        if (leader) {
                             if (part == 0) {
+                                // x_hi.w_hi into the main accumulator, x_lo.w_hi into the correction one
+                                tc_mma_tf32(d_tmem, ahi, bd, kIdesc, first);
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
-                                    tc_mma_tf32(d_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, (kc > 0 || k > 0) ? 1u : 0u);
+                                for (int k = 1; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
+                                    tc_mma_tf32(d_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, 1u);
+                                tc_mma_tf32(c_tmem, alo, bd, kIdesc, first | corr_first);
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k)
-                                    tc_mma_tf32(c_tmem, alo + 2 * k, bd + 2 * k, kIdesc,
-                                                (!p.split || kc > 0 || k > 0) ? 1u : 0u);
+                                for (int k = 1; k < BK / 8; ++k)
+                                    tc_mma_tf32(c_tmem, alo + 2 * k, bd + 2 * k, kIdesc, 1u);
                             } else {
 #pragma unroll
                                 for (int k = 0; k < BK / 8; ++k) tc_mma_tf32(c_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, 1u);
                             }
                             tc_commit(b_empty + bs);
-                            if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                         }
+                        __syncwarp();
+                        if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
-                    tc_commit(a_empty + as);
-                    if (++as == A_STAGES) { as = 0; aph ^= 1; }
                 }
-                tc_commit(acc_full);
-                accph ^= 1;
+                if (leader) tc_commit(a_empty + as);
+                __syncwarp();
+                if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
+            if (leader) tc_commit(acc_full);
+            __syncwarp();
+            accph ^= 1;
         }
-        __syncwarp();
     } else if (warp < 6) {
         // ===================== converters: raw fp32 -> (hi, lo) TF32 pair =====================
         const int t = threadIdx.x - 64;             // 0..127
