@@ -212,11 +212,11 @@ int lr_model_take_rescored(lr_model* h, void* stream, uint64_t* out) {
     Model* m = reinterpret_cast<Model*>(h);
     DeviceGuard guard(m->device);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    unsigned long long v = 0;
+    unsigned long long v = 0;                      // the device counter only ever grows
     LRS_CUDA(cudaMemcpyAsync(&v, m->status + 1, sizeof(v), cudaMemcpyDeviceToHost, s));
-    LRS_CUDA(cudaMemsetAsync(m->status + 1, 0, sizeof(v), s));
     LRS_CUDA(cudaStreamSynchronize(s));
-    *out = v;
+    *out = v - m->rescored_taken;
+    m->rescored_taken = v;
     return LR_OK;
 }
 
@@ -295,8 +295,10 @@ int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx,
             LRS_CUDA(cudaMemcpyAsync(maxprob_host + r0, st.maxprob[slot], rows * sizeof(float), cudaMemcpyDeviceToHost, s));
     }
     for (int i = 0; i < HostStage::kSlots; ++i) LRS_CUDA(cudaStreamSynchronize(st.stream[i]));
-    unsigned long long bad = 0;
-    LRS_CUDA(cudaMemcpy(&bad, m->status, sizeof(bad), cudaMemcpyDeviceToHost));
+    unsigned long long sw[2] = {0, 0};            // [0] non-finite rows, [1] rows re-scored in fp32 (running)
+    LRS_CUDA(cudaMemcpy(sw, m->status, sizeof(sw), cudaMemcpyDeviceToHost));
+    gemm_feedback(*m, n_rows, sw[1]);
+    const unsigned long long bad = sw[0];
     if (bad) {
         LRS_CUDA(cudaMemset(m->status, 0, sizeof(bad)));
         return fail(LR_ERR_NONFINITE, std::to_string(bad) + " row(s) scored to NaN or infinity (non-finite input)");

@@ -48,6 +48,7 @@ struct Model {
     int64_t narrow_bulk_min_rows = 65536;
     // status word(s): [0] = rows that scored to a non-finite value
     unsigned long long* status = nullptr;
+    unsigned long long rescored_taken = 0;   // host shadow for lr_model_take_rescored
 
     GemmPlan* gemm = nullptr;
     HostStage* stage = nullptr;
@@ -78,6 +79,8 @@ int generic_launch(const Model& m, const ScoreArgs& a);
 bool gemm_supports(const Model& m, const ScoreArgs& a);
 int gemm_prepare(Model& m, const double* coef, const double* intercept);
 void gemm_destroy(Model& m);
+void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total);
+int gemm_active_layout(const Model& m);
 int gemm_launch(const Model& m, const ScoreArgs& a);
 
 // ---- device helpers ----------------------------------------------------------------------------

@@ -744,10 +744,20 @@ struct GemmPlan {
     float* w_lo = nullptr;      // [c_pad][d] TF32 of the residual
     float* bias = nullptr;      // [c_pad], -inf beyond n_classes
     CUtensorMap map_whi, map_wlo;
-    int nb = 0, ncc = 0, c_pad = 0;
-    bool split = false;
+    // Two CTA layouts over the same W buffers:
+    //   [0] fast:     512 classes per CTA, one TMEM accumulator             (C <= 2048)
+    //   [1] accurate: 256 classes per CTA, correction products accumulate apart, 3x smaller logit
+    //                 error, so far fewer rows need the fp32 re-scoring pass  (C <= 1024)
+    // `active` starts on the fast layout where both exist (C in 257..1024) and moves to the accurate
+    // one when the re-scoring pass reports that the data is confident (lr_score_host feeds that back).
+    struct Layout { int nb = 0, ncc = 0; bool split = false; int max_clusters[64] = {0}; };
+    Layout layout[2];
+    bool has[2] = {false, false};
+    int active = 0;
+    bool adaptive = true;
+    int c_pad = 0;
+    uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen
     bool configured[64] = {false};
-    int max_clusters[64] = {0};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
 
@@ -808,17 +818,30 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
     GemmPlan* g = new GemmPlan();
     const int C = m.n_scores, d = m.n_features;
-    // Up to 1024 classes: 256 classes per CTA and a separate TMEM accumulator for the correction
-    // products (3x smaller accumulation error).  Above that, 512 classes per CTA with
-    // one shared accumulator.
-    bool split = C <= kMaxCluster * BN;
-    if (const char* e = getenv("LRS_GEMM_SPLIT")) split = split && atoi(e) != 0;
-    if (split) { g->nb = 1; g->ncc = (C + BN - 1) / BN; }
-    else if (C <= 2 * BN) { g->nb = 2; g->ncc = 1; }
-    else { g->nb = 2; g->ncc = (C + 2 * BN - 1) / (2 * BN); }
-    if (g->ncc == 3) g->ncc = 4;
-    g->split = split;
-    g->c_pad = g->ncc * g->nb * BN;
+    auto& fast = g->layout[0];
+    auto& acc = g->layout[1];
+    if (C > BN) {                                   // fast layout: 512 classes per CTA
+        fast.nb = 2;
+        fast.ncc = (C + 2 * BN - 1) / (2 * BN);
+        if (fast.ncc == 3) fast.ncc = 4;
+        g->has[0] = true;
+    }
+    if (C <= kMaxCluster * BN) {                    // accurate layout: 256 classes per CTA, split accumulators
+        acc.nb = 1;
+        acc.ncc = (C + BN - 1) / BN;
+        if (acc.ncc == 3) acc.ncc = 4;
+        acc.split = true;
+        g->has[1] = true;
+    }
+    g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
+    if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
+        const int want = atoi(e) != 0 ? 1 : 0;
+        if (g->has[want]) g->active = want;
+        g->adaptive = false;
+    }
+    g->c_pad = 0;
+    for (int i = 0; i < 2; ++i)
+        if (g->has[i] && g->layout[i].ncc * g->layout[i].nb * BN > g->c_pad) g->c_pad = g->layout[i].ncc * g->layout[i].nb * BN;
     if (const char* e = getenv("LRS_GEMM_FIXUP")) g->fixup = atoi(e) != 0;
     std::vector<float> hi((size_t)g->c_pad * d, 0.0f), lo((size_t)g->c_pad * d, 0.0f), bias(g->c_pad, -INFINITY);
     for (int c = 0; c < C; ++c) {
@@ -844,6 +867,24 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     return LR_OK;
 }
 
+// Called by lr_score_host after a synchronised batch: `rescored_total` is the running count kept in
+// the model's status block.  If the fast layout sends more than 2 % of the rows to the fp32
+// re-scoring pass, later batches use the accurate layout.
+void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total) {
+    GemmPlan* g = m.gemm;
+    if (!g || !g->adaptive || g->active != 0 || !g->has[1]) return;
+    g->rows_seen += (uint64_t)rows;
+    const uint64_t resc = rescored_total - g->rescored_seen;
+    if (g->rows_seen >= 4096 && resc * 50 > g->rows_seen) {
+        g->active = 1;
+    } else if (g->rows_seen > (1ull << 24)) {          // judge on recent data only
+        g->rows_seen = 0;
+        g->rescored_seen = rescored_total;
+    }
+}
+
+int gemm_active_layout(const Model& m) { return m.gemm ? m.gemm->active : -1; }
+
 void gemm_destroy(Model& m) {
     if (!m.gemm) return;
     cudaFree(m.gemm->w_hi);
@@ -857,6 +898,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     if (!gemm_supports(m, a))
         return fail(LR_ERR_INVALID, "gemm path needs 17..2048 classes, n_features % 4 == 0 and 16-byte aligned rows of X");
     GemmPlan* g = m.gemm;
+    GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
     int rc = make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM);
     if (rc != LR_OK) return rc;
@@ -886,9 +928,9 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.n_rows = a.n_rows;
     p.n_features = m.n_features;
     p.n_classes = m.n_scores;
-    p.nb = g->nb;
-    p.split = g->split ? 1 : 0;
-    p.ncc = g->ncc;
+    p.nb = L.nb;
+    p.split = L.split ? 1 : 0;
+    p.ncc = L.ncc;
     p.num_k_chunks = (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
     p.proba = a.proba;
@@ -907,7 +949,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     cfg.stream = a.stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)g->ncc;
+    attr[0].val.clusterDim.x = (unsigned)L.ncc;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -915,18 +957,18 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     // Persistent grid = as many clusters as can be co-resident.  A cluster must sit inside one GPC and
     // GPCs hold 16/18/20 SMs, so clusters of 4 do not tile all 148 SMs: asking for floor(148/ncc)
     // clusters would leave the last one waiting for a whole wave (measured: 2x slower).
-    if (g->max_clusters[dev] == 0) {
-        cfg.gridDim = dim3((unsigned)(m.num_sms / g->ncc * g->ncc));
+    if (L.max_clusters[dev] == 0) {
+        cfg.gridDim = dim3((unsigned)(m.num_sms / L.ncc * L.ncc));
         int nc = 0;
         if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel, &cfg) != cudaSuccess || nc < 1) {
             cudaGetLastError();
-            nc = m.num_sms / g->ncc / 2 > 0 ? m.num_sms / g->ncc / 2 : 1;
+            nc = m.num_sms / L.ncc / 2 > 0 ? m.num_sms / L.ncc / 2 : 1;
         }
-        g->max_clusters[dev] = nc;
+        L.max_clusters[dev] = nc;
     }
-    int64_t clusters = g->max_clusters[dev];
+    int64_t clusters = L.max_clusters[dev];
     if (clusters > n_tiles) clusters = n_tiles;
-    cfg.gridDim = dim3((unsigned)(clusters * g->ncc));
+    cfg.gridDim = dim3((unsigned)(clusters * L.ncc));
     LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel, map_x, g->map_whi, g->map_wlo, p));
     count_launch();
     if (fixup) {

@@ -105,6 +105,31 @@ def test_gemm_confident_models_meet_the_bar(eng, scale):
     clf.close()
 
 
+def test_gemm_layout_adapts_to_confident_data(eng):
+    """Host batches feed the re-scoring rate back: a confident model moves to the layout with the
+    separate correction accumulator, a random one stays on the fast layout; results hold either way."""
+    mlapi, lib = eng
+    d, c, n = 1024, 1000, 8192
+    X = synth.make_X(n, d, 5)
+    for scale, expect_many in ((1.0, False), (6.0, True)):
+        W, b = synth.make_model(d, c, 6)
+        W = W * scale
+        clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+        z = orc.decision_function(X, W, b)
+        P = orc.softmax(z)
+        first = clf.score_rows(X, proba=True, label=True)
+        r1 = clf.take_rescored()
+        second = clf.score_rows(X, proba=True, label=True)
+        r2 = clf.take_rescored()
+        for out in (first, second):
+            parity.assert_parity(out, z, P, z.argmax(1), f"adaptive x{scale}")
+        if expect_many:
+            assert r1 > n // 50 and r2 < r1          # second batch ran on the accurate layout
+        else:
+            assert r1 <= n // 50
+        clf.close()
+
+
 def test_gemm_device_pitch(eng):
     import torch
     mlapi, lib = eng
