@@ -28,6 +28,7 @@
 //
 // Tensor roofline: 2*d*C flops per row against half the measured bf16 peak (TF32 rate).
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 #include <cmath>
 #include <cstdlib>
@@ -42,7 +43,8 @@ namespace lrs {
 namespace {
 
 constexpr int BM = 128;          // rows per tile (TMEM lanes)
-constexpr int BK = 32;           // fp32 elements per k-chunk = 128 bytes = one swizzle-128B row
+constexpr int BK = 32;           // TF32 mode: fp32 elements per k-chunk = 128 bytes = one swizzle-128B row
+constexpr int BK16 = 64;         // FP16 mode: fp16 elements per k-chunk, again one 128-byte row
 constexpr int BN = 256;          // classes per MMA / per W stage
 constexpr int A_STAGES = 2;
 constexpr int B_STAGES = 4;
@@ -58,7 +60,8 @@ struct SmemLayout {
     static constexpr int a_lo = a_hi + A_STAGES * A_TILE_BYTES;      // [A_STAGES][16 KB]
     static constexpr int b = a_lo + A_STAGES * A_TILE_BYTES;         // [B_STAGES][32 KB]
     static constexpr int bias = b + B_STAGES * B_TILE_BYTES;         // [512] floats
-    static constexpr int xchg = bias + 512 * 4;                      // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
+    static constexpr int cscale = bias + 512 * 4;                    // [512] floats: 1 / (x scale * class scale), FP16 mode
+    static constexpr int xchg = cscale + 512 * 4;                      // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
     static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
     static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
     static constexpr int bars = glob + BM * 8;                       // mbarriers
@@ -77,6 +80,9 @@ struct GemmParams {
     int ncc;                // CTAs per cluster (class split)
     int num_k_chunks;
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
+    const float* col_inv_scale;   // FP16 mode: 1 / class scale, padded like bias
+    const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
+    int count_nonfinite;    // 1: the epilogue counts non-finite rows itself (no re-scoring pass to do it)
     float* proba;
     float* decision;
     int32_t* label;
@@ -154,6 +160,17 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, ui
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+template <bool F16>
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate);
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     uint32_t r[32];
     asm volatile(
@@ -216,8 +233,19 @@ constexpr uint32_t kIdesc = (1u << 4)      // D = f32
                             | (2u << 10)   // B = tf32
                             | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);   // K-major A and B
 
+constexpr uint32_t kIdesc16 = (1u << 4)    // D = f32, A = B = f16 (format 0), K-major
+                              | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+template <>
+__device__ __forceinline__ void tc_mma<false>(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { tc_mma_tf32(d, a, b, kIdesc, acc); }
+template <>
+__device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { tc_mma_f16(d, a, b, kIdesc16, acc); }
+
 constexpr float kLog2e = 1.4426950408889634f;
 
+// F16 = false: 3xTF32 (operands are fp32 containers, 8 K-elements per MMA).
+// F16 = true : 3xFP16 (x and w scaled by powers of two into fp16 range and split hi/lo like above,
+//              16 K-elements per MMA at twice the TF32 rate; scales are undone in the epilogue).
+template <bool F16>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                     const __grid_constant__ CUtensorMap map_wlo, const GemmParams p) {
@@ -227,7 +255,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     unsigned char* a_hi = smem + SmemLayout::a_hi;
     unsigned char* a_lo = smem + SmemLayout::a_lo;
     unsigned char* b_t = smem + SmemLayout::b;
+    constexpr int BKx = F16 ? BK16 : BK;                 // K-elements per chunk
+    constexpr int RAW_BYTES = BM * BKx * 4;              // raw fp32 X tile: 16 KB (TF32) / 32 KB (FP16)
+    constexpr int A_STAGE = 2 * A_TILE_BYTES;            // FP16: one contiguous 32 KB stage (raw -> hi | lo in place)
     float* bias_s = reinterpret_cast<float*>(smem + SmemLayout::bias);
+    float* cscale_s = reinterpret_cast<float*>(smem + SmemLayout::cscale);
     float2* xchg = reinterpret_cast<float2*>(smem + SmemLayout::xchg);
     float2* halves = reinterpret_cast<float2*>(smem + SmemLayout::halves);
     float2* glob = reinterpret_cast<float2*>(smem + SmemLayout::glob);
@@ -263,7 +295,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         for (int i = 0; i < 4; ++i) mbar_init(xchg_bar + i, 128 * p.ncc);
         mbar_fence_init();
     }
-    for (int i = threadIdx.x; i < n_cols_cta; i += kThreads) bias_s[i] = p.bias[col0 + i];
+    for (int i = threadIdx.x; i < n_cols_cta; i += kThreads) {
+        bias_s[i] = p.bias[col0 + i];
+        if constexpr (F16) cscale_s[i] = p.col_inv_scale[col0 + i] * p.x_scale[1];
+    }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(512)
@@ -291,8 +326,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(a_empty + as, aph ^ 1);
                 if (leader) {
-                    mbar_expect_tx(x_full + as, A_TILE_BYTES);
-                    tma_load_2d(a_hi + as * A_TILE_BYTES, &map_x, kc * BK, row0, x_full + as);
+                    mbar_expect_tx(x_full + as, RAW_BYTES);
+                    tma_load_2d(F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES, &map_x, kc * BKx, row0,
+                                x_full + as);
                 }
                 __syncwarp();
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
@@ -301,7 +337,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         mbar_wait(b_empty + bs, bph ^ 1);
                         if (leader) {
                             mbar_expect_tx(b_full + bs, B_TILE_BYTES);
-                            tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BK,
+                            tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
                                         col0 + nbk * BN, b_full + bs);
                         }
                         __syncwarp();
@@ -331,8 +367,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             tc_fence_after();
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(a_ready + as, aph);
-                const uint64_t ahi = ahi0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
-                const uint64_t alo = alo0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
+                // TF32: hi tiles and lo tiles are two arrays; FP16: stage = [hi 16 KB | lo 16 KB] contiguous
+                const uint64_t ahi = ahi0 + (uint64_t)(as * ((F16 ? A_STAGE : A_TILE_BYTES) >> 4));
+                const uint64_t alo = F16 ? ahi + (uint64_t)(A_TILE_BYTES >> 4)
+                                         : alo0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
                 const uint32_t first = kc > 0 ? 1u : 0u;
                 for (int part = 0; part < 2; ++part) {
                     for (int nbk = 0; nbk < p.nb; ++nbk) {
@@ -344,17 +382,17 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (leader) {
                             if (part == 0) {
                                 // x_hi.w_hi into the main accumulator, x_lo.w_hi into the correction one
-                                tc_mma_tf32(d_tmem, ahi, bd, kIdesc, first);
+                                tc_mma<F16>(d_tmem, ahi, bd, first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
-                                    tc_mma_tf32(d_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, 1u);
-                                tc_mma_tf32(c_tmem, alo, bd, kIdesc, first | corr_first);
+                                    tc_mma<F16>(d_tmem, ahi + 2 * k, bd + 2 * k, 1u);
+                                tc_mma<F16>(c_tmem, alo, bd, first | corr_first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)
-                                    tc_mma_tf32(c_tmem, alo + 2 * k, bd + 2 * k, kIdesc, 1u);
+                                    tc_mma<F16>(c_tmem, alo + 2 * k, bd + 2 * k, 1u);
                             } else {
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k) tc_mma_tf32(c_tmem, ahi + 2 * k, bd + 2 * k, kIdesc, 1u);
+                                for (int k = 0; k < BK / 8; ++k) tc_mma<F16>(c_tmem, ahi + 2 * k, bd + 2 * k, 1u);
                             }
                             tc_commit(b_empty + bs);
                         }
@@ -373,23 +411,64 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else if (warp < 6) {
         // ===================== converters: raw fp32 -> (hi, lo) TF32 pair =====================
         const int t = threadIdx.x - 64;             // 0..127
+        const float sx = F16 ? p.x_scale[0] : 1.0f;
         int as = 0;
         uint32_t aph = 0;
         for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(x_full + as, aph);
-                float4* hi = reinterpret_cast<float4*>(a_hi + as * A_TILE_BYTES);
-                float4* lo = reinterpret_cast<float4*>(a_lo + as * A_TILE_BYTES);
+                if constexpr (!F16) {
+                    float4* hi = reinterpret_cast<float4*>(a_hi + as * A_TILE_BYTES);
+                    float4* lo = reinterpret_cast<float4*>(a_lo + as * A_TILE_BYTES);
 #pragma unroll
-                for (int j = 0; j < A_TILE_BYTES / 16 / 128; ++j) {
-                    const int i = t + 128 * j;
-                    const float4 x = hi[i];
-                    float4 h, l;
-                    h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
-                    l.x = to_tf32(x.x - h.x); l.y = to_tf32(x.y - h.y);
-                    l.z = to_tf32(x.z - h.z); l.w = to_tf32(x.w - h.w);
-                    hi[i] = h;
-                    lo[i] = l;
+                    for (int j = 0; j < A_TILE_BYTES / 16 / 128; ++j) {
+                        const int i = t + 128 * j;
+                        const float4 x = hi[i];
+                        float4 h, l;
+                        h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
+                        l.x = to_tf32(x.x - h.x); l.y = to_tf32(x.y - h.y);
+                        l.z = to_tf32(x.z - h.z); l.w = to_tf32(x.w - h.w);
+                        hi[i] = h;
+                        lo[i] = l;
+                    }
+                } else {
+                    // raw tile: [128 rows][64 fp32], linear (256 B rows).  Each thread owns eight 8-element
+                    // pieces (row r, piece c): it scales them into fp16 range, splits them into hi + lo
+                    // halves and, once every thread has read its share (the tile is converted in place),
+                    // writes the two 16-byte results where the 128-byte-swizzled K-major fp16 tiles want
+                    // them: hi tile at the stage base, lo tile 16 KB above.
+                    unsigned char* stage = a_hi + as * A_STAGE;
+                    uint4 hv[8], lv[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int qd = t + 128 * j;
+                        const int r = qd >> 3, c = qd & 7;
+                        const float4* src = reinterpret_cast<const float4*>(stage + r * 256 + c * 32);
+                        const float4 x0 = src[0], x1 = src[1];
+                        const float xs[8] = {x0.x * sx, x0.y * sx, x0.z * sx, x0.w * sx,
+                                             x1.x * sx, x1.y * sx, x1.z * sx, x1.w * sx};
+                        __half2 h2[4], l2[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const __half ha = __float2half_rn(xs[2 * e]), hb = __float2half_rn(xs[2 * e + 1]);
+                            h2[e] = __halves2half2(ha, hb);
+                            l2[e] = __halves2half2(__float2half_rn(xs[2 * e] - __half2float(ha)),
+                                                   __float2half_rn(xs[2 * e + 1] - __half2float(hb)));
+                        }
+                        hv[j] = make_uint4(*reinterpret_cast<uint32_t*>(&h2[0]), *reinterpret_cast<uint32_t*>(&h2[1]),
+                                           *reinterpret_cast<uint32_t*>(&h2[2]), *reinterpret_cast<uint32_t*>(&h2[3]));
+                        lv[j] = make_uint4(*reinterpret_cast<uint32_t*>(&l2[0]), *reinterpret_cast<uint32_t*>(&l2[1]),
+                                           *reinterpret_cast<uint32_t*>(&l2[2]), *reinterpret_cast<uint32_t*>(&l2[3]));
+                    }
+                    asm volatile("bar.sync 2, 128;" ::: "memory");      // all raw data is in registers
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int qd = t + 128 * j;
+                        const int r = qd >> 3, c = qd & 7;
+                        const int off = r * 128 + ((c ^ (r & 7)) << 4);     // SWIZZLE_128B: 16-byte piece ^ (row % 8)
+                        *reinterpret_cast<uint4*>(stage + off) = hv[j];
+                        *reinterpret_cast<uint4*>(stage + A_TILE_BYTES + off) = lv[j];
+                    }
                 }
                 fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
                 mbar_arrive(a_ready + as);
@@ -440,7 +519,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 float cm = -INFINITY;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    v[i] += bias_s[cb + i];                       // padding carries -inf
+                    if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cb + i], bias_s[cb + i]);
+                    else v[i] += bias_s[cb + i];                  // padding carries -inf
                     cm = fmaxf(cm, v[i]);
                 }
                 if (cm > m) {                                     // strict: an earlier chunk keeps a tie
@@ -490,7 +570,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // A runner-up this close to the maximum may be the true winner: measured logit error of the
             // truncating TMEM accumulation is <= 3.2e-6 |z| with the split accumulator and 3x that
             // without; the band is twice that, with margin.
-            const float kappa = p.split ? 3.5e-6f : 1.1e-5f;
+            // (3xFP16 takes half as many accumulation steps as 3xTF32: measured 5.0e-6 / 2.4e-6)
+            const float kappa = F16 ? (p.split ? 2.8e-6f : 6e-6f) : (p.split ? 3.5e-6f : 1.1e-5f);
             const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
             float ssum = 0.0f;
             int near = 0;
@@ -504,7 +585,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     for (int i = 0; i < 32; ++i) v[i] += u[i];
                 }
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] += bias_s[cb + i];
+                for (int i = 0; i < 32; ++i) {
+                    if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cb + i], bias_s[cb + i]);
+                    else v[i] += bias_s[cb + i];
+                }
                 if (p.decision && live) {
                     const int64_t off = row * p.n_classes + col0 + cb;
                     if (cb + 32 <= n_real && p.vec_store) {
@@ -597,15 +681,21 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_arrive(acc_empty);                   // TMEM may be overwritten by the next tile
 
             if (live) {
-                if (risk && p.flags) p.flags[row] = 1;
+                if (risk && p.flags && p.flags[row] == 0) p.flags[row] = 1;
                 if (rank == 0 && h == 0) {
                     if (p.label) __stcs(p.label + row, garg);
                     if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
-                    if (!(finite_f(gm) && finite_f(gs))) atomicAdd(p.status, 1ull);
+                    const bool finite_row = finite_f(gm) && finite_f(gs);
+                    if (!finite_row) {
+                        // With a re-scoring pass the row is handed over (flag 2): an fp16 overflow of a
+                        // finite input would otherwise be reported as non-finite data.
+                        if (p.flags && !p.count_nonfinite) p.flags[row] = 2;
+                        else atomicAdd(p.status, 1ull);
+                    }
                     if (p.flags) {
-                        p.lse[row] = gm + logf(gs);
+                        p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
                         // a runner-up inside the error band, or a top probability the error could move
-                        if (gnear >= 2 || inv * (1.0f - inv) > risk_thr) p.flags[row] = 1;
+                        if (finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr)) p.flags[row] = 1;
                     }
                 }
             }
@@ -639,7 +729,8 @@ __global__ void __launch_bounds__(256)
 gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
                       const float* __restrict__ W, const float* __restrict__ b,
                       const unsigned char* __restrict__ flags, const float* __restrict__ lse, float* proba,
-                      float* decision, int32_t* label, float* maxprob, unsigned long long* rescored) {
+                      float* decision, int32_t* label, float* maxprob, unsigned long long* rescored,
+                      unsigned long long* status) {
     const int lane = threadIdx.x & 31;
     const int64_t warps_total = (int64_t)gridDim.x * 8;
     for (int64_t base = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 32; base < n_rows; base += warps_total * 32) {
@@ -651,6 +742,13 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
             const float* x = X + row * ldx;
             float* pr = proba + row * C;
             const float L = lse[row];
+            if (!finite_f(L)) {
+                // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
+                // score the whole row in fp32, which also settles whether the input really is non-finite
+                score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+                if (lane == 0) atomicAdd(rescored, 1ull);
+                continue;
+            }
             float pmax = 0.0f;
             for (int c = lane; c < C; c += 32) pmax = fmaxf(pmax, pr[c]);
 #pragma unroll
@@ -698,7 +796,7 @@ __global__ void __launch_bounds__(256)
 gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
                        const float* __restrict__ W, const float* __restrict__ b,
                        const unsigned char* __restrict__ flags, float* decision, int32_t* label, float* maxprob,
-                       unsigned long long* rescored) {
+                       unsigned long long* rescored, unsigned long long* status) {
     __shared__ float s_m[8], s_s[8];
     __shared__ int s_a[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -731,9 +829,44 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx,
                 if (label) label[row] = ga;
                 if (maxprob) maxprob[row] = __frcp_rn(gs);
                 atomicAdd(rescored, 1ull);
+                if (!(finite_f(gm) && finite_f(gs))) atomicAdd(status, 1ull);
             }
             __syncthreads();
         }
+    }
+}
+
+// FP16 mode: a power-of-two scale for X from the largest |x| of up to 2048 rows spread over the batch,
+// chosen so that this maximum lands in (2, 4]: fp16 then has 2^14 of headroom above it and full
+// hi+lo precision below it.  A row holding something 16 000 times larger than anything sampled
+// overflows to inf, is seen as non-finite by the epilogue and re-scored in fp32.
+__global__ void __launch_bounds__(256)
+x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, float* __restrict__ out) {
+    __shared__ float red[8];
+    const int64_t n_s = n_rows < 2048 ? n_rows : 2048;
+    const int64_t step = n_rows / n_s;
+    float mx = 0.0f;
+    for (int64_t i = threadIdx.x >> 5; i < n_s; i += 8) {
+        const float* x = X + (i * step) * ldx;
+        for (int k = threadIdx.x & 31; k < d; k += 32) {
+            const float v = fabsf(__ldg(x + k));
+            if (v <= 3.0e38f) mx = fmaxf(mx, v);            // ignores NaN / inf
+        }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) mx = fmaxf(mx, red[w]);
+        int e = 0;
+        float sc = 1.0f;
+        if (mx > 0.0f) {
+            frexpf(mx, &e);                                   // mx = f * 2^e, f in [0.5, 1)
+            sc = ldexpf(1.0f, 2 - e);                         // mx * sc in [2, 4)
+        }
+        out[0] = sc;
+        out[1] = 1.0f / sc;
     }
 }
 
@@ -744,6 +877,13 @@ struct GemmPlan {
     float* w_lo = nullptr;      // [c_pad][d] TF32 of the residual
     float* bias = nullptr;      // [c_pad], -inf beyond n_classes
     CUtensorMap map_whi, map_wlo;
+    // FP16 mode: coef_ scaled per class by a power of two into (2, 4] and split into two halves
+    __half* w16_hi = nullptr;   // [c_pad][d16]
+    __half* w16_lo = nullptr;
+    float* col_inv_scale = nullptr;   // [c_pad] 1 / class scale
+    CUtensorMap map_w16hi, map_w16lo;
+    int d16 = 0;                // row pitch of the fp16 copies (n_features rounded up to 8: TMA wants 16-byte pitches)
+    bool f16 = false;
     // Two CTA layouts over the same W buffers:
     //   [0] fast:     512 classes per CTA, one TMEM accumulator             (C <= 2048)
     //   [1] accurate: 256 classes per CTA, correction products accumulate apart, 3x smaller logit
@@ -780,18 +920,25 @@ EncodeTiledFn encode_tiled() {
 }
 
 // 2-D fp32 row-major [rows][cols] with row pitch `ld` elements; box = box_rows x 32 columns, 128B swizzle.
-int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+// 2-D row-major [rows][cols] tensor with row pitch `ld` elements of `elem_bytes`; box = box_rows x box_cols.
+int make_map_ex(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                uint32_t box_cols, int elem_bytes, bool swizzle128) {
     EncodeTiledFn fn = encode_tiled();
     if (!fn) return fail(LR_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {ld * sizeof(float)};
-    cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+    cuuint64_t strides[1] = {ld * (uint64_t)elem_bytes};
+    cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = fn(map, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                    const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(LR_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
     return LR_OK;
+}
+// fp32, box_rows x 32 columns, 128-byte swizzle (TF32 mode operands)
+int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+    return make_map_ex(map, base, rows, cols, ld, box_rows, (uint32_t)BK, 4, true);
 }
 
 // cvt.rna.tf32.f32 on the host: round to nearest (ties away), keep 10 mantissa bits.
@@ -864,6 +1011,41 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     int rc;
     if ((rc = make_map(&g->map_whi, g->w_hi, g->c_pad, d, d, BN)) != LR_OK) return rc;
     if ((rc = make_map(&g->map_wlo, g->w_lo, g->c_pad, d, d, BN)) != LR_OK) return rc;
+
+    // FP16 copies (3xFP16 mode, LRS_GEMM_F16=0 turns it off)
+    g->f16 = true;
+    if (const char* e = getenv("LRS_GEMM_F16")) g->f16 = atoi(e) != 0;
+    if (g->f16) {
+        g->d16 = (d + 7) / 8 * 8;
+        std::vector<__half> h16((size_t)g->c_pad * g->d16, __float2half_rn(0.0f)), l16(h16);
+        std::vector<float> inv(g->c_pad, 1.0f);
+        for (int c = 0; c < C; ++c) {
+            double mx = 0.0;
+            for (int k = 0; k < d; ++k) mx = std::fmax(mx, std::fabs(coef[(size_t)c * d + k]));
+            double sc = 1.0;
+            if (mx > 0.0 && std::isfinite(mx)) {
+                int e = 0;
+                std::frexp(mx, &e);
+                sc = std::ldexp(1.0, 2 - e);            // largest |w| of the class lands in [2, 4)
+            }
+            inv[c] = (float)(1.0 / sc);
+            for (int k = 0; k < d; ++k) {
+                const double w = coef[(size_t)c * d + k] * sc;
+                const __half h = __float2half_rn((float)w);
+                h16[(size_t)c * g->d16 + k] = h;
+                l16[(size_t)c * g->d16 + k] = __float2half_rn((float)(w - (double)__half2float(h)));
+            }
+        }
+        const size_t b16 = h16.size() * sizeof(__half);
+        LRS_CUDA(cudaMalloc(&g->w16_hi, b16));
+        LRS_CUDA(cudaMalloc(&g->w16_lo, b16));
+        LRS_CUDA(cudaMalloc(&g->col_inv_scale, inv.size() * sizeof(float)));
+        LRS_CUDA(cudaMemcpy(g->w16_hi, h16.data(), b16, cudaMemcpyHostToDevice));
+        LRS_CUDA(cudaMemcpy(g->w16_lo, l16.data(), b16, cudaMemcpyHostToDevice));
+        LRS_CUDA(cudaMemcpy(g->col_inv_scale, inv.data(), inv.size() * sizeof(float), cudaMemcpyHostToDevice));
+        if ((rc = make_map_ex(&g->map_w16hi, g->w16_hi, g->c_pad, d, g->d16, BN, BK16, 2, true)) != LR_OK) return rc;
+        if ((rc = make_map_ex(&g->map_w16lo, g->w16_lo, g->c_pad, d, g->d16, BN, BK16, 2, true)) != LR_OK) return rc;
+    }
     return LR_OK;
 }
 
@@ -890,6 +1072,9 @@ void gemm_destroy(Model& m) {
     cudaFree(m.gemm->w_hi);
     cudaFree(m.gemm->w_lo);
     cudaFree(m.gemm->bias);
+    cudaFree(m.gemm->w16_hi);
+    cudaFree(m.gemm->w16_lo);
+    cudaFree(m.gemm->col_inv_scale);
     delete m.gemm;
     m.gemm = nullptr;
 }
@@ -900,12 +1085,15 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     GemmPlan* g = m.gemm;
     GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
-    int rc = make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM);
+    const bool f16 = g->f16;
+    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM, BK16, 4, false)
+                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM);
     if (rc != LR_OK) return rc;
     const size_t smem = SmemLayout::total + 1024;
     const int dev = m.device & 63;
     if (!g->configured[dev]) {
-        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         g->configured[dev] = true;
     }
     // Scratch of the fp32 re-scoring pass: per row the log-sum-exp the tensor path saw and one flag
@@ -914,13 +1102,22 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
     unsigned char* flags = nullptr;
     float* lse = nullptr;
-    if (fixup) {
-        void* ptr = nullptr;
-        const size_t lse_bytes = ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256;
-        LRS_CUDA(cudaMallocAsync(&ptr, lse_bytes + (size_t)a.n_rows, a.stream));
-        lse = reinterpret_cast<float*>(ptr);
-        flags = reinterpret_cast<unsigned char*>(ptr) + lse_bytes;
-        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
+    float* x_scale = nullptr;
+    void* scratch = nullptr;
+    if (fixup || f16) {
+        // [x scale pair | lse per row | flag byte per row]
+        const size_t lse_bytes = fixup ? ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256 : 0;
+        LRS_CUDA(cudaMallocAsync(&scratch, 256 + lse_bytes + (fixup ? (size_t)a.n_rows : 0), a.stream));
+        x_scale = reinterpret_cast<float*>(scratch);
+        if (fixup) {
+            lse = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+            flags = reinterpret_cast<unsigned char*>(scratch) + 256 + lse_bytes;
+            LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
+        }
+        if (f16) {
+            x_scale_kernel<<<1, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, x_scale);
+            count_launch();
+        }
     }
     GemmParams p;
     p.flags = flags;
@@ -931,8 +1128,11 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.nb = L.nb;
     p.split = L.split ? 1 : 0;
     p.ncc = L.ncc;
-    p.num_k_chunks = (m.n_features + BK - 1) / BK;
+    p.num_k_chunks = f16 ? (m.n_features + BK16 - 1) / BK16 : (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
+    p.col_inv_scale = g->col_inv_scale;
+    p.x_scale = x_scale;
+    p.count_nonfinite = fixup ? 0 : 1;
     p.proba = a.proba;
     p.decision = a.decision;
     p.label = a.label;
@@ -960,7 +1160,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     if (L.max_clusters[dev] == 0) {
         cfg.gridDim = dim3((unsigned)(m.num_sms / L.ncc * L.ncc));
         int nc = 0;
-        if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel, &cfg) != cudaSuccess || nc < 1) {
+        if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel<false>, &cfg) != cudaSuccess || nc < 1) {
             cudaGetLastError();
             nc = m.num_sms / L.ncc / 2 > 0 ? m.num_sms / L.ncc / 2 : 1;
         }
@@ -969,21 +1169,22 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     int64_t clusters = L.max_clusters[dev];
     if (clusters > n_tiles) clusters = n_tiles;
     cfg.gridDim = dim3((unsigned)(clusters * L.ncc));
-    LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel, map_x, g->map_whi, g->map_wlo, p));
+    if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true>, map_x, g->map_w16hi, g->map_w16lo, p));
+    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false>, map_x, g->map_whi, g->map_wlo, p));
     count_launch();
     if (fixup) {
         if (a.proba)
             gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.n_scores,
                                                                       m.W, m.b, flags, lse, a.proba, a.decision,
-                                                                      a.label, a.maxprob, m.status + 1);
+                                                                      a.label, a.maxprob, m.status + 1, m.status);
         else
             gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features,
                                                                        m.n_scores, m.W, m.b, flags, a.decision,
-                                                                       a.label, a.maxprob, m.status + 1);
+                                                                       a.label, a.maxprob, m.status + 1, m.status);
         count_launch();
         LRS_CUDA(cudaGetLastError());
-        LRS_CUDA(cudaFreeAsync(lse, a.stream));
     }
+    if (scratch) LRS_CUDA(cudaFreeAsync(scratch, a.stream));
     return LR_OK;
 }
 
