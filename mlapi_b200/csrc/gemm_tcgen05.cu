@@ -50,7 +50,7 @@ constexpr int A_STAGES = 2;
 constexpr int B_STAGES = 4;
 constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB (x2: hi, lo)
 constexpr int B_TILE_BYTES = BN * BK * 4;     // 32 KB
-constexpr int kThreads = 448;                 // 14 warps: TMA, MMA, 4 converters, 8 epilogue
+constexpr int kThreads = 480;                 // 15 warps: TMA (W), MMA, 4 converters, 8 epilogue, TMA (X)
 constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 
@@ -77,11 +77,14 @@ struct GemmParams {
     int n_classes;
     int nb;                 // 256-class blocks per CTA (1 or 2)
     int split;              // 1: nb == 1 and the correction products accumulate in TMEM columns 256..511
-    int ncc;                // CTAs per cluster (class split)
+    int ncc;                // class slices per cluster: CTAs that share a row tile
+    int nrt;                // row tiles per cluster (1 or 2): CTAs that share a class slice
+                            // cluster = ncc * nrt CTAs, rank = slice + ncc * row_tile
     int num_k_chunks;
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
     const float* col_inv_scale;   // FP16 mode: 1 / class scale, padded like bias
     const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
+    int debug_skip;         // profiling only: bit0 = converters skip their work, bit1 = epilogue skips passes
     int count_nonfinite;    // 1: the epilogue counts non-finite rows itself (no re-scoring pass to do it)
     float* proba;
     float* decision;
@@ -144,11 +147,27 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
     return pred != 0;
 }
+// Same copy delivered to the same CTA-relative offset (data and mbarrier signal) in every CTA of `mask`.
+__device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                               uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// Arrive on the barrier at the same offset in every CTA of `mask` once the MMAs issued so far are done.
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(mask)
                  : "memory");
 }
 __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
@@ -211,6 +230,29 @@ __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+// Two scaled values -> packed fp16 (hi, hi) and packed fp16 residuals (lo, lo), with the packed
+// fp32x2 / f16x2 conversions of sm_100: 7 instructions per pair.
+__device__ __forceinline__ void split_pair(float a, float b, float sx, uint32_t& hi, uint32_t& lo) {
+    asm("{\n\t"
+        ".reg .b64 v, s, r;\n\t"
+        ".reg .f32 ha, hb;\n\t"
+        ".reg .b16 h0, h1;\n\t"
+        "mov.b64 v, {%2, %3};\n\t"
+        "mov.b64 s, {%4, %4};\n\t"
+        "mul.rn.f32x2 v, v, s;\n\t"
+        "mov.b64 {ha, hb}, v;\n\t"
+        "cvt.rn.f16x2.f32 %0, hb, ha;\n\t"            // low half <- a, high half <- b
+        "mov.b32 {h0, h1}, %0;\n\t"
+        "cvt.f32.f16 ha, h0;\n\t"
+        "cvt.f32.f16 hb, h1;\n\t"
+        "mov.b64 r, {ha, hb};\n\t"
+        "sub.rn.f32x2 v, v, r;\n\t"
+        "mov.b64 {ha, hb}, v;\n\t"
+        "cvt.rn.f16x2.f32 %1, hb, ha;\n\t"
+        "}"
+        : "=r"(hi), "=r"(lo)
+        : "f"(a), "f"(b), "f"(sx));
 }
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
@@ -276,19 +318,30 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const uint32_t rank = p.ncc > 1 ? cluster_ctarank() : 0;
+    const int csize = p.ncc * p.nrt;
+    const uint32_t crank = csize > 1 ? cluster_ctarank() : 0;
+    const uint32_t rank = crank % (uint32_t)p.ncc;      // class slice of this CTA
+    const uint32_t rt = crank / (uint32_t)p.ncc;        // row tile of this CTA inside the cluster's tile group
     const int n_cols_cta = p.nb * BN;
     const int col0 = (int)rank * n_cols_cta;       // first class handled by this CTA
+    // Multicast groups.  The ncc CTAs of a row tile need the same X tile: each fetches 1/ncc of its rows
+    // and multicasts them to the group.  The nrt CTAs of a class slice need the same W tiles: each
+    // fetches 1/nrt of the rows.  L2 -> SM traffic per CTA drops accordingly.
+    const uint16_t x_mask = (uint16_t)(((1u << p.ncc) - 1u) << (rt * p.ncc));
+    uint16_t w_mask = 0;
+    for (int j = 0; j < p.nrt; ++j) w_mask |= (uint16_t)(1u << (rank + j * p.ncc));
+    const int x_rows = BM / p.ncc;                 // rows of the X tile this CTA fetches
+    const int w_rows = BN / p.nrt;                 // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_STAGES; ++i) {
             mbar_init(x_full + i, 1);
             mbar_init(a_ready + i, 128);
-            mbar_init(a_empty + i, 1);
+            mbar_init(a_empty + i, p.ncc);       // every CTA sharing the X tile has consumed the stage
         }
         for (int i = 0; i < B_STAGES; ++i) {
             mbar_init(b_full + i, 1);
-            mbar_init(b_empty + i, 1);
+            mbar_init(b_empty + i, p.nrt);       // every CTA sharing the W tile has consumed the stage
         }
         mbar_init(acc_full, 1);
         mbar_init(acc_empty, kEpiThreads);
@@ -308,42 +361,67 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (p.ncc > 1) cluster_sync_all();             // peers' barriers are initialised before any remote arrive
+    if (csize > 1) cluster_sync_all();             // peers' barriers are initialised before any remote arrive
     const uint32_t tmem_base = *tmem_slot;
 
     const int64_t n_tiles = (p.n_rows + BM - 1) / BM;
-    const int64_t cluster_id = blockIdx.x / p.ncc;
-    const int64_t n_clusters = gridDim.x / p.ncc;
+    // tiles are handed out in groups of nrt consecutive row tiles, one group per cluster iteration
+    const int64_t n_groups = (n_tiles + p.nrt - 1) / p.nrt;
+    const int64_t cluster_id = blockIdx.x / csize;
+    const int64_t n_clusters = gridDim.x / csize;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer: W tiles =====================
         // (whole warp walks the loop, one elected lane issues: see the MMA issuer for why)
+        // X has a producer warp of its own (below): issued from one program-ordered loop, the next X
+        // tile waited behind the W slots of the current chunk, which free up only as the MMAs of the
+        // previous chunk retire -- the HBM latency of X plus the conversion then sat on the critical
+        // path of every chunk (measured: 5300 cycles per chunk against 3072 of MMA work).
         const bool leader = elect_one();
-        int as = 0, bs = 0;
-        uint32_t aph = 0, bph = 0;
-        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-            const int row0 = (int)(tile * BM);
+        int bs = 0;
+        uint32_t bph = 0;
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                mbar_wait(a_empty + as, aph ^ 1);
-                if (leader) {
-                    mbar_expect_tx(x_full + as, RAW_BYTES);
-                    tma_load_2d(F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES, &map_x, kc * BKx, row0,
-                                x_full + as);
-                }
-                __syncwarp();
-                if (++as == A_STAGES) { as = 0; aph ^= 1; }
                 for (int part = 0; part < 2; ++part) {            // 0: w_hi, 1: w_lo
                     for (int nbk = 0; nbk < p.nb; ++nbk) {
                         mbar_wait(b_empty + bs, bph ^ 1);
                         if (leader) {
                             mbar_expect_tx(b_full + bs, B_TILE_BYTES);
-                            tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
-                                        col0 + nbk * BN, b_full + bs);
+                            if (p.nrt > 1)
+                                tma_load_2d_mc(b_t + bs * B_TILE_BYTES + rt * w_rows * 128,
+                                               part == 0 ? &map_whi : &map_wlo, kc * BKx,
+                                               col0 + nbk * BN + (int)rt * w_rows, b_full + bs, w_mask);
+                            else
+                                tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
+                                            col0 + nbk * BN, b_full + bs);
                         }
                         __syncwarp();
                         if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
                 }
+            }
+        }
+    } else if (warp == 14) {
+        // ===================== TMA producer: X tiles =====================
+        const bool leader = elect_one();
+        int as = 0;
+        uint32_t aph = 0;
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
+            const int64_t tile = grp * p.nrt + rt;
+            const int row0 = (int)(tile * BM);
+            for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                mbar_wait(a_empty + as, aph ^ 1);
+                if (leader) {
+                    mbar_expect_tx(x_full + as, RAW_BYTES);
+                    unsigned char* xdst = F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES;
+                    if (p.ncc > 1)
+                        tma_load_2d_mc(xdst + rank * x_rows * (BKx * 4), &map_x, kc * BKx, row0 + (int)rank * x_rows,
+                                       x_full + as, x_mask);
+                    else
+                        tma_load_2d(xdst, &map_x, kc * BKx, row0, x_full + as);
+                }
+                __syncwarp();
+                if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -362,7 +440,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const uint32_t corr_first = p.split ? 0u : 1u;               // accumulate flag of the first correction MMA
         int as = 0, bs = 0;
         uint32_t aph = 0, bph = 0, accph = 0;
-        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
+            const int64_t tile = grp * p.nrt + rt;
             mbar_wait(acc_empty, accph ^ 1);
             tc_fence_after();
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
@@ -394,13 +473,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                                 for (int k = 0; k < BK / 8; ++k) tc_mma<F16>(c_tmem, ahi + 2 * k, bd + 2 * k, 1u);
                             }
-                            tc_commit(b_empty + bs);
+                            if (p.nrt > 1) tc_commit_mc(b_empty + bs, w_mask); else tc_commit(b_empty + bs);
                         }
                         __syncwarp();
                         if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
                 }
-                if (leader) tc_commit(a_empty + as);
+                if (leader) { if (p.ncc > 1) tc_commit_mc(a_empty + as, x_mask); else tc_commit(a_empty + as); }
                 __syncwarp();
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
@@ -414,10 +493,12 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const float sx = F16 ? p.x_scale[0] : 1.0f;
         int as = 0;
         uint32_t aph = 0;
-        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
+            const int64_t tile = grp * p.nrt + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(x_full + as, aph);
-                if constexpr (!F16) {
+                if (p.debug_skip & 1) {
+                } else if constexpr (!F16) {
                     float4* hi = reinterpret_cast<float4*>(a_hi + as * A_TILE_BYTES);
                     float4* lo = reinterpret_cast<float4*>(a_lo + as * A_TILE_BYTES);
 #pragma unroll
@@ -445,20 +526,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const int r = qd >> 3, c = qd & 7;
                         const float4* src = reinterpret_cast<const float4*>(stage + r * 256 + c * 32);
                         const float4 x0 = src[0], x1 = src[1];
-                        const float xs[8] = {x0.x * sx, x0.y * sx, x0.z * sx, x0.w * sx,
-                                             x1.x * sx, x1.y * sx, x1.z * sx, x1.w * sx};
-                        __half2 h2[4], l2[4];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const __half ha = __float2half_rn(xs[2 * e]), hb = __float2half_rn(xs[2 * e + 1]);
-                            h2[e] = __halves2half2(ha, hb);
-                            l2[e] = __halves2half2(__float2half_rn(xs[2 * e] - __half2float(ha)),
-                                                   __float2half_rn(xs[2 * e + 1] - __half2float(hb)));
-                        }
-                        hv[j] = make_uint4(*reinterpret_cast<uint32_t*>(&h2[0]), *reinterpret_cast<uint32_t*>(&h2[1]),
-                                           *reinterpret_cast<uint32_t*>(&h2[2]), *reinterpret_cast<uint32_t*>(&h2[3]));
-                        lv[j] = make_uint4(*reinterpret_cast<uint32_t*>(&l2[0]), *reinterpret_cast<uint32_t*>(&l2[1]),
-                                           *reinterpret_cast<uint32_t*>(&l2[2]), *reinterpret_cast<uint32_t*>(&l2[3]));
+                        uint32_t hw[4], lw[4];
+                        split_pair(x0.x, x0.y, sx, hw[0], lw[0]);
+                        split_pair(x0.z, x0.w, sx, hw[1], lw[1]);
+                        split_pair(x1.x, x1.y, sx, hw[2], lw[2]);
+                        split_pair(x1.z, x1.w, sx, hw[3], lw[3]);
+                        hv[j] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                        lv[j] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
                     }
                     asm volatile("bar.sync 2, 128;" ::: "memory");      // all raw data is in registers
 #pragma unroll
@@ -496,7 +570,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int cb_hi = h == 0 ? ((n_chunks + 1) / 2) * 32 : n_chunks * 32;
         uint32_t accph = 0;
         uint32_t it = 0;
-        for (int64_t tile = cluster_id; tile < n_tiles; tile += n_clusters, ++it) {
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters, ++it) {
+            const int64_t tile = grp * p.nrt + rt;      // may lie past the end: TMA zero-fills, nothing is stored
             const int64_t row = tile * BM + r_in_tile;
             const bool live = row < p.n_rows;
             const uint32_t par = it & 1;
@@ -507,7 +582,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // ---- pass 1: max and first argmax over my columns
             float m = -INFINITY;
             int arg = col0 + cb_lo;
-            for (int cb = cb_lo; cb < cb_hi; cb += 32) {
+            const int cb_hi1 = (p.debug_skip & 2) ? cb_lo : cb_hi;
+            for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
                 float v[32];
                 tmem_ld32(t_lane + (uint32_t)cb, v);
                 if (p.split) {
@@ -547,8 +623,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
                         const uint32_t bar = smem_u32(xchg_bar + par * 2 + 0);
                         for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, dst), m, __int_as_float(arg));
-                            mbar_arrive_cluster(map_to_cta(bar, dst));
+                            st_cluster_v2(map_to_cta(slot, rt * p.ncc + dst), m, __int_as_float(arg));
+                            mbar_arrive_cluster(map_to_cta(bar, rt * p.ncc + dst));
                         }
                         mbar_wait_cluster(xchg_bar + par * 2 + 0, (it >> 1) & 1);
                         gm = -INFINITY;
@@ -575,7 +651,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
             float ssum = 0.0f;
             int near = 0;
-            for (int cb = cb_lo; cb < cb_hi; cb += 32) {
+            for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
                 float v[32];
                 tmem_ld32(t_lane + (uint32_t)cb, v);
                 if (p.split) {
@@ -627,8 +703,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
                         const uint32_t bar = smem_u32(xchg_bar + par * 2 + 1);
                         for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, dst), ssum, __int_as_float(near));
-                            mbar_arrive_cluster(map_to_cta(bar, dst));
+                            st_cluster_v2(map_to_cta(slot, rt * p.ncc + dst), ssum, __int_as_float(near));
+                            mbar_arrive_cluster(map_to_cta(bar, rt * p.ncc + dst));
                         }
                         mbar_wait_cluster(xchg_bar + par * 2 + 1, (it >> 1) & 1);
                         gs = 0.0f;
@@ -654,7 +730,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const float risk_thr = 8e-6f / (kappa * fmaxf(fabsf(gm), 1.0f));
             bool risk = false;
             if (p.proba) {
-                for (int cb = cb_lo; cb < cb_hi; cb += 32) {
+                for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
                     float v[32];
                     tmem_ld32(t_lane + (uint32_t)cb, v);
 #pragma unroll
@@ -705,7 +781,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     // ---- teardown ----
     tc_fence_before();
     __syncthreads();
-    if (p.ncc > 1) cluster_sync_all();               // no CTA leaves while a peer may still write its smem
+    if (csize > 1) cluster_sync_all();               // no CTA leaves while a peer may still write its smem
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
@@ -876,12 +952,10 @@ struct GemmPlan {
     float* w_hi = nullptr;      // [c_pad][d] TF32 (round-to-nearest) part of coef_
     float* w_lo = nullptr;      // [c_pad][d] TF32 of the residual
     float* bias = nullptr;      // [c_pad], -inf beyond n_classes
-    CUtensorMap map_whi, map_wlo;
     // FP16 mode: coef_ scaled per class by a power of two into (2, 4] and split into two halves
     __half* w16_hi = nullptr;   // [c_pad][d16]
     __half* w16_lo = nullptr;
     float* col_inv_scale = nullptr;   // [c_pad] 1 / class scale
-    CUtensorMap map_w16hi, map_w16lo;
     int d16 = 0;                // row pitch of the fp16 copies (n_features rounded up to 8: TMA wants 16-byte pitches)
     bool f16 = false;
     // Two CTA layouts over the same W buffers:
@@ -890,7 +964,12 @@ struct GemmPlan {
     //                 error, so far fewer rows need the fp32 re-scoring pass  (C <= 1024)
     // `active` starts on the fast layout where both exist (C in 257..1024) and moves to the accurate
     // one when the re-scoring pass reports that the data is confident (lr_score_host feeds that back).
-    struct Layout { int nb = 0, ncc = 0; bool split = false; int max_clusters[64] = {0}; };
+    struct Layout {
+        int nb = 0, ncc = 0, nrt = 1;
+        bool split = false;
+        int max_clusters[64] = {0};
+        CUtensorMap map_whi, map_wlo, map_w16hi, map_w16lo;    // W boxes are BN / nrt rows
+    };
     Layout layout[2];
     bool has[2] = {false, false};
     int active = 0;
@@ -980,6 +1059,10 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         acc.split = true;
         g->has[1] = true;
     }
+    // two row tiles per cluster share every W tile through TMA multicast (cluster <= 8 CTAs)
+    bool mc = true;
+    if (const char* e = getenv("LRS_GEMM_MC")) mc = atoi(e) != 0;
+    for (int i = 0; i < 2; ++i) g->layout[i].nrt = (mc && g->layout[i].ncc * 2 <= 8) ? 2 : 1;
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -1009,8 +1092,12 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     LRS_CUDA(cudaMemcpy(g->w_lo, lo.data(), bytes, cudaMemcpyHostToDevice));
     LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
     int rc;
-    if ((rc = make_map(&g->map_whi, g->w_hi, g->c_pad, d, d, BN)) != LR_OK) return rc;
-    if ((rc = make_map(&g->map_wlo, g->w_lo, g->c_pad, d, d, BN)) != LR_OK) return rc;
+    for (int i = 0; i < 2; ++i) {
+        if (!g->has[i]) continue;
+        auto& L = g->layout[i];
+        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d, BN / L.nrt)) != LR_OK) return rc;
+        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d, BN / L.nrt)) != LR_OK) return rc;
+    }
 
     // FP16 copies (3xFP16 mode, LRS_GEMM_F16=0 turns it off)
     g->f16 = true;
@@ -1043,8 +1130,12 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         LRS_CUDA(cudaMemcpy(g->w16_hi, h16.data(), b16, cudaMemcpyHostToDevice));
         LRS_CUDA(cudaMemcpy(g->w16_lo, l16.data(), b16, cudaMemcpyHostToDevice));
         LRS_CUDA(cudaMemcpy(g->col_inv_scale, inv.data(), inv.size() * sizeof(float), cudaMemcpyHostToDevice));
-        if ((rc = make_map_ex(&g->map_w16hi, g->w16_hi, g->c_pad, d, g->d16, BN, BK16, 2, true)) != LR_OK) return rc;
-        if ((rc = make_map_ex(&g->map_w16lo, g->w16_lo, g->c_pad, d, g->d16, BN, BK16, 2, true)) != LR_OK) return rc;
+        for (int i = 0; i < 2; ++i) {
+            if (!g->has[i]) continue;
+            auto& L = g->layout[i];
+            if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, BN / L.nrt, BK16, 2, true)) != LR_OK) return rc;
+            if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, BN / L.nrt, BK16, 2, true)) != LR_OK) return rc;
+        }
     }
     return LR_OK;
 }
@@ -1086,8 +1177,8 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
     const bool f16 = g->f16;
-    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM, BK16, 4, false)
-                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM);
+    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM / L.ncc, BK16, 4, false)
+                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM / L.ncc);
     if (rc != LR_OK) return rc;
     const size_t smem = SmemLayout::total + 1024;
     const int dev = m.device & 63;
@@ -1128,11 +1219,14 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.nb = L.nb;
     p.split = L.split ? 1 : 0;
     p.ncc = L.ncc;
+    p.nrt = L.nrt;
     p.num_k_chunks = f16 ? (m.n_features + BK16 - 1) / BK16 : (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
     p.x_scale = x_scale;
     p.count_nonfinite = fixup ? 0 : 1;
+    p.debug_skip = 0;
+    if (const char* e = getenv("LRS_GEMM_DEBUG_SKIP")) p.debug_skip = atoi(e);
     p.proba = a.proba;
     p.decision = a.decision;
     p.label = a.label;
@@ -1149,7 +1243,8 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     cfg.stream = a.stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)L.ncc;
+    const int csize = L.ncc * L.nrt;
+    attr[0].val.clusterDim.x = (unsigned)csize;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -1158,19 +1253,20 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     // GPCs hold 16/18/20 SMs, so clusters of 4 do not tile all 148 SMs: asking for floor(148/ncc)
     // clusters would leave the last one waiting for a whole wave (measured: 2x slower).
     if (L.max_clusters[dev] == 0) {
-        cfg.gridDim = dim3((unsigned)(m.num_sms / L.ncc * L.ncc));
+        cfg.gridDim = dim3((unsigned)(m.num_sms / csize * csize));
         int nc = 0;
         if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel<false>, &cfg) != cudaSuccess || nc < 1) {
             cudaGetLastError();
-            nc = m.num_sms / L.ncc / 2 > 0 ? m.num_sms / L.ncc / 2 : 1;
+            nc = m.num_sms / csize / 2 > 0 ? m.num_sms / csize / 2 : 1;
         }
         L.max_clusters[dev] = nc;
     }
     int64_t clusters = L.max_clusters[dev];
-    if (clusters > n_tiles) clusters = n_tiles;
-    cfg.gridDim = dim3((unsigned)(clusters * L.ncc));
-    if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true>, map_x, g->map_w16hi, g->map_w16lo, p));
-    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false>, map_x, g->map_whi, g->map_wlo, p));
+    const int64_t n_groups = (n_tiles + L.nrt - 1) / L.nrt;
+    if (clusters > n_groups) clusters = n_groups;
+    cfg.gridDim = dim3((unsigned)(clusters * csize));
+    if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true>, map_x, L.map_w16hi, L.map_w16lo, p));
+    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false>, map_x, L.map_whi, L.map_wlo, p));
     count_launch();
     if (fixup) {
         if (a.proba)
