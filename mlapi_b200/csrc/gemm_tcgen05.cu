@@ -46,30 +46,35 @@ constexpr int BM = 128;          // rows per tile (TMEM lanes)
 constexpr int BK = 32;           // TF32 mode: fp32 elements per k-chunk = 128 bytes = one swizzle-128B row
 constexpr int BK16 = 64;         // FP16 mode: fp16 elements per k-chunk, again one 128-byte row
 constexpr int BN = 256;          // classes per MMA / per W stage
-constexpr int A_STAGES = 2;
-constexpr int B_STAGES = 4;
-constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB (x2: hi, lo)
-constexpr int B_TILE_BYTES = BN * BK * 4;     // 32 KB
+constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB: one operand tile of X (hi or lo), either mode
 constexpr int kThreads = 480;                 // 15 warps: TMA (W), MMA, 4 converters, 8 epilogue, TMA (X)
 constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 
-struct SmemLayout {
+// Shared-memory plan.  PAIR = the CTA is half of a cta_group::2 pair: it holds half of every W tile
+// (the MMA reads the other half from the peer's shared memory), which halves the shared-memory read
+// traffic of each MMA and frees room for a four-deep X ring.
+template <bool PAIR>
+struct SmemLayoutT {
+    static constexpr int a_stages = PAIR ? 4 : 2;
+    static constexpr int b_stages = 4;
+    static constexpr int b_tile = (PAIR ? BN / 2 : BN) * 128;        // 16 KB / 32 KB
     // offsets from the 1024-byte aligned base
-    static constexpr int a_hi = 0;                                   // [A_STAGES][16 KB]
-    static constexpr int a_lo = a_hi + A_STAGES * A_TILE_BYTES;      // [A_STAGES][16 KB]
-    static constexpr int b = a_lo + A_STAGES * A_TILE_BYTES;         // [B_STAGES][32 KB]
-    static constexpr int bias = b + B_STAGES * B_TILE_BYTES;         // [512] floats
+    static constexpr int a_hi = 0;                                   // [a_stages][16 KB]
+    static constexpr int a_lo = a_hi + a_stages * A_TILE_BYTES;      // [a_stages][16 KB]
+    static constexpr int b = a_lo + a_stages * A_TILE_BYTES;         // [b_stages][b_tile]
+    static constexpr int bias = b + b_stages * b_tile;               // [512] floats
     static constexpr int cscale = bias + 512 * 4;                    // [512] floats: 1 / (x scale * class scale), FP16 mode
-    static constexpr int xchg = cscale + 512 * 4;                      // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
+    static constexpr int xchg = cscale + 512 * 4;                    // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
     static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
     static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
     static constexpr int bars = glob + BM * 8;                       // mbarriers
-    static constexpr int n_bars = 3 * A_STAGES + 2 * B_STAGES + 2 + 4;
+    static constexpr int n_bars = 3 * a_stages + 2 * b_stages + 2 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
 };
-static_assert(SmemLayout::total + 1024 <= 227 * 1024, "shared memory budget");
+static_assert(SmemLayoutT<false>::total + 1024 <= 227 * 1024, "shared memory budget");
+static_assert(SmemLayoutT<true>::total + 1024 <= 227 * 1024, "shared memory budget");
 
 struct GemmParams {
     int64_t n_rows;
@@ -284,16 +289,60 @@ __device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b,
 
 constexpr float kLog2e = 1.4426950408889634f;
 
+// ---- cta_group::2 (CTA pair) forms ---------------------------------------------------------------
+// The pair shares every MMA: the even CTA of the pair issues it, each SM multiplies its own 128 rows
+// of X with a W tile whose two halves sit in the two CTAs' shared memories.
+__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* map, int c0, int c1,
+                                                uint32_t bar_cluster_addr) {
+    // data lands in THIS CTA's shared memory, the byte count is credited to the barrier at
+    // `bar_cluster_addr` (a shared::cluster address: the issuing CTA's copy of the barrier)
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_commit_2sm(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(mask)
+                 : "memory");
+}
+template <bool F16>
+__device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
+    constexpr uint32_t idesc = (F16 ? kIdesc16 : kIdesc) + ((uint32_t)(BM >> 4) << 24);   // M = 256 across the pair
+    if constexpr (F16)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                     "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+                     : "memory");
+    else
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                     "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+                     : "memory");
+}
+template <bool F16, bool PAIR>
+__device__ __forceinline__ void mma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) {
+    if constexpr (PAIR) tc_mma_2sm<F16>(d, a, b, acc);
+    else tc_mma<F16>(d, a, b, acc);
+}
+
 // F16 = false: 3xTF32 (operands are fp32 containers, 8 K-elements per MMA).
 // F16 = true : 3xFP16 (x and w scaled by powers of two into fp16 range and split hi/lo like above,
 //              16 K-elements per MMA at twice the TF32 rate; scales are undone in the epilogue).
-template <bool F16>
+// PAIR = true: cta_group::2 -- see SmemLayoutT.
+template <bool F16, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                     const __grid_constant__ CUtensorMap map_wlo, const GemmParams p) {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
 
+    using SmemLayout = SmemLayoutT<PAIR>;
+    constexpr int A_STAGES = SmemLayout::a_stages;
+    constexpr int B_STAGES = SmemLayout::b_stages;
+    constexpr int B_TILE_BYTES = SmemLayout::b_tile;
     unsigned char* a_hi = smem + SmemLayout::a_hi;
     unsigned char* a_lo = smem + SmemLayout::a_lo;
     unsigned char* b_t = smem + SmemLayout::b;
@@ -318,10 +367,18 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int csize = p.ncc * p.nrt;
+    // cluster layout: PAIR: 2 * ncc CTAs, rank = 2 * slice + row tile (pair = two row tiles of one class slice);
+    //                 else: ncc * nrt CTAs, rank = slice + ncc * row tile
+    const int gsz = PAIR ? 2 : p.nrt;                   // row tiles per cluster iteration
+    const int csize = p.ncc * gsz;
     const uint32_t crank = csize > 1 ? cluster_ctarank() : 0;
-    const uint32_t rank = crank % (uint32_t)p.ncc;      // class slice of this CTA
-    const uint32_t rt = crank / (uint32_t)p.ncc;        // row tile of this CTA inside the cluster's tile group
+    const uint32_t rank = PAIR ? (crank >> 1) : crank % (uint32_t)p.ncc;      // class slice of this CTA
+    const uint32_t rt = PAIR ? (crank & 1u) : crank / (uint32_t)p.ncc;        // row tile inside the cluster's tile group
+    const bool lead = !PAIR || rt == 0;                 // the CTA whose MMA lane issues for the pair
+    const uint32_t lead_rank = crank & ~1u;
+    const uint16_t pair_mask = (uint16_t)(3u << lead_rank);
+    const bool x_mc = !PAIR && p.ncc > 1;               // X multicast across class slices
+    const bool w_mc = !PAIR && p.nrt > 1;               // W multicast across row tiles
     const int n_cols_cta = p.nb * BN;
     const int col0 = (int)rank * n_cols_cta;       // first class handled by this CTA
     // Multicast groups.  The ncc CTAs of a row tile need the same X tile: each fetches 1/ncc of its rows
@@ -330,21 +387,21 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const uint16_t x_mask = (uint16_t)(((1u << p.ncc) - 1u) << (rt * p.ncc));
     uint16_t w_mask = 0;
     for (int j = 0; j < p.nrt; ++j) w_mask |= (uint16_t)(1u << (rank + j * p.ncc));
-    const int x_rows = BM / p.ncc;                 // rows of the X tile this CTA fetches
-    const int w_rows = BN / p.nrt;                 // rows of each W tile this CTA fetches
+    const int x_rows = x_mc ? BM / p.ncc : BM;      // rows of the X tile this CTA fetches
+    const int w_rows = PAIR ? BN / 2 : BN / p.nrt;  // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_STAGES; ++i) {
             mbar_init(x_full + i, 1);
-            mbar_init(a_ready + i, 128);
-            mbar_init(a_empty + i, p.ncc);       // every CTA sharing the X tile has consumed the stage
+            mbar_init(a_ready + i, PAIR ? 256 : 128);    // PAIR: both CTAs' converters report to the issuing CTA
+            mbar_init(a_empty + i, x_mc ? p.ncc : 1);    // every CTA sharing the X tile has consumed the stage
         }
         for (int i = 0; i < B_STAGES; ++i) {
             mbar_init(b_full + i, 1);
-            mbar_init(b_empty + i, p.nrt);       // every CTA sharing the W tile has consumed the stage
+            mbar_init(b_empty + i, w_mc ? p.nrt : 1);    // every CTA sharing the W tile has consumed the stage
         }
         mbar_init(acc_full, 1);
-        mbar_init(acc_empty, kEpiThreads);
+        mbar_init(acc_empty, PAIR ? 2 * kEpiThreads : kEpiThreads);
         for (int i = 0; i < 4; ++i) mbar_init(xchg_bar + i, 128 * p.ncc);
         mbar_fence_init();
     }
@@ -353,10 +410,17 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         if constexpr (F16) cscale_s[i] = p.col_inv_scale[col0 + i] * p.x_scale[1];
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(512)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(512)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -366,7 +430,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     const int64_t n_tiles = (p.n_rows + BM - 1) / BM;
     // tiles are handed out in groups of nrt consecutive row tiles, one group per cluster iteration
-    const int64_t n_groups = (n_tiles + p.nrt - 1) / p.nrt;
+    const int64_t n_groups = (n_tiles + gsz - 1) / gsz;
     const int64_t cluster_id = blockIdx.x / csize;
     const int64_t n_clusters = gridDim.x / csize;
 
@@ -385,9 +449,16 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 for (int part = 0; part < 2; ++part) {            // 0: w_hi, 1: w_lo
                     for (int nbk = 0; nbk < p.nb; ++nbk) {
                         mbar_wait(b_empty + bs, bph ^ 1);
-                        if (leader) {
+                        if (leader && PAIR) {
+                            // each CTA of the pair fetches its half of the tile into its own shared
+                            // memory; both transfers are counted on the issuing CTA's barrier
+                            if (lead) mbar_expect_tx(b_full + bs, 2 * B_TILE_BYTES);
+                            tma_load_2d_2sm(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
+                                            col0 + nbk * BN + (int)rt * w_rows,
+                                            map_to_cta(smem_u32(b_full + bs), lead_rank));
+                        } else if (leader) {
                             mbar_expect_tx(b_full + bs, B_TILE_BYTES);
-                            if (p.nrt > 1)
+                            if (w_mc)
                                 tma_load_2d_mc(b_t + bs * B_TILE_BYTES + rt * w_rows * 128,
                                                part == 0 ? &map_whi : &map_wlo, kc * BKx,
                                                col0 + nbk * BN + (int)rt * w_rows, b_full + bs, w_mask);
@@ -407,14 +478,14 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         int as = 0;
         uint32_t aph = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
-            const int64_t tile = grp * p.nrt + rt;
+            const int64_t tile = grp * gsz + rt;
             const int row0 = (int)(tile * BM);
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(a_empty + as, aph ^ 1);
                 if (leader) {
                     mbar_expect_tx(x_full + as, RAW_BYTES);
                     unsigned char* xdst = F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES;
-                    if (p.ncc > 1)
+                    if (x_mc)
                         tma_load_2d_mc(xdst + rank * x_rows * (BKx * 4), &map_x, kc * BKx, row0 + (int)rank * x_rows,
                                        x_full + as, x_mask);
                     else
@@ -431,7 +502,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // in uniform registers, which is what UTCHMMA takes.  Under `if (lane == 0) { loop }` every
         // operand was re-broadcast (R2UR) per instruction, ~14 instructions per MMA, and the issuing
         // lane -- not the tensor pipe -- set the pace (ncu: tensor pipe 61 % active).
-        const bool leader = elect_one();
+        const bool leader = elect_one() && lead;                      // PAIR: only the even CTA issues
         const uint64_t desc0 = make_smem_desc(0);                    // every field but the address
         const uint64_t ahi0 = desc0 | (uint64_t)((smem_u32(a_hi) & 0x3FFFF) >> 4);
         const uint64_t alo0 = desc0 | (uint64_t)((smem_u32(a_lo) & 0x3FFFF) >> 4);
@@ -440,12 +511,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const uint32_t corr_first = p.split ? 0u : 1u;               // accumulate flag of the first correction MMA
         int as = 0, bs = 0;
         uint32_t aph = 0, bph = 0, accph = 0;
-        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
-            const int64_t tile = grp * p.nrt + rt;
-            mbar_wait(acc_empty, accph ^ 1);
+        for (int64_t grp = cluster_id; lead && grp < n_groups; grp += n_clusters) {
+            if constexpr (PAIR) mbar_wait_cluster(acc_empty, accph ^ 1); else mbar_wait(acc_empty, accph ^ 1);
             tc_fence_after();
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                mbar_wait(a_ready + as, aph);
+                if constexpr (PAIR) mbar_wait_cluster(a_ready + as, aph); else mbar_wait(a_ready + as, aph);
                 // TF32: hi tiles and lo tiles are two arrays; FP16: stage = [hi 16 KB | lo 16 KB] contiguous
                 const uint64_t ahi = ahi0 + (uint64_t)(as * ((F16 ? A_STAGE : A_TILE_BYTES) >> 4));
                 const uint64_t alo = F16 ? ahi + (uint64_t)(A_TILE_BYTES >> 4)
@@ -461,29 +531,35 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (leader) {
                             if (part == 0) {
                                 // x_hi.w_hi into the main accumulator, x_lo.w_hi into the correction one
-                                tc_mma<F16>(d_tmem, ahi, bd, first);
+                                mma_issue<F16, PAIR>(d_tmem, ahi, bd, first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
-                                    tc_mma<F16>(d_tmem, ahi + 2 * k, bd + 2 * k, 1u);
-                                tc_mma<F16>(c_tmem, alo, bd, first | corr_first);
+                                    mma_issue<F16, PAIR>(d_tmem, ahi + 2 * k, bd + 2 * k, 1u);
+                                mma_issue<F16, PAIR>(c_tmem, alo, bd, first | corr_first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)
-                                    tc_mma<F16>(c_tmem, alo + 2 * k, bd + 2 * k, 1u);
+                                    mma_issue<F16, PAIR>(c_tmem, alo + 2 * k, bd + 2 * k, 1u);
                             } else {
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k) tc_mma<F16>(c_tmem, ahi + 2 * k, bd + 2 * k, 1u);
+                                for (int k = 0; k < BK / 8; ++k) mma_issue<F16, PAIR>(c_tmem, ahi + 2 * k, bd + 2 * k, 1u);
                             }
-                            if (p.nrt > 1) tc_commit_mc(b_empty + bs, w_mask); else tc_commit(b_empty + bs);
+                            if constexpr (PAIR) tc_commit_2sm(b_empty + bs, pair_mask);
+                            else if (w_mc) tc_commit_mc(b_empty + bs, w_mask);
+                            else tc_commit(b_empty + bs);
                         }
                         __syncwarp();
                         if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
                 }
-                if (leader) { if (p.ncc > 1) tc_commit_mc(a_empty + as, x_mask); else tc_commit(a_empty + as); }
+                if (leader) {
+                    if constexpr (PAIR) tc_commit_2sm(a_empty + as, pair_mask);
+                    else if (x_mc) tc_commit_mc(a_empty + as, x_mask);
+                    else tc_commit(a_empty + as);
+                }
                 __syncwarp();
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
-            if (leader) tc_commit(acc_full);
+            if (leader) { if constexpr (PAIR) tc_commit_2sm(acc_full, pair_mask); else tc_commit(acc_full); }
             __syncwarp();
             accph ^= 1;
         }
@@ -494,7 +570,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         int as = 0;
         uint32_t aph = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
-            const int64_t tile = grp * p.nrt + rt;
+            const int64_t tile = grp * gsz + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 mbar_wait(x_full + as, aph);
                 if (p.debug_skip & 1) {
@@ -545,7 +621,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     }
                 }
                 fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
-                mbar_arrive(a_ready + as);
+                if (lead) mbar_arrive(a_ready + as);
+                else mbar_arrive_cluster(map_to_cta(smem_u32(a_ready + as), lead_rank));
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
         }
@@ -571,7 +648,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         uint32_t accph = 0;
         uint32_t it = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters, ++it) {
-            const int64_t tile = grp * p.nrt + rt;      // may lie past the end: TMA zero-fills, nothing is stored
+            const int64_t tile = grp * gsz + rt;      // may lie past the end: TMA zero-fills, nothing is stored
             const int64_t row = tile * BM + r_in_tile;
             const bool live = row < p.n_rows;
             const uint32_t par = it & 1;
@@ -623,8 +700,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
                         const uint32_t bar = smem_u32(xchg_bar + par * 2 + 0);
                         for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, rt * p.ncc + dst), m, __int_as_float(arg));
-                            mbar_arrive_cluster(map_to_cta(bar, rt * p.ncc + dst));
+                            st_cluster_v2(map_to_cta(slot, PAIR ? 2 * dst + rt : rt * p.ncc + dst), m, __int_as_float(arg));
+                            mbar_arrive_cluster(map_to_cta(bar, PAIR ? 2 * dst + rt : rt * p.ncc + dst));
                         }
                         mbar_wait_cluster(xchg_bar + par * 2 + 0, (it >> 1) & 1);
                         gm = -INFINITY;
@@ -703,8 +780,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
                         const uint32_t bar = smem_u32(xchg_bar + par * 2 + 1);
                         for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, rt * p.ncc + dst), ssum, __int_as_float(near));
-                            mbar_arrive_cluster(map_to_cta(bar, rt * p.ncc + dst));
+                            st_cluster_v2(map_to_cta(slot, PAIR ? 2 * dst + rt : rt * p.ncc + dst), ssum, __int_as_float(near));
+                            mbar_arrive_cluster(map_to_cta(bar, PAIR ? 2 * dst + rt : rt * p.ncc + dst));
                         }
                         mbar_wait_cluster(xchg_bar + par * 2 + 1, (it >> 1) & 1);
                         gs = 0.0f;
@@ -754,7 +831,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
             }
             tc_fence_before();
-            mbar_arrive(acc_empty);                   // TMEM may be overwritten by the next tile
+            if (lead) mbar_arrive(acc_empty);         // TMEM may be overwritten by the next tile
+            else mbar_arrive_cluster(map_to_cta(smem_u32(acc_empty), lead_rank));
 
             if (live) {
                 if (risk && p.flags && p.flags[row] == 0) p.flags[row] = 1;
@@ -783,7 +861,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     __syncthreads();
     if (csize > 1) cluster_sync_all();               // no CTA leaves while a peer may still write its smem
     if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        if constexpr (PAIR)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
 }
 
@@ -966,6 +1047,7 @@ struct GemmPlan {
     // one when the re-scoring pass reports that the data is confident (lr_score_host feeds that back).
     struct Layout {
         int nb = 0, ncc = 0, nrt = 1;
+        bool pair = false;          // cta_group::2: cluster = 2 * ncc CTAs
         bool split = false;
         int max_clusters[64] = {0};
         CUtensorMap map_whi, map_wlo, map_w16hi, map_w16lo;    // W boxes are BN / nrt rows
@@ -1062,7 +1144,12 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     // two row tiles per cluster share every W tile through TMA multicast (cluster <= 8 CTAs)
     bool mc = true;
     if (const char* e = getenv("LRS_GEMM_MC")) mc = atoi(e) != 0;
-    for (int i = 0; i < 2; ++i) g->layout[i].nrt = (mc && g->layout[i].ncc * 2 <= 8) ? 2 : 1;
+    bool pair = true;
+    if (const char* e = getenv("LRS_GEMM_PAIR")) pair = atoi(e) != 0;
+    for (int i = 0; i < 2; ++i) {
+        g->layout[i].pair = pair && g->layout[i].ncc * 2 <= 8;
+        g->layout[i].nrt = g->layout[i].pair ? 1 : ((mc && g->layout[i].ncc * 2 <= 8) ? 2 : 1);
+    }
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -1095,8 +1182,9 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     for (int i = 0; i < 2; ++i) {
         if (!g->has[i]) continue;
         auto& L = g->layout[i];
-        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d, BN / L.nrt)) != LR_OK) return rc;
-        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d, BN / L.nrt)) != LR_OK) return rc;
+        const int wbox = L.pair ? BN / 2 : BN / L.nrt;
+        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d, wbox)) != LR_OK) return rc;
+        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d, wbox)) != LR_OK) return rc;
     }
 
     // FP16 copies (3xFP16 mode, LRS_GEMM_F16=0 turns it off)
@@ -1133,8 +1221,9 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         for (int i = 0; i < 2; ++i) {
             if (!g->has[i]) continue;
             auto& L = g->layout[i];
-            if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, BN / L.nrt, BK16, 2, true)) != LR_OK) return rc;
-            if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, BN / L.nrt, BK16, 2, true)) != LR_OK) return rc;
+            const int wbox = L.pair ? BN / 2 : BN / L.nrt;
+            if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
+            if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
         }
     }
     return LR_OK;
@@ -1177,14 +1266,18 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
     const bool f16 = g->f16;
-    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM / L.ncc, BK16, 4, false)
-                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, BM / L.ncc);
+    const int xbox = L.pair ? BM : BM / L.ncc;        // X is multicast across class slices only without pairs
+    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, xbox, BK16, 4, false)
+                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, xbox);
     if (rc != LR_OK) return rc;
-    const size_t smem = SmemLayout::total + 1024;
+    const size_t smem = (L.pair ? SmemLayoutT<true>::total : SmemLayoutT<false>::total) + 1024;
     const int dev = m.device & 63;
     if (!g->configured[dev]) {
-        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int s0 = SmemLayoutT<false>::total + 1024, s1 = SmemLayoutT<true>::total + 1024;
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s1));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s1));
         g->configured[dev] = true;
     }
     // Scratch of the fp32 re-scoring pass: per row the log-sum-exp the tensor path saw and one flag
@@ -1243,7 +1336,8 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     cfg.stream = a.stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    const int csize = L.ncc * L.nrt;
+    const int gsz = L.pair ? 2 : L.nrt;             // row tiles per cluster iteration
+    const int csize = L.ncc * gsz;
     attr[0].val.clusterDim.x = (unsigned)csize;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
@@ -1255,18 +1349,22 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     if (L.max_clusters[dev] == 0) {
         cfg.gridDim = dim3((unsigned)(m.num_sms / csize * csize));
         int nc = 0;
-        if (cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel<false>, &cfg) != cudaSuccess || nc < 1) {
+        cudaError_t qe = L.pair ? cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel<true, true>, &cfg)
+                                : cudaOccupancyMaxActiveClusters(&nc, gemm_softmax_kernel<true, false>, &cfg);
+        if (qe != cudaSuccess || nc < 1) {
             cudaGetLastError();
             nc = m.num_sms / csize / 2 > 0 ? m.num_sms / csize / 2 : 1;
         }
         L.max_clusters[dev] = nc;
     }
     int64_t clusters = L.max_clusters[dev];
-    const int64_t n_groups = (n_tiles + L.nrt - 1) / L.nrt;
+    const int64_t n_groups = (n_tiles + gsz - 1) / gsz;
     if (clusters > n_groups) clusters = n_groups;
     cfg.gridDim = dim3((unsigned)(clusters * csize));
-    if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true>, map_x, L.map_w16hi, L.map_w16lo, p));
-    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false>, map_x, L.map_whi, L.map_wlo, p));
+    if (f16 && L.pair) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, true>, map_x, L.map_w16hi, L.map_w16lo, p));
+    else if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, false>, map_x, L.map_w16hi, L.map_w16lo, p));
+    else if (L.pair) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, true>, map_x, L.map_whi, L.map_wlo, p));
+    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, false>, map_x, L.map_whi, L.map_wlo, p));
     count_launch();
     if (fixup) {
         if (a.proba)

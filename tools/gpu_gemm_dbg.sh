@@ -1,5 +1,5 @@
 B="python bench.py --workload cfg3 --steps 5 --warmup 3 --no-e2e --no-cpu"
-for sk in 0 1 2 3; do
+for sk in 0 16 2 3; do
   echo "skip=$sk: $(LRS_GEMM_MC=0 LRS_GEMM_FIXUP=0 LRS_GEMM_DEBUG_SKIP=$sk timeout 300 $B 2>&1 | python -c 'import sys,json
 t=sys.stdin.read()
 try:
