@@ -1146,9 +1146,15 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     if (const char* e = getenv("LRS_GEMM_MC")) mc = atoi(e) != 0;
     bool pair = true;
     if (const char* e = getenv("LRS_GEMM_PAIR")) pair = atoi(e) != 0;
+    // Measured on cfg 3 (tools/gpu_gemm_perf.sh): pairs help while the cluster stays at <= 4 CTAs
+    // (fast layout, 26.8-28.0 ms against 28.4-28.7); clusters of 8 leave SMs idle (GPCs hold 16/18/20
+    // SMs), so the accurate layout (4 class slices) runs unpaired and without multicast (37.3 ms against
+    // 40.3 with multicast and 43.2 paired).  LRS_GEMM_PAIR / LRS_GEMM_MC = 1 force them where legal.
+    const bool force_pair = getenv("LRS_GEMM_PAIR") && pair, force_mc = getenv("LRS_GEMM_MC") && mc;
     for (int i = 0; i < 2; ++i) {
-        g->layout[i].pair = pair && g->layout[i].ncc * 2 <= 8;
-        g->layout[i].nrt = g->layout[i].pair ? 1 : ((mc && g->layout[i].ncc * 2 <= 8) ? 2 : 1);
+        auto& L = g->layout[i];
+        L.pair = pair && (L.ncc * 2 <= 4 || (force_pair && L.ncc * 2 <= 8));
+        L.nrt = (!L.pair && force_mc && L.ncc * 2 <= 8) ? 2 : 1;
     }
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
