@@ -157,6 +157,33 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
         : "memory");
 }
 
+// "Transpose reduce" over the LANES lanes that share a row (LANES = 2 * OFF): each lane enters with
+// partial sums of U rows (x NS score columns) and leaves owning the complete sums of U / min(U, LANES)
+// distinct rows in acc[0..]; see narrow.cu for the mapping.
+template <int OFF, int ROWS, int NS, int U>
+__device__ __forceinline__ void lane_reduce(float (&acc)[U][NS], int s) {
+    if constexpr (OFF >= 1) {
+        if constexpr (ROWS > 1) {
+            constexpr int H = ROWS / 2;
+            const bool upper = (s & OFF) != 0;
+#pragma unroll
+            for (int r = 0; r < H; ++r) {
+#pragma unroll
+                for (int c = 0; c < NS; ++c) {
+                    const float keep = upper ? acc[r + H][c] : acc[r][c];
+                    const float send = upper ? acc[r][c] : acc[r + H][c];
+                    acc[r][c] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
+                }
+            }
+            lane_reduce<OFF / 2, H, NS, U>(acc, s);
+        } else {
+#pragma unroll
+            for (int c = 0; c < NS; ++c) acc[0][c] += __shfl_xor_sync(0xffffffffu, acc[0][c], OFF);
+            lane_reduce<OFF / 2, 1, NS, U>(acc, s);
+        }
+    }
+}
+
 __device__ __forceinline__ bool finite_f(float z) { return fabsf(z) <= 3.402823466e38f; }
 
 #endif  // __CUDACC__

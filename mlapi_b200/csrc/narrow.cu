@@ -28,30 +28,6 @@ namespace {
 
 constexpr int kThreads = 256;
 
-template <int OFF, int ROWS, int NS, int U>
-__device__ __forceinline__ void lane_reduce(float (&acc)[U][NS], int s) {
-    if constexpr (OFF >= 1) {
-        if constexpr (ROWS > 1) {
-            constexpr int H = ROWS / 2;
-            const bool upper = (s & OFF) != 0;
-#pragma unroll
-            for (int r = 0; r < H; ++r) {
-#pragma unroll
-                for (int c = 0; c < NS; ++c) {
-                    const float keep = upper ? acc[r + H][c] : acc[r][c];
-                    const float send = upper ? acc[r][c] : acc[r + H][c];
-                    acc[r][c] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
-                }
-            }
-            lane_reduce<OFF / 2, H, NS, U>(acc, s);
-        } else {
-#pragma unroll
-            for (int c = 0; c < NS; ++c) acc[0][c] += __shfl_xor_sync(0xffffffffu, acc[0][c], OFF);
-            lane_reduce<OFF / 2, 1, NS, U>(acc, s);
-        }
-    }
-}
-
 template <int V>
 struct Vec;
 template <>

@@ -48,11 +48,22 @@ __device__ __forceinline__ float log1pexp_f(float z) {
     return z > 0.0f ? z + log1pf(expf(-z)) : log1pf(expf(z));
 }
 
+// d in (16, 32] binary -- the cfg-1 shape -- takes a leaner body: 8 rows per lane group, the partial
+// dot products are transpose-reduced so that each of the 8 lanes evaluates the sigmoid / log-loss of
+// ONE row (instead of all 8 lanes repeating it for every row), then the residuals go round the group
+// with 8 shuffles for the outer product.
+template <int V, int LANES, int NS>
+struct RefitShape {
+    static constexpr bool lean = V == 4 && LANES == 8 && NS == 1;
+    static constexpr int rows = lean ? 8 : kU;      // rows per lane group per iteration
+};
+
 template <int V, int LANES, int NS>
 __global__ void __launch_bounds__(kThreads)
 refit_kernel(const RefitArgs a) {
     constexpr int G = 32 / LANES;
-    constexpr int ROWS_PER_ITER = G * kU;
+    constexpr bool LEAN = RefitShape<V, LANES, NS>::lean;
+    constexpr int ROWS_PER_ITER = G * RefitShape<V, LANES, NS>::rows;
     extern __shared__ float red[];                 // [kWarps][stride]
     __shared__ bool is_last;
 
@@ -85,6 +96,45 @@ refit_kernel(const RefitArgs a) {
     const int64_t n_tiles = (a.n_rows + ROWS_PER_ITER - 1) / ROWS_PER_ITER;
     for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += warps_total) {
         const int64_t base = tile * ROWS_PER_ITER;
+        if constexpr (LEAN) {
+            float4 x[8];
+            float acc[8][1];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                int64_t row = base + j * G + g;
+                row = row < a.n_rows ? row : a.n_rows - 1;
+                x[j] = ldg_stream4(a.X + row * a.ldx + kc);
+            }
+            const int64_t my_row = base + s * G + g;             // the row this lane will own
+            const bool mine = my_row < a.n_rows;
+            const float yy = mine ? (float)__ldg(a.y + my_row) : 0.0f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float t = x[j].x * w[0][0];
+                t = fmaf(x[j].y, w[0][1], t);
+                t = fmaf(x[j].z, w[0][2], t);
+                acc[j][0] = fmaf(x[j].w, w[0][3], t);
+            }
+            lane_reduce<4, 8, 1, 8>(acc, s);                      // acc[0][0] = full dot product of row s
+            const float z = acc[0][0] + bias[0];
+            const float e = expf(-fabsf(z));
+            const float big = __frcp_rn(1.0f + e);
+            const float pr = z > 0.0f ? big : e * big;
+            const float r = mine ? pr - yy : 0.0f;
+            if (mine) {
+                loss += log1pexp_f(z) - yy * z;
+                gb[0] += r;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float rj = __shfl_sync(0xffffffffu, r, (lane & ~7) | j);
+                gw[0][0] = fmaf(rj, x[j].x, gw[0][0]);
+                gw[0][1] = fmaf(rj, x[j].y, gw[0][1]);
+                gw[0][2] = fmaf(rj, x[j].z, gw[0][2]);
+                gw[0][3] = fmaf(rj, x[j].w, gw[0][3]);
+            }
+            continue;
+        }
         float x[kU][V];
         int yv[kU];
         bool live[kU];
@@ -151,6 +201,13 @@ refit_kernel(const RefitArgs a) {
         }
     }
 
+    if constexpr (LEAN) {   // loss and intercept gradient were accumulated per owning lane: fold the group
+#pragma unroll
+        for (int off = 4; off >= 1; off >>= 1) {
+            loss += __shfl_xor_sync(0xffffffffu, loss, off);
+            gb[0] += __shfl_xor_sync(0xffffffffu, gb[0], off);
+        }
+    }
     // ---- CTA reduction: lanes that own the same chunk (same s) across groups, then across warps ----
 #pragma unroll
     for (int off = 16; off >= LANES; off >>= 1) {
@@ -220,7 +277,7 @@ int launch_inst(RefitArgs a, int num_sms, size_t scratch_floats_cap, cudaStream_
     int occ = 0;
     LRS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
     if (occ < 1) occ = 1;
-    constexpr int rows_per_iter = (32 / LANES) * kU;
+    constexpr int rows_per_iter = (32 / LANES) * RefitShape<V, LANES, NS>::rows;
     const int64_t tiles = (a.n_rows + rows_per_iter - 1) / rows_per_iter;
     int64_t grid = (tiles + kWarps - 1) / kWarps;
     const int64_t cap = (int64_t)num_sms * occ;
