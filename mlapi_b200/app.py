@@ -61,6 +61,7 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
                 return pa.array
             state["pins"] = pins
         state["classes"] = list(clf.classes_) if clf is not None else list(classes)
+        state["bulk_fn"] = (engine_score_fns(clf)[0] if score_fns is None else score_fns[0])
         state["batcher"] = MicroBatcher(
             fns, n_features=4,
             max_batch=max_batch or int(os.environ.get("LR_MAX_BATCH", "4096")),
@@ -90,6 +91,35 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
         import pandas as pd
         df = pd.read_csv(StringIO(str(file, "utf-8")))
         return {"file": df.to_dict(orient="list"), "token": token}
+
+    @app.post("/files/predict")
+    async def predict_file(file: bytes = File(...), token: str = Form(...)):
+        """Bulk scoring of an uploaded CSV (the natural use of the reference's /files/ upload,
+        REF/main.py:29-39): columns sepal_length, sepal_width, petal_length, petal_width by name, or
+        the first four columns when there is no such header.  One device batch, not the micro-batcher."""
+        import numpy as np
+        import pandas as pd
+        df = pd.read_csv(StringIO(str(file, "utf-8")))
+        names = ["sepal_length", "sepal_width", "petal_length", "petal_width"]
+        if not set(names) <= set(df.columns):
+            df = pd.read_csv(StringIO(str(file, "utf-8")), header=None)
+            if df.shape[1] < 4:
+                raise ValueError(f"X has {df.shape[1]} features, but LogisticRegression is expecting 4 features as input.")
+            X = df.iloc[:, :4].to_numpy(dtype=np.float32)
+        else:
+            X = df[names].to_numpy(dtype=np.float32)
+        if not np.isfinite(X).all():
+            raise ValueError("Input X contains NaN or infinity.")
+        n = X.shape[0]
+        labels, probs = [], []
+        fn = state["bulk_fn"]
+        for lo in range(0, n, 1 << 20):
+            chunk = np.ascontiguousarray(X[lo:lo + (1 << 20)])
+            li, pi = fn(chunk, chunk.shape[0])
+            labels += [state["classes"][int(i)] for i in li[:chunk.shape[0]]]
+            probs += [float(v) for v in pi[:chunk.shape[0]]]
+        labels = [c.item() if hasattr(c, "item") else c for c in labels]
+        return {"rows": n, "predictions": labels, "probabilities": probs, "token": token}
 
     @app.get("/batcher_stats")
     async def batcher_stats():

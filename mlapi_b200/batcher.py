@@ -11,10 +11,9 @@ collective, natural load balance.
 from __future__ import annotations
 
 import asyncio
-import queue
 import threading
 import time
-from collections import Counter
+from collections import Counter, deque
 from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -31,8 +30,12 @@ class MicroBatcher:
         self.n_features = int(n_features)
         self.max_batch = int(max_batch)
         self.max_wait = float(max_wait_us) * 1e-6
-        self._q: "queue.SimpleQueue" = queue.SimpleQueue()
+        # one deque guarded by one condition variable: producers append and notify, each worker takes a
+        # batch under the lock (an item is either still queued or owned by exactly one worker)
+        self._dq: deque = deque()
+        self._cv = threading.Condition()
         self._stop = threading.Event()
+        self._stats_lock = threading.Lock()
         self.batch_sizes: Counter = Counter()
         self.requests = 0
         self._alloc = alloc or (lambda shape, dtype: np.empty(shape, dtype))
@@ -50,7 +53,7 @@ class MicroBatcher:
                              f"{self.n_features} features as input.")
         loop = asyncio.get_running_loop()
         fut = loop.create_future()
-        self._q.put((row, fut, loop))
+        self._put((row, fut, loop))
         return await fut
 
     def submit_blocking(self, row: Sequence[float], timeout: float = 30.0) -> Tuple[int, float]:
@@ -70,31 +73,47 @@ class MicroBatcher:
             def done(self):
                 return done.is_set()
 
-        self._q.put((row, _Fut(), None))
+        self._put((row, _Fut(), None))
         if not done.wait(timeout):
             raise TimeoutError("micro-batcher did not answer")
         if "e" in box:
             raise box["e"]
         return box["v"]
 
+    def _put(self, item):
+        with self._cv:
+            self._dq.append(item)
+            self._cv.notify()
+
     # ---- consumer side (one thread per replica) ----------------------------------------------------
-    def _worker(self, score_fn: ScoreFn):
-        stage = self._alloc((self.max_batch, self.n_features), np.float32)
-        while not self._stop.is_set():
-            try:
-                first = self._q.get(timeout=0.05)
-            except queue.Empty:
-                continue
-            items = [first]
+    def _take_batch(self):
+        """Block for the first request, then keep collecting until the batch is full or its oldest
+        request has waited max_wait.  Returns [] when the batcher is closing."""
+        with self._cv:
+            while not self._dq:
+                if self._stop.is_set():
+                    return []
+                self._cv.wait(0.05)
+            items = [self._dq.popleft()]
             deadline = time.perf_counter() + self.max_wait
             while len(items) < self.max_batch:
+                if self._dq:
+                    items.append(self._dq.popleft())
+                    continue
                 remaining = deadline - time.perf_counter()
-                try:
-                    items.append(self._q.get_nowait() if remaining <= 0 else self._q.get(timeout=remaining))
-                except queue.Empty:
+                if remaining <= 0 or self._stop.is_set():
                     break
-                if remaining <= 0 and self._q.empty():
-                    break
+                self._cv.wait(remaining)
+            if self._dq:
+                self._cv.notify()            # more work is queued: wake another replica
+            return items
+
+    def _worker(self, score_fn: ScoreFn):
+        stage = self._alloc((self.max_batch, self.n_features), np.float32)
+        while True:
+            items = self._take_batch()
+            if not items:
+                return
             n = len(items)
             try:
                 for i, (row, _, _) in enumerate(items):
@@ -104,8 +123,9 @@ class MicroBatcher:
                 err = None
             except Exception as e:  # noqa: BLE001 - forwarded to every waiter
                 results, err = None, e
-            self.batch_sizes[n] += 1
-            self.requests += n
+            with self._stats_lock:
+                self.batch_sizes[n] += 1
+                self.requests += n
             self._resolve(items, results, err)
 
     @staticmethod
@@ -131,6 +151,8 @@ class MicroBatcher:
 
     def close(self):
         self._stop.set()
+        with self._cv:
+            self._cv.notify_all()
         for t in self._threads:
             t.join(timeout=2.0)
 

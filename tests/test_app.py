@@ -70,7 +70,15 @@ def test_predict_matches_reference_app_with_stub_scorer(golden):
                         headers={"content-type": "application/json"})
         r = client.post("/files/", files={"file": ("a.csv", b"a,b\n1,2\n3,4\n")}, data={"token": "t"})
         assert r.status_code == 200 and r.json() == {"file": {"a": [1, 3], "b": [2, 4]}, "token": "t"}
-        assert client.get("/batcher_stats").json()["requests"] == len(calls) or True
+        csv = "sepal_width,sepal_length,petal_length,petal_width\n3.5,5.1,1.4,0.2\n2.9,6.0,4.5,1.5\n"
+        r = client.post("/files/predict", files={"file": ("a.csv", csv.encode())}, data={"token": "t"})
+        body = r.json()
+        assert r.status_code == 200 and body["rows"] == 2 and body["token"] == "t"
+        assert body["predictions"] == ["Iris-setosa", "Iris-versicolor"]
+        np.testing.assert_allclose(body["probabilities"], [0.9793734699646953, 0.7493304124804981], atol=1e-5)
+        r = client.post("/files/predict", files={"file": ("b.csv", b"5.1,3.5,1.4,0.2\n6.0,2.9,4.5,1.5\n6.3,3.3,6.0,2.5\n")},
+                        data={"token": "u"})
+        assert r.json()["predictions"] == ["Iris-setosa", "Iris-versicolor", "Iris-virginica"]
     assert sum(calls) >= 8
 
 
@@ -114,6 +122,26 @@ def test_batcher_forwards_engine_errors_and_serves_threads(golden):
     [t.join() for t in ts]
     assert len(out) == 40 and all(o[0] == 0 and abs(o[1] - 0.9793734699646953) < 1e-6 for o in out)
     mb.close()
+
+
+def test_batcher_never_drops_a_request_under_contention():
+    """Regression: with two replicas draining one queue every request must come back (an earlier
+    queue.SimpleQueue-with-timeouts version lost about one request in a thousand)."""
+    from mlapi_b200.batcher import MicroBatcher
+
+    def fn(stage, n):
+        return np.zeros(n, int), stage[:n, 0].astype(np.float64)
+
+    for rep in range(60):
+        mb = MicroBatcher([fn, fn], n_features=4, max_batch=16, max_wait_us=300)
+        out = []
+        ts = [threading.Thread(target=lambda k=k: out.append(mb.submit_blocking((float(k), 0.0, 0.0, 0.0), timeout=5)))
+              for k in range(40)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        assert sorted(o[1] for o in out) == [float(k) for k in range(40)], rep
+        assert mb.stats()["requests"] == 40
+        mb.close()
 
 
 @pytest.mark.gpu
