@@ -59,3 +59,26 @@ def test_two_rank_refit_matches_single_rank():
     np.testing.assert_array_equal(results[0][1], results[1][1])          # identical steps on both ranks
     np.testing.assert_allclose(results[0][1], single.coef_, atol=2e-3)
     np.testing.assert_allclose(results[0][2], single.intercept_, atol=2e-3)
+
+
+def test_estimator_shards_host_batches_across_two_gpus():
+    """`devices=[0, 1]`: contiguous row blocks, one replica and one host thread per GPU, no collective;
+    the reassembled result is bit-identical to the single-GPU one."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import __graft_entry__
+    __graft_entry__.build()
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import synth
+    from mlapi_b200 import B200LogisticRegression
+    X, W, b = synth.make_config("cfg1_d32_binary", 300_001)
+    one = B200LogisticRegression(W, b, [0, 1], devices=[0])
+    two = B200LogisticRegression(W, b, [0, 1], devices=[0, 1])
+    a = one.score_rows(X, proba=True, label=True, decision=True, maxprob=True)
+    c = two.score_rows(X, proba=True, label=True, decision=True, maxprob=True)
+    for k in a:
+        assert np.array_equal(a[k], c[k]), k
+    one.close()
+    two.close()

@@ -46,7 +46,9 @@ def main():
     X = torch.empty((n, d), device=dev)
     for lo in range(0, n, 1 << 21):
         X[lo:lo + (1 << 21)].normal_()
-    w_true = torch.randn(d, device=dev) / d ** 0.5
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(7)                                    # the same generating model on every rank
+    w_true = torch.randn(d, device=dev, generator=gen) / d ** 0.5
     y = (torch.rand(n, device=dev) < torch.sigmoid(X @ w_true * 3 + 0.3)).int()
     W = torch.zeros((1, d), device=dev)
     b = torch.zeros((1,), device=dev)
