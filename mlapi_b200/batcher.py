@@ -176,12 +176,16 @@ def engine_score_fns(clf) -> List[ScoreFn]:
         def make(rep=rep):
             labels = None
             probs = None
+            pins = []
 
             def fn(stage: np.ndarray, n: int):
                 nonlocal labels, probs
                 if labels is None or labels.shape[0] < stage.shape[0]:
-                    labels = np.empty(stage.shape[0], np.int32)
-                    probs = np.empty(stage.shape[0], np.float32)
+                    # pinned outputs: request-sized batches are then scored in place (zero-copy path
+                    # of lr_score_host), larger ones get asynchronous D2H copies
+                    from .estimator import PinnedArray
+                    pins[:] = [PinnedArray((stage.shape[0],), np.int32), PinnedArray((stage.shape[0],), np.float32)]
+                    labels, probs = pins[0].array, pins[1].array
                 code = rep.lib.lr_score_host(rep.handle, stage.ctypes.data_as(C.c_void_p), n, stage.shape[1],
                                              None, None, labels.ctypes.data_as(C.c_void_p),
                                              probs.ctypes.data_as(C.c_void_p))

@@ -44,7 +44,9 @@ struct HostStage {
     int32_t* label[kSlots] = {};
     float* maxprob[kSlots] = {};
     cudaStream_t stream[kSlots] = {};
+    unsigned long long* status_host = nullptr;   // pinned landing pad for the status block
     void release() {
+        if (status_host) { cudaFreeHost(status_host); status_host = nullptr; }
         for (int i = 0; i < kSlots; ++i) {
             cudaFree(x[i]); cudaFree(proba[i]); cudaFree(decision[i]); cudaFree(label[i]); cudaFree(maxprob[i]);
             if (stream[i]) cudaStreamDestroy(stream[i]);
@@ -232,6 +234,17 @@ int lr_model_set_host_chunk_rows(lr_model* h, int64_t rows) {
     return LR_OK;
 }
 
+// True when `p` is page-locked host memory the device can address directly (cudaHostAlloc /
+// cudaHostRegister under unified addressing); `*dev_ptr` receives the device-side alias.
+static bool mapped_host(const void* p, void** dev_ptr) {
+    if (!p) { *dev_ptr = nullptr; return true; }
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (attr.type != cudaMemoryTypeHost || !attr.devicePointer) return false;
+    *dev_ptr = attr.devicePointer;
+    return true;
+}
+
 static int stage_prepare(Model& m, HostStage& st) {
     if (st.chunk_rows) return LR_OK;
     const int64_t pitch = ((int64_t)m.n_features + 3) / 4 * 4;
@@ -250,6 +263,7 @@ static int stage_prepare(Model& m, HostStage& st) {
         LRS_CUDA(cudaMalloc(&st.maxprob[i], rows * sizeof(float)));
         LRS_CUDA(cudaStreamCreateWithFlags(&st.stream[i], cudaStreamNonBlocking));
     }
+    LRS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&st.status_host), 4 * sizeof(unsigned long long), cudaHostAllocDefault));
     st.pitch = pitch;
     st.chunk_rows = rows;
     return LR_OK;
@@ -268,6 +282,31 @@ int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx,
     if ((rc = stage_prepare(*m, st)) != LR_OK) { st.release(); return rc; }
 
     const int64_t d = m->n_features;
+    // A request-sized batch in pinned buffers is scored in place over PCIe (zero-copy): one launch and
+    // one synchronise instead of an H2D copy, a launch and up to four D2H copies.  Worth it while the
+    // batch is a few KB (a micro-batch of /predict rows); bigger batches want HBM-resident staging.
+    if (n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
+        void *xd, *pd, *dd, *ld, *md;
+        if (mapped_host(X_host, &xd) && mapped_host(proba_host, &pd) && mapped_host(decision_host, &dd) &&
+            mapped_host(label_host, &ld) && mapped_host(maxprob_host, &md)) {
+            cudaStream_t s = st.stream[0];
+            ScoreArgs a{static_cast<const float*>(xd), n_rows, ldx, static_cast<float*>(pd), static_cast<float*>(dd),
+                        static_cast<int32_t*>(ld), static_cast<float*>(md), s};
+            unsigned long long* flag_host = st.status_host;      // pinned copy of the status block
+            if (select_path(*m, a) == LR_PATH_GEMM) goto staged; // TMA descriptors and re-scoring want device memory
+            if ((rc = dispatch(*m, a)) != LR_OK) { cudaDeviceSynchronize(); return rc; }
+            LRS_CUDA(cudaMemcpyAsync(flag_host, m->status, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+            LRS_CUDA(cudaStreamSynchronize(s));
+            gemm_feedback(*m, n_rows, flag_host[1]);
+            if (flag_host[0]) {
+                const unsigned long long bad = flag_host[0];
+                LRS_CUDA(cudaMemset(m->status, 0, sizeof(unsigned long long)));
+                return fail(LR_ERR_NONFINITE, std::to_string(bad) + " row(s) scored to NaN or infinity (non-finite input)");
+            }
+            return LR_OK;
+        }
+    }
+staged:
     int slot = 0;
     for (int64_t r0 = 0; r0 < n_rows; r0 += st.chunk_rows, slot = (slot + 1) % HostStage::kSlots) {
         const int64_t rows = (n_rows - r0 < st.chunk_rows) ? (n_rows - r0) : st.chunk_rows;

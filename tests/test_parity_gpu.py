@@ -266,6 +266,36 @@ def test_host_chunking_is_bit_identical(eng):
     px.free()
 
 
+def test_request_sized_pinned_batches_are_scored_in_place(eng, golden):
+    """lr_score_host with page-locked X and outputs of a few KB takes the zero-copy path; the results
+    must be the bits the staged path produces, for every narrow/wide/generic shape class."""
+    _, lib = eng
+    from mlapi_b200.estimator import PinnedArray
+    L = lib.load()
+    rng = np.random.default_rng(12)
+    for d, ns in ((4, 3), (32, 1), (2000, 1), (33, 20)):
+        W, b = synth.make_model(d, ns, 70 + d)
+        clf = _model(eng, W, b)
+        rep = clf._replicas[0]
+        for n in (1, 7, 8):
+            X = rng.standard_normal((n, d), dtype=np.float32)
+            ref = clf.score_rows(X, **ALL)                       # pageable arrays: staged path
+            px = PinnedArray((n, d)); px.array[...] = X
+            pp = PinnedArray((n, max(ns, 2))); pz = PinnedArray((n,) if ns == 1 else (n, ns))
+            pl = PinnedArray((n,), np.int32); pm = PinnedArray((n,))
+            before = L.lr_launch_count()
+            ptr = lambda a: a.array.ctypes.data_as(C.c_void_p)  # noqa: E731
+            assert L.lr_score_host(rep.handle, ptr(px), n, d, ptr(pp), ptr(pz), ptr(pl), ptr(pm)) == 0, lib.last_error()
+            assert L.lr_launch_count() == before + 1
+            for got, key in ((pp, "proba"), (pz, "decision"), (pl, "label"), (pm, "maxprob")):
+                assert np.array_equal(got.array, ref[key]), (d, ns, n, key)
+            px.array[0, 0] = np.nan
+            assert L.lr_score_host(rep.handle, ptr(px), n, d, ptr(pp), None, None, None) == lib.LR_ERR_NONFINITE
+            for a in (px, pp, pz, pl, pm):
+                a.free()
+        clf.close()
+
+
 def test_c_abi_direct_call(eng):
     """Straight ctypes, no wrapper: what INTEGRATION.md's stub does."""
     _, lib = eng
