@@ -107,7 +107,9 @@ int lr_model_take_rescored(lr_model* m, void* stream, uint64_t* n_rows_rescored)
  * chunks (H2D copy, kernel, D2H copy overlapped on three streams) and the call returns when every
  * output is in host memory.  This is the call the estimator wrapper and the /predict micro-batcher
  * make, and the one bench.py's `e2e` figure times.  Returns LR_ERR_NONFINITE (outputs still
- * written) when a row scored to NaN/inf.
+ * written) when a row scored to NaN/inf.  A batch of a few KB whose X and outputs all live in
+ * page-locked memory (lr_host_alloc / lr_host_register) is scored in place over PCIe instead: one
+ * launch, no copies (not on the tensor-core path).
  */
 int lr_score_host(lr_model* m, const float* X_host, int64_t n_rows, int64_t ldx,
                   float* proba_host, float* decision_host, int32_t* label_host,
