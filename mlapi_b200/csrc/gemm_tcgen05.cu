@@ -98,7 +98,8 @@ struct GemmParams {
     unsigned long long* status;
     unsigned char* flags;   // [n_rows] set for rows to re-score in fp32 (near-ties, risky probabilities)
     float* lse;             // [n_rows] log-sum-exp of the row as the tensor path saw it (for the re-scoring pass)
-    int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned)
+    int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned);
+                            // 2: 32-byte aligned as well (C % 8 == 0): 256-bit stores, whole sectors per lane
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -230,6 +231,12 @@ __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ void st_cluster_v2(uint32_t addr, float a, float b) {
     asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+// 256-bit streaming store (sm_100): one full 32-byte sector per lane and instruction
+__device__ __forceinline__ void st_cs_v8(float* p, const float* v) {
+    asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+                 "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
 }
 __device__ __forceinline__ float ex2(float x) {
     float y;
@@ -817,7 +824,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     }
                     if (live) {
                         const int64_t off = row * p.n_classes + col0 + cb;
-                        if (cb + 32 <= n_real && p.vec_store) {
+                        if (cb + 32 <= n_real && p.vec_store == 2) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, v + i);
+                        } else if (cb + 32 <= n_real && p.vec_store) {
 #pragma unroll
                             for (int i = 0; i < 32; i += 4)
                                 __stcs(reinterpret_cast<float4*>(p.proba + off + i),
@@ -1333,7 +1343,8 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.status = m.status;
     const bool al = (m.n_scores % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) &&
                     ((reinterpret_cast<uintptr_t>(a.decision) & 15u) == 0);
-    p.vec_store = al ? 1 : 0;
+    const bool al32 = al && (m.n_scores % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 31u) == 0);
+    p.vec_store = al32 ? 2 : (al ? 1 : 0);
 
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
     cudaLaunchConfig_t cfg = {};
