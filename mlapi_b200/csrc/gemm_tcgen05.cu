@@ -89,6 +89,7 @@ struct GemmParams {
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
     const float* col_inv_scale;   // FP16 mode: 1 / class scale, padded like bias
     const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
+    int mma_n;              // N of one MMA = rows of one W tile: 256, or the class count rounded up to 16 when that is less (unpaired)
     int debug_skip;         // profiling only: bit0 = converters skip their work, bit1 = epilogue skips passes
     int count_nonfinite;    // 1: the epilogue counts non-finite rows itself (no re-scoring pass to do it)
     float* proba;
@@ -195,7 +196,7 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t a_desc, uin
         : "memory");
 }
 template <bool F16>
-__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate);
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate);
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     uint32_t r[32];
     asm volatile(
@@ -290,9 +291,9 @@ constexpr uint32_t kIdesc = (1u << 4)      // D = f32
 constexpr uint32_t kIdesc16 = (1u << 4)    // D = f32, A = B = f16 (format 0), K-major
                               | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 template <>
-__device__ __forceinline__ void tc_mma<false>(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { tc_mma_tf32(d, a, b, kIdesc, acc); }
+__device__ __forceinline__ void tc_mma<false>(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { tc_mma_tf32(d, a, b, idesc, acc); }
 template <>
-__device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) { tc_mma_f16(d, a, b, kIdesc16, acc); }
+__device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { tc_mma_f16(d, a, b, idesc, acc); }
 
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -329,10 +330,11 @@ __device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t a_desc, uin
                      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
                      : "memory");
 }
+// `idesc` (unpaired form only): instruction descriptor with the model's N, see GemmParams::mma_n
 template <bool F16, bool PAIR>
-__device__ __forceinline__ void mma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) {
+__device__ __forceinline__ void mma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
     if constexpr (PAIR) tc_mma_2sm<F16>(d, a, b, acc);
-    else tc_mma<F16>(d, a, b, acc);
+    else tc_mma<F16>(d, a, b, idesc, acc);
 }
 
 // F16 = false: 3xTF32 (operands are fp32 containers, 8 K-elements per MMA).
@@ -395,7 +397,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint16_t w_mask = 0;
     for (int j = 0; j < p.nrt; ++j) w_mask |= (uint16_t)(1u << (rank + j * p.ncc));
     const int x_rows = x_mc ? BM / p.ncc : BM;      // rows of the X tile this CTA fetches
-    const int w_rows = PAIR ? BN / 2 : BN / p.nrt;  // rows of each W tile this CTA fetches
+    const int w_rows = PAIR ? BN / 2 : p.mma_n / p.nrt;  // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_STAGES; ++i) {
@@ -464,7 +466,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                                             col0 + nbk * BN + (int)rt * w_rows,
                                             map_to_cta(smem_u32(b_full + bs), lead_rank));
                         } else if (leader) {
-                            mbar_expect_tx(b_full + bs, B_TILE_BYTES);
+                            mbar_expect_tx(b_full + bs, PAIR ? B_TILE_BYTES : p.mma_n * 128);
                             if (w_mc)
                                 tma_load_2d_mc(b_t + bs * B_TILE_BYTES + rt * w_rows * 128,
                                                part == 0 ? &map_whi : &map_wlo, kc * BKx,
@@ -516,6 +518,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const uint64_t b0 = desc0 | (uint64_t)((smem_u32(b_t) & 0x3FFFF) >> 4);
         const uint32_t c_off = p.split ? (uint32_t)BN : 0u;          // split: corrections -> columns 256..511
         const uint32_t corr_first = p.split ? 0u : 1u;               // accumulate flag of the first correction MMA
+        // N of the instruction = the model's class count rounded up to 16 when one W tile holds them all
+        const uint32_t idesc = ((F16 ? kIdesc16 : kIdesc) & ~(0x3Fu << 17)) | ((uint32_t)(p.mma_n >> 3) << 17);
         int as = 0, bs = 0;
         uint32_t aph = 0, bph = 0, accph = 0;
         for (int64_t grp = cluster_id; lead && grp < n_groups; grp += n_clusters) {
@@ -538,17 +542,17 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (leader) {
                             if (part == 0) {
                                 // x_hi.w_hi into the main accumulator, x_lo.w_hi into the correction one
-                                mma_issue<F16, PAIR>(d_tmem, ahi, bd, first);
+                                mma_issue<F16, PAIR>(d_tmem, ahi, bd, idesc, first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
-                                    mma_issue<F16, PAIR>(d_tmem, ahi + 2 * k, bd + 2 * k, 1u);
-                                mma_issue<F16, PAIR>(c_tmem, alo, bd, first | corr_first);
+                                    mma_issue<F16, PAIR>(d_tmem, ahi + 2 * k, bd + 2 * k, idesc, 1u);
+                                mma_issue<F16, PAIR>(c_tmem, alo, bd, idesc, first | corr_first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)
-                                    mma_issue<F16, PAIR>(c_tmem, alo + 2 * k, bd + 2 * k, 1u);
+                                    mma_issue<F16, PAIR>(c_tmem, alo + 2 * k, bd + 2 * k, idesc, 1u);
                             } else {
 #pragma unroll
-                                for (int k = 0; k < BK / 8; ++k) mma_issue<F16, PAIR>(c_tmem, ahi + 2 * k, bd + 2 * k, 1u);
+                                for (int k = 0; k < BK / 8; ++k) mma_issue<F16, PAIR>(c_tmem, ahi + 2 * k, bd + 2 * k, idesc, 1u);
                             }
                             if constexpr (PAIR) tc_commit_2sm(b_empty + bs, pair_mask);
                             else if (w_mc) tc_commit_mc(b_empty + bs, w_mask);
@@ -1057,6 +1061,7 @@ struct GemmPlan {
     // one when the re-scoring pass reports that the data is confident (lr_score_host feeds that back).
     struct Layout {
         int nb = 0, ncc = 0, nrt = 1;
+        int mma_n = BN;             // see GemmParams::mma_n
         bool pair = false;          // cta_group::2: cluster = 2 * ncc CTAs
         bool split = false;
         int max_clusters[64] = {0};
@@ -1166,6 +1171,10 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         L.pair = pair && (L.ncc * 2 <= 4 || (force_pair && L.ncc * 2 <= 8));
         L.nrt = (!L.pair && force_mc && L.ncc * 2 <= 8) ? 2 : 1;
     }
+    // A model whose classes fit one W tile multiplies by exactly that many columns (in whole 32-column
+    // epilogue chunks) instead of a zero-padded 256: the tensor time of a 32-class model drops 8x.
+    if (acc.ncc == 1 && !acc.pair && acc.nrt == 1) acc.mma_n = (C + 31) / 32 * 32;
+    if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -1198,7 +1207,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     for (int i = 0; i < 2; ++i) {
         if (!g->has[i]) continue;
         auto& L = g->layout[i];
-        const int wbox = L.pair ? BN / 2 : BN / L.nrt;
+        const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
         if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d, wbox)) != LR_OK) return rc;
         if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d, wbox)) != LR_OK) return rc;
     }
@@ -1237,7 +1246,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         for (int i = 0; i < 2; ++i) {
             if (!g->has[i]) continue;
             auto& L = g->layout[i];
-            const int wbox = L.pair ? BN / 2 : BN / L.nrt;
+            const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
             if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
             if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
         }
@@ -1329,6 +1338,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.split = L.split ? 1 : 0;
     p.ncc = L.ncc;
     p.nrt = L.nrt;
+    p.mma_n = L.mma_n;
     p.num_k_chunks = f16 ? (m.n_features + BK16 - 1) / BK16 : (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;

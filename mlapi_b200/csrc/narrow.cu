@@ -19,6 +19,9 @@
 // label / maxprob / decision column); W and b are read once per CTA and excluded.
 #include <cmath>
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "common.cuh"
 
@@ -27,6 +30,13 @@ namespace lrs {
 namespace {
 
 constexpr int kThreads = 256;
+constexpr size_t kWSmemMax = 96 * 1024;    // W staged in shared memory up to here
+constexpr size_t kWL1Max = 192 * 1024;     // 5..16 columns: beyond shared memory, W is read through L1
+
+// Score columns the kernels are instantiated for (padding columns carry zero weights and a -inf intercept).
+inline int padded_scores(int c) {
+    return c == 1 ? 1 : c <= 3 ? 3 : c <= 4 ? 4 : c <= 6 ? 6 : c <= 8 ? 8 : c <= 10 ? 10 : c <= 12 ? 12 : 16;
+}
 
 template <int V>
 struct Vec;
@@ -219,6 +229,144 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
     }
 }
 
+// ---- 5..16 score columns -------------------------------------------------------------------------
+// With more than four classes the kernel above runs out of shared-memory bandwidth: every 128-bit
+// piece of W it reads feeds four FMAs of ONE row (measured on B200: C=10, d=784 at 1.4 TB/s).  Here a
+// thread keeps U = 4 rows x NS classes of accumulators, so a piece of W feeds 16 FMAs, and the X
+// pieces of the next k-step are requested before the FMAs of the current one (8 loads of 16 B in
+// flight per thread at <= 128 registers).  NS is the exact padded class count (6, 8, 10, 12, 16):
+// at C=10 the kernel needs 31 of the ~70 fp32 TFLOP/s to keep up with HBM, at 16 it would need 51.
+// W comes from shared memory while it fits 96 KB, else through L1 (`__ldg`; X bypasses L1).
+// fp32 FMA arithmetic throughout, same as the kernel above.
+template <int V, int LANES, int NS, bool WSMEM>
+__global__ void __launch_bounds__(kThreads, 2)
+mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad,
+           const float* __restrict__ Wn, const float* __restrict__ bn, Outs o) {
+    constexpr int U = 4;
+    constexpr int G = 32 / LANES;
+    constexpr int M = (U < LANES) ? U : LANES;
+    constexpr int ROWS_OWNED = U / M;
+    constexpr int ROWS_PER_ITER = G * U;
+    constexpr int STEP = LANES * V;
+
+    extern __shared__ __align__(16) float w_s[];  // [NS][dpad] when WSMEM
+    if constexpr (WSMEM) {
+        for (int i = threadIdx.x; i < NS * dpad; i += kThreads) w_s[i] = Wn[i];
+        __syncthreads();
+    }
+    const float* __restrict__ wsrc = WSMEM ? w_s : Wn;
+
+    const int lane = threadIdx.x & 31;
+    const int g = lane / LANES;
+    const int s = lane % LANES;
+    const int k0 = s * V;
+    const int dloop = (d + STEP - 1) / STEP * STEP;   // <= dpad; W is zero beyond d
+
+    const int64_t warps_total = (int64_t)gridDim.x * (kThreads / 32);
+    const int64_t warp_id = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    const int64_t n_tiles = (n_rows + ROWS_PER_ITER - 1) / ROWS_PER_ITER;
+
+    for (int64_t tile = warp_id; tile < n_tiles; tile += warps_total) {
+        const int64_t base = tile * ROWS_PER_ITER;
+        const float* rowp[U];
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+            int64_t row = base + j * G + g;
+            row = row < n_rows ? row : n_rows - 1;     // clamped rows are computed and never stored
+            rowp[j] = X + row * ldx;
+        }
+        float acc[U][NS];
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+#pragma unroll
+            for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
+
+        // One k-step: every class's piece of W against the four rows' pieces of X.
+        auto fma_step = [&](const Vec<V> (&xv)[U], int k) {
+#pragma unroll
+            for (int c = 0; c < NS; ++c) {
+                float w[V];
+                if constexpr (V == 4) {
+                    float4 t;
+                    if constexpr (WSMEM) t = *reinterpret_cast<const float4*>(wsrc + c * dpad + k);
+                    else t = __ldg(reinterpret_cast<const float4*>(wsrc + c * dpad + k));
+                    w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
+                } else {
+                    w[0] = WSMEM ? wsrc[c * dpad + k] : __ldg(wsrc + c * dpad + k);
+                }
+#pragma unroll
+                for (int j = 0; j < U; ++j)
+#pragma unroll
+                    for (int v = 0; v < V; ++v) acc[j][c] = fmaf(xv[j].v[v], w[v], acc[j][c]);
+            }
+        };
+        // Software pipeline of depth one over the k-steps: the loads of step i+1 sit in the same basic
+        // block as the FMAs of step i and ahead of them (a conditional prefetch was sunk below the
+        // FMAs by the compiler, which left nothing in flight while they ran).  Every load is a real
+        // piece of the row (or column 0 against zero weights past d), none is issued twice.
+        // (Above 10 classes two X buffers no longer fit 128 registers next to 4 x NS accumulators:
+        // those run one step at a time and rely on the other warps for overlap.)
+        if constexpr (NS <= 10) {
+            Vec<V> xa[U], xb[U];
+            {
+                const int kc = k0 < d ? k0 : 0;        // past-the-end pieces meet zero weights
+#pragma unroll
+                for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
+            }
+            int k = k0;
+            for (; k + 2 * STEP < dloop; k += 2 * STEP) {
+                {
+                    const int kn = k + STEP, kc = kn < d ? kn : 0;
+#pragma unroll
+                    for (int j = 0; j < U; ++j) xb[j].load(rowp[j] + kc);
+                }
+                fma_step(xa, k);
+                {
+                    const int kn = k + 2 * STEP, kc = kn < d ? kn : 0;
+#pragma unroll
+                    for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
+                }
+                fma_step(xb, k + STEP);
+            }
+            if (k + STEP < dloop) {                    // two steps left (same for the whole warp)
+                const int kn = k + STEP, kc = kn < d ? kn : 0;
+#pragma unroll
+                for (int j = 0; j < U; ++j) xb[j].load(rowp[j] + kc);
+                fma_step(xa, k);
+                fma_step(xb, kn);
+            } else {
+                fma_step(xa, k);
+            }
+        } else {
+            for (int k = k0; k < dloop; k += STEP) {
+                Vec<V> xa[U];
+                const int kc = k < d ? k : 0;
+#pragma unroll
+                for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
+                fma_step(xa, k);
+            }
+        }
+
+        lane_reduce<LANES / 2, U, NS, U>(acc, s);
+
+        const int sel = s / (LANES / M);
+        const bool owner = (s % (LANES / M)) == 0;
+        if (owner) {
+#pragma unroll
+            for (int r = 0; r < ROWS_OWNED; ++r) {
+                const int u = sel * ROWS_OWNED + r;
+                const int64_t row = base + u * G + g;
+                if (row < n_rows) {
+                    float z[NS];
+#pragma unroll
+                    for (int c = 0; c < NS; ++c) z[c] = acc[r][c] + __ldg(bn + c);
+                    finish_row<NS>(z, row, o);
+                }
+            }
+        }
+    }
+}
+
 // ---- bulk-copy ring variant ------------------------------------------------------------------------
 // Same arithmetic as narrow_kernel<4, LANES, NS, U, true>, but X reaches the SM through the TMA
 // engine: one producer lane streams contiguous row tiles (kConsumerWarps * G * U rows) into a ring of
@@ -339,27 +487,47 @@ narrow_bulk_kernel(const float* __restrict__ X, int64_t n_rows, int d, int dpad,
     }
 }
 
+// Resident CTAs per SM of one kernel instantiation for a given dynamic shared-memory size.  The size
+// depends on the model (its padded W), not on the instantiation, so the answer is cached per kernel,
+// device and size; the opt-in above 48 KB is made once per kernel and device.  (Keyed by the kernel's
+// address: every instantiation has the same function-pointer type.)
+template <typename K>
+int resident_blocks(K kern, int dev, size_t smem, int* occ_out) {
+    struct Slot { bool opted = false; size_t smem = ~size_t(0); int occ = 0; };
+    static std::map<std::pair<const void*, int>, Slot> slots;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    Slot& sl = slots[{reinterpret_cast<const void*>(kern), dev}];
+    if (!sl.opted) {
+        LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemMax));
+        sl.opted = true;
+    }
+    if (sl.smem != smem) {
+        int occ = 0;
+        LRS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
+        sl.occ = occ > 0 ? occ : 1;
+        sl.smem = smem;
+    }
+    *occ_out = sl.occ;
+    return LR_OK;
+}
+
 template <int NS>
-constexpr int unroll_for() { return NS == 1 ? 8 : (NS <= 4 ? 4 : (NS <= 8 ? 2 : 1)); }
+constexpr int unroll_for() { return NS == 1 ? 8 : 4; }
 
 template <int V, int LANES, int NS, bool SINGLE>
 int launch_inst(const Model& m, const ScoreArgs& a) {
     constexpr int U = unroll_for<NS>();
     auto kern = narrow_kernel<V, LANES, NS, U, SINGLE>;
     const size_t smem = SINGLE ? 0 : (size_t)NS * m.narrow_dpad * sizeof(float);
-    static int blocks_per_sm[64] = {0};   // per device, per instantiation
     int dev = m.device & 63;
-    if (blocks_per_sm[dev] == 0) {
-        if (smem > 48 * 1024)
-            LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        int occ = 0;
-        LRS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
-        blocks_per_sm[dev] = occ > 0 ? occ : 1;
-    }
+    int occ = 0;
+    int rc = resident_blocks(kern, dev, smem, &occ);
+    if (rc != LR_OK) return rc;
     constexpr int rows_per_iter = (32 / LANES) * U;
     const int64_t tiles = (a.n_rows + rows_per_iter - 1) / rows_per_iter;
     const int64_t need = (tiles + (kThreads / 32) - 1) / (kThreads / 32);
-    const int64_t cap = (int64_t)m.num_sms * blocks_per_sm[dev];
+    const int64_t cap = (int64_t)m.num_sms * occ;
     const int grid = (int)(need < cap ? need : cap);
     Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
     kern<<<grid, kThreads, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad,
@@ -383,14 +551,65 @@ int launch_lanes(const Model& m, const ScoreArgs& a, bool single) {
         case 1: return launch_ns<V, LANES, 1>(m, a, single);
         case 3: return launch_ns<V, LANES, 3>(m, a, single);
         case 4: return launch_ns<V, LANES, 4>(m, a, single);
-        case 8: return launch_ns<V, LANES, 8>(m, a, single);
-        case 16: return launch_ns<V, LANES, 16>(m, a, single);
     }
     return fail(LR_ERR_INVALID, "narrow path: unsupported score count");
 }
 
+template <int V, int LANES, int NS, bool WSMEM>
+int launch_mid_inst(const Model& m, const ScoreArgs& a) {
+    auto kern = mid_kernel<V, LANES, NS, WSMEM>;
+    const size_t smem = WSMEM ? (size_t)NS * m.narrow_dpad * sizeof(float) : 0;
+    const int dev = m.device & 63;
+    int occ = 0;
+    const int rc = resident_blocks(kern, dev, smem, &occ);
+    if (rc != LR_OK) return rc;
+    constexpr int rows_per_iter = (32 / LANES) * 4;
+    const int64_t tiles = (a.n_rows + rows_per_iter - 1) / rows_per_iter;
+    const int64_t need = (tiles + (kThreads / 32) - 1) / (kThreads / 32);
+    const int64_t cap = (int64_t)m.num_sms * occ;
+    const int grid = (int)(need < cap ? need : cap);
+    Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
+    kern<<<grid, kThreads, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad, m.Wn, m.bn, o);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
+// Lanes per row for the 5..16-class kernel: few enough that every lane sweeps several pieces of the
+// row (the cross-lane reduction of 4 x NS sums is paid once per row group), 32 for long rows.
+template <int V, int LANES, int NS>
+int launch_mid_w(const Model& m, const ScoreArgs& a) {
+    const bool wsmem = (size_t)NS * m.narrow_dpad * sizeof(float) <= kWSmemMax;
+    return wsmem ? launch_mid_inst<V, LANES, NS, true>(m, a) : launch_mid_inst<V, LANES, NS, false>(m, a);
+}
+
+// Lanes per row for the 5..16-class kernel.  Fewer lanes = more rows per warp instruction, and lanes
+// of different rows read the same piece of W (one shared-memory wavefront instead of four at 32
+// lanes: with 32 the W reads cost as many cycles as the FMAs they feed); more lanes = longer
+// contiguous pieces of each row per request.  LRS_MID_LANES overrides (tuning).
+template <int V, int NS>
+int launch_mid(const Model& m, const ScoreArgs& a) {
+    const int chunks = (m.n_features + V - 1) / V;
+    int lanes = chunks <= 64 ? 4 : 8;              // measured (tools/gpu_mid.sh): 4 wins up to d=256, 8 from there to d=4096
+    static const int forced = [] { const char* e = getenv("LRS_MID_LANES"); return e ? atoi(e) : 0; }();
+    if (forced) lanes = forced;
+    switch (lanes) {
+        case 4: return launch_mid_w<V, 4, NS>(m, a);
+        case 8: return launch_mid_w<V, 8, NS>(m, a);
+        case 16: return launch_mid_w<V, 16, NS>(m, a);
+        default: return launch_mid_w<V, 32, NS>(m, a);
+    }
+}
+
 template <int V>
 int launch_v(const Model& m, const ScoreArgs& a) {
+    switch (m.narrow_ns) {
+        case 6: return launch_mid<V, 6>(m, a);
+        case 8: return launch_mid<V, 8>(m, a);
+        case 10: return launch_mid<V, 10>(m, a);
+        case 12: return launch_mid<V, 12>(m, a);
+        case 16: return launch_mid<V, 16>(m, a);
+    }
     int chunks = (m.n_features + V - 1) / V;
     int lanes = 1;
     while (lanes < chunks && lanes < 32) lanes <<= 1;
@@ -459,17 +678,19 @@ int launch_bulk(const Model& m, const ScoreArgs& a) {
 
 }  // namespace
 
-// Shapes the narrow path serves: <= 16 score columns and a padded W of at most 96 KB.
+// Shapes the narrow path serves: <= 16 score columns and a padded W that fits shared memory (<= 4
+// columns) or L1 (5..16 columns).
 bool narrow_supports(const Model& m) {
     if (m.n_scores > 16) return false;
-    int ns = m.n_scores == 1 ? 1 : (m.n_scores <= 3 ? 3 : (m.n_scores <= 4 ? 4 : (m.n_scores <= 8 ? 8 : 16)));
-    int dpad = (m.n_features + 127) / 128 * 128;
-    return (size_t)ns * dpad * sizeof(float) <= 96 * 1024 && m.n_features <= 4096;
+    const int ns = padded_scores(m.n_scores);
+    const int dpad = (m.n_features + 127) / 128 * 128;
+    const size_t bytes = (size_t)ns * dpad * sizeof(float);
+    return ns <= 4 ? (bytes <= kWSmemMax && m.n_features <= 4096) : bytes <= kWL1Max;
 }
 
 int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
     if (!narrow_supports(m)) return LR_OK;
-    const int ns = m.n_scores == 1 ? 1 : (m.n_scores <= 3 ? 3 : (m.n_scores <= 4 ? 4 : (m.n_scores <= 8 ? 8 : 16)));
+    const int ns = padded_scores(m.n_scores);
     // dpad covers whole lane-chunk sweeps for both V=4 and V=1 mappings (a multiple of 32*4).
     const int dpad = (m.n_features + 127) / 128 * 128;
     std::string w((size_t)ns * dpad * sizeof(float), '\0');

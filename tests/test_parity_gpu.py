@@ -137,6 +137,23 @@ def test_narrow_class_buckets(eng, ns):
         _check(clf, X, W, b, f"narrow ns={ns} d={d}")
 
 
+@pytest.mark.parametrize("ns", list(range(5, 17)))
+def test_mid_class_counts(eng, ns):
+    """5..16 classes: the 4-rows-by-NS register-tile kernel.  d picks the lanes-per-row variant
+    (<= 64: 4 lanes, <= 256: 8, above: 32), 4-aligned and not; d=2600 pushes W past the 96 KB that
+    fit shared memory for the larger ns (W then comes through L1)."""
+    _, lib = eng
+    rng = np.random.default_rng(ns * 101)
+    for d in (8, 61, 64, 200, 256, 784, 1023, 2600):
+        W, b = synth.make_model(d, ns, 900 + ns + d)
+        clf = _model(eng, W, b)
+        clf.set_path(lib.PATH_NARROW)
+        for n in (1, 3, 130, 2051):
+            X = rng.standard_normal((n, d), dtype=np.float32)
+            _check(clf, X, W, b, f"mid ns={ns} d={d} n={n}")
+        clf.close()
+
+
 @pytest.mark.parametrize("d", [4, 5, 1000, 1024, 4097, 10_000, 100_000])
 def test_wide_shapes(eng, d):
     _, lib = eng
