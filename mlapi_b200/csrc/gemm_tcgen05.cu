@@ -31,6 +31,7 @@
 #include <cuda_fp16.h>
 
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -50,6 +51,8 @@ constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB: one operand tile of X (h
 constexpr int kThreads = 480;                 // 15 warps: TMA (W), MMA, 4 converters, 8 epilogue, TMA (X)
 constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
+constexpr int kMaxAStages = 6;          // X ring depth the barrier block has room for
+constexpr int kMaxBStages = 16;         // W ring depth, likewise
 
 // Shared-memory plan.  PAIR = the CTA is half of a cta_group::2 pair: it holds half of every W tile
 // (the MMA reads the other half from the peer's shared memory), which halves the shared-memory read
@@ -69,7 +72,7 @@ struct SmemLayoutT {
     static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
     static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
     static constexpr int bars = glob + BM * 8;                       // mbarriers
-    static constexpr int n_bars = 3 * a_stages + 2 * b_stages + 2 + 4;
+    static constexpr int n_bars = 3 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
 };
@@ -89,6 +92,11 @@ struct GemmParams {
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
     const float* col_inv_scale;   // FP16 mode: 1 / class scale, padded like bias
     const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
+    int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
+    int b_tile_bytes;       // ... bytes reserved per W stage ...
+    int b_stages;           // ... and W ring depth: a_stages * 32 KB + b_stages * b_tile_bytes <= 192 KB
+    int acc_bufs;           // 2: N <= 128, two accumulator buffers 128 TMEM columns apart -- the epilogue of a tile
+                            // overlaps the MMAs of the next; 1 otherwise
     int mma_n;              // N of one MMA = rows of one W tile: 256, or the class count rounded up to 16 when that is less (unpaired)
     int debug_skip;         // profiling only: bit0 = converters skip their work, bit1 = epilogue skips passes
     int count_nonfinite;    // 1: the epilogue counts non-finite rows itself (no re-scoring pass to do it)
@@ -346,15 +354,19 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                     const __grid_constant__ CUtensorMap map_wlo, const GemmParams p) {
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+    // 1024-byte alignment by pointer arithmetic on the shared array itself: going through uintptr_t made
+    // every access below a generic LD/ST instead of LDS/STS
+    unsigned char* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
 
     using SmemLayout = SmemLayoutT<PAIR>;
-    constexpr int A_STAGES = SmemLayout::a_stages;
-    constexpr int B_STAGES = SmemLayout::b_stages;
-    constexpr int B_TILE_BYTES = SmemLayout::b_tile;
+    // Unpaired: a model with few classes has small W tiles and trades their room for a deeper X ring
+    // (GemmParams::a_stages / b_tile_bytes; same 192 KB in total).  Paired: the fixed plan.
+    const int A_STAGES = PAIR ? SmemLayout::a_stages : p.a_stages;
+    const int B_STAGES = PAIR ? SmemLayout::b_stages : p.b_stages;
+    const int B_TILE_BYTES = PAIR ? SmemLayout::b_tile : p.b_tile_bytes;
     unsigned char* a_hi = smem + SmemLayout::a_hi;
-    unsigned char* a_lo = smem + SmemLayout::a_lo;
-    unsigned char* b_t = smem + SmemLayout::b;
+    unsigned char* a_lo = a_hi + A_STAGES * A_TILE_BYTES;
+    unsigned char* b_t = a_lo + A_STAGES * A_TILE_BYTES;
     constexpr int BKx = F16 ? BK16 : BK;                 // K-elements per chunk
     constexpr int RAW_BYTES = BM * BKx * 4;              // raw fp32 X tile: 16 KB (TF32) / 32 KB (FP16)
     constexpr int A_STAGE = 2 * A_TILE_BYTES;            // FP16: one contiguous 32 KB stage (raw -> hi | lo in place)
@@ -365,13 +377,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     float2* glob = reinterpret_cast<float2*>(smem + SmemLayout::glob);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SmemLayout::bars);
     uint64_t* x_full = bars;                       // [A_STAGES] TMA -> converters
-    uint64_t* a_ready = x_full + A_STAGES;         // [A_STAGES] converters -> MMA
-    uint64_t* a_empty = a_ready + A_STAGES;        // [A_STAGES] MMA -> TMA
-    uint64_t* b_full = a_empty + A_STAGES;         // [B_STAGES] TMA -> MMA
-    uint64_t* b_empty = b_full + B_STAGES;         // [B_STAGES] MMA -> TMA
-    uint64_t* acc_full = b_empty + B_STAGES;       // MMA -> epilogue
-    uint64_t* acc_empty = acc_full + 1;            // epilogue -> MMA
-    uint64_t* xchg_bar = acc_empty + 1;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
+    uint64_t* a_ready = x_full + kMaxAStages;      // [A_STAGES] converters -> MMA
+    uint64_t* a_empty = a_ready + kMaxAStages;     // [A_STAGES] MMA -> TMA
+    uint64_t* b_full = a_empty + kMaxAStages;      // [B_STAGES] TMA -> MMA
+    uint64_t* b_empty = b_full + kMaxBStages;      // [B_STAGES] MMA -> TMA
+    uint64_t* acc_full = b_empty + kMaxBStages;       // [2 accumulator buffers] MMA -> epilogue
+    uint64_t* acc_empty = acc_full + 2;            // [2] epilogue -> MMA
+    uint64_t* xchg_bar = acc_empty + 2;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SmemLayout::tmem_slot);
 
     const int warp = threadIdx.x >> 5;
@@ -409,8 +421,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_init(b_full + i, 1);
             mbar_init(b_empty + i, w_mc ? p.nrt : 1);    // every CTA sharing the W tile has consumed the stage
         }
-        mbar_init(acc_full, 1);
-        mbar_init(acc_empty, PAIR ? 2 * kEpiThreads : kEpiThreads);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(acc_full + i, 1);
+            mbar_init(acc_empty + i, PAIR ? 2 * kEpiThreads : kEpiThreads);
+        }
         for (int i = 0; i < 4; ++i) mbar_init(xchg_bar + i, 128 * p.ncc);
         mbar_fence_init();
     }
@@ -521,9 +535,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // N of the instruction = the model's class count rounded up to 16 when one W tile holds them all
         const uint32_t idesc = ((F16 ? kIdesc16 : kIdesc) & ~(0x3Fu << 17)) | ((uint32_t)(p.mma_n >> 3) << 17);
         int as = 0, bs = 0;
-        uint32_t aph = 0, bph = 0, accph = 0;
-        for (int64_t grp = cluster_id; lead && grp < n_groups; grp += n_clusters) {
-            if constexpr (PAIR) mbar_wait_cluster(acc_empty, accph ^ 1); else mbar_wait(acc_empty, accph ^ 1);
+        uint32_t aph = 0, bph = 0, it = 0;
+        for (int64_t grp = cluster_id; lead && grp < n_groups; grp += n_clusters, ++it) {
+            const uint32_t buf = p.acc_bufs == 2 ? (it & 1u) : 0u;                  // accumulator buffer of this tile
+            const uint32_t accph = (p.acc_bufs == 2 ? (it >> 1) : it) & 1u;         // its use count, as a parity
+            if constexpr (PAIR) mbar_wait_cluster(acc_empty + buf, accph ^ 1); else mbar_wait(acc_empty + buf, accph ^ 1);
             tc_fence_after();
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 if constexpr (PAIR) mbar_wait_cluster(a_ready + as, aph); else mbar_wait(a_ready + as, aph);
@@ -537,7 +553,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         mbar_wait(b_full + bs, bph);
                         tc_fence_after();
                         const uint64_t bd = b0 + (uint64_t)(bs * (B_TILE_BYTES >> 4));
-                        const uint32_t d_tmem = tmem_base + (uint32_t)(nbk * BN);
+                        const uint32_t d_tmem = tmem_base + buf * 128u + (uint32_t)(nbk * BN);
                         const uint32_t c_tmem = d_tmem + c_off;
                         if (leader) {
                             if (part == 0) {
@@ -570,9 +586,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 __syncwarp();
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
-            if (leader) { if constexpr (PAIR) tc_commit_2sm(acc_full, pair_mask); else tc_commit(acc_full); }
+            if (leader) { if constexpr (PAIR) tc_commit_2sm(acc_full + buf, pair_mask); else tc_commit(acc_full + buf); }
             __syncwarp();
-            accph ^= 1;
         }
     } else if (warp < 6) {
         // ===================== converters: raw fp32 -> (hi, lo) TF32 pair =====================
@@ -650,21 +665,21 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int h = ew >> 2;                       // column half
         const int r_in_tile = q * 32 + lane;
-        const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t t_lane0 = tmem_base + ((uint32_t)(q * 32) << 16);
         int n_real = p.n_classes - col0;             // real (unpadded) classes held by this CTA
         n_real = n_real < 0 ? 0 : (n_real > n_cols_cta ? n_cols_cta : n_real);
         const int n_chunks = (n_real + 31) / 32;
         const int cb_lo = h == 0 ? 0 : ((n_chunks + 1) / 2) * 32;
         const int cb_hi = h == 0 ? ((n_chunks + 1) / 2) * 32 : n_chunks * 32;
-        uint32_t accph = 0;
         uint32_t it = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters, ++it) {
             const int64_t tile = grp * gsz + rt;      // may lie past the end: TMA zero-fills, nothing is stored
             const int64_t row = tile * BM + r_in_tile;
             const bool live = row < p.n_rows;
             const uint32_t par = it & 1;
-            mbar_wait(acc_full, accph);
-            accph ^= 1;
+            const uint32_t buf = p.acc_bufs == 2 ? (it & 1u) : 0u;
+            const uint32_t t_lane = t_lane0 + buf * 128u;
+            mbar_wait(acc_full + buf, (p.acc_bufs == 2 ? (it >> 1) : it) & 1u);
             tc_fence_after();
 
             // ---- pass 1: max and first argmax over my columns
@@ -845,8 +860,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
             }
             tc_fence_before();
-            if (lead) mbar_arrive(acc_empty);         // TMEM may be overwritten by the next tile
-            else mbar_arrive_cluster(map_to_cta(smem_u32(acc_empty), lead_rank));
+            if (lead) mbar_arrive(acc_empty + buf);   // this buffer may be overwritten
+            else mbar_arrive_cluster(map_to_cta(smem_u32(acc_empty + buf), lead_rank));
 
             if (live) {
                 if (risk && p.flags && p.flags[row] == 0) p.flags[row] = 1;
@@ -1011,33 +1026,56 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx,
 // chosen so that this maximum lands in (2, 4]: fp16 then has 2^14 of headroom above it and full
 // hi+lo precision below it.  A row holding something 16 000 times larger than anything sampled
 // overflows to inf, is seen as non-finite by the epilogue and re-scored in fp32.
+// out: [0] scale, [1] 1/scale, [2] running maximum (as bits), [3] arrival ticket -- [2] and [3] zeroed by
+// the caller.  kXScaleBlocks CTAs share the 2048 sampled rows (one CTA alone took ~1 ms at d=4096); the
+// last one to arrive turns the maximum into the scale.
+constexpr int kXScaleBlocks = 128;
 __global__ void __launch_bounds__(256)
 x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, float* __restrict__ out) {
     __shared__ float red[8];
+    __shared__ bool last;
     const int64_t n_s = n_rows < 2048 ? n_rows : 2048;
     const int64_t step = n_rows / n_s;
+    const int lane = threadIdx.x & 31;
     float mx = 0.0f;
-    for (int64_t i = threadIdx.x >> 5; i < n_s; i += 8) {
-        const float* x = X + (i * step) * ldx;
-        for (int k = threadIdx.x & 31; k < d; k += 32) {
-            const float v = fabsf(__ldg(x + k));
-            if (v <= 3.0e38f) mx = fmaxf(mx, v);            // ignores NaN / inf
+    for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < n_s; i += (int64_t)gridDim.x * 8) {
+        const float4* x = reinterpret_cast<const float4*>(X + (i * step) * ldx);     // rows are 16-byte aligned here
+#pragma unroll 4
+        for (int k = lane; k < d / 4; k += 32) {
+            const float4 v = __ldg(x + k);
+            const float m4 = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+            // NaN / inf are ignored (fmaxf drops NaN; an infinite piece is skipped as a whole)
+            if (m4 <= 3.0e38f) mx = fmaxf(mx, m4);
+            else {
+                if (fabsf(v.x) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.x));
+                if (fabsf(v.y) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.y));
+                if (fabsf(v.z) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.z));
+                if (fabsf(v.w) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.w));
+            }
         }
     }
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    if (lane == 0) red[threadIdx.x >> 5] = mx;
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < 8; ++w) mx = fmaxf(mx, red[w]);
-        int e = 0;
-        float sc = 1.0f;
-        if (mx > 0.0f) {
-            frexpf(mx, &e);                                   // mx = f * 2^e, f in [0.5, 1)
-            sc = ldexpf(1.0f, 2 - e);                         // mx * sc in [2, 4)
+        unsigned* word = reinterpret_cast<unsigned*>(out);
+        atomicMax(word + 2, __float_as_uint(mx));             // non-negative floats order like their bits
+        __threadfence();
+        last = atomicAdd(word + 3, 1u) == gridDim.x - 1;
+        if (last) {
+            __threadfence();
+            mx = __uint_as_float(atomicMax(word + 2, 0u));
+            int e = 0;
+            float sc = 1.0f;
+            if (mx > 0.0f) {
+                frexpf(mx, &e);                                   // mx = f * 2^e, f in [0.5, 1)
+                sc = ldexpf(1.0f, 2 - e);                         // mx * sc in [2, 4)
+            }
+            out[0] = sc;
+            out[1] = 1.0f / sc;
         }
-        out[0] = sc;
-        out[1] = 1.0f / sc;
     }
 }
 
@@ -1172,9 +1210,14 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         L.nrt = (!L.pair && force_mc && L.ncc * 2 <= 8) ? 2 : 1;
     }
     // A model whose classes fit one W tile multiplies by exactly that many columns (in whole 32-column
-    // epilogue chunks) instead of a zero-padded 256: the tensor time of a 32-class model drops 8x.
-    if (acc.ncc == 1 && !acc.pair && acc.nrt == 1) acc.mma_n = (C + 31) / 32 * 32;
-    if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
+    // epilogue chunks) instead of a zero-padded 256: the tensor time of a 32-class model drops 8x.  That
+    // form is unpaired (a pair would split a W tile that is already small).
+    if (acc.ncc == 1 && C <= BN - 32 && !force_pair) {
+        acc.pair = false;
+        acc.nrt = 1;
+        acc.mma_n = (C + 31) / 32 * 32;
+        if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
+    }
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -1324,7 +1367,8 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
             LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
         }
         if (f16) {
-            x_scale_kernel<<<1, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, x_scale);
+            LRS_CUDA(cudaMemsetAsync(x_scale, 0, 16, a.stream));
+            x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, x_scale);
             count_launch();
         }
     }
@@ -1339,6 +1383,26 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.ncc = L.ncc;
     p.nrt = L.nrt;
     p.mma_n = L.mma_n;
+    // Shared-memory split of the unpaired kernel (192 KB): W tiles are mma_n rows x 128 B.  With the
+    // fixed 4 x 32 KB W ring only two k-chunks of W (hi + lo tile each) were in flight, and a W slot is
+    // held from its L2 fetch until the MMAs that read it retire: ~1.15 us per chunk however deep the X
+    // ring was.  Small tiles buy a 12- or 6-deep W ring and a third X stage.
+    if (L.pair) {
+        p.b_tile_bytes = SmemLayoutT<true>::b_tile; p.a_stages = SmemLayoutT<true>::a_stages; p.b_stages = SmemLayoutT<true>::b_stages;
+    } else if (L.mma_n <= 64) {
+        p.b_tile_bytes = 8 * 1024; p.a_stages = 3; p.b_stages = 12;
+    } else if (L.mma_n <= 128) {
+        p.b_tile_bytes = 16 * 1024; p.a_stages = 3; p.b_stages = 6;
+    } else {
+        p.b_tile_bytes = 32 * 1024; p.a_stages = 2; p.b_stages = 4;
+    }
+    if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages"
+        int as = 0, bs = 0;
+        if (!L.pair && sscanf(e, "%d,%d", &as, &bs) == 2 && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages &&
+            as * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) { p.a_stages = as; p.b_stages = bs; }
+    }
+    p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
+    if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
     p.num_k_chunks = f16 ? (m.n_features + BK16 - 1) / BK16 : (m.n_features + BK - 1) / BK;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
