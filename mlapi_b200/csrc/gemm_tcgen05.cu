@@ -48,7 +48,9 @@ constexpr int BK = 32;           // TF32 mode: fp32 elements per k-chunk = 128 b
 constexpr int BK16 = 64;         // FP16 mode: fp16 elements per k-chunk, again one 128-byte row
 constexpr int BN = 256;          // classes per MMA / per W stage
 constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB: one operand tile of X (hi or lo), either mode
-constexpr int kThreads = 480;                 // 15 warps: TMA (W), MMA, 4 converters, 8 epilogue, TMA (X)
+constexpr int kConvWarps = 4;                 // converter warps (all on one k-chunk)
+constexpr int kConvThreads = kConvWarps * 32;
+constexpr int kThreads = (2 + kConvWarps + 8 + 1) * 32;   // warps: TMA (W), MMA, converters, 8 epilogue, TMA (X)
 constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 constexpr int kMaxAStages = 6;          // X ring depth the barrier block has room for
@@ -72,7 +74,7 @@ struct SmemLayoutT {
     static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
     static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
     static constexpr int bars = glob + BM * 8;                       // mbarriers
-    static constexpr int n_bars = 3 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
+    static constexpr int n_bars = 4 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
 };
@@ -94,6 +96,9 @@ struct GemmParams {
     const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
     int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
     int b_tile_bytes;       // ... bytes reserved per W stage ...
+    int raw_stages;         // > 0 (FP16, unpaired, small W tiles): raw fp32 X tiles land in a ring of their own
+                            // (raw_stages x 32 KB after the W ring) and are converted into the operand ring piece by
+                            // piece instead of in place; 0: in place
     int b_stages;           // ... and W ring depth: a_stages * 32 KB + b_stages * b_tile_bytes <= 192 KB
     int acc_bufs;           // 2: N <= 128, two accumulator buffers 128 TMEM columns apart -- the epilogue of a tile
                             // overlaps the MMAs of the next; 1 otherwise
@@ -383,7 +388,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* b_empty = b_full + kMaxBStages;      // [B_STAGES] MMA -> TMA
     uint64_t* acc_full = b_empty + kMaxBStages;       // [2 accumulator buffers] MMA -> epilogue
     uint64_t* acc_empty = acc_full + 2;            // [2] epilogue -> MMA
-    uint64_t* xchg_bar = acc_empty + 2;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
+    uint64_t* raw_empty = acc_empty + 2;           // [raw_stages] converters -> TMA (raw ring mode)
+    uint64_t* xchg_bar = raw_empty + kMaxAStages;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SmemLayout::tmem_slot);
 
     const int warp = threadIdx.x >> 5;
@@ -412,11 +418,12 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const int w_rows = PAIR ? BN / 2 : p.mma_n / p.nrt;  // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < A_STAGES; ++i) {
+        for (int i = 0; i < kMaxAStages; ++i) {     // (operand ring and raw ring may differ in depth)
             mbar_init(x_full + i, 1);
-            mbar_init(a_ready + i, PAIR ? 256 : 128);    // PAIR: both CTAs' converters report to the issuing CTA
+            mbar_init(a_ready + i, PAIR ? 2 * kConvThreads : kConvThreads);    // PAIR: both CTAs' converters report to the issuing CTA
             mbar_init(a_empty + i, x_mc ? p.ncc : 1);    // every CTA sharing the X tile has consumed the stage
         }
+        for (int i = 0; i < kMaxAStages; ++i) mbar_init(raw_empty + i, kConvWarps);
         for (int i = 0; i < B_STAGES; ++i) {
             mbar_init(b_full + i, 1);
             mbar_init(b_empty + i, w_mc ? p.nrt : 1);    // every CTA sharing the W tile has consumed the stage
@@ -495,19 +502,24 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
             }
         }
-    } else if (warp == 14) {
+    } else if (warp == 2 + kConvWarps + 8) {
         // ===================== TMA producer: X tiles =====================
         const bool leader = elect_one();
         int as = 0;
         uint32_t aph = 0;
+        const bool raw_ring = F16 && !PAIR && p.raw_stages > 0;
+        const int x_stages = raw_ring ? p.raw_stages : A_STAGES;
+        uint64_t* x_free = raw_ring ? raw_empty : a_empty;       // who hands the landing buffer back
+        unsigned char* raw_base = b_t + B_STAGES * B_TILE_BYTES;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             const int64_t tile = grp * gsz + rt;
             const int row0 = (int)(tile * BM);
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                mbar_wait(a_empty + as, aph ^ 1);
+                mbar_wait(x_free + as, aph ^ 1);
                 if (leader) {
                     mbar_expect_tx(x_full + as, RAW_BYTES);
-                    unsigned char* xdst = F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES;
+                    unsigned char* xdst = raw_ring ? raw_base + as * RAW_BYTES
+                                                   : (F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES);
                     if (x_mc)
                         tma_load_2d_mc(xdst + rank * x_rows * (BKx * 4), &map_x, kc * BKx, row0 + (int)rank * x_rows,
                                        x_full + as, x_mask);
@@ -515,7 +527,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         tma_load_2d(xdst, &map_x, kc * BKx, row0, x_full + as);
                 }
                 __syncwarp();
-                if (++as == A_STAGES) { as = 0; aph ^= 1; }
+                if (++as == x_stages) { as = 0; aph ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -589,12 +601,51 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             if (leader) { if constexpr (PAIR) tc_commit_2sm(acc_full + buf, pair_mask); else tc_commit(acc_full + buf); }
             __syncwarp();
         }
-    } else if (warp < 6) {
+    } else if (warp < 2 + kConvWarps) {
         // ===================== converters: raw fp32 -> (hi, lo) TF32 pair =====================
-        const int t = threadIdx.x - 64;             // 0..127
+        const int t = threadIdx.x - 64;             // 0..kConvThreads-1
         const float sx = F16 ? p.x_scale[0] : 1.0f;
         int as = 0;
         uint32_t aph = 0;
+        if (F16 && !PAIR && p.raw_stages > 0) {
+            // Raw-ring mode: the fp32 tile sits in a buffer of its own, so nothing is overwritten while it
+            // is read -- no barrier between reading and writing, no need to hold the whole tile in
+            // registers, and the loads of later pieces overlap the arithmetic of earlier ones.  A lane
+            // takes 4 consecutive floats (consecutive lanes = consecutive 16 bytes: conflict-free, where
+            // the in-place form's 32-byte lane stride costs two wavefronts per quarter-warp) and writes
+            // the matching 8-byte halves of the swizzled hi and lo pieces.
+            int rs = 0;
+            uint32_t rph = 0;
+            unsigned char* raw_base = b_t + B_STAGES * B_TILE_BYTES;
+            for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
+                for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                    mbar_wait(x_full + rs, rph);
+                    mbar_wait(a_empty + as, aph ^ 1);             // the operand stage has been consumed
+                    if (!(p.debug_skip & 1)) {
+                        const unsigned char* raw = raw_base + rs * RAW_BYTES;
+                        unsigned char* stage = a_hi + as * A_STAGE;
+#pragma unroll 8
+                        for (int j = 0; j < (BM * BK16 / 4) / kConvThreads; ++j) {
+                            const int qd = t + kConvThreads * j;          // float4 index in the raw tile
+                            const int r = qd >> 4, q4 = qd & 15;
+                            const float4 x = *reinterpret_cast<const float4*>(raw + qd * 16);
+                            uint32_t h0, l0, h1, l1;
+                            split_pair(x.x, x.y, sx, h0, l0);
+                            split_pair(x.z, x.w, sx, h1, l1);
+                            const int off = r * 128 + (((q4 >> 1) ^ (r & 7)) << 4) + (q4 & 1) * 8;
+                            *reinterpret_cast<uint2*>(stage + off) = make_uint2(h0, h1);
+                            *reinterpret_cast<uint2*>(stage + A_TILE_BYTES + off) = make_uint2(l0, l1);
+                        }
+                    }
+                    fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
+                    mbar_arrive(a_ready + as);
+                    __syncwarp();                        // every lane has read its share of the raw tile
+                    if (lane == 0) mbar_arrive(raw_empty + rs);
+                    if (++as == A_STAGES) { as = 0; aph ^= 1; }
+                    if (++rs == p.raw_stages) { rs = 0; rph ^= 1; }
+                }
+            }
+        } else
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             const int64_t tile = grp * gsz + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
@@ -604,8 +655,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     float4* hi = reinterpret_cast<float4*>(a_hi + as * A_TILE_BYTES);
                     float4* lo = reinterpret_cast<float4*>(a_lo + as * A_TILE_BYTES);
 #pragma unroll
-                    for (int j = 0; j < A_TILE_BYTES / 16 / 128; ++j) {
-                        const int i = t + 128 * j;
+                    for (int j = 0; j < A_TILE_BYTES / 16 / kConvThreads; ++j) {
+                        const int i = t + kConvThreads * j;
                         const float4 x = hi[i];
                         float4 h, l;
                         h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
@@ -621,10 +672,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     // writes the two 16-byte results where the 128-byte-swizzled K-major fp16 tiles want
                     // them: hi tile at the stage base, lo tile 16 KB above.
                     unsigned char* stage = a_hi + as * A_STAGE;
-                    uint4 hv[8], lv[8];
+                    constexpr int PIECES = 1024 / kConvThreads;      // 8-element pieces per thread
+                    uint4 hv[PIECES], lv[PIECES];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int qd = t + 128 * j;
+                    for (int j = 0; j < PIECES; ++j) {
+                        const int qd = t + kConvThreads * j;
                         const int r = qd >> 3, c = qd & 7;
                         const float4* src = reinterpret_cast<const float4*>(stage + r * 256 + c * 32);
                         const float4 x0 = src[0], x1 = src[1];
@@ -636,10 +688,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         hv[j] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
                         lv[j] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
                     }
-                    asm volatile("bar.sync 2, 128;" ::: "memory");      // all raw data is in registers
+                    asm volatile("bar.sync 2, %0;" ::"n"(kConvThreads) : "memory");      // all raw data is in registers
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int qd = t + 128 * j;
+                    for (int j = 0; j < PIECES; ++j) {
+                        const int qd = t + kConvThreads * j;
                         const int r = qd >> 3, c = qd & 7;
                         const int off = r * 128 + ((c ^ (r & 7)) << 4);     // SWIZZLE_128B: 16-byte piece ^ (row % 8)
                         *reinterpret_cast<uint4*>(stage + off) = hv[j];
@@ -661,7 +713,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         //                                                      -> combine halves, then CTAs
         //   3. p = e / sum -> global memory
         // so each class costs one exp, and the statistics of a row meet through shared memory.
-        const int ew = warp - 6;                     // 0..7
+        const int ew = warp - (2 + kConvWarps);      // 0..7
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int h = ew >> 2;                       // column half
         const int r_in_tile = q * 32 + lane;
@@ -903,75 +955,115 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 // weight matter for either, so the pass re-computes the logits of those classes in fp32 FMA
 // arithmetic (error ~1e-6) and patches the row: one warp per flagged row, traffic = the row of X,
 // the row of P and a few rows of W instead of all of W.
-__device__ __forceinline__ float warp_dot(const float* __restrict__ x, const float* __restrict__ w, int d, int lane) {
-    float acc = 0.0f;
-    for (int k = lane; k < d; k += 32) acc = fmaf(__ldg(x + k), __ldg(w + k), acc);
+// Dot product of one row of X with one row of W by a warp; both rows are 16-byte aligned on this path
+// (n_features % 4 == 0, row pitch % 4 == 0), so the bulk goes in 128-bit pieces, four in flight.
+__device__ __forceinline__ float warp_dot4(const float* __restrict__ x, const float* __restrict__ w, int d, int lane) {
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const float4* w4 = reinterpret_cast<const float4*>(w);
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll 4
+    for (int k = lane; k < d / 4; k += 32) {
+        const float4 xv = __ldg(x4 + k), wv = __ldg(w4 + k);
+        a0 = fmaf(xv.x, wv.x, a0); a1 = fmaf(xv.y, wv.y, a1);
+        a2 = fmaf(xv.z, wv.z, a2); a3 = fmaf(xv.w, wv.w, a3);
+    }
+    float acc = (a0 + a1) + (a2 + a3);
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
     return acc;
 }
 
+// One CTA per 256 rows; a flagged row is re-scored by the whole CTA, its eight warps sharing the
+// selected classes.  (One warp per row left the last flagged row of a long-row model as a serial tail:
+// at d=4096, C=64 most classes are "selected" and 64 dot products of 4096 in one warp took 0.28 ms for
+// a handful of rows.)
 __global__ void __launch_bounds__(256)
 gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
                       const float* __restrict__ W, const float* __restrict__ b,
                       const unsigned char* __restrict__ flags, const float* __restrict__ lse, float* proba,
                       float* decision, int32_t* label, float* maxprob, unsigned long long* rescored,
                       unsigned long long* status) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warps_total = (int64_t)gridDim.x * 8;
-    for (int64_t base = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 32; base < n_rows; base += warps_total * 32) {
-        const int64_t mine = base + lane;
-        unsigned todo = __ballot_sync(0xffffffffu, mine < n_rows && flags[mine] != 0);
-        while (todo) {
-            const int64_t row = base + (__ffs(todo) - 1);
-            todo &= todo - 1;
-            const float* x = X + row * ldx;
-            float* pr = proba + row * C;
-            const float L = lse[row];
-            if (!finite_f(L)) {
-                // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
-                // score the whole row in fp32, which also settles whether the input really is non-finite
-                score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
-                if (lane == 0) atomicAdd(rescored, 1ull);
-                continue;
-            }
-            float pmax = 0.0f;
-            for (int c = lane; c < C; c += 32) pmax = fmaxf(pmax, pr[c]);
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
-            const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
-            float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
-            int best = 0;
-            for (int c0 = 0; c0 < C; c0 += 32) {
-                const int c = c0 + lane;
-                const float pc = c < C ? pr[c] : 0.0f;
-                unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
-                float q_mine = pc;
-                while (sel) {
-                    const int j = __ffs(sel) - 1;
-                    sel &= sel - 1;
-                    const int cj = c0 + j;
-                    const float z = warp_dot(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
-                    const float q = expf(z - L);                    // in units of the old row sum
-                    old_mass += __shfl_sync(0xffffffffu, pc, j);
-                    new_mass += q;
-                    if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
-                    if (lane == j) q_mine = q;
-                    if (decision && lane == 0) decision[row * C + cj] = z;
+    __shared__ unsigned s_mask[8];
+    __shared__ float s_f[8], s_old[8], s_new[8], s_bz[8], s_bq[8];
+    __shared__ int s_bc[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = (int64_t)blockIdx.x * 256; base < n_rows; base += (int64_t)gridDim.x * 256) {
+        const int64_t mine = base + threadIdx.x;
+        const unsigned m32 = __ballot_sync(0xffffffffu, mine < n_rows && flags[mine] != 0);
+        if (lane == 0) s_mask[warp] = m32;
+        const int any = __syncthreads_or(m32 != 0);
+        if (!any) continue;
+        for (int wq = 0; wq < 8; ++wq) {
+            unsigned todo = s_mask[wq];                               // same for every thread of the CTA
+            while (todo) {
+                const int64_t row = base + wq * 32 + (__ffs(todo) - 1);
+                todo &= todo - 1;
+                const float* x = X + row * ldx;
+                float* pr = proba + row * C;
+                const float L = lse[row];
+                if (!finite_f(L)) {
+                    // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
+                    // score the whole row in fp32, which also settles whether the input really is non-finite
+                    if (warp == 0) {
+                        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+                        if (lane == 0) atomicAdd(rescored, 1ull);
+                    }
+                    continue;
                 }
-                if (c < C && q_mine != pc) pr[c] = q_mine;
-            }
-            const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
-            const float invT = __frcp_rn(T);
-            __syncwarp();
-            if (fabsf(T - 1.0f) > 1e-7f)
-                for (int c = lane; c < C; c += 32) pr[c] *= invT;
-            if (lane == 0) {
-                if (label) label[row] = best;
-                if (maxprob) maxprob[row] = best_q * invT;
-                atomicAdd(rescored, 1ull);
+                // largest probability of the row
+                float pmax = 0.0f;
+                for (int c = threadIdx.x; c < C; c += 256) pmax = fmaxf(pmax, pr[c]);
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
+                if (lane == 0) s_f[warp] = pmax;
+                __syncthreads();
+                pmax = s_f[0];
+#pragma unroll
+                for (int w = 1; w < 8; ++w) pmax = fmaxf(pmax, s_f[w]);
+                const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
+                float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
+                int best = 0x7fffffff;
+                for (int c0 = warp * 32; c0 < C; c0 += 256) {           // this warp's blocks of 32 classes, ascending
+                    const int c = c0 + lane;
+                    const float pc = c < C ? pr[c] : 0.0f;
+                    unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
+                    float q_mine = pc;
+                    while (sel) {
+                        const int j = __ffs(sel) - 1;
+                        sel &= sel - 1;
+                        const int cj = c0 + j;
+                        const float z = warp_dot4(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
+                        const float q = expf(z - L);                    // in units of the old row sum
+                        old_mass += __shfl_sync(0xffffffffu, pc, j);
+                        new_mass += q;
+                        if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+                        if (lane == j) q_mine = q;
+                        if (decision && lane == 0) decision[row * C + cj] = z;
+                    }
+                    if (c < C && q_mine != pc) pr[c] = q_mine;
+                }
+                if (lane == 0) { s_old[warp] = old_mass; s_new[warp] = new_mass; s_bz[warp] = best_z; s_bq[warp] = best_q; s_bc[warp] = best; }
+                __syncthreads();                                        // also orders the pr[] updates before the rescale
+                old_mass = 0.0f; new_mass = 0.0f; best_z = -CUDART_INF_F; best_q = 0.0f; best = 0x7fffffff;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) {                           // fixed order: every thread gets the same sums
+                    old_mass += s_old[w];
+                    new_mass += s_new[w];
+                    if (s_bz[w] > best_z || (s_bz[w] == best_z && s_bc[w] < best)) { best_z = s_bz[w]; best = s_bc[w]; best_q = s_bq[w]; }
+                }
+                const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+                const float invT = __frcp_rn(T);
+                if (fabsf(T - 1.0f) > 1e-7f)
+                    for (int c = threadIdx.x; c < C; c += 256) pr[c] *= invT;
+                if (threadIdx.x == 0) {
+                    if (label) label[row] = best;
+                    if (maxprob) maxprob[row] = best_q * invT;
+                    atomicAdd(rescored, 1ull);
+                }
+                __syncthreads();                                        // shared scratch is reused by the next row
             }
         }
+        __syncthreads();                                                // s_mask is rewritten by the next block of rows
     }
 }
 
@@ -999,7 +1091,7 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx,
             const int per = (C + 7) / 8;
             const int c_hi = min(C, (warp + 1) * per);
             for (int c = warp * per; c < c_hi; ++c) {
-                const float z = warp_dot(x, W + (int64_t)c * d, d, lane) + __ldg(b + c);
+                const float z = warp_dot4(x, W + (int64_t)c * d, d, lane) + __ldg(b + c);
                 if (decision && lane == 0) decision[row * C + c] = z;
                 if (z > m) { ssum = ssum * expf(m - z) + 1.0f; m = z; arg = c; }
                 else ssum += expf(z - m);
@@ -1034,7 +1126,10 @@ __global__ void __launch_bounds__(256)
 x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, float* __restrict__ out) {
     __shared__ float red[8];
     __shared__ bool last;
-    const int64_t n_s = n_rows < 2048 ? n_rows : 2048;
+    // up to 2048 sampled rows, fewer for long rows (about 4 MB read in all, at least 64 rows)
+    int64_t n_s = (int64_t)(1 << 20) / d;
+    n_s = n_s < 64 ? 64 : (n_s > 2048 ? 2048 : n_s);
+    n_s = n_rows < n_s ? n_rows : n_s;
     const int64_t step = n_rows / n_s;
     const int lane = threadIdx.x & 31;
     float mx = 0.0f;
@@ -1387,19 +1482,30 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     // fixed 4 x 32 KB W ring only two k-chunks of W (hi + lo tile each) were in flight, and a W slot is
     // held from its L2 fetch until the MMAs that read it retire: ~1.15 us per chunk however deep the X
     // ring was.  Small tiles buy a 12- or 6-deep W ring and a third X stage.
+    p.raw_stages = 0;
+    // Raw-ring conversion is opt-in (LRS_GEMM_RAW=1): measured 4137 against 4690 GB/s in place at d=256,
+    // C=32 and 3214 against 3457 at d=4096, C=64 -- the rings it leaves room for are shallower.
+    bool raw_ring = false;
+    if (const char* e = getenv("LRS_GEMM_RAW")) raw_ring = f16 && atoi(e) != 0;
     if (L.pair) {
         p.b_tile_bytes = SmemLayoutT<true>::b_tile; p.a_stages = SmemLayoutT<true>::a_stages; p.b_stages = SmemLayoutT<true>::b_stages;
     } else if (L.mma_n <= 64) {
         p.b_tile_bytes = 8 * 1024; p.a_stages = 3; p.b_stages = 12;
+        if (raw_ring) { p.a_stages = 2; p.b_stages = 8; p.raw_stages = 2; }
     } else if (L.mma_n <= 128) {
         p.b_tile_bytes = 16 * 1024; p.a_stages = 3; p.b_stages = 6;
+        if (raw_ring) { p.a_stages = 2; p.b_stages = 4; p.raw_stages = 2; }
     } else {
         p.b_tile_bytes = 32 * 1024; p.a_stages = 2; p.b_stages = 4;
     }
-    if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages"
-        int as = 0, bs = 0;
-        if (!L.pair && sscanf(e, "%d,%d", &as, &bs) == 2 && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages &&
-            as * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) { p.a_stages = as; p.b_stages = bs; }
+    if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages[,raw_stages]"
+        int as = 0, bs = 0, rs = 0;
+        const int n = sscanf(e, "%d,%d,%d", &as, &bs, &rs);
+        if (n == 2) rs = 0;
+        if (!L.pair && n >= 2 && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages && rs >= 0 && rs <= kMaxAStages &&
+            (rs == 0 || f16) && (as + rs) * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) {
+            p.a_stages = as; p.b_stages = bs; p.raw_stages = rs;
+        }
     }
     p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
