@@ -973,10 +973,62 @@ __device__ __forceinline__ float warp_dot4(const float* __restrict__ x, const fl
     return acc;
 }
 
-// One CTA per 256 rows; a flagged row is re-scored by the whole CTA, its eight warps sharing the
-// selected classes.  (One warp per row left the last flagged row of a long-row model as a serial tail:
-// at d=4096, C=64 most classes are "selected" and 64 dot products of 4096 in one warp took 0.28 ms for
-// a handful of rows.)
+// One flagged row re-scored by one warp (see the kernel below for when).
+__device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+                                               const float* __restrict__ W, const float* __restrict__ b, float L,
+                                               float* proba, float* decision, int32_t* label, float* maxprob,
+                                               unsigned long long* rescored, unsigned long long* status) {
+    float* pr = proba + row * C;
+    if (!finite_f(L)) {
+        // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
+        // score the whole row in fp32, which also settles whether the input really is non-finite
+        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+        if (lane == 0) atomicAdd(rescored, 1ull);
+        return;
+    }
+    float pmax = 0.0f;
+    for (int c = lane; c < C; c += 32) pmax = fmaxf(pmax, pr[c]);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
+    const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
+    float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
+    int best = 0;
+    for (int c0 = 0; c0 < C; c0 += 32) {
+        const int c = c0 + lane;
+        const float pc = c < C ? pr[c] : 0.0f;
+        unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
+        float q_mine = pc;
+        while (sel) {
+            const int j = __ffs(sel) - 1;
+            sel &= sel - 1;
+            const int cj = c0 + j;
+            const float z = warp_dot4(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
+            const float q = expf(z - L);                    // in units of the old row sum
+            old_mass += __shfl_sync(0xffffffffu, pc, j);
+            new_mass += q;
+            if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+            if (lane == j) q_mine = q;
+            if (decision && lane == 0) decision[row * C + cj] = z;
+        }
+        if (c < C && q_mine != pc) pr[c] = q_mine;
+    }
+    const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+    const float invT = __frcp_rn(T);
+    __syncwarp();
+    if (fabsf(T - 1.0f) > 1e-7f)
+        for (int c = lane; c < C; c += 32) pr[c] *= invT;
+    if (lane == 0) {
+        if (label) label[row] = best;
+        if (maxprob) maxprob[row] = best_q * invT;
+        atomicAdd(rescored, 1ull);
+    }
+}
+
+// One CTA per 256 rows.  Where flagged rows are dense (a confident model: 16 or more in the block) every
+// warp re-scores the flagged rows among its own 32, one after the other.  Where they are sparse that would
+// leave the last flagged row of a long-row model as a serial tail (d=4096, C=64: most classes are
+// "selected", 64 dot products of 4096 in one warp, 0.28 ms for a handful of rows), so the whole CTA takes
+// each flagged row, its eight warps sharing the selected classes.
 __global__ void __launch_bounds__(256)
 gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
                       const float* __restrict__ W, const float* __restrict__ b,
@@ -989,10 +1041,22 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int64_t base = (int64_t)blockIdx.x * 256; base < n_rows; base += (int64_t)gridDim.x * 256) {
         const int64_t mine = base + threadIdx.x;
-        const unsigned m32 = __ballot_sync(0xffffffffu, mine < n_rows && flags[mine] != 0);
+        const bool flagged = mine < n_rows && flags[mine] != 0;
+        const unsigned m32 = __ballot_sync(0xffffffffu, flagged);
         if (lane == 0) s_mask[warp] = m32;
-        const int any = __syncthreads_or(m32 != 0);
-        if (!any) continue;
+        const int n_flagged = __syncthreads_count(flagged);
+        if (n_flagged == 0) continue;
+        if (n_flagged >= 16) {
+            unsigned todo = m32;
+            while (todo) {
+                const int64_t row = base + warp * 32 + (__ffs(todo) - 1);
+                todo &= todo - 1;
+                fixup_row_warp(X + row * ldx, row, lane, d, C, W, b, lse[row], proba, decision, label, maxprob,
+                               rescored, status);
+            }
+            __syncthreads();                                            // s_mask is rewritten by the next block of rows
+            continue;
+        }
         for (int wq = 0; wq < 8; ++wq) {
             unsigned todo = s_mask[wq];                               // same for every thread of the CTA
             while (todo) {
@@ -1002,12 +1066,8 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
                 float* pr = proba + row * C;
                 const float L = lse[row];
                 if (!finite_f(L)) {
-                    // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
-                    // score the whole row in fp32, which also settles whether the input really is non-finite
-                    if (warp == 0) {
-                        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
-                        if (lane == 0) atomicAdd(rescored, 1ull);
-                    }
+                    if (warp == 0)
+                        fixup_row_warp(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored, status);
                     continue;
                 }
                 // largest probability of the row
@@ -1020,7 +1080,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
                 pmax = s_f[0];
 #pragma unroll
                 for (int w = 1; w < 8; ++w) pmax = fmaxf(pmax, s_f[w]);
-                const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
+                const float thr = fminf(0.01f, 0.9f * pmax);
                 float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
                 int best = 0x7fffffff;
                 for (int c0 = warp * 32; c0 < C; c0 += 256) {           // this warp's blocks of 32 classes, ascending
@@ -1033,10 +1093,10 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
                         sel &= sel - 1;
                         const int cj = c0 + j;
                         const float z = warp_dot4(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
-                        const float q = expf(z - L);                    // in units of the old row sum
+                        const float q = expf(z - L);
                         old_mass += __shfl_sync(0xffffffffu, pc, j);
                         new_mass += q;
-                        if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+                        if (z > best_z) { best_z = z; best = cj; best_q = q; }
                         if (lane == j) q_mine = q;
                         if (decision && lane == 0) decision[row * C + cj] = z;
                     }
