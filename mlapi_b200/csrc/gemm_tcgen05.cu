@@ -1244,6 +1244,8 @@ struct GemmPlan {
     __half* w16_hi = nullptr;   // [c_pad][d16]
     __half* w16_lo = nullptr;
     float* col_inv_scale = nullptr;   // [c_pad] 1 / class scale
+    float* w32_pad = nullptr;   // [C][d4] fp32 coef_ at a 16-byte pitch (only when n_features % 4 != 0)
+    int d4 = 0;                 // n_features rounded up to 4
     int d16 = 0;                // row pitch of the fp16 copies (n_features rounded up to 8: TMA wants 16-byte pitches)
     bool f16 = false;
     // Two CTA layouts over the same W buffers:
@@ -1322,18 +1324,20 @@ float tf32_rna_host(float x) {
 
 }  // namespace
 
-// Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048;
-// rows of X and W must be 16-byte aligned (TMA).
+// Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048.  TMA wants
+// 16-byte aligned rows: batches whose base or pitch is not (odd feature counts among them) are re-pitched
+// into an aligned scratch first, see gemm_launch.
 bool gemm_supports(const Model& m, const ScoreArgs& a) {
-    return m.gemm != nullptr && (a.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0) &&
-           a.n_rows < (int64_t)1 << 31;
+    return m.gemm != nullptr && a.n_rows < (int64_t)1 << 31;
 }
 
 int gemm_prepare(Model& m, const double* coef, const double* intercept) {
-    if (m.n_scores <= 16 || m.n_scores > kMaxCluster * 2 * BN || m.n_features % 4 != 0) return LR_OK;
+    if (m.n_scores <= 16 || m.n_scores > kMaxCluster * 2 * BN) return LR_OK;
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
     GemmPlan* g = new GemmPlan();
     const int C = m.n_scores, d = m.n_features;
+    const int d4 = (d + 3) / 4 * 4;                 // row pitch of the fp32 copies: TMA wants 16-byte pitches
+    g->d4 = d4;
     auto& fast = g->layout[0];
     auto& acc = g->layout[1];
     if (C > BN) {                                   // fast layout: 512 classes per CTA
@@ -1383,15 +1387,23 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     for (int i = 0; i < 2; ++i)
         if (g->has[i] && g->layout[i].ncc * g->layout[i].nb * BN > g->c_pad) g->c_pad = g->layout[i].ncc * g->layout[i].nb * BN;
     if (const char* e = getenv("LRS_GEMM_FIXUP")) g->fixup = atoi(e) != 0;
-    std::vector<float> hi((size_t)g->c_pad * d, 0.0f), lo((size_t)g->c_pad * d, 0.0f), bias(g->c_pad, -INFINITY);
+    std::vector<float> hi((size_t)g->c_pad * d4, 0.0f), lo((size_t)g->c_pad * d4, 0.0f), bias(g->c_pad, -INFINITY);
     for (int c = 0; c < C; ++c) {
         bias[c] = (float)intercept[c];
         for (int k = 0; k < d; ++k) {
             const double w = coef[(size_t)c * d + k];
             const float h = tf32_rna_host((float)w);
-            hi[(size_t)c * d + k] = h;
-            lo[(size_t)c * d + k] = tf32_rna_host((float)(w - (double)h));
+            hi[(size_t)c * d4 + k] = h;
+            lo[(size_t)c * d4 + k] = tf32_rna_host((float)(w - (double)h));
         }
+    }
+    if (d4 != d) {
+        // fp32 coefficients at the padded pitch, for the re-scoring pass over re-pitched rows (see gemm_launch)
+        std::vector<float> w32((size_t)C * d4, 0.0f);
+        for (int c = 0; c < C; ++c)
+            for (int k = 0; k < d; ++k) w32[(size_t)c * d4 + k] = (float)coef[(size_t)c * d + k];
+        LRS_CUDA(cudaMalloc(&g->w32_pad, w32.size() * sizeof(float)));
+        LRS_CUDA(cudaMemcpy(g->w32_pad, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
     m.gemm = g;
     const size_t bytes = hi.size() * sizeof(float);
@@ -1406,8 +1418,8 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         if (!g->has[i]) continue;
         auto& L = g->layout[i];
         const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
-        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d, wbox)) != LR_OK) return rc;
-        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d, wbox)) != LR_OK) return rc;
+        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
+        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
     }
 
     // FP16 copies (3xFP16 mode, LRS_GEMM_F16=0 turns it off)
@@ -1477,21 +1489,35 @@ void gemm_destroy(Model& m) {
     cudaFree(m.gemm->bias);
     cudaFree(m.gemm->w16_hi);
     cudaFree(m.gemm->w16_lo);
+    cudaFree(m.gemm->w32_pad);
     cudaFree(m.gemm->col_inv_scale);
     delete m.gemm;
     m.gemm = nullptr;
 }
 
-int gemm_launch(const Model& m, const ScoreArgs& a) {
-    if (!gemm_supports(m, a))
-        return fail(LR_ERR_INVALID, "gemm path needs 17..2048 classes, n_features % 4 == 0 and 16-byte aligned rows of X");
+namespace {
+
+// Rows of X copied to a 16-byte pitch (d4 floats, zero-filled beyond d): one warp per row.
+__global__ void __launch_bounds__(256)
+repitch_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int d4, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
+        const float* x = X + row * ldx;
+        float* o = out + row * d4;
+        for (int k = lane; k < d4; k += 32) o[k] = k < d ? ldg_stream1(x + k) : 0.0f;
+    }
+}
+
+// The tensor-core pass over rows that TMA can address: 16-byte aligned base and pitch, `d_eff` columns
+// (a multiple of 4); `w_fix` = fp32 coefficients at pitch d_eff for the re-scoring pass.
+int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix) {
     GemmPlan* g = m.gemm;
     GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
     const bool f16 = g->f16;
     const int xbox = L.pair ? BM : BM / L.ncc;        // X is multicast across class slices only without pairs
-    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, xbox, BK16, 4, false)
-                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)m.n_features, (uint64_t)a.ldx, xbox);
+    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox, BK16, 4, false)
+                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox);
     if (rc != LR_OK) return rc;
     const size_t smem = (L.pair ? SmemLayoutT<true>::total : SmemLayoutT<false>::total) + 1024;
     const int dev = m.device & 63;
@@ -1523,7 +1549,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
         }
         if (f16) {
             LRS_CUDA(cudaMemsetAsync(x_scale, 0, 16, a.stream));
-            x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, x_scale);
+            x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, x_scale);
             count_launch();
         }
     }
@@ -1531,7 +1557,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     p.flags = flags;
     p.lse = lse;
     p.n_rows = a.n_rows;
-    p.n_features = m.n_features;
+    p.n_features = d_eff;
     p.n_classes = m.n_scores;
     p.nb = L.nb;
     p.split = L.split ? 1 : 0;
@@ -1569,7 +1595,7 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     }
     p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
-    p.num_k_chunks = f16 ? (m.n_features + BK16 - 1) / BK16 : (m.n_features + BK - 1) / BK;
+    p.num_k_chunks = f16 ? (d_eff + BK16 - 1) / BK16 : (d_eff + BK - 1) / BK;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
     p.x_scale = x_scale;
@@ -1625,18 +1651,58 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     count_launch();
     if (fixup) {
         if (a.proba)
-            gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.n_scores,
-                                                                      m.W, m.b, flags, lse, a.proba, a.decision,
+            gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, m.n_scores,
+                                                                      w_fix, m.b, flags, lse, a.proba, a.decision,
                                                                       a.label, a.maxprob, m.status + 1, m.status);
         else
-            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features,
-                                                                       m.n_scores, m.W, m.b, flags, a.decision,
+            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff,
+                                                                       m.n_scores, w_fix, m.b, flags, a.decision,
                                                                        a.label, a.maxprob, m.status + 1, m.status);
         count_launch();
         LRS_CUDA(cudaGetLastError());
     }
     if (scratch) LRS_CUDA(cudaFreeAsync(scratch, a.stream));
     return LR_OK;
+}
+
+}  // namespace
+
+int gemm_launch(const Model& m, const ScoreArgs& a) {
+    if (!gemm_supports(m, a)) return fail(LR_ERR_INVALID, "gemm path needs 17..2048 classes and fewer than 2^31 rows");
+    GemmPlan* g = m.gemm;
+    const int d = m.n_features;
+    const bool aligned = d % 4 == 0 && a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
+    if (aligned) return gemm_launch_aligned(m, a, d, m.W);
+    // Odd feature counts, odd pitches, unaligned bases: TMA cannot address those rows.  They are copied in
+    // blocks of rows to an aligned scratch (stream-ordered, <= 512 MB) and the block is scored from there --
+    // one extra read and write of X, against a SIMT fallback that ran 40x slower on d=1022, C=1000.
+    const int d4 = g->d4;
+    const float* w_fix = d4 == d ? m.W : g->w32_pad;
+    int64_t block = ((int64_t)512 << 20) / ((int64_t)d4 * 4);
+    block = block < 1024 ? 1024 : block / 1024 * 1024;
+    if (block > a.n_rows) block = a.n_rows;
+    float* scratch = nullptr;
+    LRS_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), (size_t)block * d4 * sizeof(float), a.stream));
+    int rc = LR_OK;
+    const int C = m.n_scores;
+    for (int64_t r0 = 0; r0 < a.n_rows && rc == LR_OK; r0 += block) {
+        const int64_t n = a.n_rows - r0 < block ? a.n_rows - r0 : block;
+        const int64_t want = (n + 7) / 8;
+        const int grid = (int)(want < (int64_t)m.num_sms * 8 ? want : (int64_t)m.num_sms * 8);
+        repitch_kernel<<<grid, 256, 0, a.stream>>>(a.X + r0 * a.ldx, n, a.ldx, d, d4, scratch);
+        count_launch();
+        ScoreArgs s = a;
+        s.X = scratch;
+        s.ldx = d4;
+        s.n_rows = n;
+        if (a.proba) s.proba = a.proba + r0 * C;
+        if (a.decision) s.decision = a.decision + r0 * C;
+        if (a.label) s.label = a.label + r0;
+        if (a.maxprob) s.maxprob = a.maxprob + r0;
+        rc = gemm_launch_aligned(m, s, d4, w_fix);
+    }
+    cudaFreeAsync(scratch, a.stream);
+    return rc;
 }
 
 }  // namespace lrs

@@ -147,3 +147,63 @@ def test_gemm_device_pitch(eng):
                          orc.predict_index(Xh, W, b), "gemm pitched", z_atol=parity.Z_ATOL_TENSOR)
     assert clf.take_nonfinite() == 0
     clf.close()
+
+
+@pytest.mark.parametrize("d,c", [(5, 17), (33, 40), (131, 100), (1022, 300), (250, 1000), (1023, 2048)])
+def test_gemm_odd_feature_counts_are_repitched(eng, d, c):
+    """n_features % 4 != 0: TMA cannot address the rows, the library copies them to an aligned scratch
+    and stays on the tensor-core path (the SIMT fallback was 40x slower on d=1022, C=1000)."""
+    mlapi, lib = eng
+    W, b = synth.make_model(d, c, 500 + c)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    rng = np.random.default_rng(d * 3 + c)
+    for n in (1, 130, 1111):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        out = clf.score_rows(X, **ALL)                      # dispatcher: gemm (re-pitched)
+        parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                             orc.predict_index(X, W, b), f"gemm repitch d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+    Xb = rng.standard_normal((300, d), dtype=np.float32)
+    Xb[7, d - 1] = np.nan                                   # last (odd) column must be seen
+    with pytest.raises(ValueError, match="NaN or infinity"):
+        clf.predict_proba(Xb)
+    clf.close()
+
+
+def test_gemm_unaligned_device_rows_are_repitched(eng):
+    import ctypes as C
+    import torch
+    mlapi, lib = eng
+    L = lib.load()
+    d, c, n = 64, 300, 700
+    W, b = synth.make_model(d, c, 11)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    buf = np.random.default_rng(5).standard_normal((n, d + 3), dtype=np.float32)
+    for off in (0, 1):                                      # odd pitch; odd pitch + 4-byte aligned base
+        Xh = buf[:, off:off + d]
+        Xt = torch.from_numpy(buf).cuda()[:, off:off + d]
+        path = C.c_int32(0)
+        lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d + 3, C.byref(path)))
+        assert path.value == lib.PATH_GEMM
+        out = clf.score_rows(Xt, **ALL)
+        torch.cuda.synchronize()
+        host = {k: v.cpu().numpy() for k, v in out.items()}
+        parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
+                             orc.predict_index(Xh, W, b), f"gemm unaligned off={off}", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
+
+
+@pytest.mark.parametrize("d,c", [(64, 17), (64, 32), (200, 33), (256, 64), (512, 100), (96, 128), (128, 160), (64, 224), (64, 225)])
+def test_gemm_small_class_counts(eng, d, c):
+    """17..224 classes: the unpaired small-N form (N = classes rounded up to 32, two accumulator buffers
+    up to N = 128); 225..256 keep the 256-wide tile.  Several row tiles per CTA so both buffers cycle."""
+    mlapi, lib = eng
+    W, b = synth.make_model(d, c, 700 + c)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    rng = np.random.default_rng(d + 7 * c)
+    for n in (1, 128, 129, 60_000):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        out = clf.score_rows(X, **ALL)
+        parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                             orc.predict_index(X, W, b), f"gemm small-N d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
