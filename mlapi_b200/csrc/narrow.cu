@@ -487,6 +487,152 @@ narrow_bulk_kernel(const float* __restrict__ X, int64_t n_rows, int d, int dpad,
     }
 }
 
+// ---- rows that are not 16-byte aligned ---------------------------------------------------------------
+// Odd feature counts (30, 33, 785 ...), odd pitches or an unaligned base leave the kernels above with
+// scalar 4-byte loads: 2.3-2.7 TB/s measured at d = 30 / 33.  The ROWS may be unaligned, but a block of
+// them is still one contiguous span of memory: the producer lane copies whole tiles of rows
+// (TILE_ROWS x ldx floats, a multiple of 16 bytes) into a shared-memory ring with cp.async.bulk -- the
+// 16-byte aligned middle of the span in one bulk copy, the up to three floats before and after it
+// with plain loads, so nothing outside [X, X + n*ldx) is touched -- and eight consumer warps read
+// their rows back with scalar shared loads, which do not care about alignment.  Same lane mapping,
+// cross-lane reduction and epilogue as above; W in shared memory.  Serves ldx <= kFlatMaxLdx.
+constexpr int kFlatMaxLdx = 2048;
+constexpr int kFlatWarps = 16;                    // consumer warps (scalar shared loads: latency-bound with 8)
+constexpr int kFlatThreads = (kFlatWarps + 1) * 32;
+constexpr int kFlatSmemBudget = 200 * 1024;
+
+template <int LANES, int NS, int U>
+__global__ void __launch_bounds__(kFlatThreads, 1)
+narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad, int tile_rows,
+                   int stages, uint32_t stage_bytes, const float* __restrict__ Wn, const float* __restrict__ bn,
+                   Outs o) {
+    constexpr int G = 32 / LANES;
+    constexpr int M = (U < LANES) ? U : LANES;
+    constexpr int ROWS_OWNED = U / M;
+    constexpr int GROUP = G * U;                      // rows one warp takes per pass
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);          // [stages]
+    uint64_t* empty = full + stages;                                  // [stages]
+    float* w_s = reinterpret_cast<float*>(smem_raw + 128 * ((2 * stages * 8 + 127) / 128));   // [NS][dpad]
+    unsigned char* ring = reinterpret_cast<unsigned char*>(w_s + NS * dpad);                  // dpad % 32 == 0
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(full + i, 1);
+            mbar_init(empty + i, kFlatWarps);
+        }
+        mbar_fence_init();
+    }
+    for (int i = threadIdx.x; i < NS * dpad; i += kFlatThreads) w_s[i] = Wn[i];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int64_t n_tiles = (n_rows + tile_rows - 1) / tile_rows;
+    // tile_rows * ldx is a multiple of 4 floats, so every tile starts at the same offset inside a 16-byte line
+    const uint32_t a0 = (uint32_t)((reinterpret_cast<uintptr_t>(X) >> 2) & 3u);
+
+    if (warp == kFlatWarps) {
+        // ===== producer: one lane feeds the ring =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                mbar_wait(empty + stage, phase ^ 1);
+                const int64_t row0 = tile * tile_rows;
+                const int64_t rows = (n_rows - row0 < tile_rows) ? (n_rows - row0) : tile_rows;
+                // floats of this tile that exist: the last row of the matrix ends after d, not ldx
+                const int64_t nfl = (row0 + rows == n_rows) ? (rows - 1) * ldx + d : rows * ldx;
+                const float* src = X + row0 * ldx;
+                float* dst = reinterpret_cast<float*>(ring + (size_t)stage * stage_bytes) + a0;   // tile float i -> dst[i]
+                const int64_t head = nfl < (int64_t)((4 - a0) & 3u) ? nfl : (int64_t)((4 - a0) & 3u);
+                const int64_t mid = (nfl - head) & ~int64_t(3);
+                for (int64_t i = 0; i < head; ++i) dst[i] = src[i];
+                for (int64_t i = head + mid; i < nfl; ++i) dst[i] = src[i];
+                if (mid > 0) {
+                    mbar_expect_tx(full + stage, (uint32_t)(mid * 4));     // release: the plain stores above are ordered before it
+                    bulk_g2s(dst + head, src + head, (uint32_t)(mid * 4), full + stage);
+                } else {
+                    mbar_arrive(full + stage);
+                }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers =====
+    const int g = lane / LANES;
+    const int s = lane % LANES;
+    const int dloop = (d + LANES - 1) / LANES * LANES;       // <= dpad; W is zero beyond d
+    float bias[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) bias[c] = bn[c];
+
+    int stage = 0;
+    uint32_t phase = 0;
+    // A tile holds tile_rows / GROUP row groups -- fewer than there are warps when rows are long -- so
+    // the groups of successive tiles go round the warps: group number (tile sequence * groups per tile
+    // + index in tile) modulo kFlatWarps is the warp that takes it.
+    const int gpt = tile_rows / GROUP;
+    int first = warp;                                 // index in the tile of this warp's first group
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        mbar_wait(full + stage, phase);
+        const float* ts = reinterpret_cast<const float*>(ring + (size_t)stage * stage_bytes) + a0;
+        const int64_t row0 = tile * tile_rows;
+        const int rows = (int)((n_rows - row0 < tile_rows) ? (n_rows - row0) : tile_rows);
+        const int gb0 = first * GROUP;
+        first = (first + kFlatWarps - gpt % kFlatWarps) % kFlatWarps;
+        for (int gb = gb0; gb < rows; gb += kFlatWarps * GROUP) {
+            const float* rp[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                int r = gb + j * G + g;
+                r = r < rows ? r : rows - 1;                  // clamped rows are computed and never stored
+                rp[j] = ts + (int64_t)r * ldx;
+            }
+            float acc[U][NS];
+#pragma unroll
+            for (int j = 0; j < U; ++j)
+#pragma unroll
+                for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
+            for (int k = s; k < dloop; k += LANES) {
+                const int kc = k < d ? k : 0;                 // past-the-end lanes meet zero weights
+                float x[U];
+#pragma unroll
+                for (int j = 0; j < U; ++j) x[j] = rp[j][kc];
+#pragma unroll
+                for (int c = 0; c < NS; ++c) {
+                    const float w = w_s[c * dpad + k];
+#pragma unroll
+                    for (int j = 0; j < U; ++j) acc[j][c] = fmaf(x[j], w, acc[j][c]);
+                }
+            }
+            lane_reduce<LANES / 2, U, NS, U>(acc, s);
+            const int sel = s / (LANES / M);
+            const bool owner = (s % (LANES / M)) == 0;
+            if (owner) {
+#pragma unroll
+                for (int r = 0; r < ROWS_OWNED; ++r) {
+                    const int u = sel * ROWS_OWNED + r;
+                    const int rt = gb + u * G + g;
+                    if (rt < rows) {
+                        float z[NS];
+#pragma unroll
+                        for (int c = 0; c < NS; ++c) z[c] = acc[r][c] + bias[c];
+                        finish_row<NS>(z, row0 + rt, o);
+                    }
+                }
+            }
+        }
+        // every lane of this warp is done reading the stage
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + stage);
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+}
+
 // Resident CTAs per SM of one kernel instantiation for a given dynamic shared-memory size.  The size
 // depends on the model (its padded W), not on the instantiation, so the answer is cached per kernel,
 // device and size; the opt-in above 48 KB is made once per kernel and device.  (Keyed by the kernel's
@@ -712,6 +858,79 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
     return LR_OK;
 }
 
+namespace {
+
+template <int LANES, int NS>
+int launch_flat_inst(const Model& m, const ScoreArgs& a) {
+    constexpr int U = NS == 1 ? 8 : 4;
+    constexpr int GROUP = (32 / LANES) * U;
+    auto kern = narrow_flat_kernel<LANES, NS, U>;
+    // a tile = whole row groups (GROUP rows, a multiple of 4), about 32 KB of them
+    const int64_t group_bytes = (int64_t)GROUP * a.ldx * 4;
+    const int64_t gpt = group_bytes >= 32768 ? 1 : 32768 / group_bytes;
+    const int tile_rows = (int)(GROUP * gpt);
+    const uint32_t stage_bytes = (uint32_t)(((int64_t)tile_rows * a.ldx * 4 + 16 + 15) & ~int64_t(15));
+    const size_t wbytes = (size_t)NS * m.narrow_dpad * sizeof(float);
+    int stages = (int)((kFlatSmemBudget - 256 - (int64_t)wbytes) / stage_bytes);
+    if (stages > 12) stages = 12;
+    if (stages < 3) return -1;
+    const size_t smem = 128 * ((2 * stages * 8 + 127) / 128) + wbytes + (size_t)stages * stage_bytes;
+    {
+        static std::map<std::pair<const void*, int>, bool> opted;
+        static std::mutex mu;
+        std::lock_guard<std::mutex> lock(mu);
+        bool& done = opted[{reinterpret_cast<const void*>(kern), m.device}];
+        if (!done) {
+            LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatSmemBudget));
+            done = true;
+        }
+    }
+    const int64_t tiles = (a.n_rows + tile_rows - 1) / tile_rows;
+    const int grid = (int)(tiles < m.num_sms ? tiles : m.num_sms);
+    Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
+    kern<<<grid, kFlatThreads, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad, tile_rows, stages,
+                                                 stage_bytes, m.Wn, m.bn, o);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
+template <int LANES>
+int launch_flat_lanes(const Model& m, const ScoreArgs& a) {
+    switch (m.narrow_ns) {
+        case 1: return launch_flat_inst<LANES, 1>(m, a);
+        case 3: return launch_flat_inst<LANES, 3>(m, a);
+        case 4: return launch_flat_inst<LANES, 4>(m, a);
+    }
+    return -1;      // 5..16 classes: the scalar-load form of the register-tile kernel measured faster
+}
+
+// Returns -1 when the flat-tile kernel does not apply (caller falls through to the scalar-load kernels).
+int launch_flat(const Model& m, const ScoreArgs& a) {
+    // lanes per row as in the 128-bit kernels (one lane per four floats, up to 32): a lane then makes
+    // four scalar shared loads where those make one vector load, and the cross-lane reduction and the
+    // epilogue stay as cheap per row as there.  LRS_FLAT_LANES overrides (tuning).
+    const int chunks = (m.n_features + 3) / 4;
+    int lanes = 4;
+    while (lanes < chunks && lanes < 32) lanes <<= 1;
+    // d just above a power of two (33: 16 lanes x 3 steps = 48 slots): half the lanes waste less (8 x 5 = 40)
+    if (lanes > 4 && lanes <= 16) {
+        const int d = m.n_features;
+        const int full = (d + lanes - 1) / lanes * lanes, half = (d + lanes / 2 - 1) / (lanes / 2) * (lanes / 2);
+        if (half < full) lanes /= 2;
+    }
+    static const int forced = [] { const char* e = getenv("LRS_FLAT_LANES"); return e ? atoi(e) : 0; }();
+    if (forced) lanes = forced;
+    switch (lanes) {
+        case 4: return launch_flat_lanes<4>(m, a);
+        case 8: return launch_flat_lanes<8>(m, a);
+        case 16: return launch_flat_lanes<16>(m, a);
+        default: return launch_flat_lanes<32>(m, a);
+    }
+}
+
+}  // namespace
+
 int narrow_launch(const Model& m, const ScoreArgs& a) {
     if (!m.Wn) return fail(LR_ERR_INVALID, "narrow path does not serve this model shape");
     const bool vec = (m.n_features % 4 == 0) && (a.ldx % 4 == 0) &&
@@ -719,6 +938,13 @@ int narrow_launch(const Model& m, const ScoreArgs& a) {
     // Opt-in: large dense batches through the bulk-copy ring (see narrow_bulk_kernel).
     if (vec && m.narrow_bulk && a.ldx == m.n_features && m.n_features <= 128 && a.n_rows >= m.narrow_bulk_min_rows) {
         const int rc = launch_bulk(m, a);
+        if (rc >= 0) return rc;
+    }
+    // Rows that are not 16-byte aligned: whole tiles of rows through shared memory (see narrow_flat_kernel);
+    // batches of a few rows keep the plain scalar-load kernel (one launch, no ring to fill).
+    static const bool flat_on = [] { const char* e = getenv("LRS_NARROW_FLAT"); return !e || atoi(e) != 0; }();
+    if (!vec && flat_on && a.ldx <= kFlatMaxLdx && a.n_rows >= 4096) {
+        const int rc = launch_flat(m, a);
         if (rc >= 0) return rc;
     }
     return vec ? launch_v<4>(m, a) : launch_v<1>(m, a);

@@ -154,6 +154,49 @@ def test_mid_class_counts(eng, ns):
         clf.close()
 
 
+@pytest.mark.parametrize("ns", [1, 2, 3, 4, 5, 10])
+def test_unaligned_rows_go_through_flat_tiles(eng, ns):
+    """Rows that are not 16-byte aligned (odd d, odd pitch, odd base) and >= 4096 of them: tiles of rows
+    are bulk-copied to shared memory and read back with scalar loads (<= 4 classes; 5 and 10 here check
+    that wider models keep working on the scalar-load kernels).  Against the oracle, and against the
+    scalar-load kernel, which serves the same rows when they come in batches below 4096."""
+    import torch
+    mlapi, lib = eng
+    rng = np.random.default_rng(ns * 17)
+    for d in (1, 3, 5, 7, 13, 30, 33, 61, 127, 255, 509) + ((1001, 2047) if ns == 1 else (1001,)):
+        W, b = synth.make_model(d, ns, 300 + ns + d)
+        clf = _model(eng, W, b)
+        clf.set_path(lib.PATH_NARROW)
+        for n in (4096, 4099, 20_011):
+            X = rng.standard_normal((n, d), dtype=np.float32)
+            out = _check(clf, X, W, b, f"flat ns={ns} d={d} n={n}")
+            if ns <= 4:                                         # lanes per row differ: same values to rounding
+                for lo in range(0, n, 4000):
+                    ref = clf.score_rows(X[lo:lo + 4000], **ALL)
+                    np.testing.assert_allclose(out["decision"][lo:lo + 4000], ref["decision"], rtol=1e-5, atol=2e-6)
+                    np.testing.assert_allclose(out["proba"][lo:lo + 4000], ref["proba"], rtol=1e-5, atol=2e-6)
+        clf.close()
+    # device rows with an odd pitch and a base that is only 4-byte aligned
+    d, n = 30, 9001
+    W, b = synth.make_model(d, ns, 41)
+    clf = _model(eng, W, b)
+    buf = rng.standard_normal((n, d + 7), dtype=np.float32)
+    for off in (0, 1, 2, 3):
+        Xh = buf[:, off:off + d]
+        Xt = torch.from_numpy(buf).cuda()[:, off:off + d]
+        out = clf.score_rows(Xt, **ALL)
+        torch.cuda.synchronize()
+        host = {k: v.cpu().numpy() for k, v in out.items()}
+        parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
+                             orc.predict_index(Xh, W, b), f"flat pitched ns={ns} off={off}")
+    # NaN in the last column of the last row is seen (and nothing past the matrix is read)
+    Xb = rng.standard_normal((5000, d), dtype=np.float32)
+    Xb[-1, -1] = np.nan
+    with pytest.raises(ValueError, match="NaN or infinity"):
+        clf.predict_proba(Xb)
+    clf.close()
+
+
 @pytest.mark.parametrize("d", [4, 5, 1000, 1024, 4097, 10_000, 100_000])
 def test_wide_shapes(eng, d):
     _, lib = eng
