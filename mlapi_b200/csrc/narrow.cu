@@ -33,6 +33,22 @@ constexpr int kThreads = 256;
 constexpr size_t kWSmemMax = 96 * 1024;    // W staged in shared memory up to here
 constexpr size_t kWL1Max = 192 * 1024;     // 5..16 columns: beyond shared memory, W is read through L1
 
+// Lanes per row of the scalar-load kernels (rows that are not 16-byte aligned), the plain one and the
+// flat-tile one alike: one lane per four floats as in the 128-bit kernels, up to 32 -- a lane then makes
+// four scalar loads where those make one vector load, and the cross-lane reduction and the epilogue
+// stay as cheap per row as there.
+inline int scalar_lanes(int d) {
+    const int chunks = (d + 3) / 4;
+    int lanes = 4;
+    while (lanes < chunks && lanes < 32) lanes <<= 1;
+    // d just above a power of two (33: 16 lanes x 3 steps = 48 slots): half the lanes waste less (8 x 5 = 40)
+    if (lanes > 4 && lanes <= 16) {
+        const int full = (d + lanes - 1) / lanes * lanes, half = (d + lanes / 2 - 1) / (lanes / 2) * (lanes / 2);
+        if (half < full) lanes /= 2;
+    }
+    return lanes;
+}
+
 // Score columns the kernels are instantiated for (padding columns carry zero weights and a -inf intercept).
 inline int padded_scores(int c) {
     return c == 1 ? 1 : c <= 3 ? 3 : c <= 4 ? 4 : c <= 6 ? 6 : c <= 8 ? 8 : c <= 10 ? 10 : c <= 12 ? 12 : 16;
@@ -501,7 +517,7 @@ constexpr int kFlatWarps = 16;                    // consumer warps (scalar shar
 constexpr int kFlatThreads = (kFlatWarps + 1) * 32;
 constexpr int kFlatSmemBudget = 200 * 1024;
 
-template <int LANES, int NS, int U>
+template <int V, int LANES, int NS, int U>
 __global__ void __launch_bounds__(kFlatThreads, 1)
 narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad, int tile_rows,
                    int stages, uint32_t stage_bytes, const float* __restrict__ Wn, const float* __restrict__ bn,
@@ -565,7 +581,9 @@ narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int
     // ===== consumers =====
     const int g = lane / LANES;
     const int s = lane % LANES;
-    const int dloop = (d + LANES - 1) / LANES * LANES;       // <= dpad; W is zero beyond d
+    constexpr int STEP = LANES * V;
+    const int k0 = s * V;
+    const int dloop = (d + STEP - 1) / STEP * STEP;          // <= dpad; W is zero beyond d
     float bias[NS];
 #pragma unroll
     for (int c = 0; c < NS; ++c) bias[c] = bn[c];
@@ -597,16 +615,33 @@ narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int
             for (int j = 0; j < U; ++j)
 #pragma unroll
                 for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
-            for (int k = s; k < dloop; k += LANES) {
+            // Same lanes, same pieces per lane and same order of FMAs as narrow_kernel<V, LANES, NS, U>:
+            // a row scores to the same bits whichever of the two kernels its batch size selects.
+            for (int k = k0; k < dloop; k += STEP) {
                 const int kc = k < d ? k : 0;                 // past-the-end lanes meet zero weights
-                float x[U];
+                float x[U][V];
 #pragma unroll
-                for (int j = 0; j < U; ++j) x[j] = rp[j][kc];
+                for (int j = 0; j < U; ++j) {
+                    if constexpr (V == 4) {                   // aligned rows: conflict-free 128-bit shared loads
+                        const float4 t = *reinterpret_cast<const float4*>(rp[j] + kc);
+                        x[j][0] = t.x; x[j][1] = t.y; x[j][2] = t.z; x[j][3] = t.w;
+                    } else {
+                        x[j][0] = rp[j][kc];
+                    }
+                }
 #pragma unroll
                 for (int c = 0; c < NS; ++c) {
-                    const float w = w_s[c * dpad + k];
+                    float w[V];
+                    if constexpr (V == 4) {
+                        const float4 t = *reinterpret_cast<const float4*>(w_s + c * dpad + k);
+                        w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
+                    } else {
+                        w[0] = w_s[c * dpad + k];
+                    }
 #pragma unroll
-                    for (int j = 0; j < U; ++j) acc[j][c] = fmaf(x[j], w, acc[j][c]);
+                    for (int j = 0; j < U; ++j)
+#pragma unroll
+                        for (int v = 0; v < V; ++v) acc[j][c] = fmaf(x[j][v], w[v], acc[j][c]);
                 }
             }
             lane_reduce<LANES / 2, U, NS, U>(acc, s);
@@ -759,6 +794,7 @@ int launch_v(const Model& m, const ScoreArgs& a) {
     int chunks = (m.n_features + V - 1) / V;
     int lanes = 1;
     while (lanes < chunks && lanes < 32) lanes <<= 1;
+    if (V == 1) lanes = scalar_lanes(m.n_features);
     const bool single = chunks <= lanes;
     switch (lanes) {
         case 1: return launch_lanes<V, 1>(m, a, single);
@@ -860,11 +896,11 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
 
 namespace {
 
-template <int LANES, int NS>
+template <int V, int LANES, int NS>
 int launch_flat_inst(const Model& m, const ScoreArgs& a) {
-    constexpr int U = NS == 1 ? 8 : 4;
+    constexpr int U = unroll_for<NS>();
     constexpr int GROUP = (32 / LANES) * U;
-    auto kern = narrow_flat_kernel<LANES, NS, U>;
+    auto kern = narrow_flat_kernel<V, LANES, NS, U>;
     // a tile = whole row groups (GROUP rows, a multiple of 4), about 32 KB of them
     const int64_t group_bytes = (int64_t)GROUP * a.ldx * 4;
     const int64_t gpt = group_bytes >= 32768 ? 1 : 32768 / group_bytes;
@@ -895,37 +931,24 @@ int launch_flat_inst(const Model& m, const ScoreArgs& a) {
     return LR_OK;
 }
 
-template <int LANES>
+template <int V, int LANES>
 int launch_flat_lanes(const Model& m, const ScoreArgs& a) {
     switch (m.narrow_ns) {
-        case 1: return launch_flat_inst<LANES, 1>(m, a);
-        case 3: return launch_flat_inst<LANES, 3>(m, a);
-        case 4: return launch_flat_inst<LANES, 4>(m, a);
+        case 1: return launch_flat_inst<V, LANES, 1>(m, a);
+        case 3: return launch_flat_inst<V, LANES, 3>(m, a);
+        case 4: return launch_flat_inst<V, LANES, 4>(m, a);
     }
     return -1;      // 5..16 classes: the scalar-load form of the register-tile kernel measured faster
 }
 
-// Returns -1 when the flat-tile kernel does not apply (caller falls through to the scalar-load kernels).
-int launch_flat(const Model& m, const ScoreArgs& a) {
-    // lanes per row as in the 128-bit kernels (one lane per four floats, up to 32): a lane then makes
-    // four scalar shared loads where those make one vector load, and the cross-lane reduction and the
-    // epilogue stay as cheap per row as there.  LRS_FLAT_LANES overrides (tuning).
-    const int chunks = (m.n_features + 3) / 4;
-    int lanes = 4;
-    while (lanes < chunks && lanes < 32) lanes <<= 1;
-    // d just above a power of two (33: 16 lanes x 3 steps = 48 slots): half the lanes waste less (8 x 5 = 40)
-    if (lanes > 4 && lanes <= 16) {
-        const int d = m.n_features;
-        const int full = (d + lanes - 1) / lanes * lanes, half = (d + lanes / 2 - 1) / (lanes / 2) * (lanes / 2);
-        if (half < full) lanes /= 2;
-    }
-    static const int forced = [] { const char* e = getenv("LRS_FLAT_LANES"); return e ? atoi(e) : 0; }();
-    if (forced) lanes = forced;
-    switch (lanes) {
-        case 4: return launch_flat_lanes<4>(m, a);
-        case 8: return launch_flat_lanes<8>(m, a);
-        case 16: return launch_flat_lanes<16>(m, a);
-        default: return launch_flat_lanes<32>(m, a);
+// Returns -1 when the flat-tile kernel does not apply (caller falls through to the plain-load kernels).
+int launch_flat(const Model& m, const ScoreArgs& a, bool vec) {
+    if (vec) return launch_flat_lanes<4, 32>(m, a);     // only used from d = 256 up: 32 lanes, as launch_v<4> picks
+    switch (scalar_lanes(m.n_features)) {
+        case 4: return launch_flat_lanes<1, 4>(m, a);
+        case 8: return launch_flat_lanes<1, 8>(m, a);
+        case 16: return launch_flat_lanes<1, 16>(m, a);
+        default: return launch_flat_lanes<1, 32>(m, a);
     }
 }
 
@@ -942,9 +965,11 @@ int narrow_launch(const Model& m, const ScoreArgs& a) {
     }
     // Rows that are not 16-byte aligned: whole tiles of rows through shared memory (see narrow_flat_kernel);
     // batches of a few rows keep the plain scalar-load kernel (one launch, no ring to fill).
+    // Aligned rows of 1 KB and more do better through the same ring with 128-bit shared loads (measured,
+    // binary: d=256 6.05 -> 6.68 TB/s, d=1000 5.96 -> 7.06; shorter rows are faster on direct loads).
     static const bool flat_on = [] { const char* e = getenv("LRS_NARROW_FLAT"); return !e || atoi(e) != 0; }();
-    if (!vec && flat_on && a.ldx <= kFlatMaxLdx && a.n_rows >= 4096) {
-        const int rc = launch_flat(m, a);
+    if (flat_on && m.narrow_ns <= 4 && (!vec || m.n_features >= 256) && a.ldx <= kFlatMaxLdx && a.n_rows >= 4096) {
+        const int rc = launch_flat(m, a, vec);
         if (rc >= 0) return rc;
     }
     return vec ? launch_v<4>(m, a) : launch_v<1>(m, a);

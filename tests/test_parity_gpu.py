@@ -158,8 +158,9 @@ def test_mid_class_counts(eng, ns):
 def test_unaligned_rows_go_through_flat_tiles(eng, ns):
     """Rows that are not 16-byte aligned (odd d, odd pitch, odd base) and >= 4096 of them: tiles of rows
     are bulk-copied to shared memory and read back with scalar loads (<= 4 classes; 5 and 10 here check
-    that wider models keep working on the scalar-load kernels).  Against the oracle, and against the
-    scalar-load kernel, which serves the same rows when they come in batches below 4096."""
+    that wider models keep working on the scalar-load kernels).  Against the oracle, and bit-for-bit
+    against the plain scalar-load kernel, which serves the same rows when they come in batches below 4096:
+    a row's result must not depend on the size of the batch it arrives in."""
     import torch
     mlapi, lib = eng
     rng = np.random.default_rng(ns * 17)
@@ -170,11 +171,11 @@ def test_unaligned_rows_go_through_flat_tiles(eng, ns):
         for n in (4096, 4099, 20_011):
             X = rng.standard_normal((n, d), dtype=np.float32)
             out = _check(clf, X, W, b, f"flat ns={ns} d={d} n={n}")
-            if ns <= 4:                                         # lanes per row differ: same values to rounding
+            if ns <= 4:                                         # same lanes, same order of FMAs: same bits
                 for lo in range(0, n, 4000):
                     ref = clf.score_rows(X[lo:lo + 4000], **ALL)
-                    np.testing.assert_allclose(out["decision"][lo:lo + 4000], ref["decision"], rtol=1e-5, atol=2e-6)
-                    np.testing.assert_allclose(out["proba"][lo:lo + 4000], ref["proba"], rtol=1e-5, atol=2e-6)
+                    for k in ref:
+                        assert np.array_equal(ref[k], out[k][lo:lo + 4000]), (k, ns, d, n, lo)
         clf.close()
     # device rows with an odd pitch and a base that is only 4-byte aligned
     d, n = 30, 9001
@@ -195,6 +196,28 @@ def test_unaligned_rows_go_through_flat_tiles(eng, ns):
     with pytest.raises(ValueError, match="NaN or infinity"):
         clf.predict_proba(Xb)
     clf.close()
+
+
+@pytest.mark.parametrize("ns", [1, 3, 4])
+def test_long_aligned_rows_go_through_flat_tiles(eng, ns):
+    """Aligned rows of 1 KB and more (d >= 256, <= 4 classes) in batches of >= 4096 take the same ring with
+    128-bit shared loads; same bits as the direct-load kernel that serves smaller batches."""
+    _, lib = eng
+    rng = np.random.default_rng(ns + 90)
+    for d in (256, 260, 512, 1000, 2048):
+        if ns == 1 and d >= 1024:
+            continue                                            # binary d >= 1024 belongs to the wide path
+        W, b = synth.make_model(d, ns, 80 + d)
+        clf = _model(eng, W, b)
+        clf.set_path(lib.PATH_NARROW)
+        for n in (4096, 6007):
+            X = rng.standard_normal((n, d), dtype=np.float32)
+            out = _check(clf, X, W, b, f"flat aligned ns={ns} d={d} n={n}")
+            for lo in range(0, n, 4000):
+                ref = clf.score_rows(X[lo:lo + 4000], **ALL)
+                for k in ref:
+                    assert np.array_equal(ref[k], out[k][lo:lo + 4000]), (k, ns, d, n, lo)
+        clf.close()
 
 
 @pytest.mark.parametrize("d", [4, 5, 1000, 1024, 4097, 10_000, 100_000])
