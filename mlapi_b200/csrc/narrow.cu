@@ -943,7 +943,12 @@ int launch_flat_lanes(const Model& m, const ScoreArgs& a) {
 
 // Returns -1 when the flat-tile kernel does not apply (caller falls through to the plain-load kernels).
 int launch_flat(const Model& m, const ScoreArgs& a, bool vec) {
-    if (vec) return launch_flat_lanes<4, 32>(m, a);     // only used from d = 256 up: 32 lanes, as launch_v<4> picks
+    if (vec) {                                           // lanes as launch_v<4> picks them
+        const int chunks = m.n_features / 4;
+        if (chunks <= 8) return launch_flat_lanes<4, 8>(m, a);
+        if (chunks <= 16) return launch_flat_lanes<4, 16>(m, a);
+        return launch_flat_lanes<4, 32>(m, a);
+    }
     switch (scalar_lanes(m.n_features)) {
         case 4: return launch_flat_lanes<1, 4>(m, a);
         case 8: return launch_flat_lanes<1, 8>(m, a);
@@ -968,7 +973,9 @@ int narrow_launch(const Model& m, const ScoreArgs& a) {
     // Aligned rows of 1 KB and more do better through the same ring with 128-bit shared loads (measured,
     // binary: d=256 6.05 -> 6.68 TB/s, d=1000 5.96 -> 7.06; shorter rows are faster on direct loads).
     static const bool flat_on = [] { const char* e = getenv("LRS_NARROW_FLAT"); return !e || atoi(e) != 0; }();
-    if (flat_on && m.narrow_ns <= 4 && (!vec || m.n_features >= 256) && a.ldx <= kFlatMaxLdx && a.n_rows >= 4096) {
+    static const int flat_min_d = [] { const char* e = getenv("LRS_NARROW_FLAT_MIN_D"); return e ? atoi(e) : 256; }();
+    if (flat_on && m.narrow_ns <= 4 && (!vec || (m.n_features >= flat_min_d && m.n_features >= 20)) && a.ldx <= kFlatMaxLdx &&
+        a.n_rows >= 4096) {
         const int rc = launch_flat(m, a, vec);
         if (rc >= 0) return rc;
     }
