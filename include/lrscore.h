@@ -161,6 +161,18 @@ int lr_loss_grad_static(const float* X_dev, const int32_t* y_dev, int64_t n_rows
                         double* out_dev, void* stream);
 
 /*
+ * out_dev[k] = sum_i r_dev[i] * X_dev[i][k]  (float64 [n_features]): the transposed product of a binary
+ * model's gradient, `X.T @ grad_pointwise` in LinearModelLoss.loss_gradient
+ * (SK/linear_model/_linear_loss.py:353-357), for feature counts beyond lr_loss_grad (the d = 100 000
+ * config).  The forward pass of such a model is lr_score (the residual r = sigmoid(z) - y is known only
+ * after a whole row has been read), so X is streamed a second time here; HBM-bound.  Any n_features, any
+ * pitch (128-bit loads when rows are 16-byte aligned).  Sums over the rows given only: ranks all-reduce.
+ * Per-call scratch is stream-ordered (cudaMallocAsync).  Deterministic.
+ */
+int lr_weighted_row_sum(const float* X_dev, const float* r_dev, int64_t n_rows, int64_t ldx,
+                        int32_t n_features, double* out_dev, void* stream);
+
+/*
  * Page-locked host memory for the buffers handed to lr_score_host (the /predict micro-batcher's
  * staging rows, bench.py's e2e inputs).  With pageable memory the copies still work but the driver
  * stages them and the three-stream overlap is lost.  No reference counterpart: REF/main.py:20

@@ -37,6 +37,7 @@ SIGNATURES = {
                                C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "lr_loss_grad_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "lr_weighted_row_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "lr_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_uint64]),
     "lr_host_free": (C.c_int, [C.c_void_p]),
     "lr_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),

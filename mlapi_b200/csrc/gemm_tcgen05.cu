@@ -1234,6 +1234,38 @@ x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, 
     }
 }
 
+// FP16 operands of W, made on the device: class c (one CTA) is scaled by the power of two that puts its
+// largest |w| in [2, 4) and split into fp16 hi + lo halves from the float64 value; 1/scale goes to inv[c].
+__global__ void __launch_bounds__(256)
+w_split16_kernel(const double* __restrict__ coef, int d, int d16, __half* __restrict__ hi, __half* __restrict__ lo,
+                 float* __restrict__ inv) {
+    __shared__ double red[8];
+    const int c = blockIdx.x;
+    const double* w = coef + (size_t)c * d;
+    double mx = 0.0;
+    for (int k = threadIdx.x; k < d; k += 256) mx = fmax(mx, fabs(w[k]));      // fmax drops NaN, keeps inf
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmax(mx, red[i]);
+    double sc = 1.0;
+    if (mx > 0.0 && mx <= 1.7976931348623157e308) {
+        int e = 0;
+        frexp(mx, &e);
+        sc = ldexp(1.0, 2 - e);
+    }
+    if (threadIdx.x == 0) inv[c] = (float)(1.0 / sc);
+    for (int k = threadIdx.x; k < d; k += 256) {
+        const double v = w[k] * sc;
+        const __half h = __float2half_rn((float)v);
+        hi[(size_t)c * d16 + k] = h;
+        lo[(size_t)c * d16 + k] = __float2half_rn((float)(v - (double)__half2float(h)));
+    }
+}
+
 }  // namespace
 
 struct GemmPlan {
@@ -1387,16 +1419,12 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     for (int i = 0; i < 2; ++i)
         if (g->has[i] && g->layout[i].ncc * g->layout[i].nb * BN > g->c_pad) g->c_pad = g->layout[i].ncc * g->layout[i].nb * BN;
     if (const char* e = getenv("LRS_GEMM_FIXUP")) g->fixup = atoi(e) != 0;
-    std::vector<float> hi((size_t)g->c_pad * d4, 0.0f), lo((size_t)g->c_pad * d4, 0.0f), bias(g->c_pad, -INFINITY);
-    for (int c = 0; c < C; ++c) {
-        bias[c] = (float)intercept[c];
-        for (int k = 0; k < d; ++k) {
-            const double w = coef[(size_t)c * d + k];
-            const float h = tf32_rna_host((float)w);
-            hi[(size_t)c * d4 + k] = h;
-            lo[(size_t)c * d4 + k] = tf32_rna_host((float)(w - (double)h));
-        }
-    }
+    // 3xFP16 is the default arithmetic; LRS_GEMM_F16=0 selects 3xTF32.  Only the chosen one's copies of W are
+    // built (a refit rebuilds the model every iteration: the unused pair cost as much host time as the used one).
+    g->f16 = true;
+    if (const char* e = getenv("LRS_GEMM_F16")) g->f16 = atoi(e) != 0;
+    std::vector<float> bias(g->c_pad, -INFINITY);
+    for (int c = 0; c < C; ++c) bias[c] = (float)intercept[c];
     if (d4 != d) {
         // fp32 coefficients at the padded pitch, for the re-scoring pass over re-pitched rows (see gemm_launch)
         std::vector<float> w32((size_t)C * d4, 0.0f);
@@ -1406,53 +1434,53 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         LRS_CUDA(cudaMemcpy(g->w32_pad, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
     m.gemm = g;
-    const size_t bytes = hi.size() * sizeof(float);
-    LRS_CUDA(cudaMalloc(&g->w_hi, bytes));
-    LRS_CUDA(cudaMalloc(&g->w_lo, bytes));
     LRS_CUDA(cudaMalloc(&g->bias, bias.size() * sizeof(float)));
-    LRS_CUDA(cudaMemcpy(g->w_hi, hi.data(), bytes, cudaMemcpyHostToDevice));
-    LRS_CUDA(cudaMemcpy(g->w_lo, lo.data(), bytes, cudaMemcpyHostToDevice));
     LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
     int rc;
-    for (int i = 0; i < 2; ++i) {
-        if (!g->has[i]) continue;
-        auto& L = g->layout[i];
-        const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
-        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
-        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
-    }
-
-    // FP16 copies (3xFP16 mode, LRS_GEMM_F16=0 turns it off)
-    g->f16 = true;
-    if (const char* e = getenv("LRS_GEMM_F16")) g->f16 = atoi(e) != 0;
-    if (g->f16) {
-        g->d16 = (d + 7) / 8 * 8;
-        std::vector<__half> h16((size_t)g->c_pad * g->d16, __float2half_rn(0.0f)), l16(h16);
-        std::vector<float> inv(g->c_pad, 1.0f);
+    if (!g->f16) {
+        std::vector<float> hi((size_t)g->c_pad * d4, 0.0f), lo((size_t)g->c_pad * d4, 0.0f);
         for (int c = 0; c < C; ++c) {
-            double mx = 0.0;
-            for (int k = 0; k < d; ++k) mx = std::fmax(mx, std::fabs(coef[(size_t)c * d + k]));
-            double sc = 1.0;
-            if (mx > 0.0 && std::isfinite(mx)) {
-                int e = 0;
-                std::frexp(mx, &e);
-                sc = std::ldexp(1.0, 2 - e);            // largest |w| of the class lands in [2, 4)
-            }
-            inv[c] = (float)(1.0 / sc);
             for (int k = 0; k < d; ++k) {
-                const double w = coef[(size_t)c * d + k] * sc;
-                const __half h = __float2half_rn((float)w);
-                h16[(size_t)c * g->d16 + k] = h;
-                l16[(size_t)c * g->d16 + k] = __float2half_rn((float)(w - (double)__half2float(h)));
+                const double w = coef[(size_t)c * d + k];
+                const float h = tf32_rna_host((float)w);
+                hi[(size_t)c * d4 + k] = h;
+                lo[(size_t)c * d4 + k] = tf32_rna_host((float)(w - (double)h));
             }
         }
-        const size_t b16 = h16.size() * sizeof(__half);
+        const size_t bytes = hi.size() * sizeof(float);
+        LRS_CUDA(cudaMalloc(&g->w_hi, bytes));
+        LRS_CUDA(cudaMalloc(&g->w_lo, bytes));
+        LRS_CUDA(cudaMemcpy(g->w_hi, hi.data(), bytes, cudaMemcpyHostToDevice));
+        LRS_CUDA(cudaMemcpy(g->w_lo, lo.data(), bytes, cudaMemcpyHostToDevice));
+        for (int i = 0; i < 2; ++i) {
+            if (!g->has[i]) continue;
+            auto& L = g->layout[i];
+            const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
+            if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
+            if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
+        }
+    }
+
+    if (g->f16) {
+        g->d16 = (d + 7) / 8 * 8;
+        // Scale + hi/lo split on the device from the float64 coefficients (one CTA per class): on the host
+        // the software fp16 conversions took 40 ms per million coefficients, which a refit pays per iteration.
+        const size_t b16 = (size_t)g->c_pad * g->d16 * sizeof(__half);
+        std::vector<float> inv(g->c_pad, 1.0f);
+        double* coef_dev = nullptr;
         LRS_CUDA(cudaMalloc(&g->w16_hi, b16));
         LRS_CUDA(cudaMalloc(&g->w16_lo, b16));
         LRS_CUDA(cudaMalloc(&g->col_inv_scale, inv.size() * sizeof(float)));
-        LRS_CUDA(cudaMemcpy(g->w16_hi, h16.data(), b16, cudaMemcpyHostToDevice));
-        LRS_CUDA(cudaMemcpy(g->w16_lo, l16.data(), b16, cudaMemcpyHostToDevice));
+        LRS_CUDA(cudaMalloc(&coef_dev, (size_t)C * d * sizeof(double)));
+        LRS_CUDA(cudaMemset(g->w16_hi, 0, b16));
+        LRS_CUDA(cudaMemset(g->w16_lo, 0, b16));
         LRS_CUDA(cudaMemcpy(g->col_inv_scale, inv.data(), inv.size() * sizeof(float), cudaMemcpyHostToDevice));
+        LRS_CUDA(cudaMemcpy(coef_dev, coef, (size_t)C * d * sizeof(double), cudaMemcpyHostToDevice));
+        w_split16_kernel<<<C, 256>>>(coef_dev, d, g->d16, g->w16_hi, g->w16_lo, g->col_inv_scale);
+        count_launch();
+        const cudaError_t ke = cudaDeviceSynchronize();
+        cudaFree(coef_dev);
+        if (ke != cudaSuccess) return fail(LR_ERR_CUDA, std::string("w_split16_kernel: ") + cudaGetErrorString(ke));
         for (int i = 0; i < 2; ++i) {
             if (!g->has[i]) continue;
             auto& L = g->layout[i];

@@ -449,3 +449,115 @@ extern "C" int lr_loss_grad_static(const float* X_dev, const int32_t* y_dev, int
     RefitArgs a{X_dev, y_dev, n_rows, ldx, W_dev, b_dev, n_scores, n_features, out_dev, nullptr, nullptr, 0};
     return run_refit(a, scratch, kStaticScratchBytes, s);
 }
+
+// ---- lr_weighted_row_sum: out[k] = sum_i r[i] * X[i][k] -----------------------------------------------
+// The transposed product of a binary model's gradient, `X.T @ grad_pointwise`
+// (SK/linear_model/_linear_loss.py:353-357), for feature counts beyond lr_loss_grad: the forward pass of
+// such a model (d = 100k in the BASELINE config) is the wide scoring kernel, and the residual r is known
+// only after a whole row has been read, so X is streamed a second time here.  HBM-bound: 4 bytes per
+// element of X, nothing else of size.  Grid = column strips (256 threads x one 128-bit piece) x row
+// blocks; each CTA keeps its strip's sums in registers, eight rows in flight per thread; per-block partial
+// vectors are then added in float64 in a fixed order (deterministic).
+namespace lrs {
+namespace {
+
+template <int V>
+__global__ void __launch_bounds__(256)
+wsum_kernel(const float* __restrict__ X, const float* __restrict__ r, int64_t n_rows, int64_t ldx, int d,
+            int64_t rows_per_block, float* __restrict__ partial) {
+    const int k = (blockIdx.x * 256 + threadIdx.x) * V;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t r1 = r0 + rows_per_block < n_rows ? r0 + rows_per_block : n_rows;
+    float acc[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) acc[v] = 0.0f;
+    if (k < d) {                                       // V == 4: d % 4 == 0, the piece is whole
+        const float* p = X + r0 * ldx + k;
+        int64_t i = r0;
+        for (; i + 8 <= r1; i += 8, p += 8 * ldx) {
+            float x[8][V], w[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if constexpr (V == 4) {
+                    const float4 t = ldg_stream4(p + j * ldx);
+                    x[j][0] = t.x; x[j][1] = t.y; x[j][2] = t.z; x[j][3] = t.w;
+                } else {
+                    x[j][0] = ldg_stream1(p + j * ldx);
+                }
+                w[j] = __ldg(r + i + j);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int v = 0; v < V; ++v) acc[v] = fmaf(w[j], x[j][v], acc[v]);
+        }
+        for (; i < r1; ++i, p += ldx) {
+            const float w = __ldg(r + i);
+            if constexpr (V == 4) {
+                const float4 t = ldg_stream4(p);
+                acc[0] = fmaf(w, t.x, acc[0]); acc[1] = fmaf(w, t.y, acc[1]);
+                acc[2] = fmaf(w, t.z, acc[2]); acc[3] = fmaf(w, t.w, acc[3]);
+            } else {
+                acc[0] = fmaf(w, ldg_stream1(p), acc[0]);
+            }
+        }
+        float* o = partial + (size_t)blockIdx.y * d + k;
+#pragma unroll
+        for (int v = 0; v < V; ++v) o[v] = acc[v];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+wsum_reduce_kernel(const float* __restrict__ partial, int n_blocks, int d, double* __restrict__ out) {
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= d) return;
+    double s = 0.0;
+    for (int b = 0; b < n_blocks; ++b) s += (double)partial[(size_t)b * d + k];
+    out[k] = s;
+}
+
+}  // namespace
+}  // namespace lrs
+
+extern "C" int lr_weighted_row_sum(const float* X_dev, const float* r_dev, int64_t n_rows, int64_t ldx,
+                                   int32_t n_features, double* out_dev, void* stream) {
+    using namespace lrs;
+    if (!X_dev || !r_dev || !out_dev) return fail(LR_ERR_INVALID, "lr_weighted_row_sum: null pointer");
+    if (n_rows < 0 || n_features < 1 || ldx < n_features) return fail(LR_ERR_INVALID, "lr_weighted_row_sum: bad shape");
+    int dev = 0;
+    LRS_CUDA(cudaGetDevice(&dev));
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, X_dev) == cudaSuccess && attr.type == cudaMemoryTypeDevice && attr.device != dev) {
+        LRS_CUDA(cudaSetDevice(attr.device));
+        dev = attr.device;
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const int d = n_features;
+    if (n_rows == 0) {
+        LRS_CUDA(cudaMemsetAsync(out_dev, 0, (size_t)d * sizeof(double), s));
+        return LR_OK;
+    }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const bool vec = d % 4 == 0 && ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(X_dev) & 15u) == 0;
+    const int per = vec ? 1024 : 256;                      // columns per strip
+    const int strips = (d + per - 1) / per;
+    // enough row blocks for ~6 CTAs per SM, at least 64 rows each
+    int64_t blocks = ((int64_t)sms * 6 + strips - 1) / strips;
+    if (blocks > (n_rows + 63) / 64) blocks = (n_rows + 63) / 64;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 65535) blocks = 65535;
+    const int64_t rows_per_block = (n_rows + blocks - 1) / blocks;
+    blocks = (n_rows + rows_per_block - 1) / rows_per_block;
+    float* partial = nullptr;
+    LRS_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&partial), (size_t)blocks * d * sizeof(float), s));
+    const dim3 grid((unsigned)strips, (unsigned)blocks);
+    if (vec) wsum_kernel<4><<<grid, 256, 0, s>>>(X_dev, r_dev, n_rows, ldx, d, rows_per_block, partial);
+    else wsum_kernel<1><<<grid, 256, 0, s>>>(X_dev, r_dev, n_rows, ldx, d, rows_per_block, partial);
+    count_launch();
+    wsum_reduce_kernel<<<(d + 255) / 256, 256, 0, s>>>(partial, (int)blocks, d, out_dev);
+    count_launch();
+    LRS_CUDA(cudaGetLastError());
+    LRS_CUDA(cudaFreeAsync(partial, s));
+    return LR_OK;
+}

@@ -4,10 +4,19 @@ loss/gradient pass on the GPU and, across ranks, ONE NCCL all-reduce per iterati
 scikit-learn minimises  (1/n) sum_i loss_i + 1/(2 C n) ||W||^2  (intercept unpenalised) with
 scipy's L-BFGS-B (SK/linear_model/_logistic.py:580-598: maxiter=max_iter, maxls=50, gtol=tol,
 ftol=64*eps, zero start).  The same optimiser runs here on every rank in float64; per iteration the
-current (W, b) goes to the device (a few hundred bytes), `lr_loss_grad` reduces this rank's row
-shard to one float64 vector [loss | grad_W | grad_b], the ranks sum that vector
-(`sharding.allreduce_sum`: 132 B at d=32 binary), and every rank takes the identical step.
-Torch is the allocator and the NCCL binding here; the arithmetic is liblrscore's.
+current (W, b) goes to the device, this rank's row shard is reduced to one float64 vector
+[loss | grad_W | grad_b], the ranks sum that vector (`sharding.allreduce_sum`: 132 B at d=32 binary,
+400 KB at d=100k, 4.1 MB at 1000 x 1024), and every rank takes the identical step.
+
+Two ways to that vector:
+  * small models (<= 8 score rows, d <= 128): `lr_loss_grad`, one fused pass over X (refit.cu);
+  * every other shape (the d=100k binary and the 1000-class configs among them): the forward pass --
+    scores, softmax, labels -- is the scoring engine's own kernels (`lr_score` on the current iterate,
+    any path), the residual `softmax - onehot` is formed in place in the probability block, and the
+    transposed product `residual^T X` is `lr_weighted_row_sum` (a second streaming pass over X) for a
+    binary model and plain library GEMMs (cuBLAS through torch: three TF32 tensor-core products of hi/lo
+    splits, fp32-grade) for a multinomial one, taken in row blocks and accumulated in float64.
+Torch is the allocator, the NCCL binding and, in the second way, the door to cuBLAS.
 """
 from __future__ import annotations
 
@@ -47,6 +56,103 @@ def loss_grad_sums(X, y_idx, W32, b32, out):
     return out
 
 
+def fused_kernel_serves(rows: int, d: int, X) -> bool:
+    """Shapes `lr_loss_grad` takes (include/lrscore.h): <= 8 score rows and d <= 128 with 16-byte aligned
+    rows, or d <= 32 with any rows."""
+    aligned = d % 4 == 0 and X.stride(0) % 4 == 0 and X.data_ptr() % 16 == 0
+    return rows <= 8 and (d <= 32 or (d <= 128 and aligned))
+
+
+def _tf32_split(a):
+    """a = hi + lo with hi exactly representable in TF32 (top 19 bits kept): the tensor cores then take
+    hi as it is and round only lo, i.e. at 2^-21 of a."""
+    import torch
+    hi = (a.view(torch.int32) & -8192).view(torch.float32)
+    return hi, a - hi
+
+
+def _mm_t_3xtf32(R, X):
+    """R^T X (C x n times n x d) as three TF32 tensor-core GEMMs, hi*hi + hi*lo + lo*hi, accumulated in
+    fp32 -- fp32-grade products at several times the speed of cuBLAS's fp32 SIMT GEMM (58 TFLOP/s
+    measured on the 1000 x 1024 gradient)."""
+    import torch
+    r_hi, r_lo = _tf32_split(R)
+    x_hi, x_lo = _tf32_split(X)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        out = torch.mm(r_hi.t(), x_hi)
+        out.addmm_(r_hi.t(), x_lo)
+        out.addmm_(r_lo.t(), x_hi)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    return out
+
+
+def loss_grad_sums_general(X, y_idx, Wb64, out, block_rows: int = 0):
+    """[sum loss | sum r x^T | sum r] over this rank's rows for any model shape, into `out` (float64).
+
+    Forward pass by the scoring engine on the current iterate (`Wb64`: rows x (d+1), float64, last
+    column the intercept); residual in place; `residual^T X` per row block by `lr_weighted_row_sum`
+    (binary) or cuBLAS 3xTF32 (multinomial), blocks summed in float64.  Follows SK/linear_model/_linear_loss.py:291-378 like `lr_loss_grad`:
+    binary loss log(1+e^z) - y z with residual sigmoid(z) - y, multinomial logsumexp(z) - z_y with
+    softmax(z) - onehot(y)."""
+    import torch
+    from .estimator import B200LogisticRegression
+
+    n, d = X.shape
+    rows = Wb64.shape[0]
+    dev = X.device
+    est = B200LogisticRegression(Wb64[:, :d], Wb64[:, d], np.arange(max(rows, 2)), devices=[dev.index])
+    if block_rows <= 0:                                       # ~1 GB of probabilities (or of X) per block
+        block_rows = max(1024, min(n, (1 << 28) // max(rows, d // 8, 2)))
+    lib = _lib.load()
+    loss = torch.zeros((), dtype=torch.float64, device=dev)
+    gblk = torch.empty((d,), dtype=torch.float64, device=dev)
+    gW = torch.zeros((rows, d), dtype=torch.float64, device=dev)
+    gb = torch.zeros((rows,), dtype=torch.float64, device=dev)
+    tf32 = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False             # the gradient wants fp32 products
+    try:
+        for lo in range(0, n, block_rows):
+            Xc = X[lo:lo + block_rows]
+            yc = y_idx[lo:lo + block_rows].long()
+            if rows == 1:
+                res = est._score_device(Xc, True, True, False, False)
+                z = res["decision"].double()
+                yv = yc.double()
+                # log(1 + e^z) - y z, evaluated as max(z, 0) + log1p(e^-|z|) (SK/_loss/_loss.pyx.tp:728-751)
+                loss += (torch.clamp(z, min=0) + torch.log1p(torch.exp(-z.abs())) - yv * z).sum()
+                r = (res["proba"][:, 1] - yc.float()).contiguous()
+                stream = torch.cuda.current_stream(dev).cuda_stream
+                with torch.cuda.device(dev):                  # X^T r: the library's own streaming kernel
+                    _lib.check(lib.lr_weighted_row_sum(C.c_void_p(Xc.data_ptr()), C.c_void_p(r.data_ptr()), Xc.shape[0],
+                                                       Xc.stride(0), d, C.c_void_p(gblk.data_ptr()), C.c_void_p(stream)))
+                gW[0] += gblk
+                gb[0] += r.double().sum()
+            else:
+                res = est._score_device(Xc, True, True, True, True)
+                P, Z = res["proba"], res["decision"]
+                lab = res["label"].long()
+                # logsumexp from the winning class: lse = z_max - log p_max (p_max >= 1/C never underflows)
+                lse = Z.gather(1, lab[:, None]).squeeze(1).double() - torch.log(res["maxprob"].double())
+                loss += (lse - Z.gather(1, yc[:, None]).squeeze(1).double()).sum()
+                P[torch.arange(P.shape[0], device=dev), yc] -= 1.0          # residual, in place
+                gW += _mm_t_3xtf32(P, Xc).double()
+                ones = torch.ones((P.shape[0],), dtype=torch.float32, device=dev)
+                gb += torch.mv(P.t(), ones).double()
+        bad = est.take_nonfinite()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        est.close()
+    if bad:
+        raise ValueError("Input X contains NaN or infinity.")
+    out[0] = loss
+    out[1:1 + rows * d] = gW.reshape(-1)
+    out[1 + rows * d:] = gb
+    return out
+
+
 def fit(X, y, classes=None, C_reg: float = 1.0, tol: float = 1e-4, max_iter: int = 100,
         device: Optional[int] = None) -> FitResult:
     """Fit on this rank's rows `X` (n_local, d) / labels `y`.  With torch.distributed initialised
@@ -81,11 +187,16 @@ def fit(X, y, classes=None, C_reg: float = 1.0, tol: float = 1e-4, max_iter: int
     b32 = torch.empty((rows,), dtype=torch.float32, device=dev)
     evals = {"n": 0}
 
+    fused = fused_kernel_serves(rows, d, X)
+
     def fun(w):
         Wb = w.reshape(rows, d + 1)
-        W32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, :d], dtype=np.float32)))
-        b32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, d], dtype=np.float32)))
-        loss_grad_sums(X, y_idx, W32, b32, out)
+        if fused:
+            W32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, :d], dtype=np.float32)))
+            b32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, d], dtype=np.float32)))
+            loss_grad_sums(X, y_idx, W32, b32, out)
+        else:
+            loss_grad_sums_general(X, y_idx, Wb, out)
         allreduce_sum(out)                                    # the design's only collective
         h = out.cpu().numpy()
         evals["n"] += 1

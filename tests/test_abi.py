@@ -43,13 +43,14 @@ def test_ctypes_table_matches_header(lib):
 def test_argument_errors_are_status_codes(lib):
     from mlapi_b200 import _lib
     assert lib.lr_abi_version() >= 1
+    launched = lib.lr_launch_count()
     assert lib.lr_model_info(None, None, None, None) == _lib.LR_ERR_INVALID
     assert "NULL" in _lib.last_error()
     assert lib.lr_score(None, None, 1, 4, None, None, None, None, None) == _lib.LR_ERR_INVALID
     assert lib.lr_score_host(None, None, 1, 4, None, None, None, None) == _lib.LR_ERR_INVALID
     out = C.c_void_p()
     assert lib.lr_model_create(None, None, 1, 4, 0, C.byref(out)) == _lib.LR_ERR_INVALID
-    assert lib.lr_launch_count() == 0
+    assert lib.lr_launch_count() == launched                # rejected calls launch nothing
 
 
 def test_no_gpu_fails_loudly(lib):

@@ -108,3 +108,99 @@ def test_fit_binary_d32_matches_sklearn(eng):
     res = eng.fit(X, y)
     np.testing.assert_allclose(res.coef_, sk.coef_, atol=2e-3)
     np.testing.assert_allclose(res.intercept_, sk.intercept_, atol=2e-3)
+
+
+def _sums_general(refit, X, y, W, b, **kw):
+    import torch
+    Xt = torch.as_tensor(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    yt = torch.as_tensor(np.asarray(y, dtype=np.int32)).cuda()
+    Wb = np.concatenate([np.atleast_2d(W), np.atleast_1d(b)[:, None]], axis=1).astype(np.float64)
+    out = torch.empty(1 + Wb.shape[0] * Wb.shape[1], dtype=torch.float64, device="cuda")
+    refit.loss_grad_sums_general(Xt, yt, Wb, out, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("d,rows", [(300, 1), (333, 1), (2000, 1), (40, 12), (64, 20), (130, 37), (1024, 100), (256, 300)])
+def test_general_loss_grad_against_oracle(eng, d, rows):
+    """Shapes beyond the fused kernel (wide binary, 5..16 classes, tensor-core multinomial): forward pass
+    by the scoring engine, residual^T X by cuBLAS, against the float64 oracle
+    (SK/linear_model/_linear_loss.py:291-378).  Several row blocks on purpose."""
+    rng = np.random.default_rng(d + rows)
+    n = 3001
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    W, b = synth.make_model(d, rows, 3 + d)
+    y = rng.integers(0, 2 if rows == 1 else rows, n)
+    h = _sums_general(eng, X, y, W, b, block_rows=1024)
+    W32, b32 = W.astype(np.float32).astype(np.float64), b.astype(np.float32).astype(np.float64)
+    loss, gW, gb = orc.loss_gradient(W32, b32, X, y, 0.0)
+    np.testing.assert_allclose(h[0] / n, loss, rtol=2e-5, atol=1e-6)
+    np.testing.assert_allclose(h[1:1 + rows * d].reshape(rows, d) / n, gW, atol=5e-6, rtol=1e-4)
+    np.testing.assert_allclose(h[1 + rows * d:] / n, gb, atol=5e-6, rtol=1e-4)
+    # one block or several: same sums to rounding
+    h1 = _sums_general(eng, X, y, W, b)
+    np.testing.assert_allclose(h1 / n, h / n, rtol=1e-5, atol=2e-7)
+
+
+def test_fit_multinomial_20_classes_matches_sklearn(eng):
+    """A fit that needs the general path end to end (20 classes: tensor-core forward pass)."""
+    from sklearn.linear_model import LogisticRegression
+    rng = np.random.default_rng(9)
+    n, d, c = 6000, 64, 20
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Wt, bt = synth.make_model(d, c, 77)
+    P = orc.predict_proba(X, Wt * 4, bt)
+    y = np.array([rng.choice(c, p=p) for p in P])
+    sk = LogisticRegression(max_iter=200).fit(X.astype(np.float64), y)
+    res = eng.fit(X, y, max_iter=200)
+    lam = 1.0 / n
+    f_ours, gW, gb = orc.loss_gradient(res.coef_, res.intercept_, X, y, lam)
+    f_sk, _, _ = orc.loss_gradient(sk.coef_, sk.intercept_, X, y, lam)
+    assert abs(f_ours - f_sk) <= 5e-6 * max(1.0, abs(f_sk)), (f_ours, f_sk)
+    assert max(np.abs(gW).max(), np.abs(gb).max()) <= 5e-4
+    agree = np.mean(orc.predict_index(X, res.coef_, res.intercept_) == orc.predict_index(X, sk.coef_, sk.intercept_))
+    assert agree >= 0.998, agree
+
+
+def test_fit_wide_binary_matches_sklearn(eng):
+    from sklearn.linear_model import LogisticRegression
+    rng = np.random.default_rng(10)
+    n, d = 3000, 2000
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Wt, bt = synth.make_model(d, 1, 5)
+    y = (rng.random(n) < orc.expit(orc.decision_function(X, Wt * 3, bt))).astype(np.int64)
+    sk = LogisticRegression().fit(X.astype(np.float64), y)
+    res = eng.fit(X, y)
+    lam = 1.0 / n
+    f_ours, gW, gb = orc.loss_gradient(res.coef_, res.intercept_, X, y, lam)
+    f_sk, _, _ = orc.loss_gradient(sk.coef_, sk.intercept_, X, y, lam)
+    assert abs(f_ours - f_sk) <= 5e-6 * max(1.0, abs(f_sk)), (f_ours, f_sk)
+    assert max(np.abs(gW).max(), np.abs(gb).max()) <= 5e-4
+
+
+@pytest.mark.parametrize("n,d,pad", [(1, 8, 0), (63, 33, 0), (700, 1000, 0), (5000, 257, 3), (3000, 4096, 0), (129, 100_000, 0)])
+def test_weighted_row_sum_against_float64(eng, n, d, pad):
+    """lr_weighted_row_sum (X^T r, the binary gradient's transposed product,
+    SK/linear_model/_linear_loss.py:353-357): aligned and unaligned rows, padded pitch, twice the same bits."""
+    import ctypes as C
+    import torch
+    from mlapi_b200 import _lib
+    L = _lib.load()
+    rng = np.random.default_rng(n + d)
+    buf = rng.standard_normal((n, d + pad), dtype=np.float32)
+    r = rng.standard_normal(n).astype(np.float32)
+    Xt = torch.from_numpy(buf).cuda()[:, :d]
+    rt = torch.from_numpy(r).cuda()
+    out = torch.empty(d, dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+
+    def run():
+        _lib.check(L.lr_weighted_row_sum(C.c_void_p(Xt.data_ptr()), C.c_void_p(rt.data_ptr()), n, Xt.stride(0), d,
+                                         C.c_void_p(out.data_ptr()), C.c_void_p(st)))
+        torch.cuda.synchronize()
+        return out.cpu().numpy().copy()
+    got = run()
+    ref = buf[:, :d].astype(np.float64).T @ r.astype(np.float64)
+    scale = np.abs(buf[:, :d].astype(np.float64)).T @ np.abs(r.astype(np.float64))
+    assert np.all(np.abs(got - ref) <= 2e-6 * scale + 1e-9)
+    assert np.array_equal(run(), got)
