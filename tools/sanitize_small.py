@@ -34,6 +34,15 @@ for d, ns, n, path in ((32, 1, 1000, _lib.PATH_NARROW), (4, 3, 333, _lib.PATH_NA
     clf.set_path(path)
     check(f"path {_lib.PATH_NAMES[path]} d={d} C={ns} n={n}", clf, X, W, b)
 
+# this round's kernels: 5..16 classes (W in shared memory / through L1), flat tiles (unaligned and long aligned
+# rows, >= 4096 rows), small-N tensor form, re-pitched tensor path
+for d, ns, n in ((40, 10, 500), (61, 7, 300), (2600, 12, 200), (33, 1, 5000), (5, 1, 4100), (257, 3, 4100), (512, 1, 4100),
+                 (1001, 4, 4100), (64, 32, 1000), (200, 100, 700), (131, 100, 500), (1022, 300, 260)):
+    W, b = synth.make_model(d, ns, d + ns)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    clf = B200LogisticRegression(W, b, np.arange(max(ns, 2)), out_dtype=np.float32)
+    check(f"auto d={d} C={ns} n={n}", clf, X, W, b)
+
 os.environ["LRS_NARROW_BULK"] = "1"
 os.environ["LRS_NARROW_BULK_MIN_ROWS"] = "1"
 W, b = synth.make_model(32, 1, 3)
@@ -64,4 +73,13 @@ rc = L.lr_loss_grad_static(C.c_void_p(X.data_ptr()), C.c_void_p(y.data_ptr()), 5
 torch.cuda.synchronize()
 assert rc == 0 and torch.allclose(out, out2, rtol=1e-5, atol=1e-6)
 print("refit + static refit ok", flush=True)
+for n, d, rows in ((3000, 300, 1), (2000, 64, 20)):
+    Xg = torch.randn(n, d, device="cuda")
+    yg = torch.randint(0, max(rows, 2), (n,), device="cuda", dtype=torch.int32)
+    Wb = np.random.default_rng(1).standard_normal((rows, d + 1)) * 0.1
+    og = torch.empty(1 + rows * (d + 1), dtype=torch.float64, device="cuda")
+    refit.loss_grad_sums_general(Xg, yg, Wb, og, block_rows=1024)
+    torch.cuda.synchronize()
+    assert torch.isfinite(og).all()
+print("general refit (lr_weighted_row_sum, 3xTF32 GEMMs) ok", flush=True)
 print("ALL OK")
