@@ -248,17 +248,20 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
 // ---- 5..16 score columns -------------------------------------------------------------------------
 // With more than four classes the kernel above runs out of shared-memory bandwidth: every 128-bit
 // piece of W it reads feeds four FMAs of ONE row (measured on B200: C=10, d=784 at 1.4 TB/s).  Here a
-// thread keeps U = 4 rows x NS classes of accumulators, so a piece of W feeds 16 FMAs, and the X
-// pieces of the next k-step are requested before the FMAs of the current one (8 loads of 16 B in
-// flight per thread at <= 128 registers).  NS is the exact padded class count (6, 8, 10, 12, 16):
+// thread keeps U rows x NS classes of accumulators (U = 4: a piece of W feeds 16 FMAs; U = 2 at 12
+// classes), and, up to 12 classes, the X pieces of the next k-step are requested before the FMAs of
+// the current one (at 16 classes 4 x 16 accumulators plus two X buffers do not fit 128 registers).  NS is the exact padded class count (6, 8, 10, 12, 16):
 // at C=10 the kernel needs 31 of the ~70 fp32 TFLOP/s to keep up with HBM, at 16 it would need 51.
 // W comes from shared memory while it fits 96 KB, else through L1 (`__ldg`; X bypasses L1).
 // fp32 FMA arithmetic throughout, same as the kernel above.
+template <int NS>
+struct MidRows { static constexpr int value = NS == 12 ? 2 : 4; };    // rows per thread (U)
+
 template <int V, int LANES, int NS, bool WSMEM>
 __global__ void __launch_bounds__(kThreads, 2)
 mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad,
            const float* __restrict__ Wn, const float* __restrict__ bn, Outs o) {
-    constexpr int U = 4;
+    constexpr int U = MidRows<NS>::value;
     constexpr int G = 32 / LANES;
     constexpr int M = (U < LANES) ? U : LANES;
     constexpr int ROWS_OWNED = U / M;
@@ -320,9 +323,10 @@ mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int 
         // block as the FMAs of step i and ahead of them (a conditional prefetch was sunk below the
         // FMAs by the compiler, which left nothing in flight while they ran).  Every load is a real
         // piece of the row (or column 0 against zero weights past d), none is issued twice.
-        // (Above 10 classes two X buffers no longer fit 128 registers next to 4 x NS accumulators:
-        // those run one step at a time and rely on the other warps for overlap.)
-        if constexpr (NS <= 10) {
+        // Measured (B200, tools/shape_sweep.py): 12 classes do best with two rows per thread and the
+        // pipeline (4.46 against 4.04 TB/s at d=1024); 16 classes with four rows and one step at a time
+        // (two rows + pipeline: 3.0 against 3.5 TB/s at d=128) -- neither reaches past ~27 fp32 TFLOP/s.
+        if constexpr (NS <= 12) {
             Vec<V> xa[U], xb[U];
             {
                 const int kc = k0 < d ? k0 : 0;        // past-the-end pieces meet zero weights
@@ -744,7 +748,7 @@ int launch_mid_inst(const Model& m, const ScoreArgs& a) {
     int occ = 0;
     const int rc = resident_blocks(kern, dev, smem, &occ);
     if (rc != LR_OK) return rc;
-    constexpr int rows_per_iter = (32 / LANES) * 4;
+    constexpr int rows_per_iter = (32 / LANES) * MidRows<NS>::value;
     const int64_t tiles = (a.n_rows + rows_per_iter - 1) / rows_per_iter;
     const int64_t need = (tiles + (kThreads / 32) - 1) / (kThreads / 32);
     const int64_t cap = (int64_t)m.num_sms * occ;
