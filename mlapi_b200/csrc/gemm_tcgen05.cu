@@ -1366,6 +1366,20 @@ bool gemm_supports(const Model& m, const ScoreArgs& a) {
 int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     if (m.n_scores <= 16 || m.n_scores > kMaxCluster * 2 * BN) return LR_OK;
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
+    {
+        // The per-call scratch of this path (X scale, flags, log-sum-exp, re-pitched rows) comes from the device's
+        // default stream-ordered pool.  Left at its default threshold of 0 the pool hands its memory back to the
+        // driver at every synchronisation, i.e. once per lr_score_host call: let it keep up to 1 GiB.
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, m.device) == cudaSuccess) {
+            uint64_t cur = 0;
+            if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur) == cudaSuccess && cur < (1ull << 30)) {
+                uint64_t want = 1ull << 30;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &want);
+            }
+        }
+        cudaGetLastError();
+    }
     GemmPlan* g = new GemmPlan();
     const int C = m.n_scores, d = m.n_features;
     const int d4 = (d + 3) / 4 * 4;                 // row pitch of the fp32 copies: TMA wants 16-byte pitches
