@@ -356,7 +356,7 @@ def test_request_sized_pinned_batches_are_scored_in_place(eng, golden):
     from mlapi_b200.estimator import PinnedArray
     L = lib.load()
     rng = np.random.default_rng(12)
-    for d, ns in ((4, 3), (32, 1), (2000, 1), (5001, 10)):      # narrow, narrow, wide, generic (W beyond L1)
+    for d, ns in ((4, 3), (32, 1), (2000, 1), (16, 2100)):      # narrow, narrow, wide, generic (> 2048 classes)
         W, b = synth.make_model(d, ns, 70 + d)
         clf = _model(eng, W, b)
         rep = clf._replicas[0]
