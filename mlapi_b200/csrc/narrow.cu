@@ -865,19 +865,27 @@ int launch_bulk(const Model& m, const ScoreArgs& a) {
 
 }  // namespace
 
-// Shapes the narrow path serves: <= 16 score columns and a padded W that fits shared memory (<= 4
-// columns) or L1 (5..16 columns).
-bool narrow_supports(const Model& m) {
-    if (m.n_scores > 16) return false;
-    const int ns = padded_scores(m.n_scores);
+// Score columns the model runs with on this path, 0 if it does not serve it.  <= 4 columns want W in
+// shared memory (<= 96 KB, d <= 4096); a 2..4-class model with longer rows runs as a 6-column one on the
+// register-tile kernel (W through L1 / L2, padding columns cost FMAs it has to spare); 5..16 columns take
+// any W up to 16 MB.  A binary model with long rows belongs to the wide path.
+static int narrow_columns(const Model& m) {
+    if (m.n_scores > 16) return 0;
+    int ns = padded_scores(m.n_scores);
     const int dpad = (m.n_features + 127) / 128 * 128;
-    const size_t bytes = (size_t)ns * dpad * sizeof(float);
-    return ns <= 4 ? (bytes <= kWSmemMax && m.n_features <= 4096) : bytes <= kWL1Max;
+    if (ns <= 4 && !((size_t)ns * dpad * sizeof(float) <= kWSmemMax && m.n_features <= 4096)) {
+        if (ns == 1) return 0;
+        ns = 6;
+    }
+    if (ns > 4 && (size_t)ns * dpad * sizeof(float) > kWL1Max) return 0;
+    return ns;
 }
 
+bool narrow_supports(const Model& m) { return narrow_columns(m) != 0; }
+
 int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
-    if (!narrow_supports(m)) return LR_OK;
-    const int ns = padded_scores(m.n_scores);
+    const int ns = narrow_columns(m);
+    if (ns == 0) return LR_OK;
     // dpad covers whole lane-chunk sweeps for both V=4 and V=1 mappings (a multiple of 32*4).
     const int dpad = (m.n_features + 127) / 128 * 128;
     std::string w((size_t)ns * dpad * sizeof(float), '\0');

@@ -220,6 +220,24 @@ def test_long_aligned_rows_go_through_flat_tiles(eng, ns):
         clf.close()
 
 
+@pytest.mark.parametrize("d,ns", [(4100, 2), (8000, 3), (8001, 3), (6000, 4), (5001, 9), (8000, 10)])
+def test_few_classes_long_rows(eng, d, ns):
+    """2..4 classes with rows too long for W in shared memory run as a 6-column model on the register-tile
+    kernel; 5..16 classes read W through L2 there.  Dispatcher's choice must be the narrow path."""
+    import ctypes as C
+    _, lib = eng
+    L = lib.load()
+    rng = np.random.default_rng(d + ns)
+    W, b = synth.make_model(d, ns, 10 + d)
+    clf = _model(eng, W, b)
+    for n in (3, 700, 4500):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        _check(clf, X, W, b, f"long rows ns={ns} d={d} n={n}")
+    clf.set_path(lib.PATH_NARROW)                         # fails loudly if the path did not take the shape
+    _check(clf, X[:64], W, b, f"long rows forced narrow ns={ns} d={d}")
+    clf.close()
+
+
 @pytest.mark.parametrize("d", [4, 5, 1000, 1024, 4097, 10_000, 100_000])
 def test_wide_shapes(eng, d):
     _, lib = eng
