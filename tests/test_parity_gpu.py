@@ -252,6 +252,34 @@ def test_wide_shapes(eng, d):
         _check(clf, X, W, b, f"wide d={d} n={n}")
 
 
+@pytest.mark.parametrize("d", [2049, 4097, 5001, 100_001])
+def test_wide_unaligned_device_rows(eng, d):
+    """Binary models whose device rows are not 16-byte aligned (odd d, dense) and too long for the narrow
+    path: the wide path's 4-byte-load kernel (was the generic kernel at 2.6-3.0 TB/s)."""
+    import ctypes as C
+    import torch
+    _, lib = eng
+    L = lib.load()
+    rng = np.random.default_rng(d)
+    W, b = synth.make_model(d, 1, 3 + d)
+    clf = _model(eng, W, b)
+    for n in (1, 9, 700, 3000):
+        if n * d > 60_000_000:
+            continue
+        Xh = rng.standard_normal((n, d), dtype=np.float32)
+        Xt = torch.from_numpy(Xh).cuda()
+        if n == 700:
+            path = C.c_int32(0)
+            lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d, C.byref(path)))
+            assert path.value == (lib.PATH_NARROW if d <= 2048 else lib.PATH_WIDE)
+        out = clf.score_rows(Xt, **ALL)
+        torch.cuda.synchronize()
+        host = {k: v.cpu().numpy() for k, v in out.items()}
+        parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
+                             orc.predict_index(Xh, W, b), f"wide unaligned d={d} n={n}")
+    clf.close()
+
+
 @pytest.mark.parametrize("d,ns", [(1, 1), (7, 1), (33, 2), (50, 20), (130, 37), (1024, 100), (3000, 1)])
 def test_generic_shapes(eng, d, ns):
     _, lib = eng
