@@ -6,7 +6,8 @@
 // A row no longer fits a warp's registers, so a CTA streams R rows at once: in each sweep step a
 // thread loads one 128-bit piece of W (hot in L1/L2: W is d*4 bytes, 400 KB at d=100k) and the
 // matching 128-bit pieces of R different rows of X (R independent HBM requests in flight per
-// thread), so W's L2 traffic is 1/R of X's HBM traffic.  Partial sums go through a warp-shuffle and
+// thread, 2R with the two-step form used from d = 2048 up), so W's L2 traffic is 1/R of X's HBM
+// traffic.  Partial sums go through a warp-shuffle and
 // one shared-memory step; the sigmoid epilogue is fused.
 //
 // HBM roofline: algorithmic bytes per row = 4*d read + 8 written (proba) -- 400 008 B at d=100k.
@@ -17,8 +18,8 @@ namespace {
 
 constexpr int kThreads = 256;
 
-template <int R>
-__global__ void __launch_bounds__(kThreads, 3)      // <= 85 registers: 3 CTAs per SM, 96 KB of loads in flight (+3 % at d=100k)
+template <int R, int UN>
+__global__ void __launch_bounds__(kThreads, UN == 2 ? 2 : 3)   // UN = 1: <= 85 registers, 3 CTAs per SM, 96 KB of loads in flight
 wide_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d,
             const float* __restrict__ W, const float* __restrict__ b,
             float* __restrict__ proba, float* __restrict__ decision, int32_t* __restrict__ label,
@@ -39,7 +40,34 @@ wide_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d,
         for (int r = 0; r < R; ++r) acc[r] = 0.0f;
 
         const int d4 = d >> 2;
-        for (int k = threadIdx.x; k < d4; k += kThreads) {
+        int k = threadIdx.x;
+        if constexpr (UN == 2) {
+            // two sweep steps of all R rows requested before the first FMA
+            for (; k + kThreads < d4; k += 2 * kThreads) {
+                float4 x0[R], x1[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) x0[r] = ldg_stream4(xr[r] + 4 * k);
+#pragma unroll
+                for (int r = 0; r < R; ++r) x1[r] = ldg_stream4(xr[r] + 4 * (k + kThreads));
+                const float4 w0 = __ldg(reinterpret_cast<const float4*>(W) + k);
+                const float4 w1 = __ldg(reinterpret_cast<const float4*>(W) + k + kThreads);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    acc[r] = fmaf(x0[r].x, w0.x, acc[r]);
+                    acc[r] = fmaf(x0[r].y, w0.y, acc[r]);
+                    acc[r] = fmaf(x0[r].z, w0.z, acc[r]);
+                    acc[r] = fmaf(x0[r].w, w0.w, acc[r]);
+                }
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    acc[r] = fmaf(x1[r].x, w1.x, acc[r]);
+                    acc[r] = fmaf(x1[r].y, w1.y, acc[r]);
+                    acc[r] = fmaf(x1[r].z, w1.z, acc[r]);
+                    acc[r] = fmaf(x1[r].w, w1.w, acc[r]);
+                }
+            }
+        }
+        for (; k < d4; k += kThreads) {
             float4 x[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) x[r] = ldg_stream4(xr[r] + 4 * k);
@@ -176,8 +204,17 @@ int launch_r(const Model& m, const ScoreArgs& a) {
     const int64_t blocks = (a.n_rows + R - 1) / R;
     const int64_t cap = (int64_t)m.num_sms * 16;     // grid-stride beyond this; multiple of the SM count
     const int grid = (int)(blocks < cap ? blocks : cap);
-    wide_kernel<R><<<grid, kThreads, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.W, m.b,
-                                                    a.proba, a.decision, a.label, a.maxprob, m.status);
+    // Rows of 2048 floats and more: two sweep steps in flight per thread at 2 CTAs per SM (128 KB of loads
+    // per SM) -- measured 6.2 -> 7.1 TB/s at d = 4096..20000, cfg 2 (d = 100k) 4.96 -> 4.49 ms; shorter rows
+    // have a single step per row and keep the 3-CTA form.  LRS_WIDE_UNROLL=1|2 pins one (tuning).
+    static const int forced = [] { const char* e = getenv("LRS_WIDE_UNROLL"); return e ? atoi(e) : 0; }();
+    const int un = forced ? forced : (m.n_features / 4 >= 2 * kThreads ? 2 : 1);
+    if (un == 2)
+        wide_kernel<R, 2><<<grid, kThreads, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.W, m.b,
+                                                           a.proba, a.decision, a.label, a.maxprob, m.status);
+    else
+        wide_kernel<R, 1><<<grid, kThreads, 0, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.W, m.b,
+                                                           a.proba, a.decision, a.label, a.maxprob, m.status);
     count_launch();
     LRS_CUDA(cudaGetLastError());
     return LR_OK;
