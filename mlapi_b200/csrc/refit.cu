@@ -462,9 +462,10 @@ namespace lrs {
 namespace {
 
 template <int V>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 wsum_kernel(const float* __restrict__ X, const float* __restrict__ r, int64_t n_rows, int64_t ldx, int d,
             int64_t rows_per_block, float* __restrict__ partial) {
+    constexpr int RB = 16;                             // rows in flight per thread (8: 5.2 TB/s)
     const int k = (blockIdx.x * 256 + threadIdx.x) * V;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
     const int64_t r1 = r0 + rows_per_block < n_rows ? r0 + rows_per_block : n_rows;
@@ -474,10 +475,10 @@ wsum_kernel(const float* __restrict__ X, const float* __restrict__ r, int64_t n_
     if (k < d) {                                       // V == 4: d % 4 == 0, the piece is whole
         const float* p = X + r0 * ldx + k;
         int64_t i = r0;
-        for (; i + 8 <= r1; i += 8, p += 8 * ldx) {
-            float x[8][V], w[8];
+        for (; i + RB <= r1; i += RB, p += RB * ldx) {
+            float x[RB][V], w[RB];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < RB; ++j) {
                 if constexpr (V == 4) {
                     const float4 t = ldg_stream4(p + j * ldx);
                     x[j][0] = t.x; x[j][1] = t.y; x[j][2] = t.z; x[j][3] = t.w;
@@ -487,7 +488,7 @@ wsum_kernel(const float* __restrict__ X, const float* __restrict__ r, int64_t n_
                 w[j] = __ldg(r + i + j);
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
+            for (int j = 0; j < RB; ++j)
 #pragma unroll
                 for (int v = 0; v < V; ++v) acc[v] = fmaf(w[j], x[j][v], acc[v]);
         }
