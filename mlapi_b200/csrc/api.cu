@@ -62,6 +62,9 @@ static int select_path(const Model& m, const ScoreArgs& a) {
     if (m.forced_path != LR_PATH_AUTO) return m.forced_path;
     if (m.n_scores == 1) {
         if (m.Wn && m.n_features < 1024) return LR_PATH_NARROW;
+        // 1024..2047 features in a large batch: one sweep step per row on the wide path; the narrow path's
+        // flat-tile ring does better there (measured 6.5 -> 7.0 TB/s at d = 1024)
+        if (m.Wn && m.n_features < 2048 && a.n_rows >= 4096 && a.ldx <= 2048) return LR_PATH_NARROW;
         // unaligned rows up to 2048 floats: the narrow path's flat-tile ring beats 4-byte loads
         const bool aligned = a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
         if (m.Wn && !aligned && a.ldx <= 2048) return LR_PATH_NARROW;
