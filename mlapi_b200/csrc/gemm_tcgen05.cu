@@ -366,8 +366,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     using SmemLayout = SmemLayoutT<PAIR>;
     // Unpaired: a model with few classes has small W tiles and trades their room for a deeper X ring
     // (GemmParams::a_stages / b_tile_bytes; same 192 KB in total).  Paired: the fixed plan.
-    const int A_STAGES = PAIR ? SmemLayout::a_stages : p.a_stages;
-    const int B_STAGES = PAIR ? SmemLayout::b_stages : p.b_stages;
+    const int A_STAGES = p.a_stages;
+    const int B_STAGES = p.b_stages;
     const int B_TILE_BYTES = PAIR ? SmemLayout::b_tile : p.b_tile_bytes;
     unsigned char* a_hi = smem + SmemLayout::a_hi;
     unsigned char* a_lo = a_hi + A_STAGES * A_TILE_BYTES;
@@ -1630,7 +1630,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         int as = 0, bs = 0, rs = 0;
         const int n = sscanf(e, "%d,%d,%d", &as, &bs, &rs);
         if (n == 2) rs = 0;
-        if (!L.pair && n >= 2 && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages && rs >= 0 && rs <= kMaxAStages &&
+        if (n >= 2 && (!L.pair || rs == 0) && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages && rs >= 0 && rs <= kMaxAStages &&
             (rs == 0 || f16) && (as + rs) * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) {
             p.a_stages = as; p.b_stages = bs; p.raw_stages = rs;
         }
