@@ -666,36 +666,31 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         lo[i] = l;
                     }
                 } else {
-                    // raw tile: [128 rows][64 fp32], linear (256 B rows).  Each thread owns eight 8-element
-                    // pieces (row r, piece c): it scales them into fp16 range, splits them into hi + lo
-                    // halves and, once every thread has read its share (the tile is converted in place),
-                    // writes the two 16-byte results where the 128-byte-swizzled K-major fp16 tiles want
-                    // them: hi tile at the stage base, lo tile 16 KB above.
+                    // raw tile: [128 rows][64 fp32], linear (256 B rows).  A thread takes 16 quads of 4 floats,
+                    // quad index = thread + 128 j, so that a warp's 128-bit load covers 512 contiguous bytes
+                    // (conflict-free; a lane stride of 32 bytes cost two wavefronts per quarter-warp, and
+                    // shared-memory cycles are what this kernel is short of).  Once every thread holds its share
+                    // (the tile is converted in place) it scales each quad into fp16 range, splits it into
+                    // hi + lo halves and writes the two 8-byte results where the 128-byte-swizzled K-major fp16
+                    // tiles want them: hi tile at the stage base, lo tile 16 KB above.
                     unsigned char* stage = a_hi + as * A_STAGE;
-                    constexpr int PIECES = 1024 / kConvThreads;      // 8-element pieces per thread
-                    uint4 hv[PIECES], lv[PIECES];
+                    constexpr int QUADS = 2048 / kConvThreads;
+                    float4 xr[QUADS];
 #pragma unroll
-                    for (int j = 0; j < PIECES; ++j) {
-                        const int qd = t + kConvThreads * j;
-                        const int r = qd >> 3, c = qd & 7;
-                        const float4* src = reinterpret_cast<const float4*>(stage + r * 256 + c * 32);
-                        const float4 x0 = src[0], x1 = src[1];
-                        uint32_t hw[4], lw[4];
-                        split_pair(x0.x, x0.y, sx, hw[0], lw[0]);
-                        split_pair(x0.z, x0.w, sx, hw[1], lw[1]);
-                        split_pair(x1.x, x1.y, sx, hw[2], lw[2]);
-                        split_pair(x1.z, x1.w, sx, hw[3], lw[3]);
-                        hv[j] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                        lv[j] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-                    }
+                    for (int j = 0; j < QUADS; ++j)
+                        xr[j] = *reinterpret_cast<const float4*>(stage + (t + kConvThreads * j) * 16);
                     asm volatile("bar.sync 2, %0;" ::"n"(kConvThreads) : "memory");      // all raw data is in registers
 #pragma unroll
-                    for (int j = 0; j < PIECES; ++j) {
+                    for (int j = 0; j < QUADS; ++j) {
                         const int qd = t + kConvThreads * j;
-                        const int r = qd >> 3, c = qd & 7;
-                        const int off = r * 128 + ((c ^ (r & 7)) << 4);     // SWIZZLE_128B: 16-byte piece ^ (row % 8)
-                        *reinterpret_cast<uint4*>(stage + off) = hv[j];
-                        *reinterpret_cast<uint4*>(stage + A_TILE_BYTES + off) = lv[j];
+                        const int r = qd >> 4, q4 = qd & 15;
+                        uint32_t h0, l0, h1, l1;
+                        split_pair(xr[j].x, xr[j].y, sx, h0, l0);
+                        split_pair(xr[j].z, xr[j].w, sx, h1, l1);
+                        // SWIZZLE_128B: 16-byte piece ^ (row % 8); this quad is half a piece
+                        const int off = r * 128 + (((q4 >> 1) ^ (r & 7)) << 4) + (q4 & 1) * 8;
+                        *reinterpret_cast<uint2*>(stage + off) = make_uint2(h0, h1);
+                        *reinterpret_cast<uint2*>(stage + A_TILE_BYTES + off) = make_uint2(l0, l1);
                     }
                 }
                 fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
