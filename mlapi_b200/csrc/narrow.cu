@@ -258,7 +258,9 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
 template <int NS>
 struct MidRows { static constexpr int value = NS == 12 ? 2 : 4; };    // rows per thread (U)
 
-template <int V, int LANES, int NS, bool WSMEM>
+// AL = false (with V = 4): rows that are not 16-byte aligned -- a lane still owns four consecutive floats per
+// step (W pieces stay 128-bit loads), fetched with four 4-byte loads, each clamped on its own at the row end.
+template <int V, int LANES, int NS, bool WSMEM, bool AL = true>
 __global__ void __launch_bounds__(kThreads, 2)
 mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad,
            const float* __restrict__ Wn, const float* __restrict__ bn, Outs o) {
@@ -301,6 +303,14 @@ mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int 
 #pragma unroll
             for (int c = 0; c < NS; ++c) acc[j][c] = 0.0f;
 
+        auto load_piece = [&](Vec<V>& dst, const float* row, int k) {
+            if constexpr (V == 4 && !AL) {
+#pragma unroll
+                for (int v = 0; v < 4; ++v) dst.v[v] = ldg_stream1(row + (k + v < d ? k + v : 0));
+            } else {
+                dst.load(row + (k < d ? k : 0));       // past-the-end pieces meet zero weights
+            }
+        };
         // One k-step: every class's piece of W against the four rows' pieces of X.
         auto fma_step = [&](const Vec<V> (&xv)[U], int k) {
 #pragma unroll
@@ -329,30 +339,21 @@ mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int 
         // (two rows + pipeline: 3.0 against 3.5 TB/s at d=128) -- neither reaches past ~27 fp32 TFLOP/s.
         if constexpr (NS <= 12) {
             Vec<V> xa[U], xb[U];
-            {
-                const int kc = k0 < d ? k0 : 0;        // past-the-end pieces meet zero weights
 #pragma unroll
-                for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
-            }
+            for (int j = 0; j < U; ++j) load_piece(xa[j], rowp[j], k0);
             int k = k0;
             for (; k + 2 * STEP < dloop; k += 2 * STEP) {
-                {
-                    const int kn = k + STEP, kc = kn < d ? kn : 0;
 #pragma unroll
-                    for (int j = 0; j < U; ++j) xb[j].load(rowp[j] + kc);
-                }
+                for (int j = 0; j < U; ++j) load_piece(xb[j], rowp[j], k + STEP);
                 fma_step(xa, k);
-                {
-                    const int kn = k + 2 * STEP, kc = kn < d ? kn : 0;
 #pragma unroll
-                    for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
-                }
+                for (int j = 0; j < U; ++j) load_piece(xa[j], rowp[j], k + 2 * STEP);
                 fma_step(xb, k + STEP);
             }
             if (k + STEP < dloop) {                    // two steps left (same for the whole warp)
-                const int kn = k + STEP, kc = kn < d ? kn : 0;
+                const int kn = k + STEP;
 #pragma unroll
-                for (int j = 0; j < U; ++j) xb[j].load(rowp[j] + kc);
+                for (int j = 0; j < U; ++j) load_piece(xb[j], rowp[j], kn);
                 fma_step(xa, k);
                 fma_step(xb, kn);
             } else {
@@ -361,9 +362,8 @@ mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int 
         } else {
             for (int k = k0; k < dloop; k += STEP) {
                 Vec<V> xa[U];
-                const int kc = k < d ? k : 0;
 #pragma unroll
-                for (int j = 0; j < U; ++j) xa[j].load(rowp[j] + kc);
+                for (int j = 0; j < U; ++j) load_piece(xa[j], rowp[j], k);
                 fma_step(xa, k);
             }
         }
@@ -518,12 +518,17 @@ narrow_bulk_kernel(const float* __restrict__ X, int64_t n_rows, int d, int dpad,
 // their rows back with scalar shared loads, which do not care about alignment.  Same lane mapping,
 // cross-lane reduction and epilogue as above; W in shared memory.  Serves ldx <= kFlatMaxLdx.
 constexpr int kFlatMaxLdx = 2048;
-constexpr int kFlatWarps = 16;                    // consumer warps (scalar shared loads: latency-bound with 8)
-constexpr int kFlatThreads = (kFlatWarps + 1) * 32;
 constexpr int kFlatSmemBudget = 200 * 1024;
+// consumer warps: 16 (scalar shared loads were latency-bound with 8); 12 for the U x NS register tiles of
+// 5..16 classes, which need more than the 96 registers 17 warps leave each thread
+template <int NS>
+struct FlatWarps { static constexpr int value = NS <= 4 ? 16 : 12; };
 
-template <int V, int LANES, int NS, int U>
-__global__ void __launch_bounds__(kFlatThreads, 1)
+// AL = false with V = 4 (5..16 classes, unaligned rows): the lane mapping of mid_kernel<4, ..., AL = false>
+// -- four consecutive floats per lane and step, read with four scalar shared loads clamped one by one at
+// the row end, against 128-bit pieces of W.
+template <int V, int LANES, int NS, int U, bool AL = true>
+__global__ void __launch_bounds__((FlatWarps<NS>::value + 1) * 32, 1)
 narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int dpad, int tile_rows,
                    int stages, uint32_t stage_bytes, const float* __restrict__ Wn, const float* __restrict__ bn,
                    Outs o) {
@@ -531,6 +536,8 @@ narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int
     constexpr int M = (U < LANES) ? U : LANES;
     constexpr int ROWS_OWNED = U / M;
     constexpr int GROUP = G * U;                      // rows one warp takes per pass
+    constexpr int kFlatWarps = FlatWarps<NS>::value;
+    constexpr int kFlatThreads = (kFlatWarps + 1) * 32;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);          // [stages]
@@ -627,9 +634,12 @@ narrow_flat_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int
                 float x[U][V];
 #pragma unroll
                 for (int j = 0; j < U; ++j) {
-                    if constexpr (V == 4) {                   // aligned rows: conflict-free 128-bit shared loads
+                    if constexpr (V == 4 && AL) {             // aligned rows: conflict-free 128-bit shared loads
                         const float4 t = *reinterpret_cast<const float4*>(rp[j] + kc);
                         x[j][0] = t.x; x[j][1] = t.y; x[j][2] = t.z; x[j][3] = t.w;
+                    } else if constexpr (V == 4) {
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) x[j][v] = rp[j][k + v < d ? k + v : 0];
                     } else {
                         x[j][0] = rp[j][kc];
                     }
@@ -741,9 +751,9 @@ int launch_lanes(const Model& m, const ScoreArgs& a, bool single) {
     return fail(LR_ERR_INVALID, "narrow path: unsupported score count");
 }
 
-template <int V, int LANES, int NS, bool WSMEM>
+template <int V, int LANES, int NS, bool WSMEM, bool AL>
 int launch_mid_inst(const Model& m, const ScoreArgs& a) {
-    auto kern = mid_kernel<V, LANES, NS, WSMEM>;
+    auto kern = mid_kernel<V, LANES, NS, WSMEM, AL>;
     const size_t smem = WSMEM ? (size_t)NS * m.narrow_dpad * sizeof(float) : 0;
     const int dev = m.device & 63;
     int occ = 0;
@@ -761,40 +771,31 @@ int launch_mid_inst(const Model& m, const ScoreArgs& a) {
     return LR_OK;
 }
 
-// Lanes per row for the 5..16-class kernel: few enough that every lane sweeps several pieces of the
-// row (the cross-lane reduction of 4 x NS sums is paid once per row group), 32 for long rows.
-template <int V, int LANES, int NS>
+template <int LANES, int NS, bool AL>
 int launch_mid_w(const Model& m, const ScoreArgs& a) {
     const bool wsmem = (size_t)NS * m.narrow_dpad * sizeof(float) <= kWSmemMax;
-    return wsmem ? launch_mid_inst<V, LANES, NS, true>(m, a) : launch_mid_inst<V, LANES, NS, false>(m, a);
+    return wsmem ? launch_mid_inst<4, LANES, NS, true, AL>(m, a) : launch_mid_inst<4, LANES, NS, false, AL>(m, a);
 }
 
 // Lanes per row for the 5..16-class kernel.  Fewer lanes = more rows per warp instruction, and lanes
 // of different rows read the same piece of W (one shared-memory wavefront instead of four at 32
 // lanes: with 32 the W reads cost as many cycles as the FMAs they feed); more lanes = longer
-// contiguous pieces of each row per request.  LRS_MID_LANES overrides (tuning).
-template <int V, int NS>
+// contiguous pieces of each row per request.  Measured (lanes 4, 8, 16, 32 swept): 4 lanes win up to d=256,
+// 8 from there on.  AL = rows are 16-byte aligned (else the same mapping with 4-byte loads).
+template <int NS, bool AL>
 int launch_mid(const Model& m, const ScoreArgs& a) {
-    const int chunks = (m.n_features + V - 1) / V;
-    int lanes = chunks <= 64 ? 4 : 8;              // measured (tools/gpu_mid.sh): 4 wins up to d=256, 8 from there to d=4096
-    static const int forced = [] { const char* e = getenv("LRS_MID_LANES"); return e ? atoi(e) : 0; }();
-    if (forced) lanes = forced;
-    switch (lanes) {
-        case 4: return launch_mid_w<V, 4, NS>(m, a);
-        case 8: return launch_mid_w<V, 8, NS>(m, a);
-        case 16: return launch_mid_w<V, 16, NS>(m, a);
-        default: return launch_mid_w<V, 32, NS>(m, a);
-    }
+    const int chunks = (m.n_features + 3) / 4;
+    return chunks <= 64 ? launch_mid_w<4, NS, AL>(m, a) : launch_mid_w<8, NS, AL>(m, a);
 }
 
 template <int V>
 int launch_v(const Model& m, const ScoreArgs& a) {
     switch (m.narrow_ns) {
-        case 6: return launch_mid<V, 6>(m, a);
-        case 8: return launch_mid<V, 8>(m, a);
-        case 10: return launch_mid<V, 10>(m, a);
-        case 12: return launch_mid<V, 12>(m, a);
-        case 16: return launch_mid<V, 16>(m, a);
+        case 6: return launch_mid<6, V == 4>(m, a);
+        case 8: return launch_mid<8, V == 4>(m, a);
+        case 10: return launch_mid<10, V == 4>(m, a);
+        case 12: return launch_mid<12, V == 4>(m, a);
+        case 16: return launch_mid<16, V == 4>(m, a);
     }
     int chunks = (m.n_features + V - 1) / V;
     int lanes = 1;
@@ -909,11 +910,11 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
 
 namespace {
 
-template <int V, int LANES, int NS>
+template <int V, int LANES, int NS, bool AL = true>
 int launch_flat_inst(const Model& m, const ScoreArgs& a) {
-    constexpr int U = unroll_for<NS>();
+    constexpr int U = NS <= 4 ? unroll_for<NS>() : MidRows<NS>::value;     // as the direct-load kernel of the shape
     constexpr int GROUP = (32 / LANES) * U;
-    auto kern = narrow_flat_kernel<V, LANES, NS, U>;
+    auto kern = narrow_flat_kernel<V, LANES, NS, U, AL>;
     // a tile = whole row groups (GROUP rows, a multiple of 4), about 32 KB of them
     const int64_t group_bytes = (int64_t)GROUP * a.ldx * 4;
     const int64_t gpt = group_bytes >= 32768 ? 1 : 32768 / group_bytes;
@@ -937,7 +938,7 @@ int launch_flat_inst(const Model& m, const ScoreArgs& a) {
     const int64_t tiles = (a.n_rows + tile_rows - 1) / tile_rows;
     const int grid = (int)(tiles < m.num_sms ? tiles : m.num_sms);
     Outs o{a.proba, a.decision, a.label, a.maxprob, m.status, m.n_scores};
-    kern<<<grid, kFlatThreads, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad, tile_rows, stages,
+    kern<<<grid, (FlatWarps<NS>::value + 1) * 32, smem, a.stream>>>(a.X, a.n_rows, a.ldx, m.n_features, m.narrow_dpad, tile_rows, stages,
                                                  stage_bytes, m.Wn, m.bn, o);
     count_launch();
     LRS_CUDA(cudaGetLastError());
@@ -954,8 +955,27 @@ int launch_flat_lanes(const Model& m, const ScoreArgs& a) {
     return -1;      // 5..16 classes: the scalar-load form of the register-tile kernel measured faster
 }
 
+template <int LANES>
+int launch_flat_mid(const Model& m, const ScoreArgs& a) {
+    switch (m.narrow_ns) {
+        case 6: return launch_flat_inst<4, LANES, 6, false>(m, a);
+        case 8: return launch_flat_inst<4, LANES, 8, false>(m, a);
+        case 10: return launch_flat_inst<4, LANES, 10, false>(m, a);
+        case 12: return launch_flat_inst<4, LANES, 12, false>(m, a);
+        case 16: return launch_flat_inst<4, LANES, 16, false>(m, a);
+    }
+    return -1;
+}
+
 // Returns -1 when the flat-tile kernel does not apply (caller falls through to the plain-load kernels).
 int launch_flat(const Model& m, const ScoreArgs& a, bool vec) {
+    if (m.narrow_ns > 4) {
+        // 5..16 classes: unaligned rows up to d = 256 only (measured: d=54, C=7 2.5 -> 4.8 TB/s, d=61, C=10
+        // 2.5 -> 5.0; from d = 785 up the direct 4-byte loads are as fast or faster, and aligned rows never
+        // gained from the ring).  Four lanes per row, as launch_mid picks for these sizes.
+        if (vec || (m.n_features + 3) / 4 > 64) return -1;
+        return launch_flat_mid<4>(m, a);
+    }
     if (vec) {                                           // lanes as launch_v<4> picks them
         const int chunks = m.n_features / 4;
         if (chunks <= 8) return launch_flat_lanes<4, 8>(m, a);
@@ -987,7 +1007,7 @@ int narrow_launch(const Model& m, const ScoreArgs& a) {
     // binary: d=256 6.05 -> 6.68 TB/s, d=1000 5.96 -> 7.06; shorter rows are faster on direct loads).
     static const bool flat_on = [] { const char* e = getenv("LRS_NARROW_FLAT"); return !e || atoi(e) != 0; }();
     static const int flat_min_d = [] { const char* e = getenv("LRS_NARROW_FLAT_MIN_D"); return e ? atoi(e) : 256; }();
-    if (flat_on && m.narrow_ns <= 4 && (!vec || (m.n_features >= flat_min_d && m.n_features >= 20)) && a.ldx <= kFlatMaxLdx &&
+    if (flat_on && (!vec || (m.narrow_ns <= 4 && m.n_features >= flat_min_d && m.n_features >= 20)) && a.ldx <= kFlatMaxLdx &&
         a.n_rows >= 4096) {
         const int rc = launch_flat(m, a, vec);
         if (rc >= 0) return rc;

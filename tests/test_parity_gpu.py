@@ -154,11 +154,11 @@ def test_mid_class_counts(eng, ns):
         clf.close()
 
 
-@pytest.mark.parametrize("ns", [1, 2, 3, 4, 5, 10])
+@pytest.mark.parametrize("ns", [1, 2, 3, 4, 5, 7, 10, 12, 16])
 def test_unaligned_rows_go_through_flat_tiles(eng, ns):
     """Rows that are not 16-byte aligned (odd d, odd pitch, odd base) and >= 4096 of them: tiles of rows
-    are bulk-copied to shared memory and read back with scalar loads (<= 4 classes; 5 and 10 here check
-    that wider models keep working on the scalar-load kernels).  Against the oracle, and bit-for-bit
+    are bulk-copied to shared memory and read back with scalar loads (<= 4 classes: one float per lane and
+    step; 5..16 classes: four, against 128-bit pieces of W).  Against the oracle, and bit-for-bit
     against the plain scalar-load kernel, which serves the same rows when they come in batches below 4096:
     a row's result must not depend on the size of the batch it arrives in."""
     import torch
@@ -171,11 +171,10 @@ def test_unaligned_rows_go_through_flat_tiles(eng, ns):
         for n in (4096, 4099, 20_011):
             X = rng.standard_normal((n, d), dtype=np.float32)
             out = _check(clf, X, W, b, f"flat ns={ns} d={d} n={n}")
-            if ns <= 4:                                         # same lanes, same order of FMAs: same bits
-                for lo in range(0, n, 4000):
-                    ref = clf.score_rows(X[lo:lo + 4000], **ALL)
-                    for k in ref:
-                        assert np.array_equal(ref[k], out[k][lo:lo + 4000]), (k, ns, d, n, lo)
+            for lo in range(0, n, 4000):                        # same lanes, same order of FMAs: same bits
+                ref = clf.score_rows(X[lo:lo + 4000], **ALL)
+                for k in ref:
+                    assert np.array_equal(ref[k], out[k][lo:lo + 4000]), (k, ns, d, n, lo)
         clf.close()
     # device rows with an odd pitch and a base that is only 4-byte aligned
     d, n = 30, 9001
