@@ -404,24 +404,22 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     const bool lead = !PAIR || rt == 0;                 // the CTA whose MMA lane issues for the pair
     const uint32_t lead_rank = crank & ~1u;
     const uint16_t pair_mask = (uint16_t)(3u << lead_rank);
-    const bool x_mc = !PAIR && p.ncc > 1;               // X multicast across class slices
-    const bool w_mc = !PAIR && p.nrt > 1;               // W multicast across row tiles
+    // X is the caller's memory: every CTA fetches its own copy of the tile with a plain TMA load.  (TMA
+    // multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+    // GPU's memory hung the GPU -- and nothing stops a caller from handing in a peer's buffer.)
+    const bool w_mc = !PAIR && p.nrt > 1;               // W (the library's own copy, on this GPU) multicast across row tiles
     const int n_cols_cta = p.nb * BN;
     const int col0 = (int)rank * n_cols_cta;       // first class handled by this CTA
-    // Multicast groups.  The ncc CTAs of a row tile need the same X tile: each fetches 1/ncc of its rows
-    // and multicasts them to the group.  The nrt CTAs of a class slice need the same W tiles: each
-    // fetches 1/nrt of the rows.  L2 -> SM traffic per CTA drops accordingly.
-    const uint16_t x_mask = (uint16_t)(((1u << p.ncc) - 1u) << (rt * p.ncc));
+    // Multicast group of W: the nrt CTAs of a class slice need the same W tiles, each fetches 1/nrt of the rows.
     uint16_t w_mask = 0;
     for (int j = 0; j < p.nrt; ++j) w_mask |= (uint16_t)(1u << (rank + j * p.ncc));
-    const int x_rows = x_mc ? BM / p.ncc : BM;      // rows of the X tile this CTA fetches
     const int w_rows = PAIR ? BN / 2 : p.mma_n / p.nrt;  // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kMaxAStages; ++i) {     // (operand ring and raw ring may differ in depth)
             mbar_init(x_full + i, 1);
             mbar_init(a_ready + i, PAIR ? 2 * kConvThreads : kConvThreads);    // PAIR: both CTAs' converters report to the issuing CTA
-            mbar_init(a_empty + i, x_mc ? p.ncc : 1);    // every CTA sharing the X tile has consumed the stage
+            mbar_init(a_empty + i, 1);
         }
         for (int i = 0; i < kMaxAStages; ++i) mbar_init(raw_empty + i, kConvWarps);
         for (int i = 0; i < B_STAGES; ++i) {
@@ -520,11 +518,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     mbar_expect_tx(x_full + as, RAW_BYTES);
                     unsigned char* xdst = raw_ring ? raw_base + as * RAW_BYTES
                                                    : (F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES);
-                    if (x_mc)
-                        tma_load_2d_mc(xdst + rank * x_rows * (BKx * 4), &map_x, kc * BKx, row0 + (int)rank * x_rows,
-                                       x_full + as, x_mask);
-                    else
-                        tma_load_2d(xdst, &map_x, kc * BKx, row0, x_full + as);
+                    tma_load_2d(xdst, &map_x, kc * BKx, row0, x_full + as);
                 }
                 __syncwarp();
                 if (++as == x_stages) { as = 0; aph ^= 1; }
@@ -592,7 +586,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 }
                 if (leader) {
                     if constexpr (PAIR) tc_commit_2sm(a_empty + as, pair_mask);
-                    else if (x_mc) tc_commit_mc(a_empty + as, x_mask);
                     else tc_commit(a_empty + as);
                 }
                 __syncwarp();
@@ -1552,7 +1545,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     GemmPlan::Layout& L = g->layout[g->active];
     CUtensorMap map_x;
     const bool f16 = g->f16;
-    const int xbox = L.pair ? BM : BM / L.ncc;        // X is multicast across class slices only without pairs
+    const int xbox = BM;                              // every CTA loads its whole X tile
     int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox, BK16, 4, false)
                  : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox);
     if (rc != LR_OK) return rc;
