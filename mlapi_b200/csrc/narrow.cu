@@ -1,5 +1,11 @@
-// Narrow path: one fused kernel for models whose whole coefficient matrix fits in shared memory
-// (the notebook's iris model d=4,C=3 and the d=32 binary north-star config).
+// Narrow path: models with at most 16 score columns (the notebook's iris model d=4, C=3 and the d=32
+// binary north-star config among them).  Four kernels share one lane mapping, reduction and epilogue:
+//   narrow_kernel       <= 4 columns, W in registers or shared memory, direct 128-bit (or 4-byte) loads
+//   mid_kernel          5..16 columns: U rows x NS classes of accumulators per thread, W from shared memory / L1 / L2
+//   narrow_flat_kernel  rows that are not 16-byte aligned, and aligned rows of 1 KB and more, in batches of
+//                       >= 4096: whole tiles of rows through a cp.async.bulk ring in shared memory
+//   narrow_bulk_kernel  the first ring variant (aligned short rows), opt-in, kept as the measured alternative
+// A row scores to the same bits whichever of them its batch size and alignment select.
 //
 // Replaces, per row, sklearn's decision_function (SK/linear_model/_base.py:390-391),
 // _predict_proba_lr / softmax (SK/linear_model/_base.py:437-440, SK/utils/extmath.py:1012-1024),
