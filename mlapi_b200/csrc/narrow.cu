@@ -5,7 +5,7 @@
 //   narrow_flat_kernel  rows that are not 16-byte aligned, and aligned rows of 1 KB and more, in batches of
 //                       >= 4096: whole tiles of rows through a cp.async.bulk ring in shared memory
 //   narrow_bulk_kernel  the first ring variant (aligned short rows), opt-in, kept as the measured alternative
-// A row scores to the same bits whichever of them its batch size and alignment select.
+// For a given row alignment, a row scores to the same bits whichever of them its batch size selects.
 //
 // Replaces, per row, sklearn's decision_function (SK/linear_model/_base.py:390-391),
 // _predict_proba_lr / softmax (SK/linear_model/_base.py:437-440, SK/utils/extmath.py:1012-1024),
