@@ -35,7 +35,7 @@ extern "C" {
 
 /* Which kernel family serves a (model, n_rows) pair; see DESIGN.md "Kernels". */
 #define LR_PATH_AUTO     0
-#define LR_PATH_NARROW   1    /* <= 16 score columns: fused row-dot + sigmoid/softmax, few lanes per row;
+#define LR_PATH_NARROW   1    /* <= 16 score columns (<= 24 on short rows): fused row-dot + sigmoid/softmax, few lanes per row;
                                  register-tile form for 5..16 columns, shared-memory ring for unaligned / long rows */
 #define LR_PATH_WIDE     2    /* binary, rows of 1024 floats and more: row-block streaming, W re-used across 8 rows */
 #define LR_PATH_GEMM     3    /* 17..2048 classes: TMA-fed tcgen05 GEMM (3xFP16 split, 3xTF32 optional) + fused

@@ -37,6 +37,9 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr size_t kWSmemMax = 96 * 1024;    // W staged in shared memory up to here
+// 17..24 columns are served up to this many features (beyond, and for more columns: tensor cores).  Measured:
+// d=32, C=20 1.27 -> 1.86 TB/s, d=54, C=20 0.86 -> 1.69; a 32-column form lost to the tensor path (d=16, C=32: 0.9 : 1.6).
+constexpr int kMid24MaxD = 56;
 constexpr size_t kWL1Max = 16 << 20;        // 5..16 columns: beyond shared memory, W is read through L1 (hits up to
                                            // ~192 KB, L2 beyond: d=8000, C=10 still runs 4x faster than the generic kernel)
 
@@ -58,7 +61,7 @@ inline int scalar_lanes(int d) {
 
 // Score columns the kernels are instantiated for (padding columns carry zero weights and a -inf intercept).
 inline int padded_scores(int c) {
-    return c == 1 ? 1 : c <= 3 ? 3 : c <= 4 ? 4 : c <= 6 ? 6 : c <= 8 ? 8 : c <= 10 ? 10 : c <= 12 ? 12 : 16;
+    return c == 1 ? 1 : c <= 3 ? 3 : c <= 4 ? 4 : c <= 6 ? 6 : c <= 8 ? 8 : c <= 10 ? 10 : c <= 12 ? 12 : c <= 16 ? 16 : 24;
 }
 
 template <int V>
@@ -262,7 +265,7 @@ narrow_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, i
 // W comes from shared memory while it fits 96 KB, else through L1 (`__ldg`; X bypasses L1).
 // fp32 FMA arithmetic throughout, same as the kernel above.
 template <int NS>
-struct MidRows { static constexpr int value = NS == 12 ? 2 : 4; };    // rows per thread (U)
+struct MidRows { static constexpr int value = (NS == 12 || NS > 16) ? 2 : 4; };    // rows per thread (U)
 
 // AL = false (with V = 4): rows that are not 16-byte aligned -- a lane still owns four consecutive floats per
 // step (W pieces stay 128-bit loads), fetched with four 4-byte loads, each clamped on its own at the row end.
@@ -343,7 +346,7 @@ mid_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int 
         // Measured (B200, tools/shape_sweep.py): 12 classes do best with two rows per thread and the
         // pipeline (4.46 against 4.04 TB/s at d=1024); 16 classes with four rows and one step at a time
         // (two rows + pipeline: 3.0 against 3.5 TB/s at d=128) -- neither reaches past ~27 fp32 TFLOP/s.
-        if constexpr (NS <= 12) {
+        if constexpr (NS <= 12 || NS > 16) {
             Vec<V> xa[U], xb[U];
 #pragma unroll
             for (int j = 0; j < U; ++j) load_piece(xa[j], rowp[j], k0);
@@ -802,6 +805,7 @@ int launch_v(const Model& m, const ScoreArgs& a) {
         case 10: return launch_mid<10, V == 4>(m, a);
         case 12: return launch_mid<12, V == 4>(m, a);
         case 16: return launch_mid<16, V == 4>(m, a);
+        case 24: return launch_mid<24, V == 4>(m, a);
     }
     int chunks = (m.n_features + V - 1) / V;
     int lanes = 1;
@@ -875,9 +879,12 @@ int launch_bulk(const Model& m, const ScoreArgs& a) {
 // Score columns the model runs with on this path, 0 if it does not serve it.  <= 4 columns want W in
 // shared memory (<= 96 KB, d <= 4096); a 2..4-class model with longer rows runs as a 6-column one on the
 // register-tile kernel (W through L1 / L2, padding columns cost FMAs it has to spare); 5..16 columns take
-// any W up to 16 MB.  A binary model with long rows belongs to the wide path.
+// any W up to 16 MB; 17..24 columns with rows of at most 56 floats run here too (as 24
+// columns, two rows per thread): the tensor-core path cannot go below one 128-row tile per k-chunk and
+// measured 0.9-1.3 TB/s on d=54, C=20 / d=32, C=20, where plain FMAs reach 1.7-1.9.
+// A binary model with long rows belongs to the wide path.
 static int narrow_columns(const Model& m) {
-    if (m.n_scores > 16) return 0;
+    if (m.n_scores > 24 || (m.n_scores > 16 && m.n_features > kMid24MaxD)) return 0;
     int ns = padded_scores(m.n_scores);
     const int dpad = (m.n_features + 127) / 128 * 128;
     if (ns <= 4 && !((size_t)ns * dpad * sizeof(float) <= kWSmemMax && m.n_features <= 4096)) {
@@ -897,7 +904,7 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
     const int dpad = (m.n_features + 127) / 128 * 128;
     std::string w((size_t)ns * dpad * sizeof(float), '\0');
     float* wp = reinterpret_cast<float*>(&w[0]);
-    float bp[16];
+    float bp[24];
     for (int c = 0; c < ns; ++c) {
         bp[c] = c < m.n_scores ? b_host[c] : -INFINITY;   // padded classes never win, exp -> 0
         if (c < m.n_scores)
@@ -969,6 +976,7 @@ int launch_flat_mid(const Model& m, const ScoreArgs& a) {
         case 10: return launch_flat_inst<4, LANES, 10, false>(m, a);
         case 12: return launch_flat_inst<4, LANES, 12, false>(m, a);
         case 16: return launch_flat_inst<4, LANES, 16, false>(m, a);
+        case 24: return launch_flat_inst<4, LANES, 24, false>(m, a);
     }
     return -1;
 }

@@ -154,6 +154,39 @@ def test_mid_class_counts(eng, ns):
         clf.close()
 
 
+@pytest.mark.parametrize("ns", [17, 20, 24])
+def test_17_to_24_classes_short_rows(eng, ns):
+    """17..24 classes with rows of at most 56 floats run on the
+    register-tile kernel as 24 columns, not on the tensor cores: fp32 parity bar, aligned and
+    unaligned rows, and the same bits for a row in a small batch (direct loads) and a large one (ring,
+    unaligned rows only)."""
+    import ctypes as C
+    _, lib = eng
+    L = lib.load()
+    rng = np.random.default_rng(ns * 7)
+    dmax = 56
+    for d in (4, 16, 33, 54, 56):
+        W, b = synth.make_model(d, ns, 40 + ns + d)
+        clf = _model(eng, W, b)
+        for n in (1, 130, 4099):
+            X = rng.standard_normal((n, d), dtype=np.float32)
+            out = _check(clf, X, W, b, f"mid32 ns={ns} d={d} n={n}")
+        for lo in range(0, n, 4000):
+            ref = clf.score_rows(X[lo:lo + 4000], **ALL)
+            for k in ref:
+                assert np.array_equal(ref[k], out[k][lo:lo + 4000]), (k, ns, d, lo)
+        clf.set_path(lib.PATH_NARROW)                     # fails loudly if the path did not take the shape
+        _check(clf, X[:64], W, b, f"mid32 forced narrow ns={ns} d={d}")
+        clf.close()
+    W, b = synth.make_model(dmax + 1, ns, 5)              # one feature more: tensor-core path
+    clf = _model(eng, W, b)
+    X = rng.standard_normal((300, dmax + 1), dtype=np.float32)
+    out = clf.score_rows(X, **ALL)
+    parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
+                         orc.predict_index(X, W, b), f"ns={ns} d={dmax + 1} (gemm)", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
+
+
 @pytest.mark.parametrize("ns", [1, 2, 3, 4, 5, 7, 10, 12, 16])
 def test_unaligned_rows_go_through_flat_tiles(eng, ns):
     """Rows that are not 16-byte aligned (odd d, odd pitch, odd base) and >= 4096 of them: tiles of rows
