@@ -722,6 +722,100 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_wait(acc_full + buf, (p.acc_bufs == 2 ? (it >> 1) : it) & 1u);
             tc_fence_after();
 
+            // ---- at most 32 classes: the four warps of column half 0 hold whole rows, one lane per row ----
+            // One read of TMEM, everything else in registers: no write-back, no second and third pass, no
+            // meeting of halves in shared memory (the three-pass form spent 2.4 us per 128-row tile on a
+            // 32-class model, which is what bounded it).  Same arithmetic and the same re-scoring flags.
+            if (!PAIR && n_chunks == 1 && p.ncc == 1 && !(p.debug_skip & 2)) {
+                if (h == 0) {
+                    float v[32];
+                    tmem_ld32(t_lane, v);
+                    if (p.split) {
+                        float u[32];
+                        tmem_ld32(t_lane + (uint32_t)BN, u);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] += u[i];
+                    }
+                    float gm = -INFINITY;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        if constexpr (F16) v[i] = fmaf(v[i], cscale_s[i], bias_s[i]);
+                        else v[i] += bias_s[i];                       // padding carries -inf
+                        gm = fmaxf(gm, v[i]);
+                    }
+                    int garg = 31;
+#pragma unroll
+                    for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
+                    if (p.decision && live) {
+                        float* zr = p.decision + row * p.n_classes;
+                        if (n_real == 32 && p.vec_store) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4)
+                                __stcs(reinterpret_cast<float4*>(zr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (i < n_real) __stcs(zr + i, v[i]);
+                        }
+                    }
+                    const float kappa = F16 ? (p.split ? 2.8e-6f : 6e-6f) : (p.split ? 3.5e-6f : 1.1e-5f);
+                    const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
+                    const float gml = gm * kLog2e;
+                    float gs = 0.0f;
+                    int gnear = 0;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        gnear += v[i] > tau ? 1 : 0;
+                        v[i] = ex2(fmaf(v[i], kLog2e, -gml));
+                        gs += v[i];
+                    }
+                    const float inv = __frcp_rn(gs);
+                    const float risk_thr = 8e-6f / (kappa * fmaxf(fabsf(gm), 1.0f));
+                    bool risk = false;
+                    if (p.proba) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            v[i] *= inv;
+                            risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
+                        }
+                        if (live) {
+                            float* pr = p.proba + row * p.n_classes;
+                            if (n_real == 32 && p.vec_store == 2) {
+#pragma unroll
+                                for (int i = 0; i < 32; i += 8) st_cs_v8(pr + i, v + i);
+                            } else if (n_real == 32 && p.vec_store) {
+#pragma unroll
+                                for (int i = 0; i < 32; i += 4)
+                                    __stcs(reinterpret_cast<float4*>(pr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 32; ++i)
+                                    if (i < n_real) __stcs(pr + i, v[i]);
+                            }
+                        }
+                    }
+                    tc_fence_before();
+                    mbar_arrive(acc_empty + buf);
+                    if (live) {
+                        if (p.label) __stcs(p.label + row, garg);
+                        if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
+                        const bool finite_row = finite_f(gm) && finite_f(gs);
+                        if (!finite_row) {
+                            if (p.flags && !p.count_nonfinite) p.flags[row] = 2;
+                            else atomicAdd(p.status, 1ull);
+                        }
+                        if (p.flags) {
+                            p.lse[row] = gm + logf(gs);
+                            if (finite_row && (risk || gnear >= 2 || inv * (1.0f - inv) > risk_thr)) p.flags[row] = 1;
+                        }
+                    }
+                } else {
+                    tc_fence_before();
+                    mbar_arrive(acc_empty + buf);
+                }
+                continue;
+            }
+
             // ---- pass 1: max and first argmax over my columns
             float m = -INFINITY;
             int arg = col0 + cb_lo;

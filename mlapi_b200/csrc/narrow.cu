@@ -884,7 +884,8 @@ int launch_bulk(const Model& m, const ScoreArgs& a) {
 // measured 0.9-1.3 TB/s on d=54, C=20 / d=32, C=20, where plain FMAs reach 1.7-1.9.
 // A binary model with long rows belongs to the wide path.
 static int narrow_columns(const Model& m) {
-    if (m.n_scores > 24 || (m.n_scores > 16 && m.n_features > kMid24MaxD)) return 0;
+    // (aligned rows: the tensor path's single-pass epilogue overtakes from d ~ 48: d=60, C=24 2.5 : 1.9 TB/s)
+    if (m.n_scores > 24 || (m.n_scores > 16 && m.n_features > (m.n_features % 4 ? kMid24MaxD : 40))) return 0;
     int ns = padded_scores(m.n_scores);
     const int dpad = (m.n_features + 127) / 128 * 128;
     if (ns <= 4 && !((size_t)ns * dpad * sizeof(float) <= kWSmemMax && m.n_features <= 4096)) {
