@@ -74,7 +74,7 @@ struct SmemLayoutT {
     static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
     static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
     static constexpr int bars = glob + BM * 8;                       // mbarriers
-    static constexpr int n_bars = 4 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
+    static constexpr int n_bars = 3 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
 };
@@ -96,9 +96,6 @@ struct GemmParams {
     const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
     int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
     int b_tile_bytes;       // ... bytes reserved per W stage ...
-    int raw_stages;         // > 0 (FP16, unpaired, small W tiles): raw fp32 X tiles land in a ring of their own
-                            // (raw_stages x 32 KB after the W ring) and are converted into the operand ring piece by
-                            // piece instead of in place; 0: in place
     int b_stages;           // ... and W ring depth: a_stages * 32 KB + b_stages * b_tile_bytes <= 192 KB
     int acc_bufs;           // 2: N <= 128, two accumulator buffers 128 TMEM columns apart -- the epilogue of a tile
                             // overlaps the MMAs of the next; 1 otherwise
@@ -388,8 +385,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* b_empty = b_full + kMaxBStages;      // [B_STAGES] MMA -> TMA
     uint64_t* acc_full = b_empty + kMaxBStages;       // [2 accumulator buffers] MMA -> epilogue
     uint64_t* acc_empty = acc_full + 2;            // [2] epilogue -> MMA
-    uint64_t* raw_empty = acc_empty + 2;           // [raw_stages] converters -> TMA (raw ring mode)
-    uint64_t* xchg_bar = raw_empty + kMaxAStages;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
+    uint64_t* xchg_bar = acc_empty + 2;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SmemLayout::tmem_slot);
 
     const int warp = threadIdx.x >> 5;
@@ -421,7 +417,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_init(a_ready + i, PAIR ? 2 * kConvThreads : kConvThreads);    // PAIR: both CTAs' converters report to the issuing CTA
             mbar_init(a_empty + i, 1);
         }
-        for (int i = 0; i < kMaxAStages; ++i) mbar_init(raw_empty + i, kConvWarps);
         for (int i = 0; i < B_STAGES; ++i) {
             mbar_init(b_full + i, 1);
             mbar_init(b_empty + i, w_mc ? p.nrt : 1);    // every CTA sharing the W tile has consumed the stage
@@ -505,23 +500,18 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const bool leader = elect_one();
         int as = 0;
         uint32_t aph = 0;
-        const bool raw_ring = F16 && !PAIR && p.raw_stages > 0;
-        const int x_stages = raw_ring ? p.raw_stages : A_STAGES;
-        uint64_t* x_free = raw_ring ? raw_empty : a_empty;       // who hands the landing buffer back
-        unsigned char* raw_base = b_t + B_STAGES * B_TILE_BYTES;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             const int64_t tile = grp * gsz + rt;
             const int row0 = (int)(tile * BM);
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                mbar_wait(x_free + as, aph ^ 1);
+                mbar_wait(a_empty + as, aph ^ 1);
                 if (leader) {
                     mbar_expect_tx(x_full + as, RAW_BYTES);
-                    unsigned char* xdst = raw_ring ? raw_base + as * RAW_BYTES
-                                                   : (F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES);
+                    unsigned char* xdst = F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES;
                     tma_load_2d(xdst, &map_x, kc * BKx, row0, x_full + as);
                 }
                 __syncwarp();
-                if (++as == x_stages) { as = 0; aph ^= 1; }
+                if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -600,45 +590,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const float sx = F16 ? p.x_scale[0] : 1.0f;
         int as = 0;
         uint32_t aph = 0;
-        if (F16 && !PAIR && p.raw_stages > 0) {
-            // Raw-ring mode: the fp32 tile sits in a buffer of its own, so nothing is overwritten while it
-            // is read -- no barrier between reading and writing, no need to hold the whole tile in
-            // registers, and the loads of later pieces overlap the arithmetic of earlier ones.  A lane
-            // takes 4 consecutive floats (consecutive lanes = consecutive 16 bytes: conflict-free, where
-            // the in-place form's 32-byte lane stride costs two wavefronts per quarter-warp) and writes
-            // the matching 8-byte halves of the swizzled hi and lo pieces.
-            int rs = 0;
-            uint32_t rph = 0;
-            unsigned char* raw_base = b_t + B_STAGES * B_TILE_BYTES;
-            for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
-                for (int kc = 0; kc < p.num_k_chunks; ++kc) {
-                    mbar_wait(x_full + rs, rph);
-                    mbar_wait(a_empty + as, aph ^ 1);             // the operand stage has been consumed
-                    if (!(p.debug_skip & 1)) {
-                        const unsigned char* raw = raw_base + rs * RAW_BYTES;
-                        unsigned char* stage = a_hi + as * A_STAGE;
-#pragma unroll 8
-                        for (int j = 0; j < (BM * BK16 / 4) / kConvThreads; ++j) {
-                            const int qd = t + kConvThreads * j;          // float4 index in the raw tile
-                            const int r = qd >> 4, q4 = qd & 15;
-                            const float4 x = *reinterpret_cast<const float4*>(raw + qd * 16);
-                            uint32_t h0, l0, h1, l1;
-                            split_pair(x.x, x.y, sx, h0, l0);
-                            split_pair(x.z, x.w, sx, h1, l1);
-                            const int off = r * 128 + (((q4 >> 1) ^ (r & 7)) << 4) + (q4 & 1) * 8;
-                            *reinterpret_cast<uint2*>(stage + off) = make_uint2(h0, h1);
-                            *reinterpret_cast<uint2*>(stage + A_TILE_BYTES + off) = make_uint2(l0, l1);
-                        }
-                    }
-                    fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
-                    mbar_arrive(a_ready + as);
-                    __syncwarp();                        // every lane has read its share of the raw tile
-                    if (lane == 0) mbar_arrive(raw_empty + rs);
-                    if (++as == A_STAGES) { as = 0; aph ^= 1; }
-                    if (++rs == p.raw_stages) { rs = 0; rph ^= 1; }
-                }
-            }
-        } else
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             const int64_t tile = grp * gsz + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
@@ -1692,29 +1643,22 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // fixed 4 x 32 KB W ring only two k-chunks of W (hi + lo tile each) were in flight, and a W slot is
     // held from its L2 fetch until the MMAs that read it retire: ~1.15 us per chunk however deep the X
     // ring was.  Small tiles buy a 12- or 6-deep W ring and a third X stage.
-    p.raw_stages = 0;
-    // Raw-ring conversion is opt-in (LRS_GEMM_RAW=1): measured 4137 against 4690 GB/s in place at d=256,
-    // C=32 and 3214 against 3457 at d=4096, C=64 -- the rings it leaves room for are shallower.
-    bool raw_ring = false;
-    if (const char* e = getenv("LRS_GEMM_RAW")) raw_ring = f16 && atoi(e) != 0;
+    // (Converting the fp32 tile in a ring of its own instead of in place was tried: 4137 against 4690 GB/s at
+    // d=256, C=32, 3214 against 3457 at d=4096, C=64 -- the rings it leaves room for are shallower.)
     if (L.pair) {
         p.b_tile_bytes = SmemLayoutT<true>::b_tile; p.a_stages = SmemLayoutT<true>::a_stages; p.b_stages = SmemLayoutT<true>::b_stages;
     } else if (L.mma_n <= 64) {
         p.b_tile_bytes = 8 * 1024; p.a_stages = 3; p.b_stages = 12;
-        if (raw_ring) { p.a_stages = 2; p.b_stages = 8; p.raw_stages = 2; }
     } else if (L.mma_n <= 128) {
         p.b_tile_bytes = 16 * 1024; p.a_stages = 3; p.b_stages = 6;
-        if (raw_ring) { p.a_stages = 2; p.b_stages = 4; p.raw_stages = 2; }
     } else {
         p.b_tile_bytes = 32 * 1024; p.a_stages = 2; p.b_stages = 4;
     }
-    if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages[,raw_stages]"
-        int as = 0, bs = 0, rs = 0;
-        const int n = sscanf(e, "%d,%d,%d", &as, &bs, &rs);
-        if (n == 2) rs = 0;
-        if (n >= 2 && (!L.pair || rs == 0) && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages && rs >= 0 && rs <= kMaxAStages &&
-            (rs == 0 || f16) && (as + rs) * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) {
-            p.a_stages = as; p.b_stages = bs; p.raw_stages = rs;
+    if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages"
+        int as = 0, bs = 0;
+        if (sscanf(e, "%d,%d", &as, &bs) == 2 && as >= 1 && as <= kMaxAStages && bs >= 2 && bs <= kMaxBStages &&
+            as * 32 * 1024 + bs * p.b_tile_bytes <= 192 * 1024) {
+            p.a_stages = as; p.b_stages = bs;
         }
     }
     p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
