@@ -97,3 +97,35 @@ def test_cfg3_multinomial_resident_chunk(eng):
     assert bool((out["decision"].argmax(dim=1).int() == out["label"]).all())
     assert float((P.max(dim=1).values - out["maxprob"]).abs().max()) <= 1e-6
     _sample_check(clf, X, out, W, b, "cfg3 chunk", k=256, z_atol=parity.Z_ATOL_TENSOR)
+
+
+@pytest.mark.parametrize("d,c,n", [(30, 1, 50_000_000), (54, 7, 20_000_000), (100_001, 1, 30_000)])
+def test_unaligned_rows_full_size(eng, d, c, n):
+    """The kernels for rows that are not 16-byte aligned at production sizes (flat-tile ring for d=30 binary
+    and d=54 x 7 classes, 4-byte-load wide kernel for d=100001): row sums, label rule, shard invariance
+    across the 4096-row batch threshold, oracle on sampled rows (first and last row included)."""
+    import torch
+    W, b = synth.make_model(d, c, 5 + d)
+    clf = eng[0].B200LogisticRegression(W, b, list(range(max(c, 2))))
+    torch.manual_seed(d)
+    X = torch.empty((n, d), device="cuda")
+    step = max(1, (1 << 27) // d)
+    for lo in range(0, n, step):
+        X[lo:lo + step].normal_()
+    out = clf.score_rows(X, proba=True, decision=True, label=True, maxprob=True)
+    torch.cuda.synchronize()
+    assert clf.take_nonfinite() == 0
+    P, z, lab, mp = out["proba"], out["decision"], out["label"], out["maxprob"]
+    assert float((P.sum(dim=1) - 1).abs().max()) <= 4e-7
+    assert bool((P.max(dim=1).values == mp).all())
+    if c == 1:
+        assert bool(((z > 0).int() == lab).all())
+    else:
+        assert bool((z.argmax(dim=1).int() == lab).all() or (z.gather(1, lab.long()[:, None]).squeeze(1) == z.max(dim=1).values).all())
+    # a small block (below the ring's 4096-row threshold) and a large one score to the same bits
+    for lo, hi in ((n // 3, n // 3 + 1000), (n // 2 + 1, n // 2 + 1 + min(n // 4, 2_000_000))):
+        part = clf.score_rows(X[lo:hi], proba=True, label=True)
+        torch.cuda.synchronize()
+        assert bool((part["proba"] == P[lo:hi]).all()) and bool((part["label"] == lab[lo:hi]).all()), (lo, hi)
+    _sample_check(clf, X, out, W, b, f"unaligned full size d={d} C={c}", k=1024)
+    clf.close()
