@@ -523,7 +523,7 @@ narrow_bulk_kernel(const float* __restrict__ X, int64_t n_rows, int d, int dpad,
 // them is still one contiguous span of memory: the producer lane copies whole tiles of rows
 // (TILE_ROWS x ldx floats, a multiple of 16 bytes) into a shared-memory ring with cp.async.bulk -- the
 // 16-byte aligned middle of the span in one bulk copy, the up to three floats before and after it
-// with plain loads, so nothing outside [X, X + n*ldx) is touched -- and eight consumer warps read
+// with plain loads, so nothing outside [X, X + n*ldx) is touched -- and the consumer warps (16, or 12 for 5..24 classes) read
 // their rows back with scalar shared loads, which do not care about alignment.  Same lane mapping,
 // cross-lane reduction and epilogue as above; W in shared memory.  Serves ldx <= kFlatMaxLdx.
 constexpr int kFlatMaxLdx = 2048;

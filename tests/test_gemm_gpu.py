@@ -1,4 +1,4 @@
-"""The tcgen05 (3xTF32) GEMM + fused-softmax path against the oracle, through the C ABI.
+"""The tcgen05 (3xFP16 / 3xTF32 split) GEMM + fused-softmax path against the oracle, through the C ABI.
 Shapes cover one and two 256-class blocks per CTA, clusters of 1/2/4 class slices, class counts
 that are not multiples of 4 (scalar stores) or of 32 (ragged last chunk), K tails and ragged n."""
 import numpy as np

@@ -140,7 +140,7 @@ def test_narrow_class_buckets(eng, ns):
 @pytest.mark.parametrize("ns", list(range(5, 17)))
 def test_mid_class_counts(eng, ns):
     """5..16 classes: the 4-rows-by-NS register-tile kernel.  d picks the lanes-per-row variant
-    (<= 64: 4 lanes, <= 256: 8, above: 32), 4-aligned and not; d=2600 pushes W past the 96 KB that
+    (up to 256: 4 lanes, above: 8), 4-aligned and not; d=2600 pushes W past the 96 KB that
     fit shared memory for the larger ns (W then comes through L1)."""
     _, lib = eng
     rng = np.random.default_rng(ns * 101)
