@@ -104,6 +104,15 @@ int lr_model_take_nonfinite(lr_model* m, void* stream, uint64_t* n_rows_nonfinit
  * Diagnostic; 0 on the other paths. */
 int lr_model_take_rescored(lr_model* m, void* stream, uint64_t* n_rows_rescored);
 
+/* Synchronise `stream` and return (then reset) how many rows the tensor-core path scored in 3xTF32
+ * instead of its default 3xFP16 since the last call.  The arithmetic is chosen per call on the device:
+ * W is balanced per feature at load time so that unstandardised features do not matter, and each batch
+ * is sampled; when what is left of its dynamic range would push fp16 `lo` halves into subnormals far
+ * enough to move a logit by 2e-6, the whole call runs in 3xTF32 (fp32 exponent range, half the tensor
+ * rate).  Same results contract either way (decision_function / predict_proba as lr_score);
+ * diagnostic: a model that reports most of its rows here is paying 2x on that path. */
+int lr_model_take_fallback(lr_model* m, void* stream, uint64_t* n_rows_tf32);
+
 /*
  * Same contract as lr_score with HOST buffers: rows are streamed through device staging buffers in
  * chunks (H2D copy, kernel, D2H copy overlapped on three streams) and the call returns when every

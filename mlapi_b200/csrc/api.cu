@@ -223,8 +223,19 @@ int lr_model_take_rescored(lr_model* h, void* stream, uint64_t* out) {
     unsigned long long v = 0;                      // the device counter only ever grows
     LRS_CUDA(cudaMemcpyAsync(&v, m->status + 1, sizeof(v), cudaMemcpyDeviceToHost, s));
     LRS_CUDA(cudaStreamSynchronize(s));
-    *out = v - m->rescored_taken;
-    m->rescored_taken = v;
+    *out = v - m->rescored_taken.exchange(v);
+    return LR_OK;
+}
+
+int lr_model_take_fallback(lr_model* h, void* stream, uint64_t* out) {
+    if (!h || !out) return fail(LR_ERR_INVALID, "model / out is NULL");
+    Model* m = reinterpret_cast<Model*>(h);
+    DeviceGuard guard(m->device);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    unsigned long long v = 0;                      // the device counter only ever grows
+    LRS_CUDA(cudaMemcpyAsync(&v, m->status + 2, sizeof(v), cudaMemcpyDeviceToHost, s));
+    LRS_CUDA(cudaStreamSynchronize(s));
+    *out = v - m->fallback_taken.exchange(v);
     return LR_OK;
 }
 

@@ -46,9 +46,11 @@ struct Model {
     int narrow_ns = 0, narrow_dpad = 0, narrow_lanes = 0;
     bool narrow_bulk = false;             // opt-in (LRS_NARROW_BULK=1): cp.async.bulk ring, measured 4% slower than plain loads
     int64_t narrow_bulk_min_rows = 65536;
-    // status word(s): [0] = rows that scored to a non-finite value
+    // status words: [0] rows that scored to a non-finite value, [1] rows re-scored in fp32 (tensor-core path,
+    // running), [2] rows the tensor-core path scored in 3xTF32 because 3xFP16 would have lost precision (running)
     unsigned long long* status = nullptr;
-    unsigned long long rescored_taken = 0;   // host shadow for lr_model_take_rescored
+    std::atomic<unsigned long long> rescored_taken{0};   // host shadows for lr_model_take_rescored / _take_fallback
+    std::atomic<unsigned long long> fallback_taken{0};
 
     GemmPlan* gemm = nullptr;
     HostStage* stage = nullptr;
@@ -78,6 +80,7 @@ int generic_launch(const Model& m, const ScoreArgs& a);
 
 bool gemm_supports(const Model& m, const ScoreArgs& a);
 int gemm_prepare(Model& m, const double* coef, const double* intercept);
+int gemm_load(Model& m, const double* coef, const double* intercept);
 void gemm_destroy(Model& m);
 void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total);
 int gemm_active_layout(const Model& m);

@@ -93,7 +93,14 @@ struct GemmParams {
     int num_k_chunks;
     const float* bias;      // padded to ncc*nb*256, -inf beyond n_classes
     const float* col_inv_scale;   // FP16 mode: 1 / class scale, padded like bias
-    const float* x_scale;         // FP16 mode: device [2] = {scale applied to X, its inverse}, made per call
+    const float* x_scale;         // per-call block made by x_scale_kernel: [0] scale applied to X, [1] its inverse,
+                                  // [4] arithmetic chosen for this call (bits: 0 = 3xFP16, 1 = 3xTF32), [5] size of a
+                                  // typical partial sum of this batch, [6] logit error the fp16 subnormal floor can cause
+    const float* col_scale;       // FP16 mode: per-feature power of two applied to X (its inverse is folded into W), padded
+                                  // with zeros to whole k-chunks
+    float kappa;                  // relative logit error of the truncating TMEM accumulation (layout, arithmetic, row length)
+    int acc_stride;               // TMEM columns between the two accumulator buffers (acc_bufs == 2)
+    int count_fallback;           // 3xTF32 kernel launched as the fallback of a 3xFP16 model: add n_rows to status[2]
     int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
     int b_tile_bytes;       // ... bytes reserved per W stage ...
     int b_stages;           // ... and W ring depth: a_stages * 32 KB + b_stages * b_tile_bytes <= 192 KB
@@ -256,13 +263,13 @@ __device__ __forceinline__ float ex2(float x) {
 }
 // Two scaled values -> packed fp16 (hi, hi) and packed fp16 residuals (lo, lo), with the packed
 // fp32x2 / f16x2 conversions of sm_100: 7 instructions per pair.
-__device__ __forceinline__ void split_pair(float a, float b, float sx, uint32_t& hi, uint32_t& lo) {
+__device__ __forceinline__ void split_pair(float a, float b, float sa, float sb, uint32_t& hi, uint32_t& lo) {
     asm("{\n\t"
         ".reg .b64 v, s, r;\n\t"
         ".reg .f32 ha, hb;\n\t"
         ".reg .b16 h0, h1;\n\t"
         "mov.b64 v, {%2, %3};\n\t"
-        "mov.b64 s, {%4, %4};\n\t"
+        "mov.b64 s, {%4, %5};\n\t"
         "mul.rn.f32x2 v, v, s;\n\t"
         "mov.b64 {ha, hb}, v;\n\t"
         "cvt.rn.f16x2.f32 %0, hb, ha;\n\t"            // low half <- a, high half <- b
@@ -275,7 +282,7 @@ __device__ __forceinline__ void split_pair(float a, float b, float sx, uint32_t&
         "cvt.rn.f16x2.f32 %1, hb, ha;\n\t"
         "}"
         : "=r"(hi), "=r"(lo)
-        : "f"(a), "f"(b), "f"(sx));
+        : "f"(a), "f"(b), "f"(sa), "f"(sb));
 }
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
@@ -355,6 +362,11 @@ template <bool F16, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                     const __grid_constant__ CUtensorMap map_wlo, const GemmParams p) {
+    // The arithmetic of a call is chosen on the device (x_scale_kernel: 3xFP16 unless the data's dynamic range
+    // would cost precision); both kernels are enqueued and the one not chosen leaves here, every CTA alike.
+    if (reinterpret_cast<const uint32_t*>(p.x_scale)[4] != (F16 ? 0u : 1u)) return;
+    if (!F16 && p.count_fallback && blockIdx.x == 0 && threadIdx.x == 0)
+        atomicAdd(p.status + 2, (unsigned long long)p.n_rows);
     extern __shared__ unsigned char smem_dyn[];
     // 1024-byte alignment by pointer arithmetic on the shared array itself: going through uintptr_t made
     // every access below a generic LD/ST instead of LDS/STS
@@ -549,7 +561,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         mbar_wait(b_full + bs, bph);
                         tc_fence_after();
                         const uint64_t bd = b0 + (uint64_t)(bs * (B_TILE_BYTES >> 4));
-                        const uint32_t d_tmem = tmem_base + buf * 128u + (uint32_t)(nbk * BN);
+                        const uint32_t d_tmem = tmem_base + buf * (uint32_t)p.acc_stride + (uint32_t)(nbk * BN);
                         const uint32_t c_tmem = d_tmem + c_off;
                         if (leader) {
                             if (part == 0) {
@@ -588,11 +600,19 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // ===================== converters: raw fp32 -> (hi, lo) TF32 pair =====================
         const int t = threadIdx.x - 64;             // 0..kConvThreads-1
         const float sx = F16 ? p.x_scale[0] : 1.0f;
+        // FP16: the four columns of a k-chunk this thread converts are the same for all of its quads
+        // (quad index = t + 128 j, 16 quads per row), so their scales are one 128-bit load per chunk
+        const float4* cs4 = reinterpret_cast<const float4*>(p.col_scale) + (t & 15);
         int as = 0;
         uint32_t aph = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
             const int64_t tile = grp * gsz + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                float4 cs = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+                if constexpr (F16) {
+                    cs = __ldg(cs4 + kc * (BK16 / 4));
+                    cs.x *= sx; cs.y *= sx; cs.z *= sx; cs.w *= sx;      // powers of two: exact
+                }
                 mbar_wait(x_full + as, aph);
                 if (p.debug_skip & 1) {
                 } else if constexpr (!F16) {
@@ -629,8 +649,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const int qd = t + kConvThreads * j;
                         const int r = qd >> 4, q4 = qd & 15;
                         uint32_t h0, l0, h1, l1;
-                        split_pair(xr[j].x, xr[j].y, sx, h0, l0);
-                        split_pair(xr[j].z, xr[j].w, sx, h1, l1);
+                        split_pair(xr[j].x, xr[j].y, cs.x, cs.y, h0, l0);
+                        split_pair(xr[j].z, xr[j].w, cs.z, cs.w, h1, l1);
                         // SWIZZLE_128B: 16-byte piece ^ (row % 8); this quad is half a piece
                         const int off = r * 128 + (((q4 >> 1) ^ (r & 7)) << 4) + (q4 & 1) * 8;
                         *reinterpret_cast<uint2*>(stage + off) = make_uint2(h0, h1);
@@ -652,6 +672,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         //                                                      -> combine halves, then CTAs
         //   3. p = e / sum -> global memory
         // so each class costs one exp, and the statistics of a row meet through shared memory.
+        // Logit error model of this call: the truncating accumulation leaves ~kappa times the size of the
+        // partial sums -- for a row that is the larger of its top logit and what this batch's rows and this
+        // model's classes typically add up to on the way ([5]) -- plus what fp16's subnormal floor can cost ([6]).
+        const float psum_scale = p.x_scale[5];
+        const float floor_err = p.x_scale[6];
         const int ew = warp - (2 + kConvWarps);      // 0..7
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int h = ew >> 2;                       // column half
@@ -669,7 +694,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const bool live = row < p.n_rows;
             const uint32_t par = it & 1;
             const uint32_t buf = p.acc_bufs == 2 ? (it & 1u) : 0u;
-            const uint32_t t_lane = t_lane0 + buf * 128u;
+            const uint32_t t_lane = t_lane0 + buf * (uint32_t)p.acc_stride;
             mbar_wait(acc_full + buf, (p.acc_bufs == 2 ? (it >> 1) : it) & 1u);
             tc_fence_after();
 
@@ -709,8 +734,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                                 if (i < n_real) __stcs(zr + i, v[i]);
                         }
                     }
-                    const float kappa = F16 ? (p.split ? 2.8e-6f : 6e-6f) : (p.split ? 3.5e-6f : 1.1e-5f);
-                    const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
+                    const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
+                    const float tau = gm - 2.0f * ez;
                     const float gml = gm * kLog2e;
                     float gs = 0.0f;
                     int gnear = 0;
@@ -721,7 +746,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         gs += v[i];
                     }
                     const float inv = __frcp_rn(gs);
-                    const float risk_thr = 8e-6f / (kappa * fmaxf(fabsf(gm), 1.0f));
+                    const float risk_thr = 8e-6f / ez;
                     bool risk = false;
                     if (p.proba) {
 #pragma unroll
@@ -835,8 +860,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // truncating TMEM accumulation is <= 3.2e-6 |z| with the split accumulator and 3x that
             // without; the band is twice that, with margin.
             // (3xFP16 takes half as many accumulation steps as 3xTF32: measured 5.0e-6 / 2.4e-6)
-            const float kappa = F16 ? (p.split ? 2.8e-6f : 6e-6f) : (p.split ? 3.5e-6f : 1.1e-5f);
-            const float tau = gm - 2.0f * kappa * fmaxf(1.0f, fabsf(gm));
+            const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
+            const float tau = gm - 2.0f * ez;
             float ssum = 0.0f;
             int near = 0;
             for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
@@ -915,7 +940,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // ---- pass 3: normalise and store this warp's slice of the row
             // |dp| ~ p(1-p)|dz| with |dz| <= kappa |z|: flag the row when that could pass ~6e-6, which
             // needs a large maximum AND a class of middling probability
-            const float risk_thr = 8e-6f / (kappa * fmaxf(fabsf(gm), 1.0f));
+            const float risk_thr = 8e-6f / ez;
             bool risk = false;
             if (p.proba) {
                 for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
@@ -1207,132 +1232,242 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx,
     }
 }
 
-// FP16 mode: a power-of-two scale for X from the largest |x| of up to 2048 rows spread over the batch,
-// chosen so that this maximum lands in (2, 4]: fp16 then has 2^14 of headroom above it and full
-// hi+lo precision below it.  A row holding something 16 000 times larger than anything sampled
-// overflows to inf, is seen as non-finite by the epilogue and re-scored in fp32.
-// out: [0] scale, [1] 1/scale, [2] running maximum (as bits), [3] arrival ticket -- [2] and [3] zeroed by
-// the caller.  kXScaleBlocks CTAs share the 2048 sampled rows (one CTA alone took ~1 ms at d=4096); the
-// last one to arrive turns the maximum into the scale.
+// Per-call look at the batch (every arithmetic): up to 2048 rows spread over it are read once, each feature
+// multiplied by the model's per-feature power of two (w_colscale_kernel), and per row the largest magnitude and
+// the 2-norm are kept.  From those the last CTA to arrive derives
+//   out[0], out[1]  the power-of-two scale for X and its inverse: the row maximum that all but ~0.2 % of the sampled
+//                   rows stay under lands in [16, 64].  fp16 then holds hi + lo halves at full precision down to
+//                   ~2^-9 of that maximum and has ~2^10 of headroom above it; a row holding something larger still
+//                   overflows to inf, is seen as non-finite by the epilogue and re-scored in fp32 -- so one outlier
+//                   row costs itself a second pass, not every other row its low half;
+//   out[6]          the logit error fp16's subnormal floor (quantum q = 2^-24 in scaled units) can cause:
+//                   q / x_scale * max_c ||W'_c||_2 from the X side + q * max_c(1 / class scale) * ||x'||_2 from the W
+//                   side (rounding errors of the d terms add like a random walk; q is 3.5 sigma of one);
+//   out[4]          the arithmetic of this call: 3xFP16 (bits 0) while that error stays under 2e-6, else 3xTF32
+//                   (bits 1: fp32's exponent range, half the tensor rate) -- `force` 1 / 2 pins FP16 / TF32;
+//   out[5]          the size of a typical partial sum, ||x'||_2 * max_c ||W'_c||_2 / sqrt(d): what the truncating
+//                   accumulation error is proportional to when it exceeds the logit itself.
+// out[3] is the arrival ticket, zeroed by the caller.  rowstat: [2][kMaxSample] floats of scratch.
 constexpr int kXScaleBlocks = 128;
+constexpr int kMaxSample = 2048;
+constexpr int kStatBins = 2048;          // float bits >> 20: 8 exponent bits + 3 mantissa bits (12 % steps)
 __global__ void __launch_bounds__(256)
-x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, float* __restrict__ out) {
-    __shared__ float red[8];
+x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, const float* __restrict__ col_scale,
+               float w_norm_max, float inv_cscale_max, int force, float* __restrict__ out, float* __restrict__ rowstat) {
+    __shared__ unsigned hist[2][kStatBins];
+    __shared__ unsigned part[2][256];
+    __shared__ float q_s[2];
     __shared__ bool last;
     // up to 2048 sampled rows, fewer for long rows (about 4 MB read in all, at least 64 rows)
     int64_t n_s = (int64_t)(1 << 20) / d;
-    n_s = n_s < 64 ? 64 : (n_s > 2048 ? 2048 : n_s);
+    n_s = n_s < 64 ? 64 : (n_s > kMaxSample ? kMaxSample : n_s);
     n_s = n_rows < n_s ? n_rows : n_s;
     const int64_t step = n_rows / n_s;
     const int lane = threadIdx.x & 31;
-    float mx = 0.0f;
     for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < n_s; i += (int64_t)gridDim.x * 8) {
         const float4* x = reinterpret_cast<const float4*>(X + (i * step) * ldx);     // rows are 16-byte aligned here
+        const float4* c4 = reinterpret_cast<const float4*>(col_scale);
+        float mx = 0.0f, ss = 0.0f;
 #pragma unroll 4
         for (int k = lane; k < d / 4; k += 32) {
-            const float4 v = __ldg(x + k);
-            const float m4 = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-            // NaN / inf are ignored (fmaxf drops NaN; an infinite piece is skipped as a whole)
-            if (m4 <= 3.0e38f) mx = fmaxf(mx, m4);
-            else {
-                if (fabsf(v.x) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.x));
-                if (fabsf(v.y) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.y));
-                if (fabsf(v.z) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.z));
-                if (fabsf(v.w) <= 3.0e38f) mx = fmaxf(mx, fabsf(v.w));
-            }
+            const float4 v = __ldg(x + k), c = __ldg(c4 + k);
+            const float a[4] = {fabsf(v.x * c.x), fabsf(v.y * c.y), fabsf(v.z * c.z), fabsf(v.w * c.w)};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (a[j] <= 1.0e18f) {            // NaN / inf (and what would overflow the sum of squares) are left out
+                    mx = fmaxf(mx, a[j]);
+                    ss = fmaf(a[j], a[j], ss);
+                }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            ss += __shfl_xor_sync(0xffffffffu, ss, off);
+        }
+        if (lane == 0) {
+            rowstat[i] = mx;
+            rowstat[kMaxSample + i] = sqrtf(ss);
         }
     }
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    if (lane == 0) red[threadIdx.x >> 5] = mx;
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int w = 1; w < 8; ++w) mx = fmaxf(mx, red[w]);
-        unsigned* word = reinterpret_cast<unsigned*>(out);
-        atomicMax(word + 2, __float_as_uint(mx));             // non-negative floats order like their bits
         __threadfence();
-        last = atomicAdd(word + 3, 1u) == gridDim.x - 1;
-        if (last) {
-            __threadfence();
-            mx = __uint_as_float(atomicMax(word + 2, 0u));
-            int e = 0;
-            float sc = 1.0f;
-            if (mx > 0.0f) {
-                frexpf(mx, &e);                                   // mx = f * 2^e, f in [0.5, 1)
-                sc = ldexpf(1.0f, 2 - e);                         // mx * sc in [2, 4)
-            }
-            out[0] = sc;
-            out[1] = 1.0f / sc;
-        }
+        last = atomicAdd(reinterpret_cast<unsigned*>(out) + 3, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // The value that all but n_s / 512 of the sampled rows stay under, for both statistics: a histogram over
+    // the top 11 bits of the (non-negative) floats, scanned from the top; the answer is the bin's upper edge.
+    for (int i = threadIdx.x; i < 2 * kStatBins; i += 256) (&hist[0][0])[i] = 0u;
+    __syncthreads();
+    for (int i = threadIdx.x; i < (int)n_s; i += 256) {
+        atomicAdd(&hist[0][__float_as_uint(__ldcg(rowstat + i)) >> 20], 1u);
+        atomicAdd(&hist[1][__float_as_uint(__ldcg(rowstat + kMaxSample + i)) >> 20], 1u);
+    }
+    __syncthreads();
+    constexpr int PER = kStatBins / 256;
+    for (int w = 0; w < 2; ++w) {
+        unsigned sum = 0;
+        for (int j = 0; j < PER; ++j) sum += hist[w][threadIdx.x * PER + j];
+        part[w][threadIdx.x] = sum;
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        const int w = threadIdx.x;
+        const unsigned drop = (unsigned)(n_s / 512);
+        unsigned above = 0;
+        int t = 255;
+        while (t > 0 && above + part[w][t] <= drop) above += part[w][t--];
+        int bin = t * PER + PER - 1;
+        while (bin > t * PER && above + hist[w][bin] <= drop) above += hist[w][bin--];
+        // all-zero statistics end in bin 0: the edge 2^-126 * ... is harmless (scale clamps below)
+        q_s[w] = fminf(__uint_as_float((unsigned)(bin + 1) << 20), 3.0e38f);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const float qmax = q_s[0], qnorm = q_s[1];
+        int e = 0;
+        frexpf(qmax, &e);                                 // qmax = f * 2^e, f in [0.5, 1)
+        e = 6 - e;                                        // qmax * 2^e in [32, 64)
+        e = e > 60 ? 60 : (e < -60 ? -60 : e);            // col_scale is clamped likewise: products stay normal
+        const float sc = ldexpf(1.0f, e);
+        const float q = 5.9604645e-8f;                    // 2^-24
+        float floor_err = q / sc * w_norm_max + q * inv_cscale_max * qnorm;
+        if (!(floor_err <= 3.0e38f)) floor_err = 3.0e38f;
+        const unsigned mode = force == 1 ? 0u : (force == 2 ? 1u : (floor_err > 2.0e-6f ? 1u : 0u));
+        out[0] = sc;
+        out[1] = 1.0f / sc;
+        reinterpret_cast<unsigned*>(out)[4] = mode;
+        out[5] = qnorm * w_norm_max * rsqrtf((float)d);
+        out[6] = mode == 0u ? floor_err : 0.0f;
     }
 }
 
-// FP16 operands of W, made on the device: class c (one CTA) is scaled by the power of two that puts its
-// largest |w| in [2, 4) and split into fp16 hi + lo halves from the float64 value; 1/scale goes to inv[c].
+// Per-feature balance of the FP16 operands, from W alone (one thread per feature): column k of W is multiplied
+// by 2^e_k with e_k = -floor(log2 max_c |W[c][k]|), so that every column of the balanced W' peaks in [1, 2),
+// and the converter multiplies feature k of X by 2^-e_k.  Powers of two: the products are unchanged to the
+// bit.  A model fitted on unstandardised features has weights inversely proportional to the feature scales
+// (REF/Logistic Regression.ipynb:28-34 fits raw centimetres), so this also brings the features of X to one
+// scale -- without it a feature 2^10 below the largest one loses its fp16 `lo` half to subnormals.
+// x_mul[k] = 2^-e_k (0 for an all-zero column: the feature cannot matter), w_mul[k] = 2^e_k.
 __global__ void __launch_bounds__(256)
-w_split16_kernel(const double* __restrict__ coef, int d, int d16, __half* __restrict__ hi, __half* __restrict__ lo,
-                 float* __restrict__ inv) {
-    __shared__ double red[8];
+w_colscale_kernel(const double* __restrict__ coef, int C, int d, float* __restrict__ x_mul, double* __restrict__ w_mul) {
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= d) return;
+    double mx = 0.0;
+    for (int c = 0; c < C; ++c) mx = fmax(mx, fabs(coef[(size_t)c * d + k]));
+    int e = 0;
+    if (mx > 0.0 && mx <= 1.7976931348623157e308) {
+        frexp(mx, &e);                    // mx = f * 2^e, f in [0.5, 1)
+        e = 1 - e;                        // mx * 2^e in [1, 2)
+        e = e > 60 ? 60 : (e < -60 ? -60 : e);
+    }
+    x_mul[k] = mx == 0.0 ? 0.0f : (float)ldexp(1.0, -e);
+    w_mul[k] = ldexp(1.0, e);
+}
+
+// FP16 operands of W, made on the device: class c (one CTA) of the column-balanced W' is scaled by the power of
+// two that puts its largest magnitude in [2^14, 2^15) -- the top of fp16's range, the maximum being known
+// exactly: entries down to 2^-17 of it keep a normal `lo` half -- and split into fp16 hi + lo halves from the
+// float64 value; 1/scale goes to inv[c], the 2-norm of the balanced (unscaled) row to norm[c].
+__global__ void __launch_bounds__(256)
+w_split16_kernel(const double* __restrict__ coef, const double* __restrict__ w_mul, int d, int d16,
+                 __half* __restrict__ hi, __half* __restrict__ lo, float* __restrict__ inv, float* __restrict__ norm) {
+    __shared__ double red[8], red2[8];
     const int c = blockIdx.x;
     const double* w = coef + (size_t)c * d;
-    double mx = 0.0;
-    for (int k = threadIdx.x; k < d; k += 256) mx = fmax(mx, fabs(w[k]));      // fmax drops NaN, keeps inf
+    double mx = 0.0, ss = 0.0;
+    for (int k = threadIdx.x; k < d; k += 256) {
+        const double v = w[k] * w_mul[k];
+        mx = fmax(mx, fabs(v));      // fmax drops NaN, keeps inf
+        ss += v * v;
+    }
 #pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    for (int off = 16; off >= 1; off >>= 1) {
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        ss += __shfl_xor_sync(0xffffffffu, ss, off);
+    }
+    if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = mx; red2[threadIdx.x >> 5] = ss; }
     __syncthreads();
     mx = red[0];
+    ss = red2[0];
 #pragma unroll
-    for (int i = 1; i < 8; ++i) mx = fmax(mx, red[i]);
+    for (int i = 1; i < 8; ++i) { mx = fmax(mx, red[i]); ss += red2[i]; }
     double sc = 1.0;
     if (mx > 0.0 && mx <= 1.7976931348623157e308) {
         int e = 0;
         frexp(mx, &e);
-        sc = ldexp(1.0, 2 - e);
+        sc = ldexp(1.0, 15 - e);
     }
-    if (threadIdx.x == 0) inv[c] = (float)(1.0 / sc);
+    if (threadIdx.x == 0) { inv[c] = (float)(1.0 / sc); norm[c] = (float)sqrt(ss); }
     for (int k = threadIdx.x; k < d; k += 256) {
-        const double v = w[k] * sc;
+        const double v = w[k] * w_mul[k] * sc;
         const __half h = __float2half_rn((float)v);
         hi[(size_t)c * d16 + k] = h;
         lo[(size_t)c * d16 + k] = __float2half_rn((float)(v - (double)__half2float(h)));
     }
 }
 
+// TF32 operands of W (hi = round-to-nearest TF32, lo = TF32 of the residual), from the float64 coefficients.
+__global__ void __launch_bounds__(256)
+w_split_tf32_kernel(const double* __restrict__ coef, int d, int d4, float* __restrict__ hi, float* __restrict__ lo) {
+    const double* w = coef + (size_t)blockIdx.x * d;
+    for (int k = threadIdx.x; k < d; k += 256) {
+        const float h = to_tf32((float)w[k]);
+        hi[(size_t)blockIdx.x * d4 + k] = h;
+        lo[(size_t)blockIdx.x * d4 + k] = to_tf32((float)(w[k] - (double)h));
+    }
+}
+
 }  // namespace
 
 struct GemmPlan {
-    float* w_hi = nullptr;      // [c_pad][d] TF32 (round-to-nearest) part of coef_
-    float* w_lo = nullptr;      // [c_pad][d] TF32 of the residual
+    double* coef64 = nullptr;   // [C][d] float64 coef_ as handed in: what every operand copy below is made from
+    float* w_hi = nullptr;      // [c_pad][d4] TF32 (round-to-nearest) part of coef_
+    float* w_lo = nullptr;      // [c_pad][d4] TF32 of the residual
     float* bias = nullptr;      // [c_pad], -inf beyond n_classes
-    // FP16 mode: coef_ scaled per class by a power of two into (2, 4] and split into two halves
+    // FP16 operands: coef_ balanced per feature (w_colscale_kernel), scaled per class by a power of two to the
+    // top of fp16's range and split into two halves (w_split16_kernel)
     __half* w16_hi = nullptr;   // [c_pad][d16]
     __half* w16_lo = nullptr;
     float* col_inv_scale = nullptr;   // [c_pad] 1 / class scale
+    float* col_scale = nullptr;       // [d64] per-feature power of two applied to X, zero beyond n_features
+    double* w_mul = nullptr;          // [d] its inverse, applied to W
+    float* w_norm = nullptr;          // [c_pad] 2-norm of each balanced class row
+    float w_norm_max = 0.0f;          // largest of those                          } inputs of the per-call
+    float inv_cscale_max = 0.0f;      // largest 1 / class scale                    } precision guard
     float* w32_pad = nullptr;   // [C][d4] fp32 coef_ at a 16-byte pitch (only when n_features % 4 != 0)
     int d4 = 0;                 // n_features rounded up to 4
     int d16 = 0;                // row pitch of the fp16 copies (n_features rounded up to 8: TMA wants 16-byte pitches)
-    bool f16 = false;
-    // Two CTA layouts over the same W buffers:
-    //   [0] fast:     512 classes per CTA, one TMEM accumulator             (C <= 2048)
+    int d64 = 0;                // n_features rounded up to whole FP16 k-chunks
+    // Arithmetic: 0 = per call (3xFP16 unless the batch's dynamic range says 3xTF32), 1 = 3xFP16 always
+    // (LRS_GEMM_F16=2, measurements only: no guard), 2 = 3xTF32 always (LRS_GEMM_F16=0)
+    int force = 0;
+    // Three CTA layouts over the same W buffers:
+    //   [0] fast:     512 classes per CTA (CTA pairs), one TMEM accumulator that fills TMEM   (C in 257..2048)
     //   [1] accurate: 256 classes per CTA, correction products accumulate apart, 3x smaller logit
-    //                 error, so far fewer rows need the fp32 re-scoring pass  (C <= 1024)
-    // `active` starts on the fast layout where both exist (C in 257..1024) and moves to the accurate
-    // one when the re-scoring pass reports that the data is confident (lr_score_host feeds that back).
+    //                 error, so far fewer rows need the fp32 re-scoring pass                   (C <= 1024)
+    //   [2] overlap:  256 classes per CTA, one accumulator per tile but two of them in TMEM: the epilogue
+    //                 of a row tile runs under the MMAs of the next                             (C in 129..1024)
+    // `active` starts on the quickest layout the class count allows and moves to the accurate one when the
+    // re-scoring pass reports that the data is confident (lr_score_host feeds that back).
     struct Layout {
         int nb = 0, ncc = 0, nrt = 1;
         int mma_n = BN;             // see GemmParams::mma_n
         bool pair = false;          // cta_group::2: cluster = 2 * ncc CTAs
         bool split = false;
+        bool two_acc = false;       // two accumulator buffers (unsplit, unpaired, one 256-class block)
         int max_clusters[64] = {0};
         CUtensorMap map_whi, map_wlo, map_w16hi, map_w16lo;    // W boxes are BN / nrt rows
     };
-    Layout layout[2];
-    bool has[2] = {false, false};
-    int active = 0;
+    static constexpr int kLayouts = 3;
+    Layout layout[kLayouts];
+    bool has[kLayouts] = {false, false, false};
+    std::atomic<int> active{0};
     bool adaptive = true;
     int c_pad = 0;
-    uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen
+    uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen (lr_score_host holds the staging lock)
     bool configured[64] = {false};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
@@ -1377,16 +1512,6 @@ int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, u
     return make_map_ex(map, base, rows, cols, ld, box_rows, (uint32_t)BK, 4, true);
 }
 
-// cvt.rna.tf32.f32 on the host: round to nearest (ties away), keep 10 mantissa bits.
-float tf32_rna_host(float x) {
-    uint32_t u;
-    std::memcpy(&u, &x, 4);
-    if ((u & 0x7f800000u) != 0x7f800000u) u += 0x1000u;
-    u &= 0xffffe000u;
-    std::memcpy(&x, &u, 4);
-    return x;
-}
-
 }  // namespace
 
 // Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048.  TMA wants
@@ -1394,6 +1519,43 @@ float tf32_rna_host(float x) {
 // into an aligned scratch first, see gemm_launch.
 bool gemm_supports(const Model& m, const ScoreArgs& a) {
     return m.gemm != nullptr && a.n_rows < (int64_t)1 << 31;
+}
+
+// (Re)builds every operand copy of W from the float64 coefficients: called at creation and by
+// lr_model_update (a refit hands in a new iterate per evaluation; nothing is allocated here).
+int gemm_load(Model& m, const double* coef, const double* intercept) {
+    GemmPlan* g = m.gemm;
+    if (!g) return LR_OK;
+    const int C = m.n_scores, d = m.n_features, d4 = g->d4;
+    std::vector<float> bias(g->c_pad, -INFINITY);
+    for (int c = 0; c < C; ++c) bias[c] = (float)intercept[c];
+    LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+    LRS_CUDA(cudaMemcpy(g->coef64, coef, (size_t)C * d * sizeof(double), cudaMemcpyHostToDevice));
+    if (g->w32_pad) {
+        // fp32 coefficients at the padded pitch, for the re-scoring pass over re-pitched rows (see gemm_launch)
+        std::vector<float> w32((size_t)C * d4, 0.0f);
+        for (int c = 0; c < C; ++c)
+            for (int k = 0; k < d; ++k) w32[(size_t)c * d4 + k] = (float)coef[(size_t)c * d + k];
+        LRS_CUDA(cudaMemcpy(g->w32_pad, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    // Scale + hi/lo splits on the device from the float64 coefficients: on the host the software fp16
+    // conversions took 40 ms per million coefficients, which a refit pays per iteration.
+    w_split_tf32_kernel<<<C, 256>>>(g->coef64, d, d4, g->w_hi, g->w_lo);
+    w_colscale_kernel<<<(d + 255) / 256, 256>>>(g->coef64, C, d, g->col_scale, g->w_mul);
+    w_split16_kernel<<<C, 256>>>(g->coef64, g->w_mul, d, g->d16, g->w16_hi, g->w16_lo, g->col_inv_scale, g->w_norm);
+    count_launch(3);
+    std::vector<float> inv(C), norm(C);
+    LRS_CUDA(cudaMemcpy(inv.data(), g->col_inv_scale, C * sizeof(float), cudaMemcpyDeviceToHost));   // synchronises
+    LRS_CUDA(cudaMemcpy(norm.data(), g->w_norm, C * sizeof(float), cudaMemcpyDeviceToHost));
+    LRS_CUDA(cudaGetLastError());
+    float nmax = 0.0f, imax = 0.0f;
+    for (int c = 0; c < C; ++c) {
+        if (norm[c] > nmax) nmax = norm[c];          // NaN never compares greater
+        if (inv[c] > imax) imax = inv[c];
+    }
+    g->w_norm_max = nmax;
+    g->inv_cscale_max = imax;
+    return LR_OK;
 }
 
 int gemm_prepare(Model& m, const double* coef, const double* intercept) {
@@ -1414,11 +1576,15 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         cudaGetLastError();
     }
     GemmPlan* g = new GemmPlan();
+    m.gemm = g;                                     // from here on lr_model_destroy frees what was allocated
     const int C = m.n_scores, d = m.n_features;
     const int d4 = (d + 3) / 4 * 4;                 // row pitch of the fp32 copies: TMA wants 16-byte pitches
     g->d4 = d4;
+    g->d16 = (d + 7) / 8 * 8;
+    g->d64 = (d + BK16 - 1) / BK16 * BK16;
     auto& fast = g->layout[0];
     auto& acc = g->layout[1];
+    auto& ovl = g->layout[2];
     if (C > BN) {                                   // fast layout: 512 classes per CTA
         fast.nb = 2;
         fast.ncc = (C + 2 * BN - 1) / (2 * BN);
@@ -1431,6 +1597,13 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         if (acc.ncc == 3) acc.ncc = 4;
         acc.split = true;
         g->has[1] = true;
+    }
+    if (C > 128 && C <= kMaxCluster * BN) {         // overlap layout: 256 classes per CTA, two accumulator buffers
+        ovl.nb = 1;
+        ovl.ncc = (C + BN - 1) / BN;
+        if (ovl.ncc == 3) ovl.ncc = 4;
+        ovl.two_acc = true;
+        g->has[2] = true;
     }
     // two row tiles per cluster share every W tile through TMA multicast (cluster <= 8 CTAs)
     bool mc = true;
@@ -1456,87 +1629,57 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         acc.mma_n = (C + 31) / 32 * 32;
         if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
     }
+    if (g->has[2] && ovl.ncc == 1 && C <= BN - 32) ovl.mma_n = (C + 31) / 32 * 32;
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
         if (g->has[want]) g->active = want;
         g->adaptive = false;
     }
+    if (const char* e = getenv("LRS_GEMM_LAYOUT")) { // pin a layout by index
+        const int want = atoi(e);
+        if (want >= 0 && want < GemmPlan::kLayouts && g->has[want]) g->active = want;
+        g->adaptive = false;
+    }
     g->c_pad = 0;
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < GemmPlan::kLayouts; ++i)
         if (g->has[i] && g->layout[i].ncc * g->layout[i].nb * BN > g->c_pad) g->c_pad = g->layout[i].ncc * g->layout[i].nb * BN;
     if (const char* e = getenv("LRS_GEMM_FIXUP")) g->fixup = atoi(e) != 0;
-    // 3xFP16 is the default arithmetic; LRS_GEMM_F16=0 selects 3xTF32.  Only the chosen one's copies of W are
-    // built (a refit rebuilds the model every iteration: the unused pair cost as much host time as the used one).
-    g->f16 = true;
-    if (const char* e = getenv("LRS_GEMM_F16")) g->f16 = atoi(e) != 0;
-    std::vector<float> bias(g->c_pad, -INFINITY);
-    for (int c = 0; c < C; ++c) bias[c] = (float)intercept[c];
-    if (d4 != d) {
-        // fp32 coefficients at the padded pitch, for the re-scoring pass over re-pitched rows (see gemm_launch)
-        std::vector<float> w32((size_t)C * d4, 0.0f);
-        for (int c = 0; c < C; ++c)
-            for (int k = 0; k < d; ++k) w32[(size_t)c * d4 + k] = (float)coef[(size_t)c * d + k];
-        LRS_CUDA(cudaMalloc(&g->w32_pad, w32.size() * sizeof(float)));
-        LRS_CUDA(cudaMemcpy(g->w32_pad, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
-    }
-    m.gemm = g;
-    LRS_CUDA(cudaMalloc(&g->bias, bias.size() * sizeof(float)));
-    LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
-    int rc;
-    if (!g->f16) {
-        std::vector<float> hi((size_t)g->c_pad * d4, 0.0f), lo((size_t)g->c_pad * d4, 0.0f);
-        for (int c = 0; c < C; ++c) {
-            for (int k = 0; k < d; ++k) {
-                const double w = coef[(size_t)c * d + k];
-                const float h = tf32_rna_host((float)w);
-                hi[(size_t)c * d4 + k] = h;
-                lo[(size_t)c * d4 + k] = tf32_rna_host((float)(w - (double)h));
-            }
-        }
-        const size_t bytes = hi.size() * sizeof(float);
-        LRS_CUDA(cudaMalloc(&g->w_hi, bytes));
-        LRS_CUDA(cudaMalloc(&g->w_lo, bytes));
-        LRS_CUDA(cudaMemcpy(g->w_hi, hi.data(), bytes, cudaMemcpyHostToDevice));
-        LRS_CUDA(cudaMemcpy(g->w_lo, lo.data(), bytes, cudaMemcpyHostToDevice));
-        for (int i = 0; i < 2; ++i) {
-            if (!g->has[i]) continue;
-            auto& L = g->layout[i];
-            const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
-            if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
-            if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
-        }
-    }
+    if (const char* e = getenv("LRS_GEMM_F16")) g->force = atoi(e) == 0 ? 2 : (atoi(e) == 2 ? 1 : 0);
 
-    if (g->f16) {
-        g->d16 = (d + 7) / 8 * 8;
-        // Scale + hi/lo split on the device from the float64 coefficients (one CTA per class): on the host
-        // the software fp16 conversions took 40 ms per million coefficients, which a refit pays per iteration.
-        const size_t b16 = (size_t)g->c_pad * g->d16 * sizeof(__half);
-        std::vector<float> inv(g->c_pad, 1.0f);
-        double* coef_dev = nullptr;
-        LRS_CUDA(cudaMalloc(&g->w16_hi, b16));
-        LRS_CUDA(cudaMalloc(&g->w16_lo, b16));
-        LRS_CUDA(cudaMalloc(&g->col_inv_scale, inv.size() * sizeof(float)));
-        LRS_CUDA(cudaMalloc(&coef_dev, (size_t)C * d * sizeof(double)));
-        LRS_CUDA(cudaMemset(g->w16_hi, 0, b16));
-        LRS_CUDA(cudaMemset(g->w16_lo, 0, b16));
-        LRS_CUDA(cudaMemcpy(g->col_inv_scale, inv.data(), inv.size() * sizeof(float), cudaMemcpyHostToDevice));
-        LRS_CUDA(cudaMemcpy(coef_dev, coef, (size_t)C * d * sizeof(double), cudaMemcpyHostToDevice));
-        w_split16_kernel<<<C, 256>>>(coef_dev, d, g->d16, g->w16_hi, g->w16_lo, g->col_inv_scale);
-        count_launch();
-        const cudaError_t ke = cudaDeviceSynchronize();
-        cudaFree(coef_dev);
-        if (ke != cudaSuccess) return fail(LR_ERR_CUDA, std::string("w_split16_kernel: ") + cudaGetErrorString(ke));
-        for (int i = 0; i < 2; ++i) {
-            if (!g->has[i]) continue;
-            auto& L = g->layout[i];
-            const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
-            if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
-            if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
-        }
+    const size_t b32 = (size_t)g->c_pad * d4 * sizeof(float), b16 = (size_t)g->c_pad * g->d16 * sizeof(__half);
+    LRS_CUDA(cudaMalloc(&g->coef64, (size_t)C * d * sizeof(double)));
+    LRS_CUDA(cudaMalloc(&g->bias, g->c_pad * sizeof(float)));
+    LRS_CUDA(cudaMalloc(&g->w_hi, b32));
+    LRS_CUDA(cudaMalloc(&g->w_lo, b32));
+    LRS_CUDA(cudaMalloc(&g->w16_hi, b16));
+    LRS_CUDA(cudaMalloc(&g->w16_lo, b16));
+    LRS_CUDA(cudaMalloc(&g->col_inv_scale, g->c_pad * sizeof(float)));
+    LRS_CUDA(cudaMalloc(&g->w_norm, g->c_pad * sizeof(float)));
+    LRS_CUDA(cudaMalloc(&g->col_scale, g->d64 * sizeof(float)));
+    LRS_CUDA(cudaMalloc(&g->w_mul, d * sizeof(double)));
+    if (d4 != d) LRS_CUDA(cudaMalloc(&g->w32_pad, (size_t)C * d4 * sizeof(float)));
+    // padding (classes beyond C, columns beyond d) stays zero across reloads
+    LRS_CUDA(cudaMemset(g->w_hi, 0, b32));
+    LRS_CUDA(cudaMemset(g->w_lo, 0, b32));
+    LRS_CUDA(cudaMemset(g->w16_hi, 0, b16));
+    LRS_CUDA(cudaMemset(g->w16_lo, 0, b16));
+    LRS_CUDA(cudaMemset(g->col_scale, 0, g->d64 * sizeof(float)));
+    {
+        std::vector<float> ones(g->c_pad, 1.0f);
+        LRS_CUDA(cudaMemcpy(g->col_inv_scale, ones.data(), ones.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
-    return LR_OK;
+    int rc;
+    for (int i = 0; i < GemmPlan::kLayouts; ++i) {
+        if (!g->has[i]) continue;
+        auto& L = g->layout[i];
+        const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
+        if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
+        if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
+        if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
+        if ((rc = make_map_ex(&L.map_w16lo, g->w16_lo, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
+    }
+    return gemm_load(m, coef, intercept);
 }
 
 // Called by lr_score_host after a synchronised batch: `rescored_total` is the running count kept in
@@ -1544,7 +1687,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
 // re-scoring pass, later batches use the accurate layout.
 void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total) {
     GemmPlan* g = m.gemm;
-    if (!g || !g->adaptive || g->active != 0 || !g->has[1]) return;
+    if (!g || !g->adaptive || g->active == 1 || !g->has[1]) return;
     g->rows_seen += (uint64_t)rows;
     const uint64_t resc = rescored_total - g->rescored_seen;
     if (g->rows_seen >= 4096 && resc * 50 > g->rows_seen) {
@@ -1555,7 +1698,7 @@ void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total) {
     }
 }
 
-int gemm_active_layout(const Model& m) { return m.gemm ? m.gemm->active : -1; }
+int gemm_active_layout(const Model& m) { return m.gemm ? m.gemm->active.load() : -1; }
 
 void gemm_destroy(Model& m) {
     if (!m.gemm) return;
@@ -1566,6 +1709,10 @@ void gemm_destroy(Model& m) {
     cudaFree(m.gemm->w16_lo);
     cudaFree(m.gemm->w32_pad);
     cudaFree(m.gemm->col_inv_scale);
+    cudaFree(m.gemm->coef64);
+    cudaFree(m.gemm->col_scale);
+    cudaFree(m.gemm->w_mul);
+    cudaFree(m.gemm->w_norm);
     delete m.gemm;
     m.gemm = nullptr;
 }
@@ -1585,15 +1732,37 @@ repitch_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, 
 
 // The tensor-core pass over rows that TMA can address: 16-byte aligned base and pitch, `d_eff` columns
 // (a multiple of 4); `w_fix` = fp32 coefficients at pitch d_eff for the re-scoring pass.
+// Stream-ordered scratch that is handed back on every way out of the launch code.
+struct AsyncScratch {
+    void* p = nullptr;
+    cudaStream_t s = nullptr;
+    ~AsyncScratch() { if (p) cudaFreeAsync(p, s); }
+};
+
+template <bool F16>
+cudaError_t launch_gemm_kernel(const cudaLaunchConfig_t& cfg, bool pair, const CUtensorMap& map_x,
+                               const GemmPlan::Layout& L, const GemmParams& p) {
+    if constexpr (F16) {
+        return pair ? cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, true>, map_x, L.map_w16hi, L.map_w16lo, p)
+                    : cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, false>, map_x, L.map_w16hi, L.map_w16lo, p);
+    } else {
+        return pair ? cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, true>, map_x, L.map_whi, L.map_wlo, p)
+                    : cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, false>, map_x, L.map_whi, L.map_wlo, p);
+    }
+}
+
 int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix) {
     GemmPlan* g = m.gemm;
-    GemmPlan::Layout& L = g->layout[g->active];
-    CUtensorMap map_x;
-    const bool f16 = g->f16;
-    const int xbox = BM;                              // every CTA loads its whole X tile
-    int rc = f16 ? make_map_ex(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox, BK16, 4, false)
-                 : make_map(&map_x, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, xbox);
-    if (rc != LR_OK) return rc;
+    GemmPlan::Layout& L = g->layout[g->active.load()];
+    // X as the two arithmetics read it: fp32 boxes of 64 columns, unswizzled (3xFP16: converted in place) or of
+    // 32 columns, 128-byte swizzle (3xTF32)
+    CUtensorMap map_x16, map_x32;
+    int rc;
+    if (g->force != 2 &&
+        (rc = make_map_ex(&map_x16, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, BM, BK16, 4, false)) != LR_OK)
+        return rc;
+    if (g->force != 1 && (rc = make_map(&map_x32, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, BM)) != LR_OK)
+        return rc;
     const size_t smem = (L.pair ? SmemLayoutT<true>::total : SmemLayoutT<false>::total) + 1024;
     const int dev = m.device & 63;
     if (!g->configured[dev]) {
@@ -1604,30 +1773,28 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s1));
         g->configured[dev] = true;
     }
-    // Scratch of the fp32 re-scoring pass: per row the log-sum-exp the tensor path saw and one flag
-    // byte (near-ties, risky probabilities).  Per call and stream-ordered (cudaMallocAsync), so
-    // concurrent lr_score calls on one model stay independent.
+    // Per-call scratch, stream-ordered (cudaMallocAsync) so that concurrent lr_score calls on one model stay
+    // independent: [256 B: what x_scale_kernel decides | its per-row statistics | per row the log-sum-exp the
+    // tensor path saw | one flag byte per row (near-ties, risky probabilities) for the fp32 re-scoring pass].
     const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
     unsigned char* flags = nullptr;
     float* lse = nullptr;
-    float* x_scale = nullptr;
-    void* scratch = nullptr;
-    if (fixup || f16) {
-        // [x scale pair | lse per row | flag byte per row]
-        const size_t lse_bytes = fixup ? ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256 : 0;
-        LRS_CUDA(cudaMallocAsync(&scratch, 256 + lse_bytes + (fixup ? (size_t)a.n_rows : 0), a.stream));
-        x_scale = reinterpret_cast<float*>(scratch);
-        if (fixup) {
-            lse = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
-            flags = reinterpret_cast<unsigned char*>(scratch) + 256 + lse_bytes;
-            LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
-        }
-        if (f16) {
-            LRS_CUDA(cudaMemsetAsync(x_scale, 0, 16, a.stream));
-            x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, x_scale);
-            count_launch();
-        }
+    AsyncScratch scratch;
+    scratch.s = a.stream;
+    const size_t stat_bytes = 2 * kMaxSample * sizeof(float);
+    const size_t lse_bytes = fixup ? ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256 : 0;
+    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + lse_bytes + (fixup ? (size_t)a.n_rows : 0), a.stream));
+    float* x_scale = reinterpret_cast<float*>(scratch.p);
+    float* rowstat = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256);
+    if (fixup) {
+        lse = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes);
+        flags = reinterpret_cast<unsigned char*>(scratch.p) + 256 + stat_bytes + lse_bytes;
+        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
     }
+    LRS_CUDA(cudaMemsetAsync(x_scale, 0, 32, a.stream));
+    x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
+                                                        g->inv_cscale_max, g->force, x_scale, rowstat);
+    count_launch();
     GemmParams p;
     p.flags = flags;
     p.lse = lse;
@@ -1661,11 +1828,12 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
             p.a_stages = as; p.b_stages = bs;
         }
     }
-    p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
+    p.acc_bufs = ((L.mma_n <= 128 || L.two_acc) && L.nb == 1 && !L.pair) ? 2 : 1;
+    p.acc_stride = L.mma_n <= 128 ? 128 : 256;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
-    p.num_k_chunks = f16 ? (d_eff + BK16 - 1) / BK16 : (d_eff + BK - 1) / BK;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
+    p.col_scale = g->col_scale;
     p.x_scale = x_scale;
     p.count_nonfinite = fixup ? 0 : 1;
     p.debug_skip = 0;
@@ -1712,11 +1880,24 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     const int64_t n_groups = (n_tiles + gsz - 1) / gsz;
     if (clusters > n_groups) clusters = n_groups;
     cfg.gridDim = dim3((unsigned)(clusters * csize));
-    if (f16 && L.pair) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, true>, map_x, L.map_w16hi, L.map_w16lo, p));
-    else if (f16) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, false>, map_x, L.map_w16hi, L.map_w16lo, p));
-    else if (L.pair) LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, true>, map_x, L.map_whi, L.map_wlo, p));
-    else LRS_CUDA(cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, false>, map_x, L.map_whi, L.map_wlo, p));
-    count_launch();
+    // Truncating accumulation: measured relative logit error at d = 1024 (tools/gemm_precision.py), growing
+    // with the number of accumulation steps, i.e. with the row length.
+    const float len = d_eff > 1024 ? (float)d_eff / 1024.0f : 1.0f;
+    // Both arithmetics are enqueued; the kernel x_scale_kernel did not choose returns at once (a few us).
+    if (g->force != 2) {
+        p.num_k_chunks = (d_eff + BK16 - 1) / BK16;
+        p.kappa = (L.split ? 2.8e-6f : 6e-6f) * len;
+        p.count_fallback = 0;
+        LRS_CUDA(launch_gemm_kernel<true>(cfg, L.pair, map_x16, L, p));
+        count_launch();
+    }
+    if (g->force != 1) {
+        p.num_k_chunks = (d_eff + BK - 1) / BK;
+        p.kappa = (L.split ? 3.5e-6f : 1.1e-5f) * len;
+        p.count_fallback = g->force == 0 ? 1 : 0;
+        LRS_CUDA(launch_gemm_kernel<false>(cfg, L.pair, map_x32, L, p));
+        count_launch();
+    }
     if (fixup) {
         if (a.proba)
             gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, m.n_scores,
@@ -1729,7 +1910,6 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         count_launch();
         LRS_CUDA(cudaGetLastError());
     }
-    if (scratch) LRS_CUDA(cudaFreeAsync(scratch, a.stream));
     return LR_OK;
 }
 
@@ -1749,8 +1929,10 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     int64_t block = ((int64_t)512 << 20) / ((int64_t)d4 * 4);
     block = block < 1024 ? 1024 : block / 1024 * 1024;
     if (block > a.n_rows) block = a.n_rows;
-    float* scratch = nullptr;
-    LRS_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), (size_t)block * d4 * sizeof(float), a.stream));
+    AsyncScratch rows;
+    rows.s = a.stream;
+    LRS_CUDA(cudaMallocAsync(&rows.p, (size_t)block * d4 * sizeof(float), a.stream));
+    float* scratch = static_cast<float*>(rows.p);
     int rc = LR_OK;
     const int C = m.n_scores;
     for (int64_t r0 = 0; r0 < a.n_rows && rc == LR_OK; r0 += block) {
@@ -1769,7 +1951,6 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
         if (a.maxprob) s.maxprob = a.maxprob + r0;
         rc = gemm_launch_aligned(m, s, d4, w_fix);
     }
-    cudaFreeAsync(scratch, a.stream);
     return rc;
 }
 

@@ -125,6 +125,25 @@ class B200LogisticRegression:
                 raise NotFittedError(
                     f"This {type(est).__name__} instance is not fitted yet. Call 'fit' with "
                     "appropriate arguments before using this estimator.")
+        # The engine computes what a default LogisticRegression() does: sigmoid for a binary model, softmax
+        # otherwise.  Pickles from the scikit-learn the reference pins (0.24.1, REF/requirements.txt:11) can
+        # ask for something else -- one-vs-rest normalised sigmoids (multi_class='ovr', or 'auto' with
+        # solver='liblinear') for > 2 classes, softmax([-z, z]) for a binary multi_class='multinomial' model
+        # (SK 0.24 _logistic.py predict_proba) -- and would load and answer with different probabilities.
+        multi_class = getattr(est, "multi_class", "auto")
+        solver = getattr(est, "solver", "lbfgs")
+        n_classes = len(est.classes_)
+        if multi_class == "deprecated":
+            multi_class = "auto"
+        ovr = multi_class == "ovr" or (multi_class == "auto" and solver == "liblinear")
+        if n_classes > 2 and ovr:
+            raise NotImplementedError(
+                "one-vs-rest LogisticRegression (multi_class='ovr' or solver='liblinear') with more than two "
+                "classes normalises per-class sigmoids; this engine implements the softmax (multinomial) arm only")
+        if n_classes <= 2 and multi_class == "multinomial":
+            raise NotImplementedError(
+                "a binary multi_class='multinomial' model scores with softmax([-z, z]); this engine implements "
+                "the sigmoid arm for binary models")
         return cls(est.coef_, est.intercept_, est.classes_, **kw)
 
     def close(self):
@@ -237,6 +256,14 @@ class B200LogisticRegression:
         rep = self._replicas[device_index]
         v = C.c_uint64()
         _lib.check(rep.lib.lr_model_take_rescored(rep.handle, None, C.byref(v)))
+        return int(v.value)
+
+    def take_fallback(self, device_index: int = 0) -> int:
+        """Rows the tensor-core path scored in 3xTF32 because the batch's dynamic range ruled out 3xFP16,
+        since the last call (diagnostic; syncs)."""
+        rep = self._replicas[device_index]
+        v = C.c_uint64()
+        _lib.check(rep.lib.lr_model_take_fallback(rep.handle, None, C.byref(v)))
         return int(v.value)
 
     # ---- sklearn surface -----------------------------------------------------------------------

@@ -207,3 +207,155 @@ def test_gemm_small_class_counts(eng, d, c):
         parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
                              orc.predict_index(X, W, b), f"gemm small-N d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
     clf.close()
+
+
+# ---- dynamic range: what the 3xFP16 split must survive ---------------------------------------------
+# fp16 halves hold 22 bits only while the `lo` half stays out of subnormals.  The engine balances W per
+# feature at load time, puts each class row at the top of fp16's range, scales X per call from a robust
+# row maximum and falls back to 3xTF32 when what is left of the batch's range would still cost precision.
+# Every case below is held to the ordinary bar (1e-5 / 1e-5, labels outside the 1e-5 margin band), with a
+# P matrix and with labels + max probability only (the /predict pattern).
+
+def _check_both_patterns(clf, X, W, b, what, z_atol=parity.Z_ATOL_TENSOR, rows=None):
+    z = orc.decision_function(X, W, b)
+    P = orc.softmax(z)
+    idx = z.argmax(1)
+    sel = slice(None) if rows is None else rows
+    out = clf.score_rows(X, **ALL)
+    parity.assert_parity({k: v[sel] for k, v in out.items()}, z[sel], P[sel], idx[sel], what, z_atol=z_atol)
+    out2 = clf.score_rows(X, label=True, maxprob=True)
+    parity.assert_parity({k: v[sel] for k, v in out2.items() if v is not None}, z[sel], P[sel], idx[sel],
+                         what + " (label+maxprob)")
+    return out
+
+
+@pytest.mark.parametrize("d,c", [(1024, 100), (256, 1000), (64, 32)])
+def test_gemm_unstandardised_features(eng, d, c):
+    """Feature scales spread over seven decades with the weights a fit would give them (inversely
+    proportional): REF/Logistic Regression.ipynb:28-34 fits raw, unscaled columns."""
+    mlapi, lib = eng
+    rng = np.random.default_rng(1000 + d + c)
+    n = 20_000
+    W0, b = synth.make_model(d, c, 31)
+    s = 10.0 ** rng.uniform(-3, 4, d)
+    X = (rng.standard_normal((n, d)) * s).astype(np.float32)
+    W = W0 / s
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, W, b, f"feature scales d={d} C={c}")
+    assert clf.take_fallback() == 0                     # balanced at load time: stays on 3xFP16
+    assert clf.take_rescored() < 2 * n * 0.02           # two calls
+    clf.close()
+
+
+def test_gemm_one_huge_feature(eng):
+    mlapi, lib = eng
+    d, c, n = 1024, 100, 20_000
+    W, b = synth.make_model(d, c, 32)
+    X = synth.make_X(n, d, 33)
+    X[:, 7] *= 1e6
+    W[:, 7] /= 1e6
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, W, b, "one feature x1e6")
+    assert clf.take_fallback() == 0
+    clf.close()
+
+
+@pytest.mark.parametrize("sampled", [True, False])
+def test_gemm_single_outlier_element(eng, sampled):
+    """One element 1e5 times the rest, in a row the per-call sampler reads (rows i * (n // n_s)) or in one
+    it does not: that row overflows fp16 and is re-scored in fp32; no other row may lose precision."""
+    mlapi, lib = eng
+    d, c, n = 1024, 100, 20_000
+    W, b = synth.make_model(d, c, 34)
+    X = synth.make_X(n, d, 35)
+    step = n // min(n, max(64, min(2048, (1 << 20) // d)))
+    row = 5 * step + (0 if sampled else 1)
+    X[row, 11] = 1e5
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    # the outlier row itself has logits ~3e3: fp32 re-scoring leaves ~2e-4 on them
+    _check_both_patterns(clf, X, W, b, f"outlier sampled={sampled}", z_atol=1e-3)
+    assert clf.take_fallback() == 0
+    assert clf.take_rescored() >= 2
+    clf.close()
+
+
+def test_gemm_class_row_spanning_six_decades(eng):
+    mlapi, lib = eng
+    d, c, n = 1024, 100, 20_000
+    rng = np.random.default_rng(36)
+    W, b = synth.make_model(d, c, 37)
+    W[3] = W[3] * 10.0 ** rng.uniform(-6, 0, d) * 20.0
+    W[40] = W[40] * 10.0 ** rng.uniform(-6, 0, d) * 20.0
+    X = synth.make_X(n, d, 38)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, W, b, "class rows spanning 6 decades")
+    assert clf.take_fallback() == 0
+    clf.close()
+
+
+def test_gemm_fitted_on_raw_measurements(eng):
+    """The iris situation at 20 classes: positive, unscaled measurements (means of a few units, spreads of a
+    fraction of one, one column in the hundreds), a model fitted on them by LogisticRegression().fit."""
+    from sklearn.linear_model import LogisticRegression
+    mlapi, lib = eng
+    rng = np.random.default_rng(39)
+    d, c = 32, 20
+    mu = np.tile([5.8, 3.0, 3.7, 1.2], d // 4)
+    mu[5] = 250.0
+    sd = np.tile([0.8, 0.4, 1.7, 0.7], d // 4)
+    sd[5] = 40.0
+    centres = mu + rng.standard_normal((c, d)) * sd
+    ytr = rng.integers(0, c, 6000)
+    Xtr = np.abs(centres[ytr] + rng.standard_normal((6000, d)) * sd * 0.7)
+    est = LogisticRegression(max_iter=300).fit(Xtr, ytr)
+    yte = rng.integers(0, c, 30_000)
+    X = np.abs(centres[yte] + rng.standard_normal((30_000, d)) * sd * 0.7).astype(np.float32)
+    clf = mlapi.B200LogisticRegression.from_sklearn(est)
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, est.coef_, est.intercept_, "fitted on raw measurements")
+    assert clf.take_fallback() == 0
+    clf.close()
+
+
+@pytest.mark.parametrize("d,c,n", [(4096, 64, 6000), (4096, 1000, 3000), (16384, 64, 3000), (16384, 1000, 1500)])
+def test_gemm_long_rows(eng, d, c, n):
+    """The truncating accumulation error grows with the number of k-steps: the re-scoring band has to grow
+    with the row length (it was measured at d = 1024)."""
+    mlapi, lib = eng
+    W, b = synth.make_model(d, c, 40 + c)
+    X = synth.make_X(n, d, 41)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, W, b, f"long rows d={d} C={c}", z_atol=parity.Z_ATOL_TENSOR * d / 1024)
+    clf.close()
+
+
+def test_gemm_range_guard_falls_back_to_tf32(eng):
+    """2 % of the rows 1000 times larger than the rest -- more than the sampler's robust maximum sets aside:
+    scaled for them, fp16 would push every ordinary row's low halves into subnormals (predicted logit error
+    ~1e-4), so the call must run in 3xTF32 and say so; the ordinary rows stay inside the bar."""
+    mlapi, lib = eng
+    d, c, n = 1024, 100, 20_000
+    W, b = synth.make_model(d, c, 42)
+    X = synth.make_X(n, d, 43)
+    big = np.zeros(n, bool)
+    big[::50] = True
+    X[big] *= 1000.0
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    _check_both_patterns(clf, X, W, b, "range guard", rows=~big)
+    assert clf.take_fallback() == 2 * n                 # both calls, every row
+    # the large rows: logits ~1e3, fp32-grade arithmetic; labels hold wherever the margin is not tiny
+    z = orc.decision_function(X[big], W, b)
+    lab = clf.score_rows(X, label=True)["label"][big]
+    safe = parity.margins(z) > 1.0
+    assert (lab[safe] == z.argmax(1)[safe]).all()
+    # an ordinary batch on the same model goes back to 3xFP16
+    clf.take_fallback()
+    clf.score_rows(synth.make_X(4096, d, 44), proba=True)
+    assert clf.take_fallback() == 0
+    clf.close()
