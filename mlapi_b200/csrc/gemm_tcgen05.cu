@@ -70,10 +70,10 @@ struct SmemLayoutT {
     static constexpr int b = a_lo + a_stages * A_TILE_BYTES;         // [b_stages][b_tile]
     static constexpr int bias = b + b_stages * b_tile;               // [512] floats
     static constexpr int cscale = bias + 512 * 4;                    // [512] floats: 1 / (x scale * class scale), FP16 mode
-    static constexpr int xchg = cscale + 512 * 4;                    // [2 tile parities][2 exchanges][kMaxCluster][BM] float2
-    static constexpr int halves = xchg + 2 * 2 * kMaxCluster * BM * 8;  // [2 column halves][BM] float2, CTA-local
-    static constexpr int glob = halves + 2 * BM * 8;                 // [BM] float2: row statistics of the whole cluster
-    static constexpr int bars = glob + BM * 8;                       // mbarriers
+    static constexpr int xchg = cscale + 512 * 4;                    // [2 tile parities][kMaxCluster][BM] float4 (max, class, sum, -)
+    static constexpr int halves = xchg + 2 * kMaxCluster * BM * 16;  // [BM] float4: column half 1 -> column half 0, CTA-local
+    static constexpr int glob = halves + BM * 16;                    // [BM] float4: row statistics of the whole cluster
+    static constexpr int bars = glob + BM * 16;                      // mbarriers
     static constexpr int n_bars = 3 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
@@ -229,6 +229,42 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
         : "memory");
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+// The same load without the wait: the registers hold the data only after tmem_ld_wait(), which takes them as
+// in/out operands so that no use can be scheduled ahead of it.
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, float (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7]),
+          "=f"(r[8]), "=f"(r[9]), "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]), "=f"(r[14]), "=f"(r[15]),
+          "=f"(r[16]), "=f"(r[17]), "=f"(r[18]), "=f"(r[19]), "=f"(r[20]), "=f"(r[21]), "=f"(r[22]), "=f"(r[23]),
+          "=f"(r[24]), "=f"(r[25]), "=f"(r[26]), "=f"(r[27]), "=f"(r[28]), "=f"(r[29]), "=f"(r[30]), "=f"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait(float (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+f"(r[0]), "+f"(r[1]), "+f"(r[2]), "+f"(r[3]), "+f"(r[4]), "+f"(r[5]), "+f"(r[6]), "+f"(r[7]),
+                   "+f"(r[8]), "+f"(r[9]), "+f"(r[10]), "+f"(r[11]), "+f"(r[12]), "+f"(r[13]), "+f"(r[14]), "+f"(r[15]),
+                   "+f"(r[16]), "+f"(r[17]), "+f"(r[18]), "+f"(r[19]), "+f"(r[20]), "+f"(r[21]), "+f"(r[22]), "+f"(r[23]),
+                   "+f"(r[24]), "+f"(r[25]), "+f"(r[26]), "+f"(r[27]), "+f"(r[28]), "+f"(r[29]), "+f"(r[30]), "+f"(r[31])
+                 :
+                 : "memory");
+}
+// v[0..7] += eight columns (the correction accumulator of the split layout, taken in small pieces: a second
+// 32-register buffer next to the pipelined loads would spill)
+__device__ __forceinline__ void tmem_add8(uint32_t taddr, float* v) {
+    uint32_t r[8];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] += __uint_as_float(r[i]);
 }
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
     asm volatile(
@@ -386,9 +422,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     constexpr int A_STAGE = 2 * A_TILE_BYTES;            // FP16: one contiguous 32 KB stage (raw -> hi | lo in place)
     float* bias_s = reinterpret_cast<float*>(smem + SmemLayout::bias);
     float* cscale_s = reinterpret_cast<float*>(smem + SmemLayout::cscale);
-    float2* xchg = reinterpret_cast<float2*>(smem + SmemLayout::xchg);
-    float2* halves = reinterpret_cast<float2*>(smem + SmemLayout::halves);
-    float2* glob = reinterpret_cast<float2*>(smem + SmemLayout::glob);
+    float4* xchg4 = reinterpret_cast<float4*>(smem + SmemLayout::xchg);
+    float4* halves4 = reinterpret_cast<float4*>(smem + SmemLayout::halves);
+    float4* glob4 = reinterpret_cast<float4*>(smem + SmemLayout::glob);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SmemLayout::bars);
     uint64_t* x_full = bars;                       // [A_STAGES] TMA -> converters
     uint64_t* a_ready = x_full + kMaxAStages;      // [A_STAGES] converters -> MMA
@@ -397,7 +433,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     uint64_t* b_empty = b_full + kMaxBStages;      // [B_STAGES] MMA -> TMA
     uint64_t* acc_full = b_empty + kMaxBStages;       // [2 accumulator buffers] MMA -> epilogue
     uint64_t* acc_empty = acc_full + 2;            // [2] epilogue -> MMA
-    uint64_t* xchg_bar = acc_empty + 2;            // [2 tile parities][2 exchanges] row statistics from every CTA of the cluster
+    uint64_t* xchg_bar = acc_empty + 2;            // [2 tile parities] row statistics from every CTA of the cluster
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SmemLayout::tmem_slot);
 
     const int warp = threadIdx.x >> 5;
@@ -666,12 +702,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     } else {
         // ===================== epilogue (8 warps) =====================
         // Warp w may read TMEM lanes 32*(w%4)..+31 only, so the eight warps form two groups of four:
-        // group h covers half of this CTA's class columns for all 128 rows.  Three passes over TMEM:
-        //   1. row max and first argmax                       -> combine halves, then CTAs (DSMEM)
-        //   2. e = exp(z - max), sum, near-tie count; e is written back over the accumulator
-        //                                                      -> combine halves, then CTAs
-        //   3. p = e / sum -> global memory
-        // so each class costs one exp, and the statistics of a row meet through shared memory.
+        // group h covers half of this CTA's class columns for all 128 rows.  Two passes over TMEM:
+        //   1. running row max (first argmax) and sum of exp(z - running max)  -> combine halves, then CTAs (DSMEM)
+        //   2. p = exp(z - max) / sum -> global memory, near-tie count, decision values
+        // Two exps per class (the special-function unit has room) against the three reads, one write-back and two
+        // exchanges of the max / exp+sum / normalise form this replaces; each pass keeps the next TMEM load in flight.
         // Logit error model of this call: the truncating accumulation leaves ~kappa times the size of the
         // partial sums -- for a row that is the larger of its top logit and what this batch's rows and this
         // model's classes typically add up to on the way ([5]) -- plus what fp16's subnormal floor can cost ([6]).
@@ -792,189 +827,183 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 continue;
             }
 
-            // ---- pass 1: max and first argmax over my columns
-            float m = -INFINITY;
-            int arg = col0 + cb_lo;
+            // ---- pass 1: running maximum (first argmax) and sum of exp(z - running maximum) over my columns.
+            // The load of the next 32-column chunk is in flight while this one is worked on.
             const int cb_hi1 = (p.debug_skip & 2) ? cb_lo : cb_hi;
-            for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
-                float v[32];
-                tmem_ld32(t_lane + (uint32_t)cb, v);
-                if (p.split) {
-                    float u[32];
-                    tmem_ld32(t_lane + (uint32_t)(BN + cb), u);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] += u[i];
+            float m = -INFINITY, ssum = 0.0f;
+            int arg = col0 + cb_lo;
+            // raw accumulator chunk -> logits, in place
+#define LRS_CHUNK_LOGITS(v, cb)                                                                        \
+            do {                                                                                       \
+                if (p.split) {                                                                         \
+                    _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8)                               \
+                        tmem_add8(t_lane + (uint32_t)(BN + (cb) + i8), (v) + i8);                      \
+                }                                                                                      \
+                /* eight columns at a time, fenced: with all 64 scale / bias values of a chunk loaded */ \
+                /* ahead of the FMAs the second (in-flight) TMEM buffer no longer fits in registers */    \
+                _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8) {                                 \
+                    _Pragma("unroll") for (int i = i8; i < i8 + 8; ++i) {                              \
+                        if constexpr (F16) (v)[i] = fmaf((v)[i], cscale_s[(cb) + i], bias_s[(cb) + i]); \
+                        else (v)[i] += bias_s[(cb) + i]; /* padding carries -inf */                    \
+                    }                                                                                  \
+                    asm volatile("" ::: "memory");                                                     \
+                }                                                                                      \
+            } while (0)
+#define LRS_PASS1_CHUNK(v, cb)                                                                         \
+            do {                                                                                       \
+                LRS_CHUNK_LOGITS(v, cb);                                                               \
+                float cm = -INFINITY;                                                                  \
+                _Pragma("unroll") for (int i = 0; i < 32; ++i) cm = fmaxf(cm, (v)[i]);                 \
+                if (cm > m) { /* strict: an earlier chunk keeps a tie */                               \
+                    ssum *= ex2((m - cm) * kLog2e); /* m == -inf: 0 * 0 */                             \
+                    m = cm;                                                                            \
+                    int idx = 31;                                                                      \
+                    _Pragma("unroll") for (int i = 30; i >= 0; --i) idx = ((v)[i] == cm) ? i : idx;    \
+                    arg = col0 + (cb) + idx; /* first index wins */                                    \
+                }                                                                                      \
+                const float ml = m * kLog2e;                                                           \
+                float cs = 0.0f;                                                                       \
+                _Pragma("unroll") for (int i = 0; i < 32; ++i) cs += ex2(fmaf((v)[i], kLog2e, -ml));   \
+                if (m > -INFINITY) ssum += cs; /* an all-padding chunk: -inf - -inf */                 \
+            } while (0)
+            if (cb_lo < cb_hi1) {
+                // two register buffers, the next chunk's load always in flight (past the end: the last chunk
+                // again, unused -- a load under a condition made the compiler keep copies of both buffers)
+                float ra[32], rb[32];
+                const int cb_last = cb_hi1 - 32;
+                tmem_ld32_issue(t_lane + (uint32_t)cb_lo, ra);
+                for (int cb = cb_lo; cb < cb_hi1; cb += 64) {
+                    tmem_ld_wait(ra);
+                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 32, cb_last), rb);
+                    LRS_PASS1_CHUNK(ra, cb);
+                    tmem_ld_wait(rb);
+                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 64, cb_last), ra);
+                    if (cb + 32 < cb_hi1) LRS_PASS1_CHUNK(rb, cb + 32);
                 }
-                float cm = -INFINITY;
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cb + i], bias_s[cb + i]);
-                    else v[i] += bias_s[cb + i];                  // padding carries -inf
-                    cm = fmaxf(cm, v[i]);
-                }
-                if (cm > m) {                                     // strict: an earlier chunk keeps a tie
-                    m = cm;
-                    int idx = 31;
-#pragma unroll
-                    for (int i = 30; i >= 0; --i) idx = (v[i] == cm) ? i : idx;   // first index wins
-                    arg = col0 + cb + idx;
-                }
+                tmem_ld_wait(ra);
             }
-            // combine the two column halves of this CTA, then the class slices of the cluster
-            float gm;
+            // combine the two column halves of this CTA, then the class slices of the cluster: one exchange of
+            // (maximum, its class, sum of exponentials relative to that maximum) per row
+            float gm, gs;
             int garg;
             {
-                if (h == 1) halves[BM + r_in_tile] = make_float2(m, __int_as_float(arg));
+                if (h == 1) halves4[r_in_tile] = make_float4(m, __int_as_float(arg), ssum, 0.0f);
                 epi_bar_sync();
                 if (h == 0) {
-                    const float2 o = halves[BM + r_in_tile];
-                    if (o.x > m) { m = o.x; arg = __float_as_int(o.y); }          // lower columns keep a tie
+                    const float4 o = halves4[r_in_tile];
+                    const float nm = fmaxf(m, o.x);
+                    float ns = 0.0f;
+                    if (m > -INFINITY) ns += ssum * ex2((m - nm) * kLog2e);
+                    if (o.x > -INFINITY) ns += o.z * ex2((o.x - nm) * kLog2e);
+                    if (o.x > m) arg = __float_as_int(o.y);                       // lower columns keep a tie
+                    m = nm;
+                    ssum = ns;
                     gm = m;
                     garg = arg;
+                    gs = ssum;
                     if (p.ncc > 1) {
-                        float2* buf = xchg + (size_t)((par * 2 + 0) * kMaxCluster) * BM;
+                        float4* buf = xchg4 + (size_t)(par * kMaxCluster) * BM;
                         const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
-                        const uint32_t bar = smem_u32(xchg_bar + par * 2 + 0);
+                        const uint32_t bar = smem_u32(xchg_bar + par);
                         for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, PAIR ? 2 * dst + rt : rt * p.ncc + dst), m, __int_as_float(arg));
+                            st_cluster_v4(map_to_cta(slot, PAIR ? 2 * dst + rt : rt * p.ncc + dst), m, __int_as_float(arg),
+                                          ssum, 0.0f);
                             mbar_arrive_cluster(map_to_cta(bar, PAIR ? 2 * dst + rt : rt * p.ncc + dst));
                         }
-                        mbar_wait_cluster(xchg_bar + par * 2 + 0, (it >> 1) & 1);
+                        mbar_wait_cluster(xchg_bar + par, (it >> 1) & 1);
                         gm = -INFINITY;
                         for (int src = 0; src < p.ncc; ++src) {
-                            const float2 e = buf[src * BM + r_in_tile];
+                            const float4 e = buf[src * BM + r_in_tile];
                             if (e.x > gm) { gm = e.x; garg = __float_as_int(e.y); }  // lower slice keeps a tie
                         }
+                        gs = 0.0f;
+                        for (int src = 0; src < p.ncc; ++src) {      // fixed order: every CTA gets the same sum
+                            const float4 e = buf[src * BM + r_in_tile];
+                            if (e.x > -INFINITY) gs += e.z * ex2((e.x - gm) * kLog2e);
+                        }
                     }
-                    glob[r_in_tile] = make_float2(gm, __int_as_float(garg));
+                    glob4[r_in_tile] = make_float4(gm, __int_as_float(garg), gs, 0.0f);
                 }
                 epi_bar_sync();
-                const float2 gsv = glob[r_in_tile];
+                const float4 gsv = glob4[r_in_tile];
                 gm = gsv.x;
                 garg = __float_as_int(gsv.y);
-            }
-
-            // ---- pass 2: e = exp(z - max) written back to TMEM, sum, near-tie count, decision out
-            const float gml = gm * kLog2e;
-            // A runner-up this close to the maximum may be the true winner: measured logit error of the
-            // truncating TMEM accumulation is <= 3.2e-6 |z| with the split accumulator and 3x that
-            // without; the band is twice that, with margin.
-            // (3xFP16 takes half as many accumulation steps as 3xTF32: measured 5.0e-6 / 2.4e-6)
-            const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
-            const float tau = gm - 2.0f * ez;
-            float ssum = 0.0f;
-            int near = 0;
-            for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
-                float v[32];
-                tmem_ld32(t_lane + (uint32_t)cb, v);
-                if (p.split) {
-                    float u[32];
-                    tmem_ld32(t_lane + (uint32_t)(BN + cb), u);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] += u[i];
-                }
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cb + i], bias_s[cb + i]);
-                    else v[i] += bias_s[cb + i];
-                }
-                if (p.decision && live) {
-                    const int64_t off = row * p.n_classes + col0 + cb;
-                    if (cb + 32 <= n_real && p.vec_store) {
-#pragma unroll
-                        for (int i = 0; i < 32; i += 4)
-                            __stcs(reinterpret_cast<float4*>(p.decision + off + i),
-                                   make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (cb + i < n_real) __stcs(p.decision + off + i, v[i]);
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    near += v[i] > tau ? 1 : 0;
-                    v[i] = ex2(fmaf(v[i], kLog2e, -gml));
-                    ssum += v[i];
-                }
-                tmem_st32(t_lane + (uint32_t)cb, v);
-            }
-            tmem_wait_st();
-            float gs;
-            int gnear;
-            {
-                if (h == 1) halves[BM + r_in_tile] = make_float2(ssum, __int_as_float(near));
-                epi_bar_sync();
-                if (h == 0) {
-                    const float2 o = halves[BM + r_in_tile];
-                    ssum += o.x;
-                    near += __float_as_int(o.y);
-                    gs = ssum;
-                    gnear = near;
-                    if (p.ncc > 1) {
-                        float2* buf = xchg + (size_t)((par * 2 + 1) * kMaxCluster) * BM;
-                        const uint32_t slot = smem_u32(buf + rank * BM + r_in_tile);
-                        const uint32_t bar = smem_u32(xchg_bar + par * 2 + 1);
-                        for (uint32_t dst = 0; dst < (uint32_t)p.ncc; ++dst) {
-                            st_cluster_v2(map_to_cta(slot, PAIR ? 2 * dst + rt : rt * p.ncc + dst), ssum, __int_as_float(near));
-                            mbar_arrive_cluster(map_to_cta(bar, PAIR ? 2 * dst + rt : rt * p.ncc + dst));
-                        }
-                        mbar_wait_cluster(xchg_bar + par * 2 + 1, (it >> 1) & 1);
-                        gs = 0.0f;
-                        gnear = 0;
-                        for (int src = 0; src < p.ncc; ++src) {      // fixed order: every CTA gets the same sum
-                            const float2 e = buf[src * BM + r_in_tile];
-                            gs += e.x;
-                            gnear += __float_as_int(e.y);
-                        }
-                    }
-                    glob[r_in_tile] = make_float2(gs, __int_as_float(gnear));
-                }
-                epi_bar_sync();
-                const float2 gsv = glob[r_in_tile];
-                gs = gsv.x;
-                gnear = __float_as_int(gsv.y);
+                gs = gsv.z;
             }
             const float inv = __frcp_rn(gs);
 
-            // ---- pass 3: normalise and store this warp's slice of the row
-            // |dp| ~ p(1-p)|dz| with |dz| <= kappa |z|: flag the row when that could pass ~6e-6, which
-            // needs a large maximum AND a class of middling probability
+            // ---- pass 2: p = exp(z - max) / sum -> global memory; near-tie count; decision out.
+            // A runner-up this close to the maximum may be the true winner, and |dp| ~ p(1-p)|dz|: the row is
+            // flagged when a class of middling probability could move by ~8e-6 (see `ez` above the loop).
+            const float gml = gm * kLog2e;
+            const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
+            const float tau = gm - 2.0f * ez;
             const float risk_thr = 8e-6f / ez;
+            int near = 0;
             bool risk = false;
-            if (p.proba) {
-                for (int cb = cb_lo; cb < cb_hi1; cb += 32) {
-                    float v[32];
-                    tmem_ld32(t_lane + (uint32_t)cb, v);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        v[i] *= inv;
-                        risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
-                    }
-                    if (live) {
-                        const int64_t off = row * p.n_classes + col0 + cb;
-                        if (cb + 32 <= n_real && p.vec_store == 2) {
-#pragma unroll
-                            for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, v + i);
-                        } else if (cb + 32 <= n_real && p.vec_store) {
-#pragma unroll
-                            for (int i = 0; i < 32; i += 4)
-                                __stcs(reinterpret_cast<float4*>(p.proba + off + i),
-                                       make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (cb + i < n_real) __stcs(p.proba + off + i, v[i]);
-                        }
-                    }
+            const bool want_rows = p.proba != nullptr || p.decision != nullptr;
+#define LRS_PASS2_CHUNK(v, cb)                                                                         \
+            do {                                                                                       \
+                LRS_CHUNK_LOGITS(v, cb);                                                               \
+                if (p.decision && live) {                                                              \
+                    const int64_t off = row * p.n_classes + col0 + (cb);                               \
+                    if ((cb) + 32 <= n_real && p.vec_store) {                                          \
+                        _Pragma("unroll") for (int i = 0; i < 32; i += 4)                              \
+                            __stcs(reinterpret_cast<float4*>(p.decision + off + i),                    \
+                                   make_float4((v)[i], (v)[i + 1], (v)[i + 2], (v)[i + 3]));           \
+                    } else {                                                                           \
+                        _Pragma("unroll") for (int i = 0; i < 32; ++i)                                 \
+                            if ((cb) + i < n_real) __stcs(p.decision + off + i, (v)[i]);               \
+                    }                                                                                  \
+                }                                                                                      \
+                _Pragma("unroll") for (int i = 0; i < 32; ++i) near += (v)[i] > tau ? 1 : 0;           \
+                if (p.proba) {                                                                         \
+                    _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                   \
+                        (v)[i] = ex2(fmaf((v)[i], kLog2e, -gml)) * inv;                                \
+                        risk = risk || ((v)[i] * (1.0f - (v)[i]) > risk_thr);                          \
+                    }                                                                                  \
+                    if (live) {                                                                        \
+                        const int64_t off = row * p.n_classes + col0 + (cb);                           \
+                        if ((cb) + 32 <= n_real && p.vec_store == 2) {                                 \
+                            _Pragma("unroll") for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, (v) + i); \
+                        } else if ((cb) + 32 <= n_real && p.vec_store) {                               \
+                            _Pragma("unroll") for (int i = 0; i < 32; i += 4)                          \
+                                __stcs(reinterpret_cast<float4*>(p.proba + off + i),                   \
+                                       make_float4((v)[i], (v)[i + 1], (v)[i + 2], (v)[i + 3]));       \
+                        } else {                                                                       \
+                            _Pragma("unroll") for (int i = 0; i < 32; ++i)                             \
+                                if ((cb) + i < n_real) __stcs(p.proba + off + i, (v)[i]);              \
+                        }                                                                              \
+                    }                                                                                  \
+                }                                                                                      \
+            } while (0)
+            if ((want_rows || p.flags) && cb_lo < cb_hi1) {
+                // two register buffers, the next chunk's load always in flight (past the end: the last chunk
+                // again, unused -- a load under a condition made the compiler keep copies of both buffers)
+                float ra[32], rb[32];
+                const int cb_last = cb_hi1 - 32;
+                tmem_ld32_issue(t_lane + (uint32_t)cb_lo, ra);
+                for (int cb = cb_lo; cb < cb_hi1; cb += 64) {
+                    tmem_ld_wait(ra);
+                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 32, cb_last), rb);
+                    LRS_PASS2_CHUNK(ra, cb);
+                    tmem_ld_wait(rb);
+                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 64, cb_last), ra);
+                    if (cb + 32 < cb_hi1) LRS_PASS2_CHUNK(rb, cb + 32);
                 }
+                tmem_ld_wait(ra);
             }
+#undef LRS_PASS2_CHUNK
+#undef LRS_PASS1_CHUNK
+#undef LRS_CHUNK_LOGITS
             tc_fence_before();
             if (lead) mbar_arrive(acc_empty + buf);   // this buffer may be overwritten
             else mbar_arrive_cluster(map_to_cta(smem_u32(acc_empty + buf), lead_rank));
 
             if (live) {
-                if (risk && p.flags && p.flags[row] == 0) p.flags[row] = 1;
+                // the thread whose columns hold the maximum always counts it; anything else above tau is a near-tie
+                const bool owner = garg >= col0 + cb_lo && garg < col0 + cb_hi;
+                if (p.flags && (risk || near >= (owner ? 2 : 1))) p.flags[row] = 1;
                 if (rank == 0 && h == 0) {
                     if (p.label) __stcs(p.label + row, garg);
                     if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
@@ -987,8 +1016,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     }
                     if (p.flags) {
                         p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
-                        // a runner-up inside the error band, or a top probability the error could move
-                        if (finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr)) p.flags[row] = 1;
+                        // a top probability the error could move
+                        if (finite_row && inv * (1.0f - inv) > risk_thr) p.flags[row] = 1;
                     }
                 }
             }
@@ -1031,6 +1060,39 @@ __device__ __forceinline__ float warp_dot4(const float* __restrict__ x, const fl
     return acc;
 }
 
+// Up to four such dot products at once (rows c[0..3] of W against the same row of X): the pieces of X are
+// loaded once and four chains of loads are in flight instead of one -- a warp re-scoring the ~20 classes of a
+// flagged row one by one spent its time waiting on L2.
+__device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const float* __restrict__ W, const int (&c)[4],
+                                             int d, int lane, float (&z)[4]) {
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const float4* w4[4];
+    float acc[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        w4[u] = reinterpret_cast<const float4*>(W + (int64_t)c[u] * d);
+        acc[u] = 0.0f;
+    }
+#pragma unroll 2
+    for (int k = lane; k < d / 4; k += 32) {
+        const float4 xv = __ldg(x4 + k);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float4 wv = __ldg(w4[u] + k);
+            acc[u] = fmaf(xv.x, wv.x, acc[u]);
+            acc[u] = fmaf(xv.y, wv.y, acc[u]);
+            acc[u] = fmaf(xv.z, wv.z, acc[u]);
+            acc[u] = fmaf(xv.w, wv.w, acc[u]);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], off);
+        z[u] = acc[u];
+    }
+}
+
 // One flagged row re-scored by one warp (see the kernel below for when).
 __device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
                                                const float* __restrict__ W, const float* __restrict__ b, float L,
@@ -1057,16 +1119,28 @@ __device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int6
         unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
         float q_mine = pc;
         while (sel) {
-            const int j = __ffs(sel) - 1;
-            sel &= sel - 1;
-            const int cj = c0 + j;
-            const float z = warp_dot4(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
-            const float q = expf(z - L);                    // in units of the old row sum
-            old_mass += __shfl_sync(0xffffffffu, pc, j);
-            new_mass += q;
-            if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
-            if (lane == j) q_mine = q;
-            if (decision && lane == 0) decision[row * C + cj] = z;
+            int js[4], cls[4], nj = 0;
+            while (sel && nj < 4) {                         // ascending
+                js[nj] = __ffs(sel) - 1;
+                sel &= sel - 1;
+                ++nj;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) cls[u] = c0 + js[u < nj ? u : 0];
+            float z4[4];
+            warp_dot4_x4(x, W, cls, d, lane, z4);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (u >= nj) break;
+                const int j = js[u], cj = cls[u];
+                const float z = z4[u] + __ldg(b + cj);
+                const float q = expf(z - L);                    // in units of the old row sum
+                old_mass += __shfl_sync(0xffffffffu, pc, j);
+                new_mass += q;
+                if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+                if (lane == j) q_mine = q;
+                if (decision && lane == 0) decision[row * C + cj] = z;
+            }
         }
         if (c < C && q_mine != pc) pr[c] = q_mine;
     }
@@ -1082,7 +1156,7 @@ __device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int6
     }
 }
 
-// One CTA per 256 rows.  Where flagged rows are dense (a confident model: 16 or more in the block) every
+// One CTA per 256 rows.  Where flagged rows are dense (8 or more in the block: as many as there are warps) every
 // warp re-scores the flagged rows among its own 32, one after the other.  Where they are sparse that would
 // leave the last flagged row of a long-row model as a serial tail (d=4096, C=64: most classes are
 // "selected", 64 dot products of 4096 in one warp, 0.28 ms for a handful of rows), so the whole CTA takes
@@ -1104,7 +1178,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, 
         if (lane == 0) s_mask[warp] = m32;
         const int n_flagged = __syncthreads_count(flagged);
         if (n_flagged == 0) continue;
-        if (n_flagged >= 16) {
+        if (n_flagged >= 8) {
             unsigned todo = m32;
             while (todo) {
                 const int64_t row = base + warp * 32 + (__ffs(todo) - 1);
@@ -1683,14 +1757,15 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
 }
 
 // Called by lr_score_host after a synchronised batch: `rescored_total` is the running count kept in
-// the model's status block.  If the fast layout sends more than 2 % of the rows to the fp32
-// re-scoring pass, later batches use the accurate layout.
+// the model's status block.  If the fast layout sends more than a fifth of the rows to the fp32
+// re-scoring pass, later batches use the accurate layout (which takes a third longer on the tensor
+// cores; re-scoring a row costs ~1/4000 of that, so the layouts break even near 30 %).
 void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total) {
     GemmPlan* g = m.gemm;
     if (!g || !g->adaptive || g->active == 1 || !g->has[1]) return;
     g->rows_seen += (uint64_t)rows;
     const uint64_t resc = rescored_total - g->rescored_seen;
-    if (g->rows_seen >= 4096 && resc * 50 > g->rows_seen) {
+    if (g->rows_seen >= 4096 && resc * 5 > g->rows_seen) {
         g->active = 1;
     } else if (g->rows_seen > (1ull << 24)) {          // judge on recent data only
         g->rows_seen = 0;
@@ -1880,20 +1955,22 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     const int64_t n_groups = (n_tiles + gsz - 1) / gsz;
     if (clusters > n_groups) clusters = n_groups;
     cfg.gridDim = dim3((unsigned)(clusters * csize));
-    // Truncating accumulation: measured relative logit error at d = 1024 (tools/gemm_precision.py), growing
-    // with the number of accumulation steps, i.e. with the row length.
-    const float len = d_eff > 1024 ? (float)d_eff / 1024.0f : 1.0f;
+    // Truncating accumulation: the largest |dz| / max(1, |z|) over 2M logits at d = 1024 (tools/gemm_kappa.py:
+    // 1.68e-5 / 6.5e-6 for 3xFP16 on one / split accumulators, 3.1e-5 / 1.08e-5 for 3xTF32), plus a fifth.  It
+    // grows with the number of accumulation steps, i.e. linearly with the row length (measured at d = 256, 1024,
+    // 4096, 16384: 6.3e-6, 1.68e-5, 6.7e-5, 2.4e-4), a little slower than that below 1024.
+    const float len = (float)(d_eff > 384 ? d_eff : 384) / 1024.0f;
     // Both arithmetics are enqueued; the kernel x_scale_kernel did not choose returns at once (a few us).
     if (g->force != 2) {
         p.num_k_chunks = (d_eff + BK16 - 1) / BK16;
-        p.kappa = (L.split ? 2.8e-6f : 6e-6f) * len;
+        p.kappa = (L.split ? 8e-6f : 2.0e-5f) * len;
         p.count_fallback = 0;
         LRS_CUDA(launch_gemm_kernel<true>(cfg, L.pair, map_x16, L, p));
         count_launch();
     }
     if (g->force != 1) {
         p.num_k_chunks = (d_eff + BK - 1) / BK;
-        p.kappa = (L.split ? 3.5e-6f : 1.1e-5f) * len;
+        p.kappa = (L.split ? 1.3e-5f : 3.7e-5f) * len;
         p.count_fallback = g->force == 0 ? 1 : 0;
         LRS_CUDA(launch_gemm_kernel<false>(cfg, L.pair, map_x32, L, p));
         count_launch();

@@ -1,0 +1,18 @@
+#!/bin/bash
+# round 2, call C: two-pass epilogue + cheaper re-scoring: parity, cfg3 with and without the re-scoring pass, launch list
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_gemm_gpu.py -q --timeout=600 > gpurun_out/c_pytest_gemm.log 2>&1
+echo "pytest exit $?" >> gpurun_out/c_pytest_gemm.log
+tail -8 gpurun_out/c_pytest_gemm.log
+B="python bench.py --workload cfg3 --rows 4000000 --steps 6 --warmup 3 --no-e2e --no-cpu"
+for E in "LRS_GEMM_FIXUP=1" "LRS_GEMM_FIXUP=0" "LRS_GEMM_FIXUP=1" "LRS_GEMM_FIXUP=0" "LRS_GEMM_FIXUP=0 LRS_GEMM_LAYOUT=2"; do
+  sleep 3
+  echo "$E: $(env $E timeout 300 $B 2>&1 | tail -1 | python -c 'import sys,json
+try:
+    j=json.loads(sys.stdin.read()); print(j["ms_per_step"], "ms frac", round(j["roofline"]["frac"],3), j["run"]["rows_rescored_fp32"], j["clocks"])
+except Exception as e: print("FAILED", e)')"
+done
+CMD3="python bench.py --workload cfg3 --rows 400000 --steps 2 --warmup 3 --no-e2e --no-cpu"
+timeout 300 $CMD3 > gpurun_out/c_plain3.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/c_launches_cfg3.csv $CMD3 > gpurun_out/c_ncu_list.log 2>&1
+echo "ncu list exit $?"
