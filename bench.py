@@ -404,19 +404,26 @@ def refit_record(ctx):
         z = X @ torch.from_numpy(Wt.T.astype(np.float32)).to(dev) + torch.from_numpy(bt.astype(np.float32)).to(dev)
         y = (z[:, 0] > 0).int() if rows == 1 else z.argmax(1).int()
         del z
-        ev = refit.Evaluator(X, y, rows, world_size=world)
-        w0 = np.zeros(rows * (d + 1))
+        ev = refit.Evaluator(X, y, rows)
+        w0 = np.zeros((rows, d + 1))
+
+        def evaluate():
+            vec = ev.sums(w0)
+            dist.all_reduce(vec, op=dist.ReduceOp.SUM)        # the design's only collective
+            return vec.cpu()
+
         for _ in range(2):
-            ev(w0)
+            evaluate()
         torch.cuda.synchronize(dev)
         dist.barrier()
         t0 = time.perf_counter()
         k = 5
         for _ in range(k):
-            ev(w0)
+            evaluate()
         dt = torch.tensor([(time.perf_counter() - t0) / k], dtype=torch.float64, device=dev)
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        res = refit.fit(X, y, n_classes=c, max_iter=5, world_size=world)
+        ev.close()
+        res = refit.fit(X, y.cpu().numpy(), classes=np.arange(c), max_iter=5)
         mine = torch.from_numpy(np.concatenate([res.coef_.ravel(), res.intercept_.ravel()])).to(dev)
         ref = mine.clone()
         dist.broadcast(ref, src=0)

@@ -63,6 +63,12 @@ int lr_model_create(const double* coef, const double* intercept, int32_t n_score
                     int32_t n_features, int32_t device, lr_model** out);
 void lr_model_destroy(lr_model* m);
 
+/* Replace the coefficients of an existing model (same shape) in place: what a refit does once per lbfgs
+ * evaluation (REF/Logistic Regression.ipynb:33-34 -> SK/linear_model/_logistic.py:584-598), without
+ * re-allocating the device copies or re-encoding the TMA descriptors.  Synchronises the device first;
+ * not concurrent with lr_score calls on the same model. */
+int lr_model_update(lr_model* m, const double* coef, const double* intercept);
+
 int lr_model_info(const lr_model* m, int32_t* n_scores, int32_t* n_features, int32_t* device);
 
 /* Force a kernel family (tests / profiling); LR_PATH_AUTO restores the dispatcher.  A path that
@@ -182,6 +188,27 @@ int lr_loss_grad_static(const float* X_dev, const int32_t* y_dev, int64_t n_rows
  */
 int lr_weighted_row_sum(const float* X_dev, const float* r_dev, int64_t n_rows, int64_t ldx,
                         int32_t n_features, double* out_dev, void* stream);
+
+/*
+ * Gradient of a multinomial model, the transposed product: out_dev[c][k] = sum_i R[i][c] * X[i][k] and
+ * out_dev[c][n_features] = sum_i R[i][c] (float64 [n_scores][n_features + 1], the layout of [coef_ | intercept_]),
+ * i.e. `grad_pointwise.T @ X` and `grad_pointwise.sum(axis=0)` of LinearModelLoss.loss_gradient
+ * (SK/linear_model/_linear_loss.py:353-357, :375) with R = softmax(z) - onehot(y), which lr_score's probability
+ * matrix becomes by subtracting 1 at each row's label.  tcgen05 GEMM over MN-major operands (the contraction
+ * runs over the rows), 3xFP16 split with fp32-grade products, float64 combine in a fixed order: deterministic.
+ *
+ * X is constant over a fit: lr_grad_plan_create scales (per feature) and splits it into fp16 halves once and
+ * owns those copies (as many bytes as X itself) plus the scratch every call needs; lr_grad_gemm then takes a
+ * block of rows [row0, row0 + n_rows) of that X with the matching rows of R (n_rows <= max_block_rows; R_dev
+ * n_rows x n_scores fp32, row pitch ldr).  Sums cover the rows given only: blocks are added by the caller and
+ * ranks all-reduce.  1..2048 score rows.  Calls on one plan must be stream-ordered.
+ */
+typedef struct lr_grad_plan lr_grad_plan;
+int lr_grad_plan_create(const float* X_dev, int64_t n_rows, int64_t ldx, int32_t n_features, int32_t max_scores,
+                        int64_t max_block_rows, void* stream, lr_grad_plan** out);
+void lr_grad_plan_destroy(lr_grad_plan* plan);
+int lr_grad_gemm(lr_grad_plan* plan, int64_t row0, int64_t n_rows, const float* R_dev, int64_t ldr,
+                 int32_t n_scores, double* out_dev, void* stream);
 
 /*
  * Page-locked host memory for the buffers handed to lr_score_host (the /predict micro-batcher's

@@ -21,6 +21,7 @@ SIGNATURES = {
     "lr_model_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                   C.POINTER(C.c_void_p)]),
     "lr_model_destroy": (None, [C.c_void_p]),
+    "lr_model_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "lr_model_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                 C.POINTER(C.c_int32)]),
     "lr_model_set_path": (C.c_int, [C.c_void_p, C.c_int32]),
@@ -39,6 +40,11 @@ SIGNATURES = {
     "lr_loss_grad_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "lr_weighted_row_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "lr_grad_plan_create": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
+                                      C.POINTER(C.c_void_p)]),
+    "lr_grad_plan_destroy": (None, [C.c_void_p]),
+    "lr_grad_gemm": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                               C.c_void_p]),
     "lr_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_uint64]),
     "lr_host_free": (C.c_int, [C.c_void_p]),
     "lr_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),

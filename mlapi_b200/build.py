@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 LIB = os.path.join(HERE, "liblrscore.so")
-SOURCES = ["api.cu", "narrow.cu", "wide.cu", "generic.cu", "gemm_tcgen05.cu", "refit.cu"]
+SOURCES = ["api.cu", "narrow.cu", "wide.cu", "generic.cu", "gemm_tcgen05.cu", "refit.cu", "grad_gemm.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

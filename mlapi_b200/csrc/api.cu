@@ -154,6 +154,24 @@ int lr_model_create(const double* coef, const double* intercept, int32_t n_score
     return LR_OK;
 }
 
+int lr_model_update(lr_model* h, const double* coef, const double* intercept) {
+    if (!h) return fail(LR_ERR_INVALID, "model is NULL");
+    if (!coef || !intercept) return fail(LR_ERR_INVALID, "coef / intercept is NULL");
+    Model* m = reinterpret_cast<Model*>(h);
+    DeviceGuard guard(m->device);
+    if (!guard.ok) return fail(LR_ERR_CUDA, "cudaSetDevice failed");
+    LRS_CUDA(cudaDeviceSynchronize());              // nothing may still be reading the old coefficients
+    const size_t nw = (size_t)m->n_scores * m->n_features;
+    std::vector<float> w32(nw), b32(m->n_scores);
+    for (size_t i = 0; i < nw; ++i) w32[i] = (float)coef[i];
+    for (int i = 0; i < m->n_scores; ++i) b32[i] = (float)intercept[i];
+    LRS_CUDA(cudaMemcpy(m->W, w32.data(), nw * sizeof(float), cudaMemcpyHostToDevice));
+    LRS_CUDA(cudaMemcpy(m->b, b32.data(), m->n_scores * sizeof(float), cudaMemcpyHostToDevice));
+    int rc;
+    if ((rc = narrow_prepare(*m, w32.data(), b32.data())) != LR_OK) return rc;
+    return gemm_load(*m, coef, intercept);
+}
+
 void lr_model_destroy(lr_model* h) {
     if (!h) return;
     Model* m = reinterpret_cast<Model*>(h);

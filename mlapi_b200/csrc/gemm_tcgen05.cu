@@ -73,7 +73,9 @@ struct SmemLayoutT {
     static constexpr int xchg = cscale + 512 * 4;                    // [2 tile parities][kMaxCluster][BM] float4 (max, class, sum, -)
     static constexpr int halves = xchg + 2 * kMaxCluster * BM * 16;  // [BM] float4: column half 1 -> column half 0, CTA-local
     static constexpr int glob = halves + BM * 16;                    // [BM] float4: row statistics of the whole cluster
-    static constexpr int bars = glob + BM * 16;                      // mbarriers
+    static constexpr int chunk_ref = glob + BM * 16;                 // [8][kEpiThreads] floats: the maximum each 32-column
+                                                                     // chunk's exponentials (kept in TMEM) are relative to
+    static constexpr int bars = chunk_ref + 8 * kEpiThreads * 4;     // mbarriers
     static constexpr int n_bars = 3 * kMaxAStages + 2 * kMaxBStages + 4 + 4;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int total = tmem_slot + 16;
@@ -703,16 +705,21 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // ===================== epilogue (8 warps) =====================
         // Warp w may read TMEM lanes 32*(w%4)..+31 only, so the eight warps form two groups of four:
         // group h covers half of this CTA's class columns for all 128 rows.  Two passes over TMEM:
-        //   1. running row max (first argmax) and sum of exp(z - running max)  -> combine halves, then CTAs (DSMEM)
-        //   2. p = exp(z - max) / sum -> global memory, near-tie count, decision values
-        // Two exps per class (the special-function unit has room) against the three reads, one write-back and two
-        // exchanges of the max / exp+sum / normalise form this replaces; each pass keeps the next TMEM load in flight.
+        //   1. per 32-column chunk: logits (decision values out), chunk maximum, e = exp(z - chunk maximum) written
+        //      back over the accumulator, running row maximum (first argmax) and rescaled sum
+        //                                                      -> combine halves, then CTAs (DSMEM), once
+        //   2. p = e * exp(chunk maximum - row maximum) / sum -> global memory, near-tie count
+        // One exp per class, two reads and one write of TMEM, one exchange (the max / exp+sum / normalise form this
+        // replaces read TMEM three times and exchanged twice; recomputing the exponentials in pass 2 instead of
+        // keeping them saturated the special-function unit).  Each pass keeps the next TMEM load in flight.
         // Logit error model of this call: the truncating accumulation leaves ~kappa times the size of the
         // partial sums -- for a row that is the larger of its top logit and what this batch's rows and this
         // model's classes typically add up to on the way ([5]) -- plus what fp16's subnormal floor can cost ([6]).
         const float psum_scale = p.x_scale[5];
         const float floor_err = p.x_scale[6];
         const int ew = warp - (2 + kConvWarps);      // 0..7
+        const int etid = ew * 32 + lane;             // 0..255
+        float* chunk_ref = reinterpret_cast<float*>(smem + SmemLayout::chunk_ref);   // [8 chunks][256 threads]
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int h = ew >> 2;                       // column half
         const int r_in_tile = q * 32 + lane;
@@ -852,19 +859,38 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #define LRS_PASS1_CHUNK(v, cb)                                                                         \
             do {                                                                                       \
                 LRS_CHUNK_LOGITS(v, cb);                                                               \
+                if (p.decision && live) {                                                              \
+                    const int64_t off = row * p.n_classes + col0 + (cb);                               \
+                    if ((cb) + 32 <= n_real && p.vec_store) {                                          \
+                        _Pragma("unroll") for (int i = 0; i < 32; i += 4)                              \
+                            __stcs(reinterpret_cast<float4*>(p.decision + off + i),                    \
+                                   make_float4((v)[i], (v)[i + 1], (v)[i + 2], (v)[i + 3]));           \
+                    } else {                                                                           \
+                        _Pragma("unroll") for (int i = 0; i < 32; ++i)                                 \
+                            if ((cb) + i < n_real) __stcs(p.decision + off + i, (v)[i]);               \
+                    }                                                                                  \
+                }                                                                                      \
                 float cm = -INFINITY;                                                                  \
                 _Pragma("unroll") for (int i = 0; i < 32; ++i) cm = fmaxf(cm, (v)[i]);                 \
                 if (cm > m) { /* strict: an earlier chunk keeps a tie */                               \
-                    ssum *= ex2((m - cm) * kLog2e); /* m == -inf: 0 * 0 */                             \
-                    m = cm;                                                                            \
                     int idx = 31;                                                                      \
                     _Pragma("unroll") for (int i = 30; i >= 0; --i) idx = ((v)[i] == cm) ? i : idx;    \
                     arg = col0 + (cb) + idx; /* first index wins */                                    \
                 }                                                                                      \
-                const float ml = m * kLog2e;                                                           \
+                /* exponentials relative to the chunk's own maximum (<= 1), kept in TMEM for pass 2 */ \
+                const float cml = cm * kLog2e;                                                         \
                 float cs = 0.0f;                                                                       \
-                _Pragma("unroll") for (int i = 0; i < 32; ++i) cs += ex2(fmaf((v)[i], kLog2e, -ml));   \
-                if (m > -INFINITY) ssum += cs; /* an all-padding chunk: -inf - -inf */                 \
+                _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
+                    (v)[i] = ex2(fmaf((v)[i], kLog2e, -cml));                                          \
+                    cs += (v)[i];                                                                      \
+                }                                                                                      \
+                tmem_st32(t_lane + (uint32_t)(cb), v);                                                 \
+                chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid] = cm;                            \
+                if (cm > -INFINITY) { /* an all-padding chunk: -inf - -inf */                          \
+                    const float nm = fmaxf(m, cm);                                                     \
+                    ssum = ssum * ex2((m - nm) * kLog2e) + cs * ex2((cm - nm) * kLog2e);               \
+                    m = nm;                                                                            \
+                }                                                                                      \
             } while (0)
             if (cb_lo < cb_hi1) {
                 // two register buffers, the next chunk's load always in flight (past the end: the last chunk
@@ -881,6 +907,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     if (cb + 32 < cb_hi1) LRS_PASS1_CHUNK(rb, cb + 32);
                 }
                 tmem_ld_wait(ra);
+                tmem_wait_st();
             }
             // combine the two column halves of this CTA, then the class slices of the cluster: one exchange of
             // (maximum, its class, sum of exponentials relative to that maximum) per row
@@ -932,48 +959,35 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             }
             const float inv = __frcp_rn(gs);
 
-            // ---- pass 2: p = exp(z - max) / sum -> global memory; near-tie count; decision out.
+            // ---- pass 2: p = e * exp(chunk max - max) / sum -> global memory; near-tie count.
             // A runner-up this close to the maximum may be the true winner, and |dp| ~ p(1-p)|dz|: the row is
             // flagged when a class of middling probability could move by ~8e-6 (see `ez` above the loop).
             const float gml = gm * kLog2e;
             const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
-            const float tau = gm - 2.0f * ez;
             const float risk_thr = 8e-6f / ez;
+            const float near_thr = inv * ex2(-2.0f * ez * kLog2e);   // z > max - 2 ez, as a probability
             int near = 0;
             bool risk = false;
-            const bool want_rows = p.proba != nullptr || p.decision != nullptr;
+            const bool want_rows = p.proba != nullptr;
 #define LRS_PASS2_CHUNK(v, cb)                                                                         \
             do {                                                                                       \
-                LRS_CHUNK_LOGITS(v, cb);                                                               \
-                if (p.decision && live) {                                                              \
+                const float fj = ex2(fmaf(chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid], kLog2e, -gml)) * inv; \
+                _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
+                    (v)[i] *= fj;                                                                      \
+                    near += (v)[i] > near_thr ? 1 : 0;                                                 \
+                    risk = risk || ((v)[i] * (1.0f - (v)[i]) > risk_thr);                              \
+                }                                                                                      \
+                if (p.proba && live) {                                                                 \
                     const int64_t off = row * p.n_classes + col0 + (cb);                               \
-                    if ((cb) + 32 <= n_real && p.vec_store) {                                          \
+                    if ((cb) + 32 <= n_real && p.vec_store == 2) {                                     \
+                        _Pragma("unroll") for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, (v) + i); \
+                    } else if ((cb) + 32 <= n_real && p.vec_store) {                                   \
                         _Pragma("unroll") for (int i = 0; i < 32; i += 4)                              \
-                            __stcs(reinterpret_cast<float4*>(p.decision + off + i),                    \
+                            __stcs(reinterpret_cast<float4*>(p.proba + off + i),                       \
                                    make_float4((v)[i], (v)[i + 1], (v)[i + 2], (v)[i + 3]));           \
                     } else {                                                                           \
                         _Pragma("unroll") for (int i = 0; i < 32; ++i)                                 \
-                            if ((cb) + i < n_real) __stcs(p.decision + off + i, (v)[i]);               \
-                    }                                                                                  \
-                }                                                                                      \
-                _Pragma("unroll") for (int i = 0; i < 32; ++i) near += (v)[i] > tau ? 1 : 0;           \
-                if (p.proba) {                                                                         \
-                    _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                   \
-                        (v)[i] = ex2(fmaf((v)[i], kLog2e, -gml)) * inv;                                \
-                        risk = risk || ((v)[i] * (1.0f - (v)[i]) > risk_thr);                          \
-                    }                                                                                  \
-                    if (live) {                                                                        \
-                        const int64_t off = row * p.n_classes + col0 + (cb);                           \
-                        if ((cb) + 32 <= n_real && p.vec_store == 2) {                                 \
-                            _Pragma("unroll") for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, (v) + i); \
-                        } else if ((cb) + 32 <= n_real && p.vec_store) {                               \
-                            _Pragma("unroll") for (int i = 0; i < 32; i += 4)                          \
-                                __stcs(reinterpret_cast<float4*>(p.proba + off + i),                   \
-                                       make_float4((v)[i], (v)[i + 1], (v)[i + 2], (v)[i + 3]));       \
-                        } else {                                                                       \
-                            _Pragma("unroll") for (int i = 0; i < 32; ++i)                             \
-                                if ((cb) + i < n_real) __stcs(p.proba + off + i, (v)[i]);              \
-                        }                                                                              \
+                            if ((cb) + i < n_real) __stcs(p.proba + off + i, (v)[i]);                  \
                     }                                                                                  \
                 }                                                                                      \
             } while (0)
@@ -1093,31 +1107,36 @@ __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const 
     }
 }
 
-// One flagged row re-scored by one warp (see the kernel below for when).
-__device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
-                                               const float* __restrict__ W, const float* __restrict__ b, float L,
-                                               float* proba, float* decision, int32_t* label, float* maxprob,
-                                               unsigned long long* rescored, unsigned long long* status) {
+// NPER = classes per lane the row of P is held in (C <= 32 * NPER): the whole row is fetched in one batch of
+// loads and worked on in registers -- walking it from memory (maximum, selection block by block, rescale) put
+// ~70 dependent DRAM round trips on every flagged row, which is what the pass cost (0.5 ms per 13 000 rows).
+template <int NPER>
+__device__ __forceinline__ void fixup_row_warp_n(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+                                                 const float* __restrict__ W, const float* __restrict__ b, float L,
+                                                 float* proba, float* decision, int32_t* label, float* maxprob,
+                                                 unsigned long long* rescored) {
     float* pr = proba + row * C;
-    if (!finite_f(L)) {
-        // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
-        // score the whole row in fp32, which also settles whether the input really is non-finite
-        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
-        if (lane == 0) atomicAdd(rescored, 1ull);
-        return;
+    float pv[NPER];
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) {
+        const int c = j * 32 + lane;
+        pv[j] = c < C ? __ldcg(pr + c) : 0.0f;
     }
     float pmax = 0.0f;
-    for (int c = lane; c < C; c += 32) pmax = fmaxf(pmax, pr[c]);
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) pmax = fmaxf(pmax, pv[j]);
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
     const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
     float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
     int best = 0;
-    for (int c0 = 0; c0 < C; c0 += 32) {
+#pragma unroll
+    for (int jb = 0; jb < NPER; ++jb) {
+        const int c0 = jb * 32;
+        if (c0 >= C) break;
         const int c = c0 + lane;
-        const float pc = c < C ? pr[c] : 0.0f;
+        const float pc = pv[jb];
         unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
-        float q_mine = pc;
         while (sel) {
             int js[4], cls[4], nj = 0;
             while (sel && nj < 4) {                         // ascending
@@ -1138,22 +1157,41 @@ __device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int6
                 old_mass += __shfl_sync(0xffffffffu, pc, j);
                 new_mass += q;
                 if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
-                if (lane == j) q_mine = q;
+                if (lane == j) pv[jb] = q;
                 if (decision && lane == 0) decision[row * C + cj] = z;
             }
         }
-        if (c < C && q_mine != pc) pr[c] = q_mine;
     }
     const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
     const float invT = __frcp_rn(T);
-    __syncwarp();
-    if (fabsf(T - 1.0f) > 1e-7f)
-        for (int c = lane; c < C; c += 32) pr[c] *= invT;
+    const bool rescale = fabsf(T - 1.0f) > 1e-7f;
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) {
+        const int c = j * 32 + lane;
+        if (c < C) __stcs(pr + c, rescale ? pv[j] * invT : pv[j]);
+    }
     if (lane == 0) {
         if (label) label[row] = best;
         if (maxprob) maxprob[row] = best_q * invT;
         atomicAdd(rescored, 1ull);
     }
+}
+
+// One flagged row re-scored by one warp (see the kernel below for when).
+__device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+                                               const float* __restrict__ W, const float* __restrict__ b, float L,
+                                               float* proba, float* decision, int32_t* label, float* maxprob,
+                                               unsigned long long* rescored, unsigned long long* status) {
+    if (!finite_f(L)) {
+        // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
+        // score the whole row in fp32, which also settles whether the input really is non-finite
+        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+        if (lane == 0) atomicAdd(rescored, 1ull);
+        return;
+    }
+    if (C <= 256) fixup_row_warp_n<8>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
+    else if (C <= 1024) fixup_row_warp_n<32>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
+    else fixup_row_warp_n<64>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
 }
 
 // One CTA per 256 rows.  Where flagged rows are dense (8 or more in the block: as many as there are warps) every

@@ -911,8 +911,10 @@ int narrow_prepare(Model& m, const float* W_host, const float* b_host) {
         if (c < m.n_scores)
             for (int k = 0; k < m.n_features; ++k) wp[(size_t)c * dpad + k] = W_host[(size_t)c * m.n_features + k];
     }
-    LRS_CUDA(cudaMalloc(&m.Wn, w.size()));
-    LRS_CUDA(cudaMalloc(&m.bn, ns * sizeof(float)));
+    if (!m.Wn) {                                  // lr_model_update reloads into the same buffers
+        LRS_CUDA(cudaMalloc(&m.Wn, w.size()));
+        LRS_CUDA(cudaMalloc(&m.bn, ns * sizeof(float)));
+    }
     LRS_CUDA(cudaMemcpy(m.Wn, wp, w.size(), cudaMemcpyHostToDevice));
     LRS_CUDA(cudaMemcpy(m.bn, bp, ns * sizeof(float), cudaMemcpyHostToDevice));
     m.narrow_ns = ns;

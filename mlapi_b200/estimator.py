@@ -146,6 +146,20 @@ class B200LogisticRegression:
                 "the sigmoid arm for binary models")
         return cls(est.coef_, est.intercept_, est.classes_, **kw)
 
+    def update(self, coef, intercept):
+        """New coefficients of the same shape, in place on every replica (`lr_model_update`): what the refit
+        driver does once per lbfgs evaluation instead of building a new model."""
+        coef64 = np.ascontiguousarray(np.atleast_2d(np.asarray(coef, dtype=np.float64)))
+        intercept64 = np.ascontiguousarray(np.asarray(intercept, dtype=np.float64).reshape(-1))
+        if coef64.shape != self.coef_.shape or intercept64.shape != self.intercept_.shape:
+            raise ValueError(f"update keeps the shape: coef_ {self.coef_.shape}, got {coef64.shape}")
+        with self._lock:
+            for r in self._replicas:
+                _lib.check(r.lib.lr_model_update(r.handle, coef64.ctypes.data_as(C.c_void_p),
+                                                 intercept64.ctypes.data_as(C.c_void_p)))
+        self.coef_ = coef64
+        self.intercept_ = intercept64
+
     def close(self):
         for r in self._replicas:
             r.close()

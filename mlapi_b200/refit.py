@@ -14,9 +14,10 @@ Two ways to that vector:
     scores, softmax, labels -- is the scoring engine's own kernels (`lr_score` on the current iterate,
     any path), the residual `softmax - onehot` is formed in place in the probability block, and the
     transposed product `residual^T X` is `lr_weighted_row_sum` (a second streaming pass over X) for a
-    binary model and plain library GEMMs (cuBLAS through torch: three TF32 tensor-core products of hi/lo
-    splits, fp32-grade) for a multinomial one, taken in row blocks and accumulated in float64.
-Torch is the allocator, the NCCL binding and, in the second way, the door to cuBLAS.
+    binary model and `lr_grad_gemm` (the library's own tcgen05 kernel over MN-major operands, 3xFP16 split,
+    fp32-grade) for a multinomial one, taken in row blocks and accumulated in float64.
+Torch is the allocator and the NCCL binding; the elementwise steps between the two library calls of the
+second way (loss terms, the -1 at each row's label) are torch tensor expressions.
 """
 from __future__ import annotations
 
@@ -63,60 +64,83 @@ def fused_kernel_serves(rows: int, d: int, X) -> bool:
     return rows <= 8 and (d <= 32 or (d <= 128 and aligned))
 
 
-def _tf32_split(a):
-    """a = hi + lo with hi exactly representable in TF32 (top 19 bits kept): the tensor cores then take
-    hi as it is and round only lo, i.e. at 2^-21 of a."""
-    import torch
-    hi = (a.view(torch.int32) & -8192).view(torch.float32)
-    return hi, a - hi
+class Evaluator:
+    """[sum loss | sum r x^T | sum r] over this rank's rows at a point (W, b), for any model shape.
 
+    Holds what does not change between the evaluations of a fit: the device model (`lr_model_update` swaps the
+    coefficients in place), and for a multinomial model the gradient plan (`lr_grad_plan_create`: X scaled and
+    split into fp16 halves once).  Follows SK/linear_model/_linear_loss.py:291-378: binary loss
+    log(1+e^z) - y z with residual sigmoid(z) - y, multinomial logsumexp(z) - z_y with softmax(z) - onehot(y).
 
-def _mm_t_3xtf32(R, X):
-    """R^T X (C x n times n x d) as three TF32 tensor-core GEMMs, hi*hi + hi*lo + lo*hi, accumulated in
-    fp32 -- fp32-grade products at several times the speed of cuBLAS's fp32 SIMT GEMM (58 TFLOP/s
-    measured on the 1000 x 1024 gradient)."""
-    import torch
-    r_hi, r_lo = _tf32_split(R)
-    x_hi, x_lo = _tf32_split(X)
-    prev = torch.backends.cuda.matmul.allow_tf32
-    torch.backends.cuda.matmul.allow_tf32 = True
-    try:
-        out = torch.mm(r_hi.t(), x_hi)
-        out.addmm_(r_hi.t(), x_lo)
-        out.addmm_(r_lo.t(), x_hi)
-    finally:
-        torch.backends.cuda.matmul.allow_tf32 = prev
-    return out
+    Small models (`fused_kernel_serves`) take `lr_loss_grad`, one fused pass over X.  Every other shape: the
+    forward pass -- scores, softmax, labels -- is the scoring engine on the current iterate (`lr_score`, whichever
+    path the shape selects); the residual is formed in place in the probability block; the transposed product
+    `residual^T X` is `lr_weighted_row_sum` for a binary model (a second streaming pass over X) and
+    `lr_grad_gemm` for a multinomial one (tcgen05, MN-major operands, fp32-grade 3xFP16 split), per row block,
+    blocks summed in float64.
+    """
 
+    def __init__(self, X, y_idx, rows: int, block_rows: int = 0, force_general: bool = False):
+        import torch
+        self.X, self.y_idx, self.rows = X, y_idx, int(rows)
+        self.n, self.d = X.shape
+        self.dev = X.device
+        self.lib = _lib.load()
+        self.fused = fused_kernel_serves(self.rows, self.d, X) and not force_general
+        self.out = torch.empty(1 + self.rows * (self.d + 1), dtype=torch.float64, device=self.dev)
+        self.est = None
+        self.plan = C.c_void_p()
+        if self.fused:
+            self.W32 = torch.empty((self.rows, self.d), dtype=torch.float32, device=self.dev)
+            self.b32 = torch.empty((self.rows,), dtype=torch.float32, device=self.dev)
+            return
+        if block_rows <= 0:                                       # ~1 GB of probabilities (or of X) per block
+            block_rows = max(1024, min(self.n, (1 << 28) // max(self.rows, self.d // 8, 2)))
+        self.block_rows = min(int(block_rows), self.n)
+        if self.rows > 1:
+            stream = torch.cuda.current_stream(self.dev).cuda_stream
+            with torch.cuda.device(self.dev):
+                _lib.check(self.lib.lr_grad_plan_create(C.c_void_p(X.data_ptr()), self.n, X.stride(0), self.d, self.rows,
+                                                        self.block_rows, C.c_void_p(stream), C.byref(self.plan)))
+            self.gblk = torch.empty((self.rows, self.d + 1), dtype=torch.float64, device=self.dev)
+        else:
+            self.gblk = torch.empty((self.d,), dtype=torch.float64, device=self.dev)
 
-def loss_grad_sums_general(X, y_idx, Wb64, out, block_rows: int = 0):
-    """[sum loss | sum r x^T | sum r] over this rank's rows for any model shape, into `out` (float64).
+    def close(self):
+        if self.est is not None:
+            self.est.close()
+            self.est = None
+        if self.plan:
+            self.lib.lr_grad_plan_destroy(self.plan)
+            self.plan = C.c_void_p()
 
-    Forward pass by the scoring engine on the current iterate (`Wb64`: rows x (d+1), float64, last
-    column the intercept); residual in place; `residual^T X` per row block by `lr_weighted_row_sum`
-    (binary) or cuBLAS 3xTF32 (multinomial), blocks summed in float64.  Follows SK/linear_model/_linear_loss.py:291-378 like `lr_loss_grad`:
-    binary loss log(1+e^z) - y z with residual sigmoid(z) - y, multinomial logsumexp(z) - z_y with
-    softmax(z) - onehot(y)."""
-    import torch
-    from .estimator import B200LogisticRegression
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
 
-    n, d = X.shape
-    rows = Wb64.shape[0]
-    dev = X.device
-    est = B200LogisticRegression(Wb64[:, :d], Wb64[:, d], np.arange(max(rows, 2)), devices=[dev.index])
-    if block_rows <= 0:                                       # ~1 GB of probabilities (or of X) per block
-        block_rows = max(1024, min(n, (1 << 28) // max(rows, d // 8, 2)))
-    lib = _lib.load()
-    loss = torch.zeros((), dtype=torch.float64, device=dev)
-    gblk = torch.empty((d,), dtype=torch.float64, device=dev)
-    gW = torch.zeros((rows, d), dtype=torch.float64, device=dev)
-    gb = torch.zeros((rows,), dtype=torch.float64, device=dev)
-    tf32 = torch.backends.cuda.matmul.allow_tf32
-    torch.backends.cuda.matmul.allow_tf32 = False             # the gradient wants fp32 products
-    try:
-        for lo in range(0, n, block_rows):
-            Xc = X[lo:lo + block_rows]
-            yc = y_idx[lo:lo + block_rows].long()
+    def sums(self, Wb64):
+        """`Wb64`: rows x (d+1) float64, last column the intercept.  Returns the float64 device vector of local sums."""
+        import torch
+        rows, d, dev = self.rows, self.d, self.dev
+        Wb64 = np.asarray(Wb64, dtype=np.float64).reshape(rows, d + 1)
+        if self.fused:
+            self.W32.copy_(torch.from_numpy(np.ascontiguousarray(Wb64[:, :d], dtype=np.float32)))
+            self.b32.copy_(torch.from_numpy(np.ascontiguousarray(Wb64[:, d], dtype=np.float32)))
+            return loss_grad_sums(self.X, self.y_idx, self.W32, self.b32, self.out)
+        from .estimator import B200LogisticRegression
+        if self.est is None:
+            self.est = B200LogisticRegression(Wb64[:, :d], Wb64[:, d], np.arange(max(rows, 2)), devices=[dev.index])
+        else:
+            self.est.update(Wb64[:, :d], Wb64[:, d])
+        est, lib = self.est, self.lib
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        loss = torch.zeros((), dtype=torch.float64, device=dev)
+        G = torch.zeros((rows, d + 1), dtype=torch.float64, device=dev)
+        for lo in range(0, self.n, self.block_rows):
+            Xc = self.X[lo:lo + self.block_rows]
+            yc = self.y_idx[lo:lo + self.block_rows].long()
             if rows == 1:
                 res = est._score_device(Xc, True, True, False, False)
                 z = res["decision"].double()
@@ -124,12 +148,11 @@ def loss_grad_sums_general(X, y_idx, Wb64, out, block_rows: int = 0):
                 # log(1 + e^z) - y z, evaluated as max(z, 0) + log1p(e^-|z|) (SK/_loss/_loss.pyx.tp:728-751)
                 loss += (torch.clamp(z, min=0) + torch.log1p(torch.exp(-z.abs())) - yv * z).sum()
                 r = (res["proba"][:, 1] - yc.float()).contiguous()
-                stream = torch.cuda.current_stream(dev).cuda_stream
                 with torch.cuda.device(dev):                  # X^T r: the library's own streaming kernel
                     _lib.check(lib.lr_weighted_row_sum(C.c_void_p(Xc.data_ptr()), C.c_void_p(r.data_ptr()), Xc.shape[0],
-                                                       Xc.stride(0), d, C.c_void_p(gblk.data_ptr()), C.c_void_p(stream)))
-                gW[0] += gblk
-                gb[0] += r.double().sum()
+                                                       Xc.stride(0), d, C.c_void_p(self.gblk.data_ptr()), C.c_void_p(stream)))
+                G[0, :d] += self.gblk
+                G[0, d] += r.double().sum()
             else:
                 res = est._score_device(Xc, True, True, True, True)
                 P, Z = res["proba"], res["decision"]
@@ -138,18 +161,27 @@ def loss_grad_sums_general(X, y_idx, Wb64, out, block_rows: int = 0):
                 lse = Z.gather(1, lab[:, None]).squeeze(1).double() - torch.log(res["maxprob"].double())
                 loss += (lse - Z.gather(1, yc[:, None]).squeeze(1).double()).sum()
                 P[torch.arange(P.shape[0], device=dev), yc] -= 1.0          # residual, in place
-                gW += _mm_t_3xtf32(P, Xc).double()
-                ones = torch.ones((P.shape[0],), dtype=torch.float32, device=dev)
-                gb += torch.mv(P.t(), ones).double()
-        bad = est.take_nonfinite()
+                with torch.cuda.device(dev):                  # R^T X and the column sums of R: the library's tcgen05 kernel
+                    _lib.check(lib.lr_grad_gemm(self.plan, lo, P.shape[0], C.c_void_p(P.data_ptr()), P.stride(0), rows,
+                                                C.c_void_p(self.gblk.data_ptr()), C.c_void_p(stream)))
+                G += self.gblk
+        if est.take_nonfinite():
+            raise ValueError("Input X contains NaN or infinity.")
+        out = self.out
+        out[0] = loss
+        out[1:1 + rows * d] = G[:, :d].reshape(-1)
+        out[1 + rows * d:] = G[:, d]
+        return out
+
+
+def loss_grad_sums_general(X, y_idx, Wb64, out, block_rows: int = 0):
+    """One evaluation through the general path (see `Evaluator`) even where `lr_loss_grad` would serve -- tests
+    compare the two -- into `out` (float64)."""
+    ev = Evaluator(X, y_idx, np.asarray(Wb64).shape[0], block_rows, force_general=True)
+    try:
+        out.copy_(ev.sums(Wb64))
     finally:
-        torch.backends.cuda.matmul.allow_tf32 = tf32
-        est.close()
-    if bad:
-        raise ValueError("Input X contains NaN or infinity.")
-    out[0] = loss
-    out[1:1 + rows * d] = gW.reshape(-1)
-    out[1 + rows * d:] = gb
+        ev.close()
     return out
 
 
@@ -182,21 +214,12 @@ def fit(X, y, classes=None, C_reg: float = 1.0, tol: float = 1e-4, max_iter: int
     allreduce_sum(n_total)
     n = float(n_total.item())
     lam = 1.0 / (C_reg * n)                                   # SK/linear_model/_logistic.py:580
-    out = torch.empty(1 + rows * (d + 1), dtype=torch.float64, device=dev)
-    W32 = torch.empty((rows, d), dtype=torch.float32, device=dev)
-    b32 = torch.empty((rows,), dtype=torch.float32, device=dev)
     evals = {"n": 0}
-
-    fused = fused_kernel_serves(rows, d, X)
+    ev = Evaluator(X, y_idx, rows)
 
     def fun(w):
         Wb = w.reshape(rows, d + 1)
-        if fused:
-            W32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, :d], dtype=np.float32)))
-            b32.copy_(torch.from_numpy(np.ascontiguousarray(Wb[:, d], dtype=np.float32)))
-            loss_grad_sums(X, y_idx, W32, b32, out)
-        else:
-            loss_grad_sums_general(X, y_idx, Wb, out)
+        out = ev.sums(Wb)
         allreduce_sum(out)                                    # the design's only collective
         h = out.cpu().numpy()
         evals["n"] += 1
@@ -208,6 +231,7 @@ def fit(X, y, classes=None, C_reg: float = 1.0, tol: float = 1e-4, max_iter: int
     res = minimize(fun, np.zeros(rows * (d + 1)), method="L-BFGS-B", jac=True,
                    options={"maxiter": max_iter, "maxls": 50, "gtol": tol,
                             "ftol": 64 * np.finfo(float).eps})
+    ev.close()
     Wb = res.x.reshape(rows, d + 1)
     r = FitResult(Wb[:, :d].copy(), Wb[:, d].copy(), classes, int(res.nit), float(res.fun))
     r.n_evals_ = evals["n"]

@@ -204,3 +204,60 @@ def test_weighted_row_sum_against_float64(eng, n, d, pad):
     scale = np.abs(buf[:, :d].astype(np.float64)).T @ np.abs(r.astype(np.float64))
     assert np.all(np.abs(got - ref) <= 2e-6 * scale + 1e-9)
     assert np.array_equal(run(), got)
+
+
+@pytest.mark.parametrize("n,d,c,row0", [(1, 8, 17, 0), (200, 130, 20, 0), (5000, 64, 300, 0), (4097, 1024, 1000, 0),
+                                        (9000, 257, 37, 1111), (70_000, 256, 128, 0), (3000, 40, 2048, 64)])
+def test_grad_gemm_against_float64(eng, n, d, c, row0):
+    """lr_grad_gemm: R^T X and the column sums of R (`grad_pointwise.T @ X`, `grad_pointwise.sum(0)`,
+    SK/linear_model/_linear_loss.py:353-357, :375) on the tensor cores with MN-major operands, against float64.
+    Feature scales spread over six decades (the per-feature scaling of the plan), ragged k-chunks, a block that
+    starts inside the plan's rows, class and feature counts off every tile boundary; twice the same bits."""
+    import ctypes as C
+    import torch
+    from mlapi_b200 import _lib
+    L = _lib.load()
+    rng = np.random.default_rng(n + d + c)
+    n_plan = n + row0 + 5
+    X = (rng.standard_normal((n_plan, d)) * 10.0 ** rng.uniform(-3, 3, d)).astype(np.float32)
+    P = rng.random((n, c)).astype(np.float32)
+    P /= P.sum(1, keepdims=True)
+    R = P.copy()
+    R[np.arange(n), rng.integers(0, c, n)] -= 1.0              # softmax - onehot: entries in [-1, 1]
+    Xt = torch.from_numpy(X).cuda()
+    Rt = torch.from_numpy(R).cuda()
+    out = torch.empty((c, d + 1), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    plan = C.c_void_p()
+    _lib.check(L.lr_grad_plan_create(C.c_void_p(Xt.data_ptr()), n_plan, d, d, c, 0, C.c_void_p(st), C.byref(plan)))
+
+    def run():
+        _lib.check(L.lr_grad_gemm(plan, row0, n, C.c_void_p(Rt.data_ptr()), c, c, C.c_void_p(out.data_ptr()), C.c_void_p(st)))
+        torch.cuda.synchronize()
+        return out.cpu().numpy().copy()
+    got = run()
+    Xb = X[row0:row0 + n].astype(np.float64)
+    ref = R.astype(np.float64).T @ Xb
+    scale = np.abs(R.astype(np.float64)).T @ np.abs(Xb)
+    err = np.abs(got[:, :d] - ref)
+    assert np.all(err <= 4e-6 * scale + 1e-12), float((err / (scale + 1e-30)).max())
+    np.testing.assert_allclose(got[:, d], R.astype(np.float64).sum(0), rtol=1e-12, atol=1e-9)
+    assert np.array_equal(run(), got)
+    L.lr_grad_plan_destroy(plan)
+
+
+def test_model_update_in_place(eng):
+    """lr_model_update swaps the coefficients of a live model on every path a refit's forward pass can take."""
+    import mlapi_b200
+    for d, c in ((32, 1), (64, 7), (256, 100), (4096, 1)):
+        rng = np.random.default_rng(d + c)
+        X = rng.standard_normal((500, d), dtype=np.float32)
+        W0, b0 = synth.make_model(d, c, 1)
+        W1, b1 = synth.make_model(d, c, 2)
+        clf = mlapi_b200.B200LogisticRegression(W0, b0, np.arange(max(c, 2)))
+        p0 = clf.predict_proba(X)
+        clf.update(W1, b1)
+        p1 = clf.predict_proba(X)
+        np.testing.assert_allclose(p0, orc.predict_proba(X, W0, b0), atol=1e-5)
+        np.testing.assert_allclose(p1, orc.predict_proba(X, W1, b1), atol=1e-5)
+        clf.close()
