@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import math
 import os
+import threading
 from contextlib import asynccontextmanager
 from io import StringIO
 from typing import Optional
@@ -62,6 +63,7 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
             state["pins"] = pins
         state["classes"] = list(clf.classes_) if clf is not None else list(classes)
         state["bulk_fn"] = (engine_score_fns(clf)[0] if score_fns is None else score_fns[0])
+        state["bulk_lock"] = threading.Lock()    # the closure owns one set of output buffers
         state["batcher"] = MicroBatcher(
             fns, n_features=4,
             max_batch=max_batch or int(os.environ.get("LR_MAX_BATCH", "4096")),
@@ -77,7 +79,8 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
     async def predict_species(iris: IrisSpecies):
         # REF/main.py:18-22: dict -> [[sl, sw, pl, pw]] -> predict + predict_proba.max()
         row = (iris.sepal_length, iris.sepal_width, iris.petal_length, iris.petal_width)
-        if not all(math.isfinite(v) for v in row):
+        # finite as float32, which is what the engine computes in: 1e39 is a finite Python float and inf on the device
+        if not all(math.isfinite(v) and abs(v) <= 3.4028234663852886e38 for v in row):
             # sklearn raises ValueError here (SK/linear_model/_base.py:385-389) -> HTTP 500, as in the reference
             raise ValueError("Input X contains NaN or infinity.")
         label_idx, prob = await state["batcher"].submit(row)
@@ -111,14 +114,20 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
         if not np.isfinite(X).all():
             raise ValueError("Input X contains NaN or infinity.")
         n = X.shape[0]
-        labels, probs = [], []
         fn = state["bulk_fn"]
-        for lo in range(0, n, 1 << 20):
-            chunk = np.ascontiguousarray(X[lo:lo + (1 << 20)])
-            li, pi = fn(chunk, chunk.shape[0])
-            labels += [state["classes"][int(i)] for i in li[:chunk.shape[0]]]
-            probs += [float(v) for v in pi[:chunk.shape[0]]]
-        labels = [c.item() if hasattr(c, "item") else c for c in labels]
+
+        def score_all():                      # blocking device calls: off the event loop (/predict keeps flowing)
+            labels, probs = [], []
+            with state["bulk_lock"]:
+                for lo in range(0, n, 1 << 20):
+                    chunk = np.ascontiguousarray(X[lo:lo + (1 << 20)])
+                    li, pi = fn(chunk, chunk.shape[0])
+                    labels += [state["classes"][int(i)] for i in li[:chunk.shape[0]]]
+                    probs += [float(v) for v in pi[:chunk.shape[0]]]
+            return [c.item() if hasattr(c, "item") else c for c in labels], probs
+
+        import asyncio
+        labels, probs = await asyncio.get_running_loop().run_in_executor(None, score_all)
         return {"rows": n, "predictions": labels, "probabilities": probs, "token": token}
 
     @app.get("/batcher_stats")

@@ -119,7 +119,11 @@ class MicroBatcher:
                 for i, (row, _, _) in enumerate(items):
                     stage[i] = row
                 labels, probs = score_fn(stage, n)
-                results = [(int(labels[i]), float(probs[i])) for i in range(n)]
+                # A row that scored to NaN / infinity (sklearn: ValueError, SK/linear_model/_base.py:385-389) fails
+                # alone: the other requests that happened to share its batch get their answers.
+                results = [(int(labels[i]), float(probs[i])) if np.isfinite(probs[i])
+                           else ValueError("Input X contains NaN or infinity (or a value too large for float32).")
+                           for i in range(n)]
                 err = None
             except Exception as e:  # noqa: BLE001 - forwarded to every waiter
                 results, err = None, e
@@ -140,6 +144,8 @@ class MicroBatcher:
                     continue
                 if err is not None:
                     fut.set_exception(err)
+                elif isinstance(res, Exception):
+                    fut.set_exception(res)
                 else:
                     fut.set_result(res)
 
@@ -189,9 +195,10 @@ def engine_score_fns(clf) -> List[ScoreFn]:
                 code = rep.lib.lr_score_host(rep.handle, stage.ctypes.data_as(C.c_void_p), n, stage.shape[1],
                                              None, None, labels.ctypes.data_as(C.c_void_p),
                                              probs.ctypes.data_as(C.c_void_p))
-                if code == _lib.LR_ERR_NONFINITE:
-                    raise ValueError("Input X contains NaN or infinity.")
-                _lib.check(code)
+                # LR_ERR_NONFINITE: the outputs are written all the same, the offending rows hold a non-finite
+                # maximum probability -- the batcher fails those requests only
+                if code != _lib.LR_ERR_NONFINITE:
+                    _lib.check(code)
                 return labels, probs
 
             return fn

@@ -271,12 +271,20 @@ int lr_model_set_host_chunk_rows(lr_model* h, int64_t rows) {
 
 // True when `p` is page-locked host memory the device can address directly (cudaHostAlloc /
 // cudaHostRegister under unified addressing); `*dev_ptr` receives the device-side alias.
-static bool mapped_host(const void* p, void** dev_ptr) {
+static bool mapped_host(const void* p, size_t bytes, void** dev_ptr) {
     if (!p) { *dev_ptr = nullptr; return true; }
     cudaPointerAttributes attr;
     if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
     if (attr.type != cudaMemoryTypeHost || !attr.devicePointer) return false;
     *dev_ptr = attr.devicePointer;
+    if (bytes > 1) {                               // the last byte must belong to the same mapped range
+        cudaPointerAttributes end;
+        const char* last = static_cast<const char*>(p) + bytes - 1;
+        if (cudaPointerGetAttributes(&end, last) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (end.type != cudaMemoryTypeHost || !end.devicePointer ||
+            static_cast<const char*>(end.devicePointer) - static_cast<const char*>(attr.devicePointer) != (ptrdiff_t)(bytes - 1))
+            return false;
+    }
     return true;
 }
 
@@ -322,8 +330,11 @@ int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx,
     // batch is a few KB (a micro-batch of /predict rows); bigger batches want HBM-resident staging.
     if (n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
         void *xd, *pd, *dd, *ld, *md;
-        if (mapped_host(X_host, &xd) && mapped_host(proba_host, &pd) && mapped_host(decision_host, &dd) &&
-            mapped_host(label_host, &ld) && mapped_host(maxprob_host, &md)) {
+        const size_t nr = (size_t)n_rows;
+        if (mapped_host(X_host, ((nr - 1) * (size_t)ldx + (size_t)d) * sizeof(float), &xd) &&
+            mapped_host(proba_host, nr * m->n_out * sizeof(float), &pd) &&
+            mapped_host(decision_host, nr * m->n_scores * sizeof(float), &dd) &&
+            mapped_host(label_host, nr * sizeof(int32_t), &ld) && mapped_host(maxprob_host, nr * sizeof(float), &md)) {
             cudaStream_t s = st.stream[0];
             ScoreArgs a{static_cast<const float*>(xd), n_rows, ldx, static_cast<float*>(pd), static_cast<float*>(dd),
                         static_cast<int32_t*>(ld), static_cast<float*>(md), s};
@@ -342,32 +353,46 @@ int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx,
         }
     }
 staged:
+    // Any failure inside the loop first waits for the copies already in flight on the other slots' streams:
+    // they write into the caller's host buffers, which the caller is free to release once this returns.
+    auto drain = [&]() { for (int i = 0; i < HostStage::kSlots; ++i) cudaStreamSynchronize(st.stream[i]); };
+#define LRS_STAGE(expr)                                                                            \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            drain();                                                                               \
+            return fail(LR_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));          \
+        }                                                                                          \
+    } while (0)
     int slot = 0;
     for (int64_t r0 = 0; r0 < n_rows; r0 += st.chunk_rows, slot = (slot + 1) % HostStage::kSlots) {
         const int64_t rows = (n_rows - r0 < st.chunk_rows) ? (n_rows - r0) : st.chunk_rows;
         cudaStream_t s = st.stream[slot];
         const float* src = X_host + r0 * ldx;
         if (ldx == st.pitch) {
-            LRS_CUDA(cudaMemcpyAsync(st.x[slot], src, rows * ldx * sizeof(float), cudaMemcpyHostToDevice, s));
+            // one contiguous copy; the last row ends after its d features (a pitch padded to 4 floats may run
+            // past the caller's buffer there)
+            LRS_STAGE(cudaMemcpyAsync(st.x[slot], src, ((rows - 1) * ldx + d) * sizeof(float), cudaMemcpyHostToDevice, s));
         } else {
-            LRS_CUDA(cudaMemcpy2DAsync(st.x[slot], st.pitch * sizeof(float), src, ldx * sizeof(float),
-                                       d * sizeof(float), rows, cudaMemcpyHostToDevice, s));
+            LRS_STAGE(cudaMemcpy2DAsync(st.x[slot], st.pitch * sizeof(float), src, ldx * sizeof(float),
+                                        d * sizeof(float), rows, cudaMemcpyHostToDevice, s));
         }
         ScoreArgs a{st.x[slot], rows, st.pitch,
                     proba_host ? st.proba[slot] : nullptr, decision_host ? st.decision[slot] : nullptr,
                     label_host ? st.label[slot] : nullptr, maxprob_host ? st.maxprob[slot] : nullptr, s};
-        if ((rc = dispatch(*m, a)) != LR_OK) { cudaDeviceSynchronize(); return rc; }
+        if ((rc = dispatch(*m, a)) != LR_OK) { drain(); return rc; }
         if (proba_host)
-            LRS_CUDA(cudaMemcpyAsync(proba_host + r0 * m->n_out, st.proba[slot], rows * m->n_out * sizeof(float),
-                                     cudaMemcpyDeviceToHost, s));
+            LRS_STAGE(cudaMemcpyAsync(proba_host + r0 * m->n_out, st.proba[slot], rows * m->n_out * sizeof(float),
+                                      cudaMemcpyDeviceToHost, s));
         if (decision_host)
-            LRS_CUDA(cudaMemcpyAsync(decision_host + r0 * m->n_scores, st.decision[slot],
-                                     rows * m->n_scores * sizeof(float), cudaMemcpyDeviceToHost, s));
+            LRS_STAGE(cudaMemcpyAsync(decision_host + r0 * m->n_scores, st.decision[slot],
+                                      rows * m->n_scores * sizeof(float), cudaMemcpyDeviceToHost, s));
         if (label_host)
-            LRS_CUDA(cudaMemcpyAsync(label_host + r0, st.label[slot], rows * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+            LRS_STAGE(cudaMemcpyAsync(label_host + r0, st.label[slot], rows * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
         if (maxprob_host)
-            LRS_CUDA(cudaMemcpyAsync(maxprob_host + r0, st.maxprob[slot], rows * sizeof(float), cudaMemcpyDeviceToHost, s));
+            LRS_STAGE(cudaMemcpyAsync(maxprob_host + r0, st.maxprob[slot], rows * sizeof(float), cudaMemcpyDeviceToHost, s));
     }
+#undef LRS_STAGE
     for (int i = 0; i < HostStage::kSlots; ++i) LRS_CUDA(cudaStreamSynchronize(st.stream[i]));
     unsigned long long sw[2] = {0, 0};            // [0] non-finite rows, [1] rows re-scored in fp32 (running)
     LRS_CUDA(cudaMemcpy(sw, m->status, sizeof(sw), cudaMemcpyDeviceToHost));

@@ -116,7 +116,10 @@ struct GemmParams {
     int32_t* label;
     float* maxprob;
     unsigned long long* status;
-    unsigned char* flags;   // [n_rows] set for rows to re-score in fp32 (near-ties, risky probabilities)
+    unsigned* flags;        // [n_rows] one word per row, non-zero once the row is on the re-scoring list (several threads
+                            // may find a reason to flag the same row)
+    unsigned* flag_list;    // [n_rows] the rows to re-score in fp32 (near-ties, risky probabilities, overflowed rows) ...
+    unsigned* n_flagged;    // ... and how many there are
     float* lse;             // [n_rows] log-sum-exp of the row as the tensor path saw it (for the re-scoring pass)
     int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned);
                             // 2: 32-byte aligned as well (C % 8 == 0): 256-bit stores, whole sectors per lane
@@ -351,6 +354,11 @@ template <>
 __device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { tc_mma_f16(d, a, b, idesc, acc); }
 
 constexpr float kLog2e = 1.4426950408889634f;
+
+// Put `row` on the re-scoring list, once.
+__device__ __forceinline__ void flag_row(unsigned* flags, unsigned* list, unsigned* count, int64_t row) {
+    if (atomicExch(flags + row, 1u) == 0u) list[atomicAdd(count, 1u)] = (unsigned)row;
+}
 
 // ---- cta_group::2 (CTA pair) forms ---------------------------------------------------------------
 // The pair shares every MMA: the even CTA of the pair issues it, each SM multiplies its own 128 rows
@@ -819,12 +827,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
                         const bool finite_row = finite_f(gm) && finite_f(gs);
                         if (!finite_row) {
-                            if (p.flags && !p.count_nonfinite) p.flags[row] = 2;
+                            if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                             else atomicAdd(p.status, 1ull);
                         }
                         if (p.flags) {
                             p.lse[row] = gm + logf(gs);
-                            if (finite_row && (risk || gnear >= 2 || inv * (1.0f - inv) > risk_thr)) p.flags[row] = 1;
+                            if (finite_row && (risk || gnear >= 2 || inv * (1.0f - inv) > risk_thr))
+                                flag_row(p.flags, p.flag_list, p.n_flagged, row);
                         }
                     }
                 } else {
@@ -878,10 +887,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     arg = col0 + (cb) + idx; /* first index wins */                                    \
                 }                                                                                      \
                 /* exponentials relative to the chunk's own maximum (<= 1), kept in TMEM for pass 2 */ \
-                const float cml = cm * kLog2e;                                                         \
+                /* (z - cm) first: exactly 0 for the maximum itself, whatever its size (an fma against a */ \
+                /* pre-multiplied cm * log2e leaves the product's rounding error in the exponent)        */ \
                 float cs = 0.0f;                                                                       \
                 _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
-                    (v)[i] = ex2(fmaf((v)[i], kLog2e, -cml));                                          \
+                    (v)[i] = ex2(((v)[i] - cm) * kLog2e);                                              \
                     cs += (v)[i];                                                                      \
                 }                                                                                      \
                 tmem_st32(t_lane + (uint32_t)(cb), v);                                                 \
@@ -962,7 +972,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // ---- pass 2: p = e * exp(chunk max - max) / sum -> global memory; near-tie count.
             // A runner-up this close to the maximum may be the true winner, and |dp| ~ p(1-p)|dz|: the row is
             // flagged when a class of middling probability could move by ~8e-6 (see `ez` above the loop).
-            const float gml = gm * kLog2e;
             const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
             const float risk_thr = 8e-6f / ez;
             const float near_thr = inv * ex2(-2.0f * ez * kLog2e);   // z > max - 2 ez, as a probability
@@ -971,7 +980,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const bool want_rows = p.proba != nullptr;
 #define LRS_PASS2_CHUNK(v, cb)                                                                         \
             do {                                                                                       \
-                const float fj = ex2(fmaf(chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid], kLog2e, -gml)) * inv; \
+                const float fj = ex2((chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid] - gm) * kLog2e) * inv; \
                 _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
                     (v)[i] *= fj;                                                                      \
                     near += (v)[i] > near_thr ? 1 : 0;                                                 \
@@ -1017,7 +1026,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             if (live) {
                 // the thread whose columns hold the maximum always counts it; anything else above tau is a near-tie
                 const bool owner = garg >= col0 + cb_lo && garg < col0 + cb_hi;
-                if (p.flags && (risk || near >= (owner ? 2 : 1))) p.flags[row] = 1;
+                if (p.flags && (risk || near >= (owner ? 2 : 1))) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                 if (rank == 0 && h == 0) {
                     if (p.label) __stcs(p.label + row, garg);
                     if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
@@ -1025,13 +1034,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     if (!finite_row) {
                         // With a re-scoring pass the row is handed over (flag 2): an fp16 overflow of a
                         // finite input would otherwise be reported as non-finite data.
-                        if (p.flags && !p.count_nonfinite) p.flags[row] = 2;
+                        if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                         else atomicAdd(p.status, 1ull);
                     }
                     if (p.flags) {
                         p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
                         // a top probability the error could move
-                        if (finite_row && inv * (1.0f - inv) > risk_thr) p.flags[row] = 1;
+                        if (finite_row && inv * (1.0f - inv) > risk_thr) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                     }
                 }
             }
@@ -1055,28 +1064,12 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 // probability that error could move by more than the parity bar.  Only the classes that carry
 // weight matter for either, so the pass re-computes the logits of those classes in fp32 FMA
 // arithmetic (error ~1e-6) and patches the row: one warp per flagged row, traffic = the row of X,
-// the row of P and a few rows of W instead of all of W.
-// Dot product of one row of X with one row of W by a warp; both rows are 16-byte aligned on this path
-// (n_features % 4 == 0, row pitch % 4 == 0), so the bulk goes in 128-bit pieces, four in flight.
-__device__ __forceinline__ float warp_dot4(const float* __restrict__ x, const float* __restrict__ w, int d, int lane) {
-    const float4* x4 = reinterpret_cast<const float4*>(x);
-    const float4* w4 = reinterpret_cast<const float4*>(w);
-    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
-#pragma unroll 4
-    for (int k = lane; k < d / 4; k += 32) {
-        const float4 xv = __ldg(x4 + k), wv = __ldg(w4 + k);
-        a0 = fmaf(xv.x, wv.x, a0); a1 = fmaf(xv.y, wv.y, a1);
-        a2 = fmaf(xv.z, wv.z, a2); a3 = fmaf(xv.w, wv.w, a3);
-    }
-    float acc = (a0 + a1) + (a2 + a3);
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-    return acc;
-}
-
-// Up to four such dot products at once (rows c[0..3] of W against the same row of X): the pieces of X are
-// loaded once and four chains of loads are in flight instead of one -- a warp re-scoring the ~20 classes of a
-// flagged row one by one spent its time waiting on L2.
+// the row of P and a few rows of W instead of all of W.  The epilogue leaves a compact list of the flagged
+// rows, so the warps of this pass share them evenly whatever their density.
+//
+// Four dot products at once (rows c[0..3] of W against the same row of X; both are 16-byte aligned on this
+// path): the pieces of X are loaded once and sixteen independent loads are in flight per lane -- taken one
+// class at a time, a row's ~20 selected classes were ~20 dependent trips to L2.
 __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const float* __restrict__ W, const int (&c)[4],
                                              int d, int lane, float (&z)[4]) {
     const float4* x4 = reinterpret_cast<const float4*>(x);
@@ -1087,7 +1080,7 @@ __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const 
         w4[u] = reinterpret_cast<const float4*>(W + (int64_t)c[u] * d);
         acc[u] = 0.0f;
     }
-#pragma unroll 2
+#pragma unroll 4
     for (int k = lane; k < d / 4; k += 32) {
         const float4 xv = __ldg(x4 + k);
 #pragma unroll
@@ -1107,240 +1100,158 @@ __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const 
     }
 }
 
-// NPER = classes per lane the row of P is held in (C <= 32 * NPER): the whole row is fetched in one batch of
-// loads and worked on in registers -- walking it from memory (maximum, selection block by block, rescale) put
-// ~70 dependent DRAM round trips on every flagged row, which is what the pass cost (0.5 ms per 13 000 rows).
-template <int NPER>
-__device__ __forceinline__ void fixup_row_warp_n(const float* __restrict__ x, int64_t row, int lane, int d, int C,
-                                                 const float* __restrict__ W, const float* __restrict__ b, float L,
-                                                 float* proba, float* decision, int32_t* label, float* maxprob,
-                                                 unsigned long long* rescored) {
-    float* pr = proba + row * C;
-    float pv[NPER];
-#pragma unroll
-    for (int j = 0; j < NPER; ++j) {
-        const int c = j * 32 + lane;
-        pv[j] = c < C ? __ldcg(pr + c) : 0.0f;
-    }
-    float pmax = 0.0f;
-#pragma unroll
-    for (int j = 0; j < NPER; ++j) pmax = fmaxf(pmax, pv[j]);
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
-    const float thr = fminf(0.01f, 0.9f * pmax);   // classes that carry weight, or rival the maximum
-    float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
-    int best = 0;
-#pragma unroll
-    for (int jb = 0; jb < NPER; ++jb) {
-        const int c0 = jb * 32;
-        if (c0 >= C) break;
-        const int c = c0 + lane;
-        const float pc = pv[jb];
-        unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
-        while (sel) {
-            int js[4], cls[4], nj = 0;
-            while (sel && nj < 4) {                         // ascending
-                js[nj] = __ffs(sel) - 1;
-                sel &= sel - 1;
-                ++nj;
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) cls[u] = c0 + js[u < nj ? u : 0];
-            float z4[4];
-            warp_dot4_x4(x, W, cls, d, lane, z4);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (u >= nj) break;
-                const int j = js[u], cj = cls[u];
-                const float z = z4[u] + __ldg(b + cj);
-                const float q = expf(z - L);                    // in units of the old row sum
-                old_mass += __shfl_sync(0xffffffffu, pc, j);
-                new_mass += q;
-                if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
-                if (lane == j) pv[jb] = q;
-                if (decision && lane == 0) decision[row * C + cj] = z;
-            }
-        }
-    }
-    const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
-    const float invT = __frcp_rn(T);
-    const bool rescale = fabsf(T - 1.0f) > 1e-7f;
-#pragma unroll
-    for (int j = 0; j < NPER; ++j) {
-        const int c = j * 32 + lane;
-        if (c < C) __stcs(pr + c, rescale ? pv[j] * invT : pv[j]);
-    }
-    if (lane == 0) {
-        if (label) label[row] = best;
-        if (maxprob) maxprob[row] = best_q * invT;
-        atomicAdd(rescored, 1ull);
-    }
-}
+constexpr int kFixWarps = 8;
+constexpr int kFixQueue = 64;          // selected classes waiting for their dot products (per warp)
 
-// One flagged row re-scored by one warp (see the kernel below for when).
-__device__ __forceinline__ void fixup_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
-                                               const float* __restrict__ W, const float* __restrict__ b, float L,
-                                               float* proba, float* decision, int32_t* label, float* maxprob,
-                                               unsigned long long* rescored, unsigned long long* status) {
-    if (!finite_f(L)) {
-        // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
-        // score the whole row in fp32, which also settles whether the input really is non-finite
-        score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
-        if (lane == 0) atomicAdd(rescored, 1ull);
-        return;
-    }
-    if (C <= 256) fixup_row_warp_n<8>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
-    else if (C <= 1024) fixup_row_warp_n<32>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
-    else fixup_row_warp_n<64>(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored);
-}
-
-// One CTA per 256 rows.  Where flagged rows are dense (8 or more in the block: as many as there are warps) every
-// warp re-scores the flagged rows among its own 32, one after the other.  Where they are sparse that would
-// leave the last flagged row of a long-row model as a serial tail (d=4096, C=64: most classes are
-// "selected", 64 dot products of 4096 in one warp, 0.28 ms for a handful of rows), so the whole CTA takes
-// each flagged row, its eight warps sharing the selected classes.
-__global__ void __launch_bounds__(256)
-gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
+// grid-stride over the list, one warp per flagged row.  Dynamic shared memory: [kFixWarps][c_pad] floats (the
+// row of P a warp works on) + [kFixWarps][kFixQueue] ints.
+__global__ void __launch_bounds__(kFixWarps * 32)
+gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int c_pad,
                       const float* __restrict__ W, const float* __restrict__ b,
-                      const unsigned char* __restrict__ flags, const float* __restrict__ lse, float* proba,
+                      const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
+                      const float* __restrict__ lse, float* proba,
                       float* decision, int32_t* label, float* maxprob, unsigned long long* rescored,
                       unsigned long long* status) {
-    __shared__ unsigned s_mask[8];
-    __shared__ float s_f[8], s_old[8], s_new[8], s_bz[8], s_bq[8];
-    __shared__ int s_bc[8];
+    extern __shared__ float fix_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = (int64_t)blockIdx.x * 256; base < n_rows; base += (int64_t)gridDim.x * 256) {
-        const int64_t mine = base + threadIdx.x;
-        const bool flagged = mine < n_rows && flags[mine] != 0;
-        const unsigned m32 = __ballot_sync(0xffffffffu, flagged);
-        if (lane == 0) s_mask[warp] = m32;
-        const int n_flagged = __syncthreads_count(flagged);
-        if (n_flagged == 0) continue;
-        if (n_flagged >= 8) {
-            unsigned todo = m32;
-            while (todo) {
-                const int64_t row = base + warp * 32 + (__ffs(todo) - 1);
-                todo &= todo - 1;
-                fixup_row_warp(X + row * ldx, row, lane, d, C, W, b, lse[row], proba, decision, label, maxprob,
-                               rescored, status);
-            }
-            __syncthreads();                                            // s_mask is rewritten by the next block of rows
+    float* prow = fix_smem + (size_t)warp * c_pad;
+    int* queue = reinterpret_cast<int*>(fix_smem + (size_t)kFixWarps * c_pad) + warp * kFixQueue;
+    const unsigned n = *n_list;
+    for (unsigned li = blockIdx.x * kFixWarps + warp; li < n; li += gridDim.x * kFixWarps) {
+        const int64_t row = list[li];
+        const float* x = X + row * ldx;
+        const float L = lse[row];
+        if (!finite_f(L)) {
+            // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
+            // score the whole row in fp32, which also settles whether the input really is non-finite
+            score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+            if (lane == 0) atomicAdd(rescored, 1ull);
             continue;
         }
-        for (int wq = 0; wq < 8; ++wq) {
-            unsigned todo = s_mask[wq];                               // same for every thread of the CTA
-            while (todo) {
-                const int64_t row = base + wq * 32 + (__ffs(todo) - 1);
-                todo &= todo - 1;
-                const float* x = X + row * ldx;
-                float* pr = proba + row * C;
-                const float L = lse[row];
-                if (!finite_f(L)) {
-                    if (warp == 0)
-                        fixup_row_warp(x, row, lane, d, C, W, b, L, proba, decision, label, maxprob, rescored, status);
-                    continue;
-                }
-                // largest probability of the row
-                float pmax = 0.0f;
-                for (int c = threadIdx.x; c < C; c += 256) pmax = fmaxf(pmax, pr[c]);
+        float* pr = proba + row * C;
+        float pmax = 0.0f;
+        for (int c = lane; c < C; c += 32) {             // independent loads: one trip to memory for the row
+            const float v = __ldcg(pr + c);
+            prow[c] = v;
+            pmax = fmaxf(pmax, v);
+        }
 #pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
-                if (lane == 0) s_f[warp] = pmax;
-                __syncthreads();
-                pmax = s_f[0];
+        for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
+        __syncwarp();
+        const float thr = fminf(0.01f, 0.9f * pmax);    // classes that carry weight, or rival the maximum
+        float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
+        int best = 0, nq = 0;
+        // queue of selected classes in ascending order, worked off four at a time
+        auto drain = [&](bool all) {
+            int done = 0;
+            while (nq - done >= 4 || (all && done < nq)) {
+                const int take = min(4, nq - done);
+                int cls[4];
 #pragma unroll
-                for (int w = 1; w < 8; ++w) pmax = fmaxf(pmax, s_f[w]);
-                const float thr = fminf(0.01f, 0.9f * pmax);
-                float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
-                int best = 0x7fffffff;
-                for (int c0 = warp * 32; c0 < C; c0 += 256) {           // this warp's blocks of 32 classes, ascending
-                    const int c = c0 + lane;
-                    const float pc = c < C ? pr[c] : 0.0f;
-                    unsigned sel = __ballot_sync(0xffffffffu, c < C && pc >= thr);
-                    float q_mine = pc;
-                    while (sel) {
-                        const int j = __ffs(sel) - 1;
-                        sel &= sel - 1;
-                        const int cj = c0 + j;
-                        const float z = warp_dot4(x, W + (int64_t)cj * d, d, lane) + __ldg(b + cj);
-                        const float q = expf(z - L);
-                        old_mass += __shfl_sync(0xffffffffu, pc, j);
-                        new_mass += q;
-                        if (z > best_z) { best_z = z; best = cj; best_q = q; }
-                        if (lane == j) q_mine = q;
-                        if (decision && lane == 0) decision[row * C + cj] = z;
+                for (int u = 0; u < 4; ++u) cls[u] = queue[done + (u < take ? u : 0)];
+                float z4[4];
+                warp_dot4_x4(x, W, cls, d, lane, z4);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (u >= take) break;
+                    const int cj = cls[u];
+                    const float z = z4[u] + __ldg(b + cj);
+                    const float q = expf(z - L);                    // in units of the old row sum
+                    old_mass += prow[cj];
+                    new_mass += q;
+                    if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
+                    __syncwarp();
+                    if (lane == 0) {
+                        prow[cj] = q;
+                        if (decision) decision[row * C + cj] = z;
                     }
-                    if (c < C && q_mine != pc) pr[c] = q_mine;
                 }
-                if (lane == 0) { s_old[warp] = old_mass; s_new[warp] = new_mass; s_bz[warp] = best_z; s_bq[warp] = best_q; s_bc[warp] = best; }
-                __syncthreads();                                        // also orders the pr[] updates before the rescale
-                old_mass = 0.0f; new_mass = 0.0f; best_z = -CUDART_INF_F; best_q = 0.0f; best = 0x7fffffff;
-#pragma unroll
-                for (int w = 0; w < 8; ++w) {                           // fixed order: every thread gets the same sums
-                    old_mass += s_old[w];
-                    new_mass += s_new[w];
-                    if (s_bz[w] > best_z || (s_bz[w] == best_z && s_bc[w] < best)) { best_z = s_bz[w]; best = s_bc[w]; best_q = s_bq[w]; }
-                }
-                const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
-                const float invT = __frcp_rn(T);
-                if (fabsf(T - 1.0f) > 1e-7f)
-                    for (int c = threadIdx.x; c < C; c += 256) pr[c] *= invT;
-                if (threadIdx.x == 0) {
-                    if (label) label[row] = best;
-                    if (maxprob) maxprob[row] = best_q * invT;
-                    atomicAdd(rescored, 1ull);
-                }
-                __syncthreads();                                        // shared scratch is reused by the next row
+                done += take;
+            }
+            __syncwarp();
+            // what is left (fewer than four) moves to the front
+            const int left = nq - done;
+            const int keep = lane < left ? queue[done + lane] : 0;
+            __syncwarp();
+            if (lane < left) queue[lane] = keep;
+            nq = left;
+            __syncwarp();
+        };
+        for (int c0 = 0; c0 < C; c0 += 32) {
+            const int c = c0 + lane;
+            const bool sel = c < C && prow[c] >= thr;
+            const unsigned mask = __ballot_sync(0xffffffffu, sel);
+            if (mask) {
+                if (nq + __popc(mask) > kFixQueue) drain(false);          // leaves at most 3
+                if (sel) queue[nq + __popc(mask & ((1u << lane) - 1u))] = c;
+                nq += __popc(mask);
+                __syncwarp();
+                if (nq >= 16) drain(false);
             }
         }
-        __syncthreads();                                                // s_mask is rewritten by the next block of rows
+        drain(true);
+        const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+        const float invT = __frcp_rn(T);
+        const float sc = fabsf(T - 1.0f) > 1e-7f ? invT : 1.0f;
+        for (int c = lane; c < C; c += 32) __stcs(pr + c, prow[c] * sc);
+        if (lane == 0) {
+            if (label) label[row] = best;
+            if (maxprob) maxprob[row] = best_q * invT;
+            atomicAdd(rescored, 1ull);
+        }
+        __syncwarp();
     }
 }
 
 // Same purpose when the caller asked for no probability matrix (labels / max probability only, the
 // /predict pattern): there is no row of P to pick classes from, so a whole CTA re-scores every class
-// of the flagged row, eight warps splitting the classes.
+// of the flagged row, eight warps splitting the classes, four classes per step.
 __global__ void __launch_bounds__(256)
-gemm_fixup_full_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C,
+gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
                        const float* __restrict__ W, const float* __restrict__ b,
-                       const unsigned char* __restrict__ flags, float* decision, int32_t* label, float* maxprob,
+                       const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
+                       float* decision, int32_t* label, float* maxprob,
                        unsigned long long* rescored, unsigned long long* status) {
     __shared__ float s_m[8], s_s[8];
     __shared__ int s_a[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = (int64_t)blockIdx.x * 256; base < n_rows; base += (int64_t)gridDim.x * 256) {
-        const int64_t mine = base + threadIdx.x;
-        const int any = __syncthreads_or(mine < n_rows && flags[mine] != 0);
-        if (!any) continue;
-        for (int j = 0; j < 256 && base + j < n_rows; ++j) {
-            if (!flags[base + j]) continue;                         // uniform across the CTA
-            const int64_t row = base + j;
-            const float* x = X + row * ldx;
-            float m = -CUDART_INF_F, ssum = 0.0f;
-            int arg = 0;
-            const int per = (C + 7) / 8;
-            const int c_hi = min(C, (warp + 1) * per);
-            for (int c = warp * per; c < c_hi; ++c) {
-                const float z = warp_dot4(x, W + (int64_t)c * d, d, lane) + __ldg(b + c);
-                if (decision && lane == 0) decision[row * C + c] = z;
-                if (z > m) { ssum = ssum * expf(m - z) + 1.0f; m = z; arg = c; }
+    const unsigned n = *n_list;
+    for (unsigned li = blockIdx.x; li < n; li += gridDim.x) {
+        const int64_t row = list[li];
+        const float* x = X + row * ldx;
+        float m = -CUDART_INF_F, ssum = 0.0f;
+        int arg = 0;
+        const int per = (C + 7) / 8;
+        const int c_hi = min(C, (warp + 1) * per);
+        for (int c = warp * per; c < c_hi; c += 4) {
+            int cls[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) cls[u] = min(c + u, c_hi - 1);
+            float z4[4];
+            warp_dot4_x4(x, W, cls, d, lane, z4);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (c + u >= c_hi) break;
+                const float z = z4[u] + __ldg(b + c + u);
+                if (decision && lane == 0) decision[row * C + c + u] = z;
+                if (z > m) { ssum = ssum * expf(m - z) + 1.0f; m = z; arg = c + u; }
                 else ssum += expf(z - m);
             }
-            if (lane == 0) { s_m[warp] = m; s_s[warp] = ssum; s_a[warp] = arg; }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                float gm = -CUDART_INF_F;
-                int ga = 0;
-                for (int w = 0; w < 8; ++w) if (s_m[w] > gm) { gm = s_m[w]; ga = s_a[w]; }
-                float gs = 0.0f;
-                for (int w = 0; w < 8; ++w) if (s_s[w] > 0.0f) gs += s_s[w] * expf(s_m[w] - gm);
-                if (label) label[row] = ga;
-                if (maxprob) maxprob[row] = __frcp_rn(gs);
-                atomicAdd(rescored, 1ull);
-                if (!(finite_f(gm) && finite_f(gs))) atomicAdd(status, 1ull);
-            }
-            __syncthreads();
         }
+        if (lane == 0) { s_m[warp] = m; s_s[warp] = ssum; s_a[warp] = arg; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float gm = -CUDART_INF_F;
+            int ga = 0;
+            for (int w = 0; w < 8; ++w) if (s_m[w] > gm) { gm = s_m[w]; ga = s_a[w]; }
+            float gs = 0.0f;
+            for (int w = 0; w < 8; ++w) if (s_s[w] > 0.0f) gs += s_s[w] * expf(s_m[w] - gm);
+            if (label) label[row] = ga;
+            if (maxprob) maxprob[row] = __frcp_rn(gs);
+            atomicAdd(rescored, 1ull);
+            if (!(finite_f(gm) && finite_f(gs))) atomicAdd(status, 1ull);
+        }
+        __syncthreads();
     }
 }
 
@@ -1581,6 +1492,7 @@ struct GemmPlan {
     int c_pad = 0;
     uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen (lr_score_host holds the staging lock)
     bool configured[64] = {false};
+    bool fix_configured[64] = {false};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
 
@@ -1890,26 +1802,30 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // independent: [256 B: what x_scale_kernel decides | its per-row statistics | per row the log-sum-exp the
     // tensor path saw | one flag byte per row (near-ties, risky probabilities) for the fp32 re-scoring pass].
     const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
-    unsigned char* flags = nullptr;
+    unsigned* flags = nullptr;
+    unsigned* flag_list = nullptr;
     float* lse = nullptr;
     AsyncScratch scratch;
     scratch.s = a.stream;
     const size_t stat_bytes = 2 * kMaxSample * sizeof(float);
     const size_t lse_bytes = fixup ? ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256 : 0;
-    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + lse_bytes + (fixup ? (size_t)a.n_rows : 0), a.stream));
+    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + 3 * lse_bytes, a.stream));
     float* x_scale = reinterpret_cast<float*>(scratch.p);
     float* rowstat = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256);
     if (fixup) {
         lse = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes);
-        flags = reinterpret_cast<unsigned char*>(scratch.p) + 256 + stat_bytes + lse_bytes;
-        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows, a.stream));
+        flags = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + lse_bytes);
+        flag_list = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + 2 * lse_bytes);
+        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows * sizeof(unsigned), a.stream));
     }
-    LRS_CUDA(cudaMemsetAsync(x_scale, 0, 32, a.stream));
+    LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));          // ticket, decisions, [8] = length of the re-scoring list
     x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
                                                         g->inv_cscale_max, g->force, x_scale, rowstat);
     count_launch();
     GemmParams p;
     p.flags = flags;
+    p.flag_list = flag_list;
+    p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
     p.lse = lse;
     p.n_rows = a.n_rows;
     p.n_features = d_eff;
@@ -2014,14 +1930,21 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         count_launch();
     }
     if (fixup) {
-        if (a.proba)
-            gemm_fixup_sel_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, m.n_scores,
-                                                                      w_fix, m.b, flags, lse, a.proba, a.decision,
-                                                                      a.label, a.maxprob, m.status + 1, m.status);
-        else
-            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff,
-                                                                       m.n_scores, w_fix, m.b, flags, a.decision,
-                                                                       a.label, a.maxprob, m.status + 1, m.status);
+        if (a.proba) {
+            const int c_pad = (m.n_scores + 31) / 32 * 32;
+            const size_t fsm = (size_t)kFixWarps * c_pad * sizeof(float) + (size_t)kFixWarps * kFixQueue * sizeof(int);
+            if (fsm > 48 * 1024 && !g->fix_configured[dev]) {
+                LRS_CUDA(cudaFuncSetAttribute(gemm_fixup_sel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
+                g->fix_configured[dev] = true;
+            }
+            gemm_fixup_sel_kernel<<<m.num_sms * 3, kFixWarps * 32, fsm, a.stream>>>(
+                a.X, a.ldx, d_eff, m.n_scores, c_pad, w_fix, m.b, flag_list, p.n_flagged, lse, a.proba, a.decision,
+                a.label, a.maxprob, m.status + 1, m.status);
+        } else {
+            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_eff, m.n_scores, w_fix, m.b,
+                                                                       flag_list, p.n_flagged, a.decision, a.label,
+                                                                       a.maxprob, m.status + 1, m.status);
+        }
         count_launch();
         LRS_CUDA(cudaGetLastError());
     }

@@ -348,15 +348,24 @@ extern "C" int lr_loss_grad(const float* X_dev, const int32_t* y_dev, int64_t n_
                             double* out_dev, void* stream) {
     int rc = check_refit_args(X_dev, y_dev, n_rows, ldx, W_dev, b_dev, n_scores, n_features, out_dev);
     if (rc != LR_OK) return rc;
-    int dev = 0;
+    // the shape limits come first: nothing is allocated (and kept) for a call that is then refused
+    if (n_scores > 8) return fail(LR_ERR_LIMIT, "refit kernel serves at most 8 score columns");
+    {
+        const bool vec = (n_features % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(X_dev) & 15u) == 0);
+        if (n_features > (vec ? 128 : 32))
+            return fail(LR_ERR_LIMIT, "refit kernel serves n_features <= 128 (16-byte aligned rows) or <= 32 (any rows)");
+    }
+    int dev = 0, prev = -1;
     LRS_CUDA(cudaGetDevice(&dev));
+    prev = dev;
     cudaPointerAttributes attr;
     if (cudaPointerGetAttributes(&attr, X_dev) == cudaSuccess && attr.type == cudaMemoryTypeDevice && attr.device != dev) {
         LRS_CUDA(cudaSetDevice(attr.device));
         dev = attr.device;
     }
+    struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev, dev};
     // scratch: ticket word + one partial vector per CTA (at most SMs x 8 CTAs), grown on demand
-    const size_t stride = (size_t)(1 + n_scores * (n_features + 1) + 3) / 4 * 4;
+    const size_t stride = ((size_t)1 + (size_t)n_scores * ((size_t)n_features + 1) + 3) / 4 * 4;
     const size_t want = 256 + stride * sizeof(float) * 148 * 8;
     void* scratch = nullptr;
     {
@@ -527,11 +536,13 @@ extern "C" int lr_weighted_row_sum(const float* X_dev, const float* r_dev, int64
     if (n_rows < 0 || n_features < 1 || ldx < n_features) return fail(LR_ERR_INVALID, "lr_weighted_row_sum: bad shape");
     int dev = 0;
     LRS_CUDA(cudaGetDevice(&dev));
+    const int prev = dev;
     cudaPointerAttributes attr;
     if (cudaPointerGetAttributes(&attr, X_dev) == cudaSuccess && attr.type == cudaMemoryTypeDevice && attr.device != dev) {
         LRS_CUDA(cudaSetDevice(attr.device));
         dev = attr.device;
     }
+    struct Restore { int prev, cur; ~Restore() { if (prev != cur) cudaSetDevice(prev); } } restore{prev, dev};   // the caller's device
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const int d = n_features;
     if (n_rows == 0) {

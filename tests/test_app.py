@@ -189,3 +189,81 @@ def test_batcher_under_concurrent_load_on_gpu(golden):
     assert mb.stats()["mean_batch"] > 4
     mb.close()
     clf.close()
+
+
+def test_one_bad_row_fails_alone_in_its_batch():
+    """A request whose row scores to a non-finite value must not take the rest of its micro-batch down
+    (the reference scores every request on its own, REF/main.py:20-22)."""
+    from mlapi_b200.batcher import MicroBatcher
+
+    def fn(stage, n):                           # stand-in engine: the probability is the first feature
+        return np.zeros(n, int), stage[:n, 0].astype(np.float32)
+
+    mb = MicroBatcher([fn], n_features=4, max_batch=64, max_wait_us=20_000)
+
+    async def burst():
+        rows = [(0.5, 0.0, 0.0, 0.0)] * 10 + [(float("inf"), 0.0, 0.0, 0.0)] + [(0.25, 0.0, 0.0, 0.0)] * 10
+        return await asyncio.gather(*[mb.submit(r) for r in rows], return_exceptions=True)
+
+    res = asyncio.run(burst())
+    assert isinstance(res[10], ValueError) and "NaN or infinity" in str(res[10])
+    assert all(r == (0, 0.5) for r in res[:10]) and all(r == (0, 0.25) for r in res[11:])
+    assert max(mb.batch_sizes) > 1              # they did share a batch
+    mb.close()
+
+
+def test_predict_rejects_values_beyond_float32(golden):
+    """1e39 is a finite Python float but infinite in the float32 staging row: that request fails by itself."""
+    from fastapi.testclient import TestClient
+    from mlapi_b200.app import create_app
+    fn, calls, classes = _oracle_score_fn(golden)
+    with TestClient(create_app(score_fns=[fn], classes=classes, max_wait_us=50)) as client:
+        with pytest.raises(ValueError, match="NaN or infinity"):
+            client.post("/predict", json={"sepal_length": 1e39, "sepal_width": 1, "petal_length": 1, "petal_width": 1})
+        r = client.post("/predict", json={"sepal_length": 5.1, "sepal_width": 3.5, "petal_length": 1.4, "petal_width": 0.2})
+        assert r.status_code == 200 and r.json()["prediction"] == "Iris-setosa"
+
+
+def test_from_sklearn_rejects_pickles_the_engine_does_not_implement():
+    """scikit-learn 0.24 (the reference's pin) pickles may ask for one-vs-rest probabilities or a binary
+    softmax: loading them must fail, not answer with different numbers."""
+    from mlapi_b200.estimator import B200LogisticRegression
+
+    class Est:
+        pass
+
+    e = Est()
+    e.coef_, e.intercept_, e.classes_ = np.zeros((3, 4)), np.zeros(3), np.arange(3)
+    e.multi_class, e.solver = "ovr", "lbfgs"
+    with pytest.raises(NotImplementedError, match="one-vs-rest"):
+        B200LogisticRegression.from_sklearn(e)
+    e.multi_class, e.solver = "auto", "liblinear"
+    with pytest.raises(NotImplementedError, match="one-vs-rest"):
+        B200LogisticRegression.from_sklearn(e)
+    b = Est()
+    b.coef_, b.intercept_, b.classes_ = np.zeros((1, 4)), np.zeros(1), np.arange(2)
+    b.multi_class, b.solver = "multinomial", "lbfgs"
+    with pytest.raises(NotImplementedError, match="softmax"):
+        B200LogisticRegression.from_sklearn(b)
+
+
+@pytest.mark.gpu
+def test_overflowing_row_fails_alone_on_gpu(golden):
+    """Finite inputs whose score overflows float32 sit in one device batch with good rows."""
+    import __graft_entry__
+    __graft_entry__.build()
+    from mlapi_b200 import B200LogisticRegression
+    from mlapi_b200.batcher import MicroBatcher, engine_score_fns
+    m = golden("iris_model.npz")
+    clf = B200LogisticRegression(m["coef"] * 1e3, m["intercept"], m["classes"])
+    mb = MicroBatcher(engine_score_fns(clf), n_features=4, max_batch=64, max_wait_us=20_000)
+
+    async def burst():
+        rows = [(5.1, 3.5, 1.4, 0.2)] * 8 + [(3e38, -3e38, 3e38, -3e38)] + [(6.0, 2.9, 4.5, 1.5)] * 8
+        return await asyncio.gather(*[mb.submit(r) for r in rows], return_exceptions=True)
+
+    res = asyncio.run(burst())
+    assert isinstance(res[8], ValueError)
+    assert all(isinstance(r, tuple) and np.isfinite(r[1]) for r in res[:8] + res[9:])
+    mb.close()
+    clf.close()
