@@ -12,6 +12,9 @@ What changes underneath: the pickle is loaded ONCE at start-up into device-resid
 
 Environment: LR_MODEL_PATH (default 'LRClassifier.pkl', the reference's hard-coded path),
 LR_DEVICES (comma list, default '0'), LR_MAX_BATCH (4096), LR_MAX_WAIT_US (200).
+LR_ENGINE_SOCKET: when set, this process is an HTTP front only -- it owns no model and forwards its rows to
+the scoring engine process listening there (`python -m mlapi_b200.engine_link`, or `python -m mlapi_b200.serve`
+which starts both), so that several uvicorn workers fill the same device batches (engine_link.py).
 """
 from __future__ import annotations
 
@@ -23,6 +26,7 @@ from io import StringIO
 from typing import Optional
 
 from fastapi import FastAPI, File, Form
+from fastapi.responses import JSONResponse
 from pydantic import BaseModel
 
 from .batcher import MicroBatcher, engine_score_fns
@@ -37,13 +41,26 @@ class IrisSpecies(BaseModel):
 
 
 def create_app(model=None, model_path: Optional[str] = None, devices=None, max_batch: Optional[int] = None,
-               max_wait_us: Optional[float] = None, score_fns=None, classes=None) -> FastAPI:
+               max_wait_us: Optional[float] = None, score_fns=None, classes=None,
+               engine_socket: Optional[str] = None) -> FastAPI:
     """Build the app.  `model` may be a ready `B200LogisticRegression` (tests); otherwise the pickle
-    at `model_path` is loaded at start-up.  `score_fns` (+ `classes`) lets host-logic tests inject a scorer."""
+    at `model_path` is loaded at start-up.  `score_fns` (+ `classes`) lets host-logic tests inject a scorer.
+    `engine_socket` (or LR_ENGINE_SOCKET): be a front of the engine process listening there instead."""
     state = {}
+    if engine_socket is None and model is None and score_fns is None:
+        engine_socket = os.environ.get("LR_ENGINE_SOCKET") or None
 
     @asynccontextmanager
     async def lifespan(app: FastAPI):
+        if engine_socket:
+            from .engine_link import EngineClient
+            client = await EngineClient(engine_socket).connect()
+            state["client"] = client
+            state["classes"] = client.classes
+            state["submit"] = client.submit
+            yield
+            await client.close()
+            return
         clf = model
         if clf is None and score_fns is None:
             from .estimator import load_model
@@ -70,6 +87,7 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
             max_wait_us=max_wait_us if max_wait_us is not None else float(os.environ.get("LR_MAX_WAIT_US", "200")),
             alloc=alloc)
         app.state.batcher = state["batcher"]
+        state["submit"] = state["batcher"].submit
         yield
         state["batcher"].close()
 
@@ -83,9 +101,10 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
         if not all(math.isfinite(v) and abs(v) <= 3.4028234663852886e38 for v in row):
             # sklearn raises ValueError here (SK/linear_model/_base.py:385-389) -> HTTP 500, as in the reference
             raise ValueError("Input X contains NaN or infinity.")
-        label_idx, prob = await state["batcher"].submit(row)
+        label_idx, prob = await state["submit"](row)
         cls = state["classes"][label_idx]
-        return {"prediction": cls.item() if hasattr(cls, "item") else cls, "probability": prob}
+        # same body as the reference's dict return (REF/main.py:24-27), without FastAPI's generic encoder walk
+        return JSONResponse({"prediction": cls.item() if hasattr(cls, "item") else cls, "probability": prob})
 
     @app.post("/files/")
     async def create_file(file: bytes = File(...), token: str = Form(...)):
@@ -114,6 +133,11 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
         if not np.isfinite(X).all():
             raise ValueError("Input X contains NaN or infinity.")
         n = X.shape[0]
+        if "client" in state:                 # front process: the rows travel to the engine as one frame
+            import asyncio
+            res = await asyncio.gather(*[state["submit"](tuple(map(float, r))) for r in X])
+            labels = [state["classes"][li] for li, _ in res]
+            return {"rows": n, "predictions": labels, "probabilities": [p for _, p in res], "token": token}
         fn = state["bulk_fn"]
 
         def score_all():                      # blocking device calls: off the event loop (/predict keeps flowing)
@@ -132,6 +156,14 @@ def create_app(model=None, model_path: Optional[str] = None, devices=None, max_b
 
     @app.get("/batcher_stats")
     async def batcher_stats():
+        if "client" in state:
+            out = {"front": state["client"].stats()}
+            path = os.environ.get("LR_ENGINE_STATS", "")
+            if path and os.path.exists(path):
+                import json
+                with open(path) as fh:
+                    out.update(json.load(fh))
+            return out
         return state["batcher"].stats()
 
     return app

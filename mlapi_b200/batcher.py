@@ -80,6 +80,21 @@ class MicroBatcher:
             raise box["e"]
         return box["v"]
 
+    async def submit_block(self, rows: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        """Queue k rows at once (k <= max_batch; an HTTP front process forwards what it collected in one event-loop
+        turn); resolves to (label indices [k], max probabilities [k]).  A row that scored to a non-finite value
+        carries a NaN probability: the caller fails that request alone."""
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        if rows.ndim != 2 or rows.shape[1] != self.n_features:
+            raise ValueError(f"X has {rows.shape[-1]} features, but LogisticRegression is expecting "
+                             f"{self.n_features} features as input.")
+        if rows.shape[0] > self.max_batch:
+            raise ValueError(f"block of {rows.shape[0]} rows exceeds max_batch {self.max_batch}")
+        loop = asyncio.get_running_loop()
+        fut = loop.create_future()
+        self._put((rows, fut, loop))
+        return await fut
+
     def _put(self, item):
         with self._cv:
             self._dq.append(item)
@@ -95,10 +110,15 @@ class MicroBatcher:
                     return []
                 self._cv.wait(0.05)
             items = [self._dq.popleft()]
+            rows = self._rows_of(items[0])
             deadline = time.perf_counter() + self.max_wait
-            while len(items) < self.max_batch:
+            while rows < self.max_batch:
                 if self._dq:
+                    k = self._rows_of(self._dq[0])
+                    if rows + k > self.max_batch:
+                        break                # a block is never split: it opens the next batch
                     items.append(self._dq.popleft())
+                    rows += k
                     continue
                 remaining = deadline - time.perf_counter()
                 if remaining <= 0 or self._stop.is_set():
@@ -108,25 +128,39 @@ class MicroBatcher:
                 self._cv.notify()            # more work is queued: wake another replica
             return items
 
+    @staticmethod
+    def _rows_of(item) -> int:
+        return item[0].shape[0] if isinstance(item[0], np.ndarray) else 1
+
     def _worker(self, score_fn: ScoreFn):
         stage = self._alloc((self.max_batch, self.n_features), np.float32)
         while True:
             items = self._take_batch()
             if not items:
                 return
-            n = len(items)
+            n = 0
             try:
-                for i, (row, _, _) in enumerate(items):
-                    stage[i] = row
+                spans = []
+                for row, _, _ in items:
+                    k = self._rows_of((row,))
+                    stage[n:n + k] = row
+                    spans.append((n, k, isinstance(row, np.ndarray)))
+                    n += k
                 labels, probs = score_fn(stage, n)
                 # A row that scored to NaN / infinity (sklearn: ValueError, SK/linear_model/_base.py:385-389) fails
                 # alone: the other requests that happened to share its batch get their answers.
-                results = [(int(labels[i]), float(probs[i])) if np.isfinite(probs[i])
-                           else ValueError("Input X contains NaN or infinity (or a value too large for float32).")
-                           for i in range(n)]
+                results = []
+                for lo, k, block in spans:
+                    if block:
+                        results.append((np.array(labels[lo:lo + k], dtype=np.int32), np.array(probs[lo:lo + k], dtype=np.float32)))
+                    elif np.isfinite(probs[lo]):
+                        results.append((int(labels[lo]), float(probs[lo])))
+                    else:
+                        results.append(ValueError("Input X contains NaN or infinity (or a value too large for float32)."))
                 err = None
             except Exception as e:  # noqa: BLE001 - forwarded to every waiter
                 results, err = None, e
+                n = sum(self._rows_of(it) for it in items)
             with self._stats_lock:
                 self.batch_sizes[n] += 1
                 self.requests += n
@@ -165,9 +199,15 @@ class MicroBatcher:
     def stats(self) -> dict:
         sizes = sorted(self.batch_sizes.items())
         total = sum(c for _, c in sizes)
+        # histogram in powers of two: {upper bound: batches}
+        hist = {}
+        for size, count in sizes:
+            ub = 1 << max(0, int(size - 1).bit_length())
+            hist[ub] = hist.get(ub, 0) + count
         return {"requests": self.requests, "batches": total,
                 "mean_batch": (self.requests / total) if total else 0.0,
-                "max_batch_seen": sizes[-1][0] if sizes else 0}
+                "max_batch_seen": sizes[-1][0] if sizes else 0,
+                "batch_size_histogram": {str(k): v for k, v in sorted(hist.items())}}
 
 
 def engine_score_fns(clf) -> List[ScoreFn]:

@@ -1583,7 +1583,7 @@ int gemm_load(Model& m, const double* coef, const double* intercept) {
 }
 
 int gemm_prepare(Model& m, const double* coef, const double* intercept) {
-    if (m.n_scores <= 16 || m.n_scores > kMaxCluster * 2 * BN) return LR_OK;
+    if (m.n_scores < 13 || m.n_scores > kMaxCluster * 2 * BN) return LR_OK;
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
     {
         // The per-call scratch of this path (X scale, flags, log-sum-exp, re-pitched rows) comes from the device's
@@ -1954,7 +1954,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
 }  // namespace
 
 int gemm_launch(const Model& m, const ScoreArgs& a) {
-    if (!gemm_supports(m, a)) return fail(LR_ERR_INVALID, "gemm path needs 17..2048 classes and fewer than 2^31 rows");
+    if (!gemm_supports(m, a)) return fail(LR_ERR_INVALID, "gemm path needs 13..2048 classes and fewer than 2^31 rows");
     GemmPlan* g = m.gemm;
     const int d = m.n_features;
     const bool aligned = d % 4 == 0 && a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;

@@ -267,3 +267,76 @@ def test_overflowing_row_fails_alone_on_gpu(golden):
     assert all(isinstance(r, tuple) and np.isfinite(r[1]) for r in res[:8] + res[9:])
     mb.close()
     clf.close()
+
+
+def test_engine_link_fronts_share_one_batcher(golden, tmp_path):
+    """Two front connections forward rows over the Unix socket to one engine-side MicroBatcher: answers match the
+    oracle, come back to the right request, a non-finite row fails alone, and the engine saw blocks, not rows."""
+    from mlapi_b200.batcher import MicroBatcher
+    from mlapi_b200.engine_link import EngineClient, EngineServer
+    g = golden("iris_model.npz")
+    X = g["X"].astype(np.float32)
+    fn, calls, classes = _oracle_score_fn(golden)
+    sock = str(tmp_path / "e.sock")
+
+    async def main():
+        mb = MicroBatcher([fn], n_features=4, max_batch=64, max_wait_us=5_000)
+        srv = await EngineServer(mb, classes, 4, sock).start()
+        a = await EngineClient(sock).connect()
+        b = await EngineClient(sock).connect()
+        assert a.classes == list(classes) and a.n_features == 4
+        rows = [tuple(map(float, r)) for r in X]
+        res = await asyncio.gather(*[(a if i % 2 else b).submit(r) for i, r in enumerate(rows)])
+        bad = await asyncio.gather(a.submit((float("nan"), 1.0, 1.0, 1.0)), b.submit(rows[0]), return_exceptions=True)
+        with pytest.raises(ValueError, match="expecting 4 features"):
+            await a.submit((1.0, 2.0))
+        stats = (a.stats(), b.stats(), srv.frames)
+        await a.close()
+        await b.close()
+        await srv.close()
+        mb.close()
+        return res, bad, stats
+
+    res, bad, (sa, sb, frames) = asyncio.run(main())
+    assert [r[0] for r in res] == list(orc.predict_index(X, g["coef"], g["intercept"]))
+    np.testing.assert_allclose([r[1] for r in res], orc.max_proba(X, g["coef"], g["intercept"]), rtol=1e-6)
+    assert isinstance(bad[0], ValueError) and bad[1] == res[0]
+    assert sa["rows_sent"] + sb["rows_sent"] == 152 and frames <= 8          # 150 rows travelled in a handful of frames
+    assert max(calls) > 1                                                    # and were scored in shared batches
+
+
+def test_app_as_front_of_an_engine(golden, tmp_path):
+    """The FastAPI app with `engine_socket`: same route, schema and answers, no model in the HTTP process."""
+    import threading as th
+    from fastapi.testclient import TestClient
+    from mlapi_b200.app import create_app
+    from mlapi_b200.batcher import MicroBatcher
+    from mlapi_b200.engine_link import EngineServer
+    fn, calls, classes = _oracle_score_fn(golden)
+    sock = str(tmp_path / "e.sock")
+    ready, stop = th.Event(), th.Event()
+
+    def engine():
+        async def main():
+            mb = MicroBatcher([fn], n_features=4, max_batch=64, max_wait_us=50)
+            srv = await EngineServer(mb, classes, 4, sock).start()
+            ready.set()
+            while not stop.is_set():
+                await asyncio.sleep(0.02)
+            await srv.close()
+            mb.close()
+        asyncio.run(main())
+
+    t = th.Thread(target=engine, daemon=True)
+    t.start()
+    assert ready.wait(10)
+    try:
+        with TestClient(create_app(engine_socket=sock)) as client:
+            _check_against_reference(client)
+            csv = "sepal_width,sepal_length,petal_length,petal_width\n3.5,5.1,1.4,0.2\n2.9,6.0,4.5,1.5\n"
+            r = client.post("/files/predict", files={"file": ("a.csv", csv.encode())}, data={"token": "t"})
+            assert r.json()["predictions"] == ["Iris-setosa", "Iris-versicolor"]
+            assert client.get("/batcher_stats").json()["front"]["rows_sent"] >= 8
+    finally:
+        stop.set()
+        t.join(5)

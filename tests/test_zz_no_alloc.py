@@ -14,6 +14,8 @@ import ctypes as C
 import numpy as np
 import pytest
 
+from oracle import lr_oracle as orc
+
 pytestmark = pytest.mark.gpu
 
 
@@ -62,6 +64,12 @@ def test_static_scratch_entry_point_matches_allocating_one_twice_in_a_row(lib):
         # same tolerance as tests/test_refit_gpu.py, on the per-row means
         np.testing.assert_allclose(got[0] / n, ref[0] / n, rtol=5e-6, atol=1e-7)
         np.testing.assert_allclose(got[1:] / n, ref[1:] / n, rtol=1e-4, atol=3e-6)
+        # and against the float64 restatement of scikit-learn's loss_gradient itself, not only its sibling
+        Wh, bh = W.cpu().numpy().astype(np.float64), b.cpu().numpy().astype(np.float64)
+        loss, gW, gb = orc.loss_gradient(Wh, bh, X.cpu().numpy(), y.cpu().numpy(), 0.0)
+        np.testing.assert_allclose(got[0] / n, loss, rtol=2e-5, atol=1e-6)
+        np.testing.assert_allclose(got[1:1 + rows * d].reshape(rows, d) / n, gW, rtol=1e-4, atol=5e-6)
+        np.testing.assert_allclose(got[1 + rows * d:] / n, gb, rtol=1e-4, atol=5e-6)
     # and the very same call again gives the very same bits (nothing left over changes the result)
     code, again = _call(lib, "lr_loss_grad_static", X, y, W, b)
     assert code == lib.LR_OK and np.array_equal(again, got)

@@ -73,10 +73,56 @@ def client_proc(port, concurrency, seconds, seed, q):
     q.put(lat)
 
 
-def run_load(port, clients, concurrency, seconds):
+def fast_client_proc(port, concurrency, seconds, seed, q):
+    """Raw-socket keep-alive client: pre-built request bytes, just enough HTTP parsing to find the end of the
+    response.  httpx spends ~0.5 ms of client CPU per request, which made the load generator the bottleneck."""
+    rng = np.random.default_rng(seed)
+    reqs = []
+    for a, b, c, d in rng.uniform([4, 2, 1, 0.1], [8, 4.5, 7, 2.5], size=(512, 4)):
+        body = json.dumps(dict(sepal_length=float(a), sepal_width=float(b), petal_length=float(c), petal_width=float(d))).encode()
+        reqs.append(b"POST /predict HTTP/1.1\r\nHost: 127.0.0.1\r\nContent-Type: application/json\r\nContent-Length: "
+                    + str(len(body)).encode() + b"\r\n\r\n" + body)
+    lat = []
+    errors = [0]
+
+    async def worker(t_end, k):
+        reader, writer = await asyncio.open_connection("127.0.0.1", port)
+        i = k
+        while time.perf_counter() < t_end:
+            t0 = time.perf_counter()
+            writer.write(reqs[i % len(reqs)])
+            head = await reader.readuntil(b"\r\n\r\n")
+            n = 0
+            for line in head.split(b"\r\n"):
+                if line[:15].lower() == b"content-length:":
+                    n = int(line[15:])
+            if n:
+                await reader.readexactly(n)
+            if not head.startswith(b"HTTP/1.1 200"):
+                errors[0] += 1
+            lat.append(time.perf_counter() - t0)
+            i += 7
+        writer.close()
+
+    async def main():
+        t_end = time.perf_counter() + seconds
+        await asyncio.gather(*[worker(t_end, k) for k in range(concurrency)])
+
+    try:
+        import uvloop
+        uvloop.install()
+    except ImportError:
+        pass
+    asyncio.run(main())
+    assert errors[0] == 0, f"{errors[0]} non-200 answers"
+    q.put(lat)
+
+
+def run_load(port, clients, concurrency, seconds, fast=False):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=client_proc, args=(port, concurrency, seconds, 100 + i, q)) for i in range(clients)]
+    target = fast_client_proc if fast else client_proc
+    procs = [ctx.Process(target=target, args=(port, concurrency, seconds, 100 + i, q)) for i in range(clients)]
     t0 = time.perf_counter()
     [p.start() for p in procs]
     lats = []
@@ -87,7 +133,7 @@ def run_load(port, clients, concurrency, seconds):
     lat = np.array(lats)
     return {"requests": int(lat.size), "req_per_s": float(lat.size / seconds), "p50_ms": float(np.percentile(lat, 50) * 1e3),
             "p99_ms": float(np.percentile(lat, 99) * 1e3), "mean_ms": float(lat.mean() * 1e3), "wall_s": wall,
-            "clients": clients, "concurrency_per_client": concurrency}
+            "clients": clients, "concurrency_per_client": concurrency, "client": "raw sockets" if fast else "httpx"}
 
 
 def serve(module_app, cwd, env, port, workers=1):
@@ -128,9 +174,16 @@ def main():
     ap.add_argument("--seconds", type=float, default=8.0)
     ap.add_argument("--clients", type=int, default=4)
     ap.add_argument("--concurrency", type=int, default=64)
-    ap.add_argument("--reference", default="")
+    ap.add_argument("--reference", default="", help="path of the unmodified reference main.py (where it exists)")
+    ap.add_argument("--reference-restated", action="store_true",
+                    help="serve tools/ref_handler_app.py: the reference handler's per-request work, restated")
     ap.add_argument("--skip-b200", action="store_true")
     ap.add_argument("--workers", type=int, default=1, help="uvicorn worker processes (the reference's README uses 1)")
+    ap.add_argument("--engine", action="store_true",
+                    help="one scoring engine process + --workers HTTP fronts (mlapi_b200.serve) instead of a model per worker")
+    ap.add_argument("--devices", default="0")
+    ap.add_argument("--fast-client", action="store_true")
+    ap.add_argument("--no-batcher-only", action="store_true")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
 
@@ -141,36 +194,67 @@ def main():
     with open(model_path, "wb") as fh:
         pickle.dump(clf, fh)
     result = {"host_cores": len(os.sched_getaffinity(0)), "seconds": args.seconds}
+    load = lambda port, c, k, s: run_load(port, c, k, s, fast=args.fast_client)  # noqa: E731
 
     if not args.skip_b200:
         port = free_port()
-        env = dict(os.environ, LR_MODEL_PATH=model_path, PYTHONPATH=ROOT)
-        srv = serve("mlapi_b200.app:app", ROOT, env, port, args.workers)
+        procs = []
         try:
-            assert wait_port(port), "B200 app did not start: " + (srv.stderr.read().decode() if srv.poll() is not None else "")
+            if args.engine:
+                from mlapi_b200 import serve as lr_serve
+                engine, fronts, env = lr_serve.start(model_path, args.devices, args.workers, port)
+                procs = [fronts, engine]
+            else:
+                env = dict(os.environ, LR_MODEL_PATH=model_path, LR_DEVICES=args.devices, PYTHONPATH=ROOT)
+                procs = [serve("mlapi_b200.app:app", ROOT, env, port, args.workers)]
+            assert wait_port(port, 300), "B200 app did not start"
             time.sleep(3.0 if args.workers > 1 else 0.5)
-            result["b200_app"] = run_load(port, args.clients, args.concurrency, args.seconds)
-            result["b200_app"]["uvicorn_workers"] = args.workers
+            load(port, 1, 8, 1.0)                                   # every worker has connected / warmed up
             import httpx
-            result["b200_app"]["batcher"] = httpx.get(f"http://127.0.0.1:{port}/batcher_stats").json()
+            before = httpx.get(f"http://127.0.0.1:{port}/batcher_stats").json()
+            result["b200_app"] = load(port, args.clients, args.concurrency, args.seconds)
+            result["b200_app"]["uvicorn_workers"] = args.workers
+            result["b200_app"]["devices"] = args.devices
+            result["b200_app"]["layout"] = ("one engine process (all devices, one micro-batcher) + HTTP front workers"
+                                            if args.engine else "a model and a micro-batcher in every worker")
+            time.sleep(1.5)                                         # the engine rewrites its statistics once a second
+            after = httpx.get(f"http://127.0.0.1:{port}/batcher_stats").json()
+            result["b200_app"]["batcher_before_load"] = before
+            result["b200_app"]["batcher"] = after
+            if "requests" in after and "requests" in before and after.get("batches", 0) > before.get("batches", 0):
+                result["b200_app"]["mean_batch_under_load"] = ((after["requests"] - before["requests"]) /
+                                                               (after["batches"] - before["batches"]))
             # latency at light load: few requests in flight, so queueing does not hide the service time
-            result["b200_app_light_load"] = run_load(port, 2, 4, min(args.seconds, 5.0))
+            result["b200_app_light_load"] = load(port, 2, 4, min(args.seconds, 5.0))
         finally:
-            srv.terminate()
-            srv.wait(timeout=20)
-        result["b200_batcher_only"] = batcher_only(model_path)
+            for p in procs:
+                p.terminate()
+            for p in procs:
+                p.wait(timeout=30)
+        if not args.no_batcher_only:
+            result["b200_batcher_only"] = batcher_only(model_path)
 
+    ref_runs = []
     if args.reference and os.path.exists(args.reference):
         shutil.copy(args.reference, os.path.join(tmp, "main.py"))
+        ref_runs.append(("reference_app", "main:app", tmp,
+                         "unmodified REF/main.py (per-request unpickle, blocking handler), uvicorn 1 worker"))
+    if args.reference_restated:
+        shutil.copy(os.path.join(ROOT, "tools", "ref_handler_app.py"), os.path.join(tmp, "ref_handler_app.py"))
+        ref_runs.append(("reference_restated_app", "ref_handler_app:app", tmp,
+                         "tools/ref_handler_app.py: the per-request work of REF/main.py:16-27 restated (per-request "
+                         "unpickle, predict + predict_proba on the event loop), uvicorn 1 worker"))
+    for key, target, cwd, note in ref_runs:
         port = free_port()
-        srv = serve("main:app", tmp, dict(os.environ), port, args.workers)
+        srv = serve(target, cwd, dict(os.environ), port, 1)
         try:
-            assert wait_port(port), "reference app did not start"
-            time.sleep(3.0 if args.workers > 1 else 0.5)
-            result["reference_app"] = run_load(port, args.clients, args.concurrency, args.seconds)
-            result["reference_app"]["uvicorn_workers"] = args.workers
-            result["reference_app_light_load"] = run_load(port, 2, 4, min(args.seconds, 5.0))
-            result["reference_app"]["note"] = "unmodified REF/main.py (per-request unpickle, blocking handler), uvicorn 1 worker"
+            assert wait_port(port), f"{key} did not start"
+            time.sleep(0.5)
+            load(port, 1, 2, 1.5)                                   # first requests import scikit-learn's estimator code
+            result[key] = load(port, args.clients, args.concurrency, args.seconds)
+            result[key]["uvicorn_workers"] = 1
+            result[key + "_light_load"] = load(port, 2, 4, min(args.seconds, 5.0))
+            result[key]["note"] = note
         finally:
             srv.terminate()
             srv.wait(timeout=20)
