@@ -72,6 +72,7 @@ static int select_path(const Model& m, const ScoreArgs& a) {
         if (m.Wn) return LR_PATH_NARROW;
         return LR_PATH_GENERIC;
     }
+    if (m.n_scores > 1 && gemm_short_rows(m, a)) return LR_PATH_GEMM;
     if (m.Wn) {
         // 13..16 classes on rows of 64 floats and more: the register-tile kernel is issue-bound there (~27 fp32
         // TFLOP/s: 3.4 TB/s at 16 classes), the tensor path's small-N form is not (4.4-5.1 TB/s measured at 32).

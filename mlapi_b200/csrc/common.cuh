@@ -85,6 +85,7 @@ void gemm_destroy(Model& m);
 void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total);
 int gemm_active_layout(const Model& m);
 int gemm_launch(const Model& m, const ScoreArgs& a);
+bool gemm_short_rows(const Model& m, const ScoreArgs& a);   // 13..32 classes, dense rows of <= 64 floats: the short-row tensor form
 
 // ---- device helpers ----------------------------------------------------------------------------
 #ifdef __CUDACC__

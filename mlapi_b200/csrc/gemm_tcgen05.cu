@@ -1255,6 +1255,352 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
     }
 }
 
+// ---- short rows, 13..32 classes -------------------------------------------------------------------
+// Rows of at most 64 floats against at most 32 classes (covertype: d=54, C=7..20; letters: d=16, C=26): one
+// 128-row tile is ONE k-chunk and one tiny MMA group, so the kernel above -- a W ring, an X ring converted in
+// place, one mbarrier round trip per tile and stage -- spends its time on hand-overs (d=16, C=26: 1.1 TB/s),
+// and the fp32 register-tile kernel is issue-bound (27 TFLOP/s: 1.7-1.9 TB/s at 20 classes).  Here W (8 KB as
+// fp16 hi + lo) stays in shared memory for the whole launch, dense rows arrive as plain 1-D bulk copies of whole
+// tiles (any d: no 16-byte row pitch needed), several raw tiles, three operand tiles and eight 32-column
+// accumulators are in flight, and each stage is its own set of warps:
+//   warp 0       bulk-copy producer (raw fp32 tiles, ring of up to 8)
+//   warps 1-4    converters: raw tile -> column balance, scale, fp16 hi / lo halves, K-major 128B-swizzled tiles
+//   warp 5       MMA issuer: 3 x (dk / 16) MMAs of M=128, N=32 per tile into one of 8 TMEM buffers
+//   warps 6-13   epilogue, two sets of four (TMEM lane quadrants) on alternate tiles: one TMEM read, softmax in
+//                registers, outputs, re-scoring flags -- the single-pass form of the kernel above
+// Same arithmetic (3xFP16 split, truncating TMEM accumulation) and the same error band as that kernel; flagged
+// rows are re-scored whole in fp32 (32 classes x 64 features is nothing) by short_fixup_kernel.
+constexpr int kSrConvWarps = 4;
+constexpr int kSrEpiWarps = 8;
+constexpr int kSrThreads = (1 + kSrConvWarps + 1 + kSrEpiWarps) * 32;      // 448
+constexpr int kSrOpStages = 3;
+constexpr int kSrAccBufs = 8;
+constexpr int kSrMaxRaw = 8;
+constexpr int kSrOpBytes = 2 * A_TILE_BYTES;             // hi | lo, 128-byte rows
+struct SrSmem {
+    static constexpr int op = 0;                                         // [kSrOpStages][32 KB]
+    static constexpr int w = op + kSrOpStages * kSrOpBytes;              // W hi 4 KB | lo 4 KB
+    static constexpr int cs = w + 2 * 32 * 128;                          // [64] per-feature scale x call scale
+    static constexpr int bias = cs + 64 * 4;                             // [32]
+    static constexpr int cscale = bias + 32 * 4;                         // [32]
+    static constexpr int bars = cscale + 32 * 4;                         // raw_full/empty[8], op_full/empty[3], acc_full/empty[8], w_full
+    static constexpr int n_bars = 2 * kSrMaxRaw + 2 * kSrOpStages + 2 * kSrAccBufs + 1;
+    static constexpr int tmem_slot = bars + n_bars * 8;
+    static constexpr int raw = (tmem_slot + 16 + 127) / 128 * 128;       // [raw_stages][stage_bytes]
+};
+struct ShortParams {
+    const float* X;
+    int64_t n_rows;
+    int d, dk;                  // features, features rounded up to 16
+    int n_classes;
+    int raw_stages, stage_bytes;
+    const float* bias;
+    const float* col_inv_scale;
+    const float* x_scale;
+    const float* col_scale;
+    float kappa;
+    int count_nonfinite, vec_store;
+    float* proba;
+    float* decision;
+    int32_t* label;
+    float* maxprob;
+    unsigned long long* status;
+    unsigned* flags;
+    unsigned* flag_list;
+    unsigned* n_flagged;
+    float* lse;
+};
+
+__global__ void __launch_bounds__(kSrThreads, 1)
+short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_constant__ CUtensorMap map_wlo,
+                  const ShortParams p) {
+    if (reinterpret_cast<const uint32_t*>(p.x_scale)[4] != 0u) return;        // this call was given to the fp32 fallback
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+    float* cs_s = reinterpret_cast<float*>(smem + SrSmem::cs);
+    float* bias_s = reinterpret_cast<float*>(smem + SrSmem::bias);
+    float* cscale_s = reinterpret_cast<float*>(smem + SrSmem::cscale);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SrSmem::bars);
+    uint64_t* raw_full = bars;
+    uint64_t* raw_empty = raw_full + kSrMaxRaw;
+    uint64_t* op_full = raw_empty + kSrMaxRaw;
+    uint64_t* op_empty = op_full + kSrOpStages;
+    uint64_t* acc_full = op_empty + kSrOpStages;
+    uint64_t* acc_empty = acc_full + kSrAccBufs;
+    uint64_t* w_full = acc_empty + kSrAccBufs;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SrSmem::tmem_slot);
+    unsigned char* raw = smem + SrSmem::raw;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int d = p.d, dk = p.dk;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kSrMaxRaw; ++i) { mbar_init(raw_full + i, 1); mbar_init(raw_empty + i, kSrConvWarps * 32); }
+        for (int i = 0; i < kSrOpStages; ++i) { mbar_init(op_full + i, kSrConvWarps * 32); mbar_init(op_empty + i, 1); }
+        for (int i = 0; i < kSrAccBufs; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 128); }
+        mbar_init(w_full, 1);
+        mbar_fence_init();
+    }
+    if (threadIdx.x < 64) cs_s[threadIdx.x] = threadIdx.x < d ? p.col_scale[threadIdx.x] * p.x_scale[0] : 0.0f;
+    if (threadIdx.x < 32) {
+        bias_s[threadIdx.x] = p.bias[threadIdx.x];
+        cscale_s[threadIdx.x] = p.col_inv_scale[threadIdx.x] * p.x_scale[1];
+    }
+    if (warp == kSrConvWarps + 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int64_t n_tiles = (p.n_rows + BM - 1) / BM;
+    const int64_t tile_floats = (int64_t)BM * d;
+
+    if (warp == 0) {
+        // ===================== producer: W once, then raw tiles =====================
+        const bool leader = elect_one();
+        if (leader) {
+            mbar_expect_tx(w_full, 2 * 32 * 128);
+            tma_load_2d(smem + SrSmem::w, &map_whi, 0, 0, w_full);
+            tma_load_2d(smem + SrSmem::w + 32 * 128, &map_wlo, 0, 0, w_full);
+        }
+        int st = 0;
+        uint32_t ph = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(raw_empty + st, ph ^ 1);
+            if (leader) {
+                const int64_t left = (p.n_rows - tile * BM) * d;                 // floats of X from this tile on
+                // whole 16-byte pieces only; the <= 3 floats a last, ragged tile may have beyond them are read
+                // from global memory by the converters
+                const uint32_t bytes = (uint32_t)((left < tile_floats ? left : tile_floats) * 4) & ~15u;
+                if (bytes) {
+                    mbar_expect_tx(raw_full + st, bytes);
+                    bulk_g2s(raw + (size_t)st * p.stage_bytes, p.X + tile * tile_floats, bytes, raw_full + st);
+                } else {
+                    mbar_arrive(raw_full + st);
+                }
+            }
+            __syncwarp();
+            if (++st == p.raw_stages) { st = 0; ph ^= 1; }
+        }
+    } else if (warp <= kSrConvWarps) {
+        // ===================== converters =====================
+        const int t = threadIdx.x - 32;                          // 0..127
+        const int qpr = dk >> 2;                                 // 4-float pieces per row
+        const int items = BM * qpr / (kSrConvWarps * 32);        // per thread: dk / 4
+        const bool vec = (d & 3) == 0;
+        int st = 0, os = 0;
+        uint32_t ph = 0, oph = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(raw_full + st, ph);
+            mbar_wait(op_empty + os, oph ^ 1);
+            const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
+            unsigned char* dst = smem + SrSmem::op + os * kSrOpBytes;
+            const int64_t left = (p.n_rows - tile * BM) * d;
+            const bool ragged = left < tile_floats;
+            const int n_in_smem = ragged ? (int)(((left * 4) & ~15ll) >> 2) : (int)tile_floats;
+            const int n_valid = ragged ? (int)left : (int)tile_floats;
+            const float* gsrc = p.X + tile * tile_floats;
+            for (int j = 0; j < items; ++j) {
+                const int it = t + kSrConvWarps * 32 * j;
+                const int r = it / qpr, q = it - r * qpr;
+                const int e0 = r * d + 4 * q;                    // first of the four floats in the tile
+                float x[4];
+                if (vec && !ragged) {
+                    const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int e = e0 + i;
+                        x[i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
+                    }
+                }
+                const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
+                uint32_t h0, l0, h1, l1;
+                split_pair(x[0], x[1], cs.x, cs.y, h0, l0);
+                split_pair(x[2], x[3], cs.z, cs.w, h1, l1);
+                const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
+                *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
+                *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
+            }
+            fence_proxy_async();
+            mbar_arrive(op_full + os);
+            mbar_arrive(raw_empty + st);
+            if (++st == p.raw_stages) { st = 0; ph ^= 1; }
+            if (++os == kSrOpStages) { os = 0; oph ^= 1; }
+        }
+    } else if (warp == kSrConvWarps + 1) {
+        // ===================== MMA issuer =====================
+        const bool leader = elect_one();
+        const uint64_t desc0 = make_smem_desc(0);
+        const uint64_t a0 = desc0 | (uint64_t)((smem_u32(smem + SrSmem::op) & 0x3FFFF) >> 4);
+        const uint64_t whi = desc0 | (uint64_t)((smem_u32(smem + SrSmem::w) & 0x3FFFF) >> 4);
+        const uint64_t wlo = whi + (uint64_t)((32 * 128) >> 4);
+        const uint32_t idesc = (kIdesc16 & ~(0x3Fu << 17)) | ((uint32_t)(32 >> 3) << 17);
+        const int ksteps = dk >> 4;
+        mbar_wait(w_full, 0);
+        int os = 0, ab = 0;
+        uint32_t oph = 0, aph = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(op_full + os, oph);
+            mbar_wait(acc_empty + ab, aph ^ 1);
+            tc_fence_after();
+            if (leader) {
+                const uint64_t ahi = a0 + (uint64_t)((os * kSrOpBytes) >> 4);
+                const uint64_t alo = ahi + (uint64_t)(A_TILE_BYTES >> 4);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(ab * 32);
+                for (int k = 0; k < ksteps; ++k) {
+                    tc_mma_f16(d_tmem, ahi + 2 * k, whi + 2 * k, idesc, k > 0 ? 1u : 0u);
+                    tc_mma_f16(d_tmem, alo + 2 * k, whi + 2 * k, idesc, 1u);
+                    tc_mma_f16(d_tmem, ahi + 2 * k, wlo + 2 * k, idesc, 1u);
+                }
+                tc_commit(op_empty + os);
+                tc_commit(acc_full + ab);
+            }
+            __syncwarp();
+            if (++os == kSrOpStages) { os = 0; oph ^= 1; }
+            if (++ab == kSrAccBufs) { ab = 0; aph ^= 1; }
+        }
+    } else {
+        // ===================== epilogue: two sets of four warps on alternate tiles =====================
+        const int ew = warp - (kSrConvWarps + 2);                // 0..7
+        const int set = ew >> 2;
+        const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
+        const int r_in_tile = q * 32 + lane;
+        const float psum_scale = p.x_scale[5];
+        const float floor_err = p.x_scale[6];
+        const int C = p.n_classes;
+        int64_t seq = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
+            if ((seq & 1) != set) continue;
+            const int ab = (int)(seq % kSrAccBufs);
+            mbar_wait(acc_full + ab, (uint32_t)((seq / kSrAccBufs) & 1));
+            tc_fence_after();
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 32), v);
+            tc_fence_before();
+            mbar_arrive(acc_empty + ab);
+            const int64_t row = tile * BM + r_in_tile;
+            const bool live = row < p.n_rows;
+            float gm = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                v[i] = fmaf(v[i], cscale_s[i], bias_s[i]);       // padding carries -inf
+                gm = fmaxf(gm, v[i]);
+            }
+            int garg = 31;
+#pragma unroll
+            for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
+            if (p.decision && live) {
+                float* zr = p.decision + row * C;
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (i < C) __stcs(zr + i, v[i]);
+            }
+            const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
+            const float tau = gm - 2.0f * ez;
+            float gs = 0.0f;
+            int gnear = 0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                gnear += v[i] > tau ? 1 : 0;
+                v[i] = i < C ? ex2((v[i] - gm) * kLog2e) : 0.0f;
+                gs += v[i];
+            }
+            const float inv = __frcp_rn(gs);
+            const float risk_thr = 8e-6f / ez;
+            bool risk = false;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                v[i] *= inv;
+                risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
+            }
+            if (live) {
+                if (p.proba) {
+                    float* pr = p.proba + row * C;
+                    if (p.vec_store) {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4)
+                            if (i < C) __stcs(reinterpret_cast<float4*>(pr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (i < C) __stcs(pr + i, v[i]);
+                    }
+                }
+                if (p.label) __stcs(p.label + row, garg);
+                if (p.maxprob) __stcs(p.maxprob + row, inv);
+                const bool finite_row = finite_f(gm) && finite_f(gs);
+                if (!finite_row) {
+                    if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                    else atomicAdd(p.status, 1ull);
+                } else if (p.flags && (risk || gnear >= 2)) {
+                    flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kSrConvWarps + 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+}
+
+// Flagged rows of the kernel above, re-scored whole in fp32: one warp per row, lane c owns class c.
+__global__ void __launch_bounds__(256)
+short_fixup_kernel(const float* __restrict__ X, int d, int C, const float* __restrict__ W, const float* __restrict__ b,
+                   const unsigned* __restrict__ list, const unsigned* __restrict__ n_list, float* proba, float* decision,
+                   int32_t* label, float* maxprob, unsigned long long* rescored, unsigned long long* status) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned n = *n_list;
+    for (unsigned li = blockIdx.x * 8 + warp; li < n; li += gridDim.x * 8) {
+        const int64_t row = list[li];
+        const float* x = X + row * d;
+        const float x0 = lane < d ? __ldg(x + lane) : 0.0f, x1 = lane + 32 < d ? __ldg(x + lane + 32) : 0.0f;
+        const float* w = W + (int64_t)(lane < C ? lane : 0) * d;
+        float z = 0.0f;
+        for (int k = 0; k < d; ++k) {
+            const float xk = __shfl_sync(0xffffffffu, k < 32 ? x0 : x1, k & 31);
+            z = fmaf(xk, __ldg(w + k), z);
+        }
+        z = lane < C ? z + __ldg(b + lane) : -CUDART_INF_F;
+        float m = z;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+        const unsigned win = __ballot_sync(0xffffffffu, z == m);
+        const float e = lane < C ? expf(z - m) : 0.0f;
+        float ssum = e;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, off);
+        const float inv = __frcp_rn(ssum);
+        if (lane < C) {
+            if (proba) proba[row * C + lane] = e * inv;
+            if (decision) decision[row * C + lane] = z;
+        }
+        if (lane == 0) {
+            if (label) label[row] = __ffs(win) - 1;                     // first index wins
+            if (maxprob) maxprob[row] = inv;
+            atomicAdd(rescored, 1ull);
+            if (!(finite_f(m) && finite_f(ssum))) atomicAdd(status, 1ull);
+        }
+    }
+}
+
+// What scores a short-row call whose dynamic range ruled out 3xFP16: plain fp32, one warp per row (rare; the
+// batch is counted in status[2] like the 3xTF32 fallback of the kernel above).
+__global__ void __launch_bounds__(256)
+short_fallback_kernel(const float* __restrict__ X, int64_t n_rows, int d, int C, const float* __restrict__ W,
+                      const float* __restrict__ b, const float* __restrict__ x_scale, float* proba, float* decision,
+                      int32_t* label, float* maxprob, unsigned long long* status) {
+    if (reinterpret_cast<const uint32_t*>(x_scale)[4] != 1u) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(status + 2, (unsigned long long)n_rows);
+    const int lane = threadIdx.x & 31;
+    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8)
+        score_row_warp(X + row * d, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+}
+
 // Per-call look at the batch (every arithmetic): up to 2048 rows spread over it are read once, each feature
 // multiplied by the model's per-feature power of two (w_colscale_kernel), and per row the largest magnitude and
 // the 2-norm are kept.  From those the last CTA to arrive derives
@@ -1274,6 +1620,7 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
 constexpr int kXScaleBlocks = 128;
 constexpr int kMaxSample = 2048;
 constexpr int kStatBins = 2048;          // float bits >> 20: 8 exponent bits + 3 mantissa bits (12 % steps)
+template <bool VEC>       // VEC: rows are 16-byte aligned and d % 4 == 0 (128-bit loads); else 4-byte loads
 __global__ void __launch_bounds__(256)
 x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, const float* __restrict__ col_scale,
                float w_norm_max, float inv_cscale_max, int force, float* __restrict__ out, float* __restrict__ rowstat) {
@@ -1288,19 +1635,30 @@ x_scale_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, 
     const int64_t step = n_rows / n_s;
     const int lane = threadIdx.x & 31;
     for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < n_s; i += (int64_t)gridDim.x * 8) {
-        const float4* x = reinterpret_cast<const float4*>(X + (i * step) * ldx);     // rows are 16-byte aligned here
-        const float4* c4 = reinterpret_cast<const float4*>(col_scale);
         float mx = 0.0f, ss = 0.0f;
+        if constexpr (VEC) {
+            const float4* x = reinterpret_cast<const float4*>(X + (i * step) * ldx);
+            const float4* c4 = reinterpret_cast<const float4*>(col_scale);
 #pragma unroll 4
-        for (int k = lane; k < d / 4; k += 32) {
-            const float4 v = __ldg(x + k), c = __ldg(c4 + k);
-            const float a[4] = {fabsf(v.x * c.x), fabsf(v.y * c.y), fabsf(v.z * c.z), fabsf(v.w * c.w)};
+            for (int k = lane; k < d / 4; k += 32) {
+                const float4 v = __ldg(x + k), c = __ldg(c4 + k);
+                const float a[4] = {fabsf(v.x * c.x), fabsf(v.y * c.y), fabsf(v.z * c.z), fabsf(v.w * c.w)};
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (a[j] <= 1.0e18f) {            // NaN / inf (and what would overflow the sum of squares) are left out
-                    mx = fmaxf(mx, a[j]);
-                    ss = fmaf(a[j], a[j], ss);
+                for (int j = 0; j < 4; ++j)
+                    if (a[j] <= 1.0e18f) {            // NaN / inf (and what would overflow the sum of squares) are left out
+                        mx = fmaxf(mx, a[j]);
+                        ss = fmaf(a[j], a[j], ss);
+                    }
+            }
+        } else {
+            const float* x = X + (i * step) * ldx;
+            for (int k = lane; k < d; k += 32) {
+                const float a = fabsf(__ldg(x + k) * __ldg(col_scale + k));
+                if (a <= 1.0e18f) {
+                    mx = fmaxf(mx, a);
+                    ss = fmaf(a, a, ss);
                 }
+            }
         }
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) {
@@ -1493,6 +1851,7 @@ struct GemmPlan {
     uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen (lr_score_host holds the staging lock)
     bool configured[64] = {false};
     bool fix_configured[64] = {false};
+    bool short_configured[64] = {false};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
 
@@ -1819,8 +2178,8 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows * sizeof(unsigned), a.stream));
     }
     LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));          // ticket, decisions, [8] = length of the re-scoring list
-    x_scale_kernel<<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
-                                                        g->inv_cscale_max, g->force, x_scale, rowstat);
+    x_scale_kernel<true><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
+                                                              g->inv_cscale_max, g->force, x_scale, rowstat);
     count_launch();
     GemmParams p;
     p.flags = flags;
@@ -1951,12 +2310,98 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     return LR_OK;
 }
 
+// 13..32 classes on dense rows of at most 64 floats: short_rows_kernel (see there).
+bool short_rows_serve(const Model& m, const ScoreArgs& a) {
+    const GemmPlan* g = m.gemm;
+    return g && g->force != 2 && m.n_scores >= 13 && m.n_scores <= 32 && m.n_features <= 64 && a.ldx == m.n_features &&
+           (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0 && a.n_rows >= 4096 && g->has[1] && g->layout[1].mma_n == 32 &&
+           !g->layout[1].pair && !getenv("LRS_NO_SHORT_ROWS");
+}
+
+int short_launch(const Model& m, const ScoreArgs& a) {
+    GemmPlan* g = m.gemm;
+    GemmPlan::Layout& L = g->layout[1];
+    const int d = m.n_features, C = m.n_scores, dev = m.device & 63;
+    const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
+    AsyncScratch scratch;
+    scratch.s = a.stream;
+    const size_t stat_bytes = 2 * kMaxSample * sizeof(float);
+    const size_t row_bytes = fixup ? ((size_t)a.n_rows * sizeof(unsigned) + 255) / 256 * 256 : 0;
+    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + 2 * row_bytes, a.stream));
+    float* x_scale = reinterpret_cast<float*>(scratch.p);
+    float* rowstat = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256);
+    unsigned* flags = nullptr;
+    unsigned* flag_list = nullptr;
+    if (fixup) {
+        flags = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes);
+        flag_list = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + row_bytes);
+        LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows * sizeof(unsigned), a.stream));
+    }
+    LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));
+    if (d % 4 == 0)
+        x_scale_kernel<true><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d, g->col_scale, g->w_norm_max,
+                                                                  g->inv_cscale_max, g->force, x_scale, rowstat);
+    else
+        x_scale_kernel<false><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d, g->col_scale, g->w_norm_max,
+                                                                   g->inv_cscale_max, g->force, x_scale, rowstat);
+    count_launch();
+    ShortParams p;
+    p.X = a.X;
+    p.n_rows = a.n_rows;
+    p.d = d;
+    p.dk = (d + 15) / 16 * 16;
+    p.n_classes = C;
+    p.stage_bytes = (BM * d * 4 + 127) / 128 * 128;
+    const int room = 227 * 1024 - 1024 - SrSmem::raw;
+    p.raw_stages = room / p.stage_bytes < kSrMaxRaw ? room / p.stage_bytes : kSrMaxRaw;
+    p.bias = g->bias;
+    p.col_inv_scale = g->col_inv_scale;
+    p.x_scale = x_scale;
+    p.col_scale = g->col_scale;
+    p.kappa = 2.0e-5f * 384.0f / 1024.0f;            // one accumulator, rows shorter than 384 floats: see gemm_launch_aligned
+    p.count_nonfinite = fixup ? 0 : 1;
+    p.vec_store = (C % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) ? 1 : 0;
+    p.proba = a.proba;
+    p.decision = a.decision;
+    p.label = a.label;
+    p.maxprob = a.maxprob;
+    p.status = m.status;
+    p.flags = flags;
+    p.flag_list = flag_list;
+    p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
+    p.lse = nullptr;
+    const size_t smem = (size_t)SrSmem::raw + (size_t)p.raw_stages * p.stage_bytes + 1024;
+    if (!g->short_configured[dev]) {
+        LRS_CUDA(cudaFuncSetAttribute(short_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        g->short_configured[dev] = true;
+    }
+    const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
+    const int grid = (int)(n_tiles < m.num_sms ? n_tiles : m.num_sms);
+    short_rows_kernel<<<grid, kSrThreads, smem, a.stream>>>(L.map_w16hi, L.map_w16lo, p);
+    count_launch();
+    if (g->force == 0) {
+        short_fallback_kernel<<<m.num_sms * 8, 256, 0, a.stream>>>(a.X, a.n_rows, d, C, m.W, m.b, x_scale, a.proba,
+                                                                   a.decision, a.label, a.maxprob, m.status);
+        count_launch();
+    }
+    if (fixup) {
+        short_fixup_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, d, C, m.W, m.b, flag_list, p.n_flagged, a.proba,
+                                                                a.decision, a.label, a.maxprob, m.status + 1, m.status);
+        count_launch();
+    }
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
+}
+
 }  // namespace
+
+bool gemm_short_rows(const Model& m, const ScoreArgs& a) { return short_rows_serve(m, a); }
 
 int gemm_launch(const Model& m, const ScoreArgs& a) {
     if (!gemm_supports(m, a)) return fail(LR_ERR_INVALID, "gemm path needs 13..2048 classes and fewer than 2^31 rows");
     GemmPlan* g = m.gemm;
     const int d = m.n_features;
+    if (short_rows_serve(m, a)) return short_launch(m, a);
     const bool aligned = d % 4 == 0 && a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
     if (aligned) return gemm_launch_aligned(m, a, d, m.W);
     // Odd feature counts, odd pitches, unaligned bases: TMA cannot address those rows.  They are copied in

@@ -359,3 +359,63 @@ def test_gemm_range_guard_falls_back_to_tf32(eng):
     clf.score_rows(synth.make_X(4096, d, 44), proba=True)
     assert clf.take_fallback() == 0
     clf.close()
+
+
+# ---- short rows: 13..32 classes on dense rows of at most 64 floats -----------------------------------
+@pytest.mark.parametrize("d,c", [(16, 26), (32, 20), (54, 20), (64, 32), (20, 13), (3, 17), (61, 31), (48, 16)])
+def test_short_rows_tensor_form(eng, d, c):
+    """The short-row kernel (W resident in shared memory, 1-D bulk copies of whole tiles, eight accumulators in
+    flight): aligned and unaligned row lengths, ragged last tiles, unstandardised features, an outlier row."""
+    import ctypes as C
+    import torch
+    mlapi, lib = eng
+    L = lib.load()
+    rng = np.random.default_rng(900 + d + c)
+    W0, b = synth.make_model(d, c, 900 + c)
+    s = 10.0 ** rng.uniform(-2, 3, d)
+    W = W0 / s
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    for n in (4096, 4097, 50_003):
+        X = (rng.standard_normal((n, d)) * s).astype(np.float32)
+        X[n // 2, d // 2] = 3e4 * s[d // 2]                 # overflows the fp16 scale: that row is re-scored in fp32
+        Xt = torch.from_numpy(X).cuda()
+        path = C.c_int32(0)
+        lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d, C.byref(path)))
+        assert path.value == lib.PATH_GEMM
+        z = orc.decision_function(X, W, b)
+        P = orc.softmax(z)
+        idx = z.argmax(1)
+        out = clf.score_rows(Xt, **ALL)
+        torch.cuda.synchronize()
+        host = {k: v.cpu().numpy() for k, v in out.items()}
+        # the outlier row's logits are ~1e3: fp32 re-scoring leaves ~1e-4 on them
+        parity.assert_parity(host, z, P, idx, f"short rows d={d} C={c} n={n}", z_atol=3e-4)
+        out2 = clf.score_rows(Xt, label=True, maxprob=True)
+        torch.cuda.synchronize()
+        parity.assert_parity({k: v.cpu().numpy() for k, v in out2.items() if v is not None}, z, P, idx,
+                             f"short rows d={d} C={c} n={n} (label+maxprob)")
+    assert clf.take_fallback() == 0 and clf.take_rescored() >= 6 and clf.take_nonfinite() == 0
+    Xb = torch.from_numpy(rng.standard_normal((5000, d)).astype(np.float32)).cuda()
+    Xb[17, 0] = float("nan")
+    clf.score_rows(Xb, proba=True)
+    assert clf.take_nonfinite() == 1
+    clf.close()
+
+
+def test_short_rows_range_guard_falls_back_to_fp32(eng):
+    import torch
+    mlapi, lib = eng
+    d, c, n = 32, 20, 20_000
+    W, b = synth.make_model(d, c, 77)
+    X = synth.make_X(n, d, 78)
+    big = np.zeros(n, bool)
+    big[::50] = True
+    X[big] *= 3000.0
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    out = clf.score_rows(torch.from_numpy(X).cuda(), **ALL)
+    torch.cuda.synchronize()
+    host = {k: v.cpu().numpy()[~big] for k, v in out.items()}
+    z = orc.decision_function(X[~big], W, b)
+    parity.assert_parity(host, z, orc.softmax(z), z.argmax(1), "short rows, fp32 fallback")
+    assert clf.take_fallback() == n
+    clf.close()
