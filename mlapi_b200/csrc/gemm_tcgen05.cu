@@ -1270,20 +1270,22 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
 //                registers, outputs, re-scoring flags -- the single-pass form of the kernel above
 // Same arithmetic (3xFP16 split, truncating TMEM accumulation) and the same error band as that kernel; flagged
 // rows are re-scored whole in fp32 (32 classes x 64 features is nothing) by short_fixup_kernel.
-constexpr int kSrConvWarps = 4;
-constexpr int kSrEpiWarps = 8;
-constexpr int kSrThreads = (1 + kSrConvWarps + 1 + kSrEpiWarps) * 32;      // 448
-constexpr int kSrOpStages = 3;
+constexpr int kSrConvWarps = 8;                          // two sets of four on alternate tiles
+constexpr int kSrEpiWarps = 8;                           // likewise
+constexpr int kSrThreads = (1 + kSrConvWarps + 1 + kSrEpiWarps) * 32;      // 576
+constexpr int kSrOpStages = 2;                           // operand tile of converter set s = stage s
 constexpr int kSrAccBufs = 8;
 constexpr int kSrMaxRaw = 8;
 constexpr int kSrOpBytes = 2 * A_TILE_BYTES;             // hi | lo, 128-byte rows
+constexpr int kSrOutPitch = 33;                          // floats per staged output row (odd: conflict-free columns)
 struct SrSmem {
     static constexpr int op = 0;                                         // [kSrOpStages][32 KB]
     static constexpr int w = op + kSrOpStages * kSrOpBytes;              // W hi 4 KB | lo 4 KB
     static constexpr int cs = w + 2 * 32 * 128;                          // [64] per-feature scale x call scale
     static constexpr int bias = cs + 64 * 4;                             // [32]
     static constexpr int cscale = bias + 32 * 4;                         // [32]
-    static constexpr int bars = cscale + 32 * 4;                         // raw_full/empty[8], op_full/empty[3], acc_full/empty[8], w_full
+    static constexpr int out = cscale + 32 * 4;                          // [kSrEpiWarps][32 rows][kSrOutPitch] floats
+    static constexpr int bars = out + kSrEpiWarps * 32 * kSrOutPitch * 4;   // raw_full/empty[8], op_full/empty[2], acc_full/empty[8], w_full
     static constexpr int n_bars = 2 * kSrMaxRaw + 2 * kSrOpStages + 2 * kSrAccBufs + 1;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int raw = (tmem_slot + 16 + 127) / 128 * 128;       // [raw_stages][stage_bytes]
@@ -1291,7 +1293,7 @@ struct SrSmem {
 struct ShortParams {
     const float* X;
     int64_t n_rows;
-    int d, dk;                  // features, features rounded up to 16
+    int d;                      // features (dk = features rounded up to 16 is the kernel's template argument)
     int n_classes;
     int raw_stages, stage_bytes;
     const float* bias;
@@ -1308,9 +1310,51 @@ struct ShortParams {
     unsigned* flags;
     unsigned* flag_list;
     unsigned* n_flagged;
-    float* lse;
 };
 
+// A warp's 32 rows x C values, one row per lane in registers, to their place in an [n][C] matrix: staged in
+// shared memory (row pitch 33 floats) and written out as the one contiguous span they are, 512 bytes per
+// instruction.  (Each lane storing its own row put 32 different cache lines under every store instruction.)
+__device__ __forceinline__ void store_rows_coalesced(float* __restrict__ stage, const float (&v)[32], int C, int lane,
+                                                     float* __restrict__ dst /* first row of the warp */, int rows_valid,
+                                                     bool aligned16) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+        if (i < C) stage[lane * kSrOutPitch + i] = v[i];
+    __syncwarp();
+    const int total = rows_valid * C;
+    if (aligned16 && rows_valid == 32) {
+        const int q128 = 128 / C, r128 = 128 - q128 * C;
+        int e = lane * 4;
+        int r = e / C, c = e - r * C;
+        for (; e < total; e += 128) {
+            float o[4];
+            int rr = r, cc = c;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                o[i] = stage[rr * kSrOutPitch + cc];
+                if (++cc == C) { cc = 0; ++rr; }
+            }
+            __stcs(reinterpret_cast<float4*>(dst + e), make_float4(o[0], o[1], o[2], o[3]));
+            r += q128;
+            c += r128;
+            if (c >= C) { c -= C; ++r; }
+        }
+    } else {
+        int r = lane / C, c = lane - r * C;
+        const int q32 = 32 / C, r32 = 32 - q32 * C;
+        for (int e = lane; e < total; e += 32) {
+            __stcs(dst + e, stage[r * kSrOutPitch + c]);
+            r += q32;
+            c += r32;
+            if (c >= C) { c -= C; ++r; }
+        }
+    }
+    __syncwarp();
+}
+
+// DK = features rounded up to 16 (the K extent of a tile); VEC: d % 4 == 0, rows of a raw tile are 16-byte aligned
+template <int DK, bool VEC>
 __global__ void __launch_bounds__(kSrThreads, 1)
 short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_constant__ CUtensorMap map_wlo,
                   const ShortParams p) {
@@ -1331,11 +1375,12 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SrSmem::tmem_slot);
     unsigned char* raw = smem + SrSmem::raw;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int d = p.d, dk = p.dk;
+    const int d = p.d;
+    constexpr int kMmaWarp = 1 + kSrConvWarps;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kSrMaxRaw; ++i) { mbar_init(raw_full + i, 1); mbar_init(raw_empty + i, kSrConvWarps * 32); }
-        for (int i = 0; i < kSrOpStages; ++i) { mbar_init(op_full + i, kSrConvWarps * 32); mbar_init(op_empty + i, 1); }
+        for (int i = 0; i < kSrMaxRaw; ++i) { mbar_init(raw_full + i, 1); mbar_init(raw_empty + i, 128); }
+        for (int i = 0; i < kSrOpStages; ++i) { mbar_init(op_full + i, 128); mbar_init(op_empty + i, 1); }
         for (int i = 0; i < kSrAccBufs; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 128); }
         mbar_init(w_full, 1);
         mbar_fence_init();
@@ -1345,7 +1390,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         bias_s[threadIdx.x] = p.bias[threadIdx.x];
         cscale_s[threadIdx.x] = p.col_inv_scale[threadIdx.x] * p.x_scale[1];
     }
-    if (warp == kSrConvWarps + 1) {
+    if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -1384,54 +1429,73 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             __syncwarp();
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
         }
-    } else if (warp <= kSrConvWarps) {
-        // ===================== converters =====================
-        const int t = threadIdx.x - 32;                          // 0..127
-        const int qpr = dk >> 2;                                 // 4-float pieces per row
-        const int items = BM * qpr / (kSrConvWarps * 32);        // per thread: dk / 4
-        const bool vec = (d & 3) == 0;
-        int st = 0, os = 0;
-        uint32_t ph = 0, oph = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            mbar_wait(raw_full + st, ph);
-            mbar_wait(op_empty + os, oph ^ 1);
-            const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
-            unsigned char* dst = smem + SrSmem::op + os * kSrOpBytes;
-            const int64_t left = (p.n_rows - tile * BM) * d;
-            const bool ragged = left < tile_floats;
-            const int n_in_smem = ragged ? (int)(((left * 4) & ~15ll) >> 2) : (int)tile_floats;
-            const int n_valid = ragged ? (int)left : (int)tile_floats;
-            const float* gsrc = p.X + tile * tile_floats;
-            for (int j = 0; j < items; ++j) {
-                const int it = t + kSrConvWarps * 32 * j;
-                const int r = it / qpr, q = it - r * qpr;
-                const int e0 = r * d + 4 * q;                    // first of the four floats in the tile
-                float x[4];
-                if (vec && !ragged) {
-                    const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
-                } else {
+    } else if (warp < kMmaWarp) {
+        // ===================== converters: two sets of four warps on alternate tiles =====================
+        const int set = (warp - 1) >> 2;
+        const int t = (threadIdx.x - 32) & 127;                  // 0..127 inside the set
+        constexpr int QPR = DK / 4;                              // 4-float pieces per row
+        constexpr int ITEMS = QPR;                               // per thread: 128 rows x QPR pieces / 128 threads
+        int st = 0;
+        uint32_t ph = 0;
+        int64_t seq = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
+            const bool mine = (seq & 1) == set;
+            if (mine) {
+                mbar_wait(raw_full + st, ph);
+                mbar_wait(op_empty + set, (uint32_t)(((seq >> 1) & 1) ^ 1));
+                const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
+                unsigned char* dst = smem + SrSmem::op + set * kSrOpBytes;
+                const int64_t left = (p.n_rows - tile * BM) * d;
+                const bool ragged = left < tile_floats;
+                float x[ITEMS][4];
+                if (!ragged) {
+                    // all the loads of the tile first, then the arithmetic
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int e = e0 + i;
-                        x[i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
+                    for (int j = 0; j < ITEMS; ++j) {
+                        const int it = t + 128 * j;
+                        const int r = it / QPR, q = it % QPR;
+                        const int e0 = r * d + 4 * q;
+                        if constexpr (VEC) {
+                            const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) x[j][i] = 4 * q + i < d ? src[e0 + i] : 0.0f;
+                        }
+                    }
+                } else {
+                    const int n_in_smem = (int)(((left * 4) & ~15ll) >> 2), n_valid = (int)left;
+                    const float* gsrc = p.X + tile * tile_floats;
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) {
+                        const int it = t + 128 * j;
+                        const int r = it / QPR, q = it % QPR;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int e = r * d + 4 * q + i;
+                            x[j][i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
+                        }
                     }
                 }
-                const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
-                uint32_t h0, l0, h1, l1;
-                split_pair(x[0], x[1], cs.x, cs.y, h0, l0);
-                split_pair(x[2], x[3], cs.z, cs.w, h1, l1);
-                const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
-                *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
-                *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    const int it = t + 128 * j;
+                    const int r = it / QPR, q = it % QPR;
+                    const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
+                    uint32_t h0, l0, h1, l1;
+                    split_pair(x[j][0], x[j][1], cs.x, cs.y, h0, l0);
+                    split_pair(x[j][2], x[j][3], cs.z, cs.w, h1, l1);
+                    const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
+                    *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
+                    *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
+                }
+                fence_proxy_async();
+                mbar_arrive(op_full + set);
+                mbar_arrive(raw_empty + st);
             }
-            fence_proxy_async();
-            mbar_arrive(op_full + os);
-            mbar_arrive(raw_empty + st);
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
-            if (++os == kSrOpStages) { os = 0; oph ^= 1; }
         }
-    } else if (warp == kSrConvWarps + 1) {
+    } else if (warp == kMmaWarp) {
         // ===================== MMA issuer =====================
         const bool leader = elect_one();
         const uint64_t desc0 = make_smem_desc(0);
@@ -1439,19 +1503,21 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         const uint64_t whi = desc0 | (uint64_t)((smem_u32(smem + SrSmem::w) & 0x3FFFF) >> 4);
         const uint64_t wlo = whi + (uint64_t)((32 * 128) >> 4);
         const uint32_t idesc = (kIdesc16 & ~(0x3Fu << 17)) | ((uint32_t)(32 >> 3) << 17);
-        const int ksteps = dk >> 4;
         mbar_wait(w_full, 0);
-        int os = 0, ab = 0;
-        uint32_t oph = 0, aph = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            mbar_wait(op_full + os, oph);
+        int ab = 0;
+        uint32_t aph = 0;
+        int64_t seq = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
+            const int os = (int)(seq & 1);
+            mbar_wait(op_full + os, (uint32_t)((seq >> 1) & 1));
             mbar_wait(acc_empty + ab, aph ^ 1);
             tc_fence_after();
             if (leader) {
                 const uint64_t ahi = a0 + (uint64_t)((os * kSrOpBytes) >> 4);
                 const uint64_t alo = ahi + (uint64_t)(A_TILE_BYTES >> 4);
                 const uint32_t d_tmem = tmem_base + (uint32_t)(ab * 32);
-                for (int k = 0; k < ksteps; ++k) {
+#pragma unroll
+                for (int k = 0; k < DK / 16; ++k) {
                     tc_mma_f16(d_tmem, ahi + 2 * k, whi + 2 * k, idesc, k > 0 ? 1u : 0u);
                     tc_mma_f16(d_tmem, alo + 2 * k, whi + 2 * k, idesc, 1u);
                     tc_mma_f16(d_tmem, ahi + 2 * k, wlo + 2 * k, idesc, 1u);
@@ -1460,18 +1526,19 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
                 tc_commit(acc_full + ab);
             }
             __syncwarp();
-            if (++os == kSrOpStages) { os = 0; oph ^= 1; }
             if (++ab == kSrAccBufs) { ab = 0; aph ^= 1; }
         }
     } else {
         // ===================== epilogue: two sets of four warps on alternate tiles =====================
-        const int ew = warp - (kSrConvWarps + 2);                // 0..7
+        const int ew = warp - (kMmaWarp + 1);                    // 0..7
         const int set = ew >> 2;
         const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
         const int r_in_tile = q * 32 + lane;
+        float* stage = reinterpret_cast<float*>(smem + SrSmem::out) + ew * 32 * kSrOutPitch;
         const float psum_scale = p.x_scale[5];
         const float floor_err = p.x_scale[6];
         const int C = p.n_classes;
+        const bool p_al = (reinterpret_cast<uintptr_t>(p.proba) & 15u) == 0, z_al = (reinterpret_cast<uintptr_t>(p.decision) & 15u) == 0;
         int64_t seq = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
             if ((seq & 1) != set) continue;
@@ -1482,8 +1549,10 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 32), v);
             tc_fence_before();
             mbar_arrive(acc_empty + ab);
-            const int64_t row = tile * BM + r_in_tile;
+            const int64_t row0 = tile * BM + q * 32;             // first row of this warp
+            const int64_t row = row0 + lane;
             const bool live = row < p.n_rows;
+            const int rows_valid = (int)(p.n_rows - row0 >= 32 ? 32 : (p.n_rows - row0 > 0 ? p.n_rows - row0 : 0));
             float gm = -INFINITY;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
@@ -1493,12 +1562,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             int garg = 31;
 #pragma unroll
             for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
-            if (p.decision && live) {
-                float* zr = p.decision + row * C;
-#pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (i < C) __stcs(zr + i, v[i]);
-            }
+            if (p.decision) store_rows_coalesced(stage, v, C, lane, p.decision + row0 * C, rows_valid, z_al);
             const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
             const float tau = gm - 2.0f * ez;
             float gs = 0.0f;
@@ -1517,19 +1581,8 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
                 v[i] *= inv;
                 risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
             }
+            if (p.proba) store_rows_coalesced(stage, v, C, lane, p.proba + row0 * C, rows_valid, p_al);
             if (live) {
-                if (p.proba) {
-                    float* pr = p.proba + row * C;
-                    if (p.vec_store) {
-#pragma unroll
-                        for (int i = 0; i < 32; i += 4)
-                            if (i < C) __stcs(reinterpret_cast<float4*>(pr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (i < C) __stcs(pr + i, v[i]);
-                    }
-                }
                 if (p.label) __stcs(p.label + row, garg);
                 if (p.maxprob) __stcs(p.maxprob + row, inv);
                 const bool finite_row = finite_f(gm) && finite_f(gs);
@@ -1544,7 +1597,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kSrConvWarps + 1)
+    if (warp == kMmaWarp)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
 }
 
@@ -1851,7 +1904,6 @@ struct GemmPlan {
     uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen (lr_score_host holds the staging lock)
     bool configured[64] = {false};
     bool fix_configured[64] = {false};
-    bool short_configured[64] = {false};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
 };
 
@@ -2321,7 +2373,7 @@ bool short_rows_serve(const Model& m, const ScoreArgs& a) {
 int short_launch(const Model& m, const ScoreArgs& a) {
     GemmPlan* g = m.gemm;
     GemmPlan::Layout& L = g->layout[1];
-    const int d = m.n_features, C = m.n_scores, dev = m.device & 63;
+    const int d = m.n_features, C = m.n_scores;
     const bool fixup = g->fixup && (a.label || a.maxprob || a.proba || a.decision);
     AsyncScratch scratch;
     scratch.s = a.stream;
@@ -2349,7 +2401,6 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.X = a.X;
     p.n_rows = a.n_rows;
     p.d = d;
-    p.dk = (d + 15) / 16 * 16;
     p.n_classes = C;
     p.stage_bytes = (BM * d * 4 + 127) / 128 * 128;
     const int room = 227 * 1024 - 1024 - SrSmem::raw;
@@ -2360,7 +2411,7 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.col_scale = g->col_scale;
     p.kappa = 2.0e-5f * 384.0f / 1024.0f;            // one accumulator, rows shorter than 384 floats: see gemm_launch_aligned
     p.count_nonfinite = fixup ? 0 : 1;
-    p.vec_store = (C % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) ? 1 : 0;
+    p.vec_store = 0;
     p.proba = a.proba;
     p.decision = a.decision;
     p.label = a.label;
@@ -2369,15 +2420,23 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.flags = flags;
     p.flag_list = flag_list;
     p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
-    p.lse = nullptr;
     const size_t smem = (size_t)SrSmem::raw + (size_t)p.raw_stages * p.stage_bytes + 1024;
-    if (!g->short_configured[dev]) {
-        LRS_CUDA(cudaFuncSetAttribute(short_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        g->short_configured[dev] = true;
-    }
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
     const int grid = (int)(n_tiles < m.num_sms ? n_tiles : m.num_sms);
-    short_rows_kernel<<<grid, kSrThreads, smem, a.stream>>>(L.map_w16hi, L.map_w16lo, p);
+    const bool vec = d % 4 == 0;
+    auto launch = [&](auto kern) -> int {
+        LRS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        kern<<<grid, kSrThreads, smem, a.stream>>>(L.map_w16hi, L.map_w16lo, p);
+        return LR_OK;
+    };
+    int rc;
+    switch ((d + 15) / 16) {
+        case 1: rc = vec ? launch(short_rows_kernel<16, true>) : launch(short_rows_kernel<16, false>); break;
+        case 2: rc = vec ? launch(short_rows_kernel<32, true>) : launch(short_rows_kernel<32, false>); break;
+        case 3: rc = vec ? launch(short_rows_kernel<48, true>) : launch(short_rows_kernel<48, false>); break;
+        default: rc = vec ? launch(short_rows_kernel<64, true>) : launch(short_rows_kernel<64, false>); break;
+    }
+    if (rc != LR_OK) return rc;
     count_launch();
     if (g->force == 0) {
         short_fallback_kernel<<<m.num_sms * 8, 256, 0, a.stream>>>(a.X, a.n_rows, d, C, m.W, m.b, x_scale, a.proba,
