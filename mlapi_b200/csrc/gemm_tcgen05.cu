@@ -797,13 +797,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     }
                     const float inv = __frcp_rn(gs);
                     const float risk_thr = 8e-6f / ez;
-                    bool risk = false;
                     if (p.proba) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            v[i] *= inv;
-                            risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
-                        }
+                        for (int i = 0; i < 32; ++i) v[i] *= inv;
                         if (live) {
                             float* pr = p.proba + row * p.n_classes;
                             if (n_real == 32 && p.vec_store == 2) {
@@ -832,7 +828,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         }
                         if (p.flags) {
                             p.lse[row] = gm + logf(gs);
-                            if (finite_row && (risk || gnear >= 2 || inv * (1.0f - inv) > risk_thr))
+                            if (finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
                                 flag_row(p.flags, p.flag_list, p.n_flagged, row);
                         }
                     }
@@ -976,7 +972,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const float risk_thr = 8e-6f / ez;
             const float near_thr = inv * ex2(-2.0f * ez * kLog2e);   // z > max - 2 ez, as a probability
             int near = 0;
-            bool risk = false;
             const bool want_rows = p.proba != nullptr;
 #define LRS_PASS2_CHUNK(v, cb)                                                                         \
             do {                                                                                       \
@@ -984,7 +979,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
                     (v)[i] *= fj;                                                                      \
                     near += (v)[i] > near_thr ? 1 : 0;                                                 \
-                    risk = risk || ((v)[i] * (1.0f - (v)[i]) > risk_thr);                              \
                 }                                                                                      \
                 if (p.proba && live) {                                                                 \
                     const int64_t off = row * p.n_classes + col0 + (cb);                               \
@@ -1026,7 +1020,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             if (live) {
                 // the thread whose columns hold the maximum always counts it; anything else above tau is a near-tie
                 const bool owner = garg >= col0 + cb_lo && garg < col0 + cb_hi;
-                if (p.flags && (risk || near >= (owner ? 2 : 1))) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                if (p.flags && near >= (owner ? 2 : 1)) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                 if (rank == 0 && h == 0) {
                     if (p.label) __stcs(p.label + row, garg);
                     if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
@@ -1039,7 +1033,8 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     }
                     if (p.flags) {
                         p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
-                        // a top probability the error could move
+                        // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, which is always the top
+                        // one (p (1 - p) rises up to 1/2 and no class but the top one can pass it): p_top = inv
                         if (finite_row && inv * (1.0f - inv) > risk_thr) flag_row(p.flags, p.flag_list, p.n_flagged, row);
                     }
                 }
@@ -1270,25 +1265,24 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
 //                registers, outputs, re-scoring flags -- the single-pass form of the kernel above
 // Same arithmetic (3xFP16 split, truncating TMEM accumulation) and the same error band as that kernel; flagged
 // rows are re-scored whole in fp32 (32 classes x 64 features is nothing) by short_fixup_kernel.
-constexpr int kSrConvWarps = 8;                          // two sets of four on alternate tiles
-constexpr int kSrEpiWarps = 8;                           // likewise
+constexpr int kSrConvWarps = 4;
+constexpr int kSrEpiSets = 3;                            // the epilogue is the long stage: three sets of four warps
+constexpr int kSrEpiWarps = 4 * kSrEpiSets;              // (TMEM lane quadrants) take the tiles in turn
 constexpr int kSrThreads = (1 + kSrConvWarps + 1 + kSrEpiWarps) * 32;      // 576
-constexpr int kSrOpStages = 2;                           // operand tile of converter set s = stage s
+constexpr int kSrMaxOpStages = 4;                        // operand tiles in flight: 2 or 4 (runtime: shared memory)
 constexpr int kSrAccBufs = 8;
 constexpr int kSrMaxRaw = 8;
 constexpr int kSrOpBytes = 2 * A_TILE_BYTES;             // hi | lo, 128-byte rows
-constexpr int kSrOutPitch = 33;                          // floats per staged output row (odd: conflict-free columns)
 struct SrSmem {
-    static constexpr int op = 0;                                         // [kSrOpStages][32 KB]
-    static constexpr int w = op + kSrOpStages * kSrOpBytes;              // W hi 4 KB | lo 4 KB
+    static constexpr int w = 0;                                          // W hi 4 KB | lo 4 KB
     static constexpr int cs = w + 2 * 32 * 128;                          // [64] per-feature scale x call scale
     static constexpr int bias = cs + 64 * 4;                             // [32]
     static constexpr int cscale = bias + 32 * 4;                         // [32]
-    static constexpr int out = cscale + 32 * 4;                          // [kSrEpiWarps][32 rows][kSrOutPitch] floats
-    static constexpr int bars = out + kSrEpiWarps * 32 * kSrOutPitch * 4;   // raw_full/empty[8], op_full/empty[2], acc_full/empty[8], w_full
-    static constexpr int n_bars = 2 * kSrMaxRaw + 2 * kSrOpStages + 2 * kSrAccBufs + 1;
+    static constexpr int out = cscale + 32 * 4;                          // [kSrEpiWarps][32 rows x 32] floats
+    static constexpr int bars = out + kSrEpiWarps * 32 * 32 * 4;         // raw_full/empty[8], op_full/empty[4], acc_full/empty[8], w_full
+    static constexpr int n_bars = 2 * kSrMaxRaw + 2 * kSrMaxOpStages + 2 * kSrAccBufs + 1;
     static constexpr int tmem_slot = bars + n_bars * 8;
-    static constexpr int raw = (tmem_slot + 16 + 127) / 128 * 128;       // [raw_stages][stage_bytes]
+    static constexpr int op = (tmem_slot + 16 + 1023) / 1024 * 1024;     // [op_stages][32 KB], then [raw_stages][stage_bytes]
 };
 struct ShortParams {
     const float* X;
@@ -1296,6 +1290,7 @@ struct ShortParams {
     int d;                      // features (dk = features rounded up to 16 is the kernel's template argument)
     int n_classes;
     int raw_stages, stage_bytes;
+    int op_stages;              // 2 or 4 operand tiles per CTA
     const float* bias;
     const float* col_inv_scale;
     const float* x_scale;
@@ -1313,41 +1308,41 @@ struct ShortParams {
 };
 
 // A warp's 32 rows x C values, one row per lane in registers, to their place in an [n][C] matrix: staged in
-// shared memory (row pitch 33 floats) and written out as the one contiguous span they are, 512 bytes per
-// instruction.  (Each lane storing its own row put 32 different cache lines under every store instruction.)
+// shared memory exactly as they will lie in global memory (row pitch C) and written out as the one contiguous
+// span they are, 512 bytes per instruction.  (Each lane storing its own row put 32 different cache lines
+// under every store instruction.)  With C a multiple of 4 the rows go in as 16-byte pieces whose position is
+// XOR-swizzled by the piece's 128-byte line, so that neither the row-wise writes nor the span-wise reads
+// collide on banks; other C are written word by word (at most 2-way conflicts).
 __device__ __forceinline__ void store_rows_coalesced(float* __restrict__ stage, const float (&v)[32], int C, int lane,
                                                      float* __restrict__ dst /* first row of the warp */, int rows_valid,
                                                      bool aligned16) {
+    const bool quads = (C & 3) == 0;
+    if (quads) {
+        const int u0 = lane * (C >> 2);
 #pragma unroll
-    for (int i = 0; i < 32; ++i)
-        if (i < C) stage[lane * kSrOutPitch + i] = v[i];
+        for (int j = 0; j < 8; ++j)
+            if (4 * j < C) {
+                const int u = u0 + j;
+                *reinterpret_cast<float4*>(stage + 4 * (u ^ ((u >> 3) & 7))) =
+                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            if (i < C) stage[lane * C + i] = v[i];
+    }
     __syncwarp();
     const int total = rows_valid * C;
     if (aligned16 && rows_valid == 32) {
-        const int q128 = 128 / C, r128 = 128 - q128 * C;
-        int e = lane * 4;
-        int r = e / C, c = e - r * C;
-        for (; e < total; e += 128) {
-            float o[4];
-            int rr = r, cc = c;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                o[i] = stage[rr * kSrOutPitch + cc];
-                if (++cc == C) { cc = 0; ++rr; }
-            }
-            __stcs(reinterpret_cast<float4*>(dst + e), make_float4(o[0], o[1], o[2], o[3]));
-            r += q128;
-            c += r128;
-            if (c >= C) { c -= C; ++r; }
+        for (int e = lane * 4; e < total; e += 128) {
+            const int u = e >> 2;
+            const float4 o = *reinterpret_cast<const float4*>(stage + 4 * (quads ? u ^ ((u >> 3) & 7) : u));
+            __stcs(reinterpret_cast<float4*>(dst + e), o);
         }
     } else {
-        int r = lane / C, c = lane - r * C;
-        const int q32 = 32 / C, r32 = 32 - q32 * C;
         for (int e = lane; e < total; e += 32) {
-            __stcs(dst + e, stage[r * kSrOutPitch + c]);
-            r += q32;
-            c += r32;
-            if (c >= C) { c -= C; ++r; }
+            const int u = e >> 2;
+            __stcs(dst + e, stage[quads ? 4 * (u ^ ((u >> 3) & 7)) + (e & 3) : e]);
         }
     }
     __syncwarp();
@@ -1368,19 +1363,19 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
     uint64_t* raw_full = bars;
     uint64_t* raw_empty = raw_full + kSrMaxRaw;
     uint64_t* op_full = raw_empty + kSrMaxRaw;
-    uint64_t* op_empty = op_full + kSrOpStages;
-    uint64_t* acc_full = op_empty + kSrOpStages;
+    uint64_t* op_empty = op_full + kSrMaxOpStages;
+    uint64_t* acc_full = op_empty + kSrMaxOpStages;
     uint64_t* acc_empty = acc_full + kSrAccBufs;
     uint64_t* w_full = acc_empty + kSrAccBufs;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SrSmem::tmem_slot);
-    unsigned char* raw = smem + SrSmem::raw;
+    unsigned char* raw = smem + SrSmem::op + p.op_stages * kSrOpBytes;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int d = p.d;
     constexpr int kMmaWarp = 1 + kSrConvWarps;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kSrMaxRaw; ++i) { mbar_init(raw_full + i, 1); mbar_init(raw_empty + i, 128); }
-        for (int i = 0; i < kSrOpStages; ++i) { mbar_init(op_full + i, 128); mbar_init(op_empty + i, 1); }
+        for (int i = 0; i < kSrMaxOpStages; ++i) { mbar_init(op_full + i, 128); mbar_init(op_empty + i, 1); }
         for (int i = 0; i < kSrAccBufs; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 128); }
         mbar_init(w_full, 1);
         mbar_fence_init();
@@ -1430,70 +1425,66 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
         }
     } else if (warp < kMmaWarp) {
-        // ===================== converters: two sets of four warps on alternate tiles =====================
-        const int set = (warp - 1) >> 2;
-        const int t = (threadIdx.x - 32) & 127;                  // 0..127 inside the set
+        // ===================== converters =====================
+        const int t = threadIdx.x - 32;                          // 0..127
         constexpr int QPR = DK / 4;                              // 4-float pieces per row
         constexpr int ITEMS = QPR;                               // per thread: 128 rows x QPR pieces / 128 threads
-        int st = 0;
-        uint32_t ph = 0;
-        int64_t seq = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
-            const bool mine = (seq & 1) == set;
-            if (mine) {
-                mbar_wait(raw_full + st, ph);
-                mbar_wait(op_empty + set, (uint32_t)(((seq >> 1) & 1) ^ 1));
-                const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
-                unsigned char* dst = smem + SrSmem::op + set * kSrOpBytes;
-                const int64_t left = (p.n_rows - tile * BM) * d;
-                const bool ragged = left < tile_floats;
-                float x[ITEMS][4];
-                if (!ragged) {
-                    // all the loads of the tile first, then the arithmetic
-#pragma unroll
-                    for (int j = 0; j < ITEMS; ++j) {
-                        const int it = t + 128 * j;
-                        const int r = it / QPR, q = it % QPR;
-                        const int e0 = r * d + 4 * q;
-                        if constexpr (VEC) {
-                            const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                            x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) x[j][i] = 4 * q + i < d ? src[e0 + i] : 0.0f;
-                        }
-                    }
-                } else {
-                    const int n_in_smem = (int)(((left * 4) & ~15ll) >> 2), n_valid = (int)left;
-                    const float* gsrc = p.X + tile * tile_floats;
-#pragma unroll
-                    for (int j = 0; j < ITEMS; ++j) {
-                        const int it = t + 128 * j;
-                        const int r = it / QPR, q = it % QPR;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int e = r * d + 4 * q + i;
-                            x[j][i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
-                        }
-                    }
-                }
+        int st = 0, os = 0;
+        uint32_t ph = 0, oph = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(raw_full + st, ph);
+            mbar_wait(op_empty + os, oph ^ 1);
+            const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
+            unsigned char* dst = smem + SrSmem::op + os * kSrOpBytes;
+            const int64_t left = (p.n_rows - tile * BM) * d;
+            const bool ragged = left < tile_floats;
+            float x[ITEMS][4];
+            if (!ragged) {
+                // all the loads of the tile first, then the arithmetic
 #pragma unroll
                 for (int j = 0; j < ITEMS; ++j) {
                     const int it = t + 128 * j;
                     const int r = it / QPR, q = it % QPR;
-                    const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
-                    uint32_t h0, l0, h1, l1;
-                    split_pair(x[j][0], x[j][1], cs.x, cs.y, h0, l0);
-                    split_pair(x[j][2], x[j][3], cs.z, cs.w, h1, l1);
-                    const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
-                    *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
-                    *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
+                    const int e0 = r * d + 4 * q;
+                    if constexpr (VEC) {
+                        const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) x[j][i] = 4 * q + i < d ? src[e0 + i] : 0.0f;
+                    }
                 }
-                fence_proxy_async();
-                mbar_arrive(op_full + set);
-                mbar_arrive(raw_empty + st);
+            } else {
+                const int n_in_smem = (int)(((left * 4) & ~15ll) >> 2), n_valid = (int)left;
+                const float* gsrc = p.X + tile * tile_floats;
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    const int it = t + 128 * j;
+                    const int r = it / QPR, q = it % QPR;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int e = r * d + 4 * q + i;
+                        x[j][i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
+                    }
+                }
             }
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) {
+                const int it = t + 128 * j;
+                const int r = it / QPR, q = it % QPR;
+                const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
+                uint32_t h0, l0, h1, l1;
+                split_pair(x[j][0], x[j][1], cs.x, cs.y, h0, l0);
+                split_pair(x[j][2], x[j][3], cs.z, cs.w, h1, l1);
+                const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
+                *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
+                *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
+            }
+            fence_proxy_async();
+            mbar_arrive(op_full + os);
+            mbar_arrive(raw_empty + st);
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
+            if (++os == p.op_stages) { os = 0; oph ^= 1; }
         }
     } else if (warp == kMmaWarp) {
         // ===================== MMA issuer =====================
@@ -1504,12 +1495,10 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         const uint64_t wlo = whi + (uint64_t)((32 * 128) >> 4);
         const uint32_t idesc = (kIdesc16 & ~(0x3Fu << 17)) | ((uint32_t)(32 >> 3) << 17);
         mbar_wait(w_full, 0);
-        int ab = 0;
-        uint32_t aph = 0;
-        int64_t seq = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
-            const int os = (int)(seq & 1);
-            mbar_wait(op_full + os, (uint32_t)((seq >> 1) & 1));
+        int ab = 0, os = 0;
+        uint32_t aph = 0, oph = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            mbar_wait(op_full + os, oph);
             mbar_wait(acc_empty + ab, aph ^ 1);
             tc_fence_after();
             if (leader) {
@@ -1527,21 +1516,22 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             }
             __syncwarp();
             if (++ab == kSrAccBufs) { ab = 0; aph ^= 1; }
+            if (++os == p.op_stages) { os = 0; oph ^= 1; }
         }
     } else {
-        // ===================== epilogue: two sets of four warps on alternate tiles =====================
-        const int ew = warp - (kMmaWarp + 1);                    // 0..7
+        // ===================== epilogue: three sets of four warps take the tiles in turn =====================
+        const int ew = warp - (kMmaWarp + 1);                    // 0..11
         const int set = ew >> 2;
         const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
         const int r_in_tile = q * 32 + lane;
-        float* stage = reinterpret_cast<float*>(smem + SrSmem::out) + ew * 32 * kSrOutPitch;
+        float* stage = reinterpret_cast<float*>(smem + SrSmem::out) + ew * 32 * 32;
         const float psum_scale = p.x_scale[5];
         const float floor_err = p.x_scale[6];
         const int C = p.n_classes;
         const bool p_al = (reinterpret_cast<uintptr_t>(p.proba) & 15u) == 0, z_al = (reinterpret_cast<uintptr_t>(p.decision) & 15u) == 0;
         int64_t seq = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
-            if ((seq & 1) != set) continue;
+            if ((int)(seq % kSrEpiSets) != set) continue;
             const int ab = (int)(seq % kSrAccBufs);
             mbar_wait(acc_full + ab, (uint32_t)((seq / kSrAccBufs) & 1));
             tc_fence_after();
@@ -1574,13 +1564,11 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
                 gs += v[i];
             }
             const float inv = __frcp_rn(gs);
-            const float risk_thr = 8e-6f / ez;
-            bool risk = false;
+            // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, and that is always the top one
+            // (p (1 - p) rises up to 1/2, and no class but the top one can pass it): its probability is `inv`
+            const bool risk = inv * (1.0f - inv) > 8e-6f / ez;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                v[i] *= inv;
-                risk = risk || (v[i] * (1.0f - v[i]) > risk_thr);
-            }
+            for (int i = 0; i < 32; ++i) v[i] *= inv;
             if (p.proba) store_rows_coalesced(stage, v, C, lane, p.proba + row0 * C, rows_valid, p_al);
             if (live) {
                 if (p.label) __stcs(p.label + row, garg);
@@ -1601,22 +1589,31 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
 }
 
-// Flagged rows of the kernel above, re-scored whole in fp32: one warp per row, lane c owns class c.
+// Flagged rows of the kernel above, re-scored whole in fp32: one warp per row, lane c owns class c; W (at most
+// 32 x 64 floats) sits transposed in shared memory (read from global per row, the 64 dependent trips to L2 cost
+// 35 us a row).
 __global__ void __launch_bounds__(256)
 short_fixup_kernel(const float* __restrict__ X, int d, int C, const float* __restrict__ W, const float* __restrict__ b,
                    const unsigned* __restrict__ list, const unsigned* __restrict__ n_list, float* proba, float* decision,
                    int32_t* label, float* maxprob, unsigned long long* rescored, unsigned long long* status) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ float Ws[64 * 33];
     const unsigned n = *n_list;
+    if (blockIdx.x * 8 >= n) return;
+    for (int i = threadIdx.x; i < C * d; i += 256) {
+        const int c = i / d, k = i - c * d;
+        Ws[k * 33 + c] = __ldg(W + i);
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cl = lane < C ? lane : 0;
     for (unsigned li = blockIdx.x * 8 + warp; li < n; li += gridDim.x * 8) {
         const int64_t row = list[li];
         const float* x = X + row * d;
         const float x0 = lane < d ? __ldg(x + lane) : 0.0f, x1 = lane + 32 < d ? __ldg(x + lane + 32) : 0.0f;
-        const float* w = W + (int64_t)(lane < C ? lane : 0) * d;
         float z = 0.0f;
         for (int k = 0; k < d; ++k) {
             const float xk = __shfl_sync(0xffffffffu, k < 32 ? x0 : x1, k & 31);
-            z = fmaf(xk, __ldg(w + k), z);
+            z = fmaf(xk, Ws[k * 33 + cl], z);
         }
         z = lane < C ? z + __ldg(b + lane) : -CUDART_INF_F;
         float m = z;
@@ -2403,13 +2400,19 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.d = d;
     p.n_classes = C;
     p.stage_bytes = (BM * d * 4 + 127) / 128 * 128;
-    const int room = 227 * 1024 - 1024 - SrSmem::raw;
+    // rows of at most 32 floats leave room for two operand tiles per converter set: a set then converts its next
+    // tile while the MMAs of its previous one are still on their way (measured: the hand-over, not the work, set the pace)
+    p.op_stages = 2;             // four (rows of <= 32 floats leave the room) measured the same: the epilogue sets the pace
+    const int room = 227 * 1024 - 1024 - SrSmem::op - p.op_stages * kSrOpBytes;
     p.raw_stages = room / p.stage_bytes < kSrMaxRaw ? room / p.stage_bytes : kSrMaxRaw;
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
     p.x_scale = x_scale;
     p.col_scale = g->col_scale;
-    p.kappa = 2.0e-5f * 384.0f / 1024.0f;            // one accumulator, rows shorter than 384 floats: see gemm_launch_aligned
+    // 3 x (dk / 16) accumulation steps only: the truncation error measured on these shapes (tools/gemm_kappa.py
+    // --short) is 0.7-1.9e-6 |z|; the longer-row kernel's floor (7.5e-6) flagged 2-5 % of the rows of a
+    // 26..32-class model for nothing
+    p.kappa = float(getenv("LRS_SHORT_KAPPA") ? atof(getenv("LRS_SHORT_KAPPA")) : 1.0e-6 + 2.5e-6 * ((d + 15) / 16) / 4.0);
     p.count_nonfinite = fixup ? 0 : 1;
     p.vec_store = 0;
     p.proba = a.proba;
@@ -2420,7 +2423,7 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.flags = flags;
     p.flag_list = flag_list;
     p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
-    const size_t smem = (size_t)SrSmem::raw + (size_t)p.raw_stages * p.stage_bytes + 1024;
+    const size_t smem = (size_t)SrSmem::op + (size_t)p.op_stages * kSrOpBytes + (size_t)p.raw_stages * p.stage_bytes + 1024;
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
     const int grid = (int)(n_tiles < m.num_sms ? n_tiles : m.num_sms);
     const bool vec = d % 4 == 0;
