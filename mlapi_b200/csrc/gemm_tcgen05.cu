@@ -1265,10 +1265,12 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
 //                registers, outputs, re-scoring flags -- the single-pass form of the kernel above
 // Same arithmetic (3xFP16 split, truncating TMEM accumulation) and the same error band as that kernel; flagged
 // rows are re-scored whole in fp32 (32 classes x 64 features is nothing) by short_fixup_kernel.
-constexpr int kSrConvWarps = 4;
-constexpr int kSrEpiSets = 3;                            // the epilogue is the long stage: three sets of four warps
-constexpr int kSrEpiWarps = 4 * kSrEpiSets;              // (TMEM lane quadrants) take the tiles in turn
-constexpr int kSrThreads = (1 + kSrConvWarps + 1 + kSrEpiWarps) * 32;      // 576
+// Sixteen worker warps in sets of four, split at launch between the two long stages: rows of up to 32 floats
+// convert quickly and want three epilogue sets (1 + 3); longer rows want two converter sets (2 + 2).  Sets of a
+// stage take the tiles in turn.
+constexpr int kSrWorkWarps = 16;
+constexpr int kSrMaxEpiWarps = 12;
+constexpr int kSrThreads = (2 + kSrWorkWarps) * 32;                        // 576
 constexpr int kSrMaxOpStages = 4;                        // operand tiles in flight: 2 or 4 (runtime: shared memory)
 constexpr int kSrAccBufs = 8;
 constexpr int kSrMaxRaw = 8;
@@ -1278,8 +1280,8 @@ struct SrSmem {
     static constexpr int cs = w + 2 * 32 * 128;                          // [64] per-feature scale x call scale
     static constexpr int bias = cs + 64 * 4;                             // [32]
     static constexpr int cscale = bias + 32 * 4;                         // [32]
-    static constexpr int out = cscale + 32 * 4;                          // [kSrEpiWarps][32 rows x 32] floats
-    static constexpr int bars = out + kSrEpiWarps * 32 * 32 * 4;         // raw_full/empty[8], op_full/empty[4], acc_full/empty[8], w_full
+    static constexpr int out = cscale + 32 * 4;                          // [epilogue warps][32 rows x 32] floats
+    static constexpr int bars = out + kSrMaxEpiWarps * 32 * 32 * 4;      // raw_full/empty[8], op_full/empty[4], acc_full/empty[8], w_full
     static constexpr int n_bars = 2 * kSrMaxRaw + 2 * kSrMaxOpStages + 2 * kSrAccBufs + 1;
     static constexpr int tmem_slot = bars + n_bars * 8;
     static constexpr int op = (tmem_slot + 16 + 1023) / 1024 * 1024;     // [op_stages][32 KB], then [raw_stages][stage_bytes]
@@ -1291,6 +1293,7 @@ struct ShortParams {
     int n_classes;
     int raw_stages, stage_bytes;
     int op_stages;              // 2 or 4 operand tiles per CTA
+    int conv_sets;              // 1 or 2 sets of four converter warps; the other 4 - conv_sets sets are epilogue warps
     const float* bias;
     const float* col_inv_scale;
     const float* x_scale;
@@ -1371,7 +1374,8 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
     unsigned char* raw = smem + SrSmem::op + p.op_stages * kSrOpBytes;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int d = p.d;
-    constexpr int kMmaWarp = 1 + kSrConvWarps;
+    const int kMmaWarp = 1 + 4 * p.conv_sets;
+    const int epi_sets = kSrWorkWarps / 4 - p.conv_sets;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kSrMaxRaw; ++i) { mbar_init(raw_full + i, 1); mbar_init(raw_empty + i, 128); }
@@ -1425,64 +1429,69 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
         }
     } else if (warp < kMmaWarp) {
-        // ===================== converters =====================
-        const int t = threadIdx.x - 32;                          // 0..127
+        // ===================== converters: conv_sets sets of four warps take the tiles in turn =====================
+        const int set = (warp - 1) >> 2;
+        const int t = (threadIdx.x - 32) & 127;                  // 0..127 inside the set
         constexpr int QPR = DK / 4;                              // 4-float pieces per row
         constexpr int ITEMS = QPR;                               // per thread: 128 rows x QPR pieces / 128 threads
         int st = 0, os = 0;
         uint32_t ph = 0, oph = 0;
+        int turn = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            mbar_wait(raw_full + st, ph);
-            mbar_wait(op_empty + os, oph ^ 1);
-            const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
-            unsigned char* dst = smem + SrSmem::op + os * kSrOpBytes;
-            const int64_t left = (p.n_rows - tile * BM) * d;
-            const bool ragged = left < tile_floats;
-            float x[ITEMS][4];
-            if (!ragged) {
-                // all the loads of the tile first, then the arithmetic
+            if (turn == set) {
+                mbar_wait(raw_full + st, ph);
+                mbar_wait(op_empty + os, oph ^ 1);
+                const float* src = reinterpret_cast<const float*>(raw + (size_t)st * p.stage_bytes);
+                unsigned char* dst = smem + SrSmem::op + os * kSrOpBytes;
+                const int64_t left = (p.n_rows - tile * BM) * d;
+                const bool ragged = left < tile_floats;
+                float x[ITEMS][4];
+                if (!ragged) {
+                    // all the loads of the tile first, then the arithmetic
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) {
+                        const int it = t + 128 * j;
+                        const int r = it / QPR, q = it % QPR;
+                        const int e0 = r * d + 4 * q;
+                        if constexpr (VEC) {
+                            const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) x[j][i] = 4 * q + i < d ? src[e0 + i] : 0.0f;
+                        }
+                    }
+                } else {
+                    const int n_in_smem = (int)(((left * 4) & ~15ll) >> 2), n_valid = (int)left;
+                    const float* gsrc = p.X + tile * tile_floats;
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) {
+                        const int it = t + 128 * j;
+                        const int r = it / QPR, q = it % QPR;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int e = r * d + 4 * q + i;
+                            x[j][i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
+                        }
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < ITEMS; ++j) {
                     const int it = t + 128 * j;
                     const int r = it / QPR, q = it % QPR;
-                    const int e0 = r * d + 4 * q;
-                    if constexpr (VEC) {
-                        const float4 v = 4 * q < d ? *reinterpret_cast<const float4*>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) x[j][i] = 4 * q + i < d ? src[e0 + i] : 0.0f;
-                    }
+                    const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
+                    uint32_t h0, l0, h1, l1;
+                    split_pair(x[j][0], x[j][1], cs.x, cs.y, h0, l0);
+                    split_pair(x[j][2], x[j][3], cs.z, cs.w, h1, l1);
+                    const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
+                    *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
+                    *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
                 }
-            } else {
-                const int n_in_smem = (int)(((left * 4) & ~15ll) >> 2), n_valid = (int)left;
-                const float* gsrc = p.X + tile * tile_floats;
-#pragma unroll
-                for (int j = 0; j < ITEMS; ++j) {
-                    const int it = t + 128 * j;
-                    const int r = it / QPR, q = it % QPR;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int e = r * d + 4 * q + i;
-                        x[j][i] = (4 * q + i < d && e < n_valid) ? (e < n_in_smem ? src[e] : __ldg(gsrc + e)) : 0.0f;
-                    }
-                }
+                fence_proxy_async();
+                mbar_arrive(op_full + os);
+                mbar_arrive(raw_empty + st);
             }
-#pragma unroll
-            for (int j = 0; j < ITEMS; ++j) {
-                const int it = t + 128 * j;
-                const int r = it / QPR, q = it % QPR;
-                const float4 cs = *reinterpret_cast<const float4*>(cs_s + 4 * q);
-                uint32_t h0, l0, h1, l1;
-                split_pair(x[j][0], x[j][1], cs.x, cs.y, h0, l0);
-                split_pair(x[j][2], x[j][3], cs.z, cs.w, h1, l1);
-                const int off = r * 128 + (((q >> 1) ^ (r & 7)) << 4) + (q & 1) * 8;     // SWIZZLE_128B
-                *reinterpret_cast<uint2*>(dst + off) = make_uint2(h0, h1);
-                *reinterpret_cast<uint2*>(dst + A_TILE_BYTES + off) = make_uint2(l0, l1);
-            }
-            fence_proxy_async();
-            mbar_arrive(op_full + os);
-            mbar_arrive(raw_empty + st);
+            if (++turn == p.conv_sets) turn = 0;
             if (++st == p.raw_stages) { st = 0; ph ^= 1; }
             if (++os == p.op_stages) { os = 0; oph ^= 1; }
         }
@@ -1519,7 +1528,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             if (++os == p.op_stages) { os = 0; oph ^= 1; }
         }
     } else {
-        // ===================== epilogue: three sets of four warps take the tiles in turn =====================
+        // ===================== epilogue: epi_sets sets of four warps take the tiles in turn =====================
         const int ew = warp - (kMmaWarp + 1);                    // 0..11
         const int set = ew >> 2;
         const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
@@ -1531,7 +1540,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         const bool p_al = (reinterpret_cast<uintptr_t>(p.proba) & 15u) == 0, z_al = (reinterpret_cast<uintptr_t>(p.decision) & 15u) == 0;
         int64_t seq = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++seq) {
-            if ((int)(seq % kSrEpiSets) != set) continue;
+            if ((int)(seq % epi_sets) != set) continue;
             const int ab = (int)(seq % kSrAccBufs);
             mbar_wait(acc_full + ab, (uint32_t)((seq / kSrAccBufs) & 1));
             tc_fence_after();
@@ -2402,7 +2411,10 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.stage_bytes = (BM * d * 4 + 127) / 128 * 128;
     // rows of at most 32 floats leave room for two operand tiles per converter set: a set then converts its next
     // tile while the MMAs of its previous one are still on their way (measured: the hand-over, not the work, set the pace)
-    p.op_stages = 2;             // four (rows of <= 32 floats leave the room) measured the same: the epilogue sets the pace
+    p.op_stages = 2;             // four (rows of <= 32 floats leave the room) measured the same
+    // measured (tools/shape_sweep.py): d=16, C=26 2.8 -> 3.9 TB/s with 1 + 3 sets, d=54, C=20 3.0 -> 3.9 with 2 + 2
+    p.conv_sets = d <= 32 ? 1 : 2;
+    if (const char* e = getenv("LRS_SHORT_CONV_SETS")) p.conv_sets = atoi(e) == 1 ? 1 : 2;
     const int room = 227 * 1024 - 1024 - SrSmem::op - p.op_stages * kSrOpBytes;
     p.raw_stages = room / p.stage_bytes < kSrMaxRaw ? room / p.stage_bytes : kSrMaxRaw;
     p.bias = g->bias;
