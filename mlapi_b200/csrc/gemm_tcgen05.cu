@@ -1884,26 +1884,28 @@ struct GemmPlan {
     // Arithmetic: 0 = per call (3xFP16 unless the batch's dynamic range says 3xTF32), 1 = 3xFP16 always
     // (LRS_GEMM_F16=2, measurements only: no guard), 2 = 3xTF32 always (LRS_GEMM_F16=0)
     int force = 0;
-    // Three CTA layouts over the same W buffers:
+    // Two CTA layouts over the same W buffers:
     //   [0] fast:     512 classes per CTA (CTA pairs), one TMEM accumulator that fills TMEM   (C in 257..2048)
     //   [1] accurate: 256 classes per CTA, correction products accumulate apart, 3x smaller logit
     //                 error, so far fewer rows need the fp32 re-scoring pass                   (C <= 1024)
-    //   [2] overlap:  256 classes per CTA, one accumulator per tile but two of them in TMEM: the epilogue
-    //                 of a row tile runs under the MMAs of the next                             (C in 129..1024)
-    // `active` starts on the quickest layout the class count allows and moves to the accurate one when the
-    // re-scoring pass reports that the data is confident (lr_score_host feeds that back).
+    // `active` starts on the fast layout where both exist and moves to the accurate one when the re-scoring
+    // pass reports that the data is confident (lr_score_host feeds that back).
+    // (A third layout -- 256 classes per CTA, unsplit, two accumulators of 256 columns so that the epilogue of a
+    // row tile runs under the MMAs of the next -- was built and measured in round 2: 8 % fewer cycles on cfg 3,
+    // but every X tile is converted by four CTAs instead of two and W crosses L2 twice as often; under the 1 kW
+    // cap the SM clock fell from ~1.9 to ~1.6 GHz and the step took 27.4-30.6 ms against 24.9-29.3; d=768, C=256
+    // ran at 2.32 TB/s against 2.72 on the accurate layout.  Removed.)
     struct Layout {
         int nb = 0, ncc = 0, nrt = 1;
         int mma_n = BN;             // see GemmParams::mma_n
         bool pair = false;          // cta_group::2: cluster = 2 * ncc CTAs
         bool split = false;
-        bool two_acc = false;       // two accumulator buffers (unsplit, unpaired, one 256-class block)
         int max_clusters[64] = {0};
         CUtensorMap map_whi, map_wlo, map_w16hi, map_w16lo;    // W boxes are BN / nrt rows
     };
-    static constexpr int kLayouts = 3;
+    static constexpr int kLayouts = 2;
     Layout layout[kLayouts];
-    bool has[kLayouts] = {false, false, false};
+    bool has[kLayouts] = {false, false};
     std::atomic<int> active{0};
     bool adaptive = true;
     int c_pad = 0;
@@ -2025,7 +2027,6 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     g->d64 = (d + BK16 - 1) / BK16 * BK16;
     auto& fast = g->layout[0];
     auto& acc = g->layout[1];
-    auto& ovl = g->layout[2];
     if (C > BN) {                                   // fast layout: 512 classes per CTA
         fast.nb = 2;
         fast.ncc = (C + 2 * BN - 1) / (2 * BN);
@@ -2038,13 +2039,6 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         if (acc.ncc == 3) acc.ncc = 4;
         acc.split = true;
         g->has[1] = true;
-    }
-    if (C > 128 && C <= kMaxCluster * BN) {         // overlap layout: 256 classes per CTA, two accumulator buffers
-        ovl.nb = 1;
-        ovl.ncc = (C + BN - 1) / BN;
-        if (ovl.ncc == 3) ovl.ncc = 4;
-        ovl.two_acc = true;
-        g->has[2] = true;
     }
     // two row tiles per cluster share every W tile through TMA multicast (cluster <= 8 CTAs)
     bool mc = true;
@@ -2070,7 +2064,6 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         acc.mma_n = (C + 31) / 32 * 32;
         if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
     }
-    if (g->has[2] && ovl.ncc == 1 && C <= BN - 32) ovl.mma_n = (C + 31) / 32 * 32;
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -2274,8 +2267,8 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
             p.a_stages = as; p.b_stages = bs;
         }
     }
-    p.acc_bufs = ((L.mma_n <= 128 || L.two_acc) && L.nb == 1 && !L.pair) ? 2 : 1;
-    p.acc_stride = L.mma_n <= 128 ? 128 : 256;
+    p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
+    p.acc_stride = 128;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
