@@ -14,8 +14,8 @@
  *     model, C for a C-class multinomial one); a probability row has max(n_scores, 2) columns;
  *   - `*_dev` pointers are device pointers on the model's device (a torch tensor's data_ptr()
  *     works); `*_host` pointers are host pointers (pinned memory makes the copies asynchronous);
- *   - a model is immutable after creation: concurrent lr_score calls on distinct streams are safe;
- *     lr_score_host serialises on the model's own staging buffers;
+ *   - a model is immutable between lr_model_create and lr_model_update: concurrent lr_score calls on distinct
+ *     streams are safe; lr_score_host serialises on the model's own staging buffers;
  *   - there is no CPU fallback: without a CUDA device every call fails with LR_ERR_CUDA.
  */
 #ifndef LRSCORE_H_
@@ -36,10 +36,12 @@ extern "C" {
 /* Which kernel family serves a (model, n_rows) pair; see DESIGN.md "Kernels". */
 #define LR_PATH_AUTO     0
 #define LR_PATH_NARROW   1    /* <= 16 score columns (<= 24 on short rows): fused row-dot + sigmoid/softmax, few lanes per row;
-                                 register-tile form for 5..16 columns, shared-memory ring for unaligned / long rows */
+                                 register-tile form for 5..16 columns, shared-memory ring for unaligned / long rows
+                                 (large batches of 13..16 classes on rows of >= 64 floats take LR_PATH_GEMM)        */
 #define LR_PATH_WIDE     2    /* binary, rows of 1024 floats and more: row-block streaming, W re-used across 8 rows */
-#define LR_PATH_GEMM     3    /* 17..2048 classes: TMA-fed tcgen05 GEMM (3xFP16 split, 3xTF32 optional) + fused
-                                 softmax; unaligned rows are re-pitched first                                   */
+#define LR_PATH_GEMM     3    /* 13..2048 classes: TMA-fed tcgen05 GEMM (3xFP16 split, 3xTF32 when the batch's dynamic
+                                 range demands it) + fused softmax; unaligned rows are re-pitched first; dense rows of
+                                 <= 64 floats with <= 32 classes take its short-row form                           */
 #define LR_PATH_GENERIC  4    /* any shape: SIMT row-per-warp fallback (what is left: > 2048 classes)            */
 
 typedef struct lr_model lr_model;

@@ -7,26 +7,33 @@
 // predict (SK/linear_model/_base.py:415-418), with the softmax fused into the epilogue so the
 // n x C score matrix is written exactly once (as probabilities).
 //
-// Precision.  tcgen05 has no fp32 MMA; a single TF32 pass leaves ~1e-3 error on a d=1024 logit,
-// far outside the 1e-5 parity bar.  Each product is therefore split (3xTF32):
-//     x = x_hi + x_lo,  w = w_hi + w_lo   (hi = round-to-nearest TF32, lo = TF32 of the residual)
-//     x.w ~= x_hi.w_hi + x_lo.w_hi + x_hi.w_lo     (fp32 accumulation in TMEM)
-// w_hi / w_lo are made once on the host from the float64 coef_; x_hi / x_lo are made on the fly
-// in shared memory by four converter warps, so X is read from HBM exactly once.  The dropped
-// x_lo.w_lo term is ~2^-22 relative.  Algorithmic flops (2*d*C per row) are counted once; the
-// tensor pipe executes three times that.
+// Precision.  tcgen05 has no fp32 MMA; a single reduced-precision pass leaves ~1e-3 error on a d=1024
+// logit, far outside the 1e-5 parity bar.  Each product is therefore split,
+//     x = x_hi + x_lo,  w = w_hi + w_lo,     x.w ~= x_hi.w_hi + x_lo.w_hi + x_hi.w_lo   (fp32 accumulation in TMEM)
+// in fp16 halves by default (3xFP16, kind::f16 at the full tensor rate) or TF32 halves (3xTF32, half the
+// rate, fp32's exponent range).  fp16 has 5 exponent bits, so range is managed explicitly: W is balanced
+// per feature and scaled per class when the model is loaded (w_colscale_kernel, w_split16_kernel), X is
+// scaled per call from a robust row maximum of a sample of the batch (x_scale_kernel), rows that overflow
+// are re-scored in fp32, and a per-call bound on what the fp16 subnormal floor can still cost decides on the
+// device whether the call runs in 3xFP16 or 3xTF32 (both kernels are enqueued; the one not chosen returns at
+// once).  The halves of W are made once per model; those of X on the fly in shared memory by four converter
+// warps, so X is read from HBM exactly once.  The dropped x_lo.w_lo term is ~2^-22 relative.  Algorithmic
+// flops (2*d*C per row) are counted once; the tensor pipe executes three times that.
 //
-// Structure (one CTA = 128 rows x up to 512 classes; a cluster of ncc CTAs covers all classes of
-// the same 128 rows and exchanges softmax statistics through distributed shared memory):
-//   warp 0      TMA producer: X tile [128 x 32] and W tiles [256 x 32] (hi, lo) into mbarrier rings
-//   warp 1      MMA issuer: one lane issues tcgen05.mma.kind::tf32 (M=128, N=256, K=8) into TMEM
-//   warps 2-5   converters: raw X tile -> x_hi (in place) and x_lo, elementwise (swizzle-agnostic)
-//   warps 6-9   epilogue: tcgen05.ld accumulators, bias, online max/sum, DSMEM exchange,
-//               normalise, store proba / decision / label / maxprob
-// Accumulators fill TMEM (2 x 256 columns), so the epilogue of a tile and the MMAs of the next do
-// not overlap inside a CTA; the producer and converters do run ahead.
+// Structure (one CTA = 128 rows x up to 512 classes; a cluster of CTAs covers all classes of the same rows
+// and exchanges softmax statistics through distributed shared memory; in the 512-class layout two CTAs
+// form a cta_group::2 pair that shares every W tile):
+//   warp 0      TMA producer, W tiles (hi, lo) into an mbarrier ring
+//   warp 1      MMA issuer: one lane issues tcgen05.mma (M=128 or 256 across the pair, N up to 256) into TMEM
+//   warps 2-5   converters: raw fp32 X tile -> scaled fp16 hi | lo operand tiles, in place (128B swizzle)
+//   warps 6-13  epilogue: two TMEM passes (exp written back in between), one DSMEM exchange per tile,
+//               outputs, re-scoring list
+//   warp 14     TMA producer, X tiles
+// Rows whose answer the accumulation error could change (near-ties, a top probability near one half)
+// are put on a list by the epilogue and re-scored in fp32 by a second kernel.
+// Models of 13..32 classes on dense rows of at most 64 floats take short_rows_kernel instead (below).
 //
-// Tensor roofline: 2*d*C flops per row against half the measured bf16 peak (TF32 rate).
+// Tensor roofline: 2*d*C flops per row against the measured 16-bit tensor peak (TF32: half of it).
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -102,6 +109,10 @@ struct GemmParams {
                                   // with zeros to whole k-chunks
     float kappa;                  // relative logit error of the truncating TMEM accumulation (layout, arithmetic, row length)
     int acc_stride;               // TMEM columns between the two accumulator buffers (acc_bufs == 2)
+    int seg_w;                    // columns reserved per main accumulator when ksplit > 1: 32 or 64
+    int ksplit;                   // 1..7 main accumulators per tile, each over a contiguous third of the k-chunks (split
+                                  // layout, N <= 64 only: there is room in TMEM for 3, for 7 when N <= 32): the truncation error of a logit grows
+                                  // with the accumulation steps behind it, so long rows are summed in pieces
     int count_fallback;           // 3xTF32 kernel launched as the fallback of a 3xFP16 model: add n_rows to status[2]
     int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
     int b_tile_bytes;       // ... bytes reserved per W stage ...
@@ -120,6 +131,7 @@ struct GemmParams {
                             // may find a reason to flag the same row)
     unsigned* flag_list;    // [n_rows] the rows to re-score in fp32 (near-ties, risky probabilities, overflowed rows) ...
     unsigned* n_flagged;    // ... and how many there are
+    float* ezr;             // [n_rows] per flagged row: the logit error bound it was flagged under
     float* lse;             // [n_rows] log-sum-exp of the row as the tensor path saw it (for the re-scoring pass)
     int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned);
                             // 2: 32-byte aligned as well (C % 8 == 0): 256-bit stores, whole sectors per lane
@@ -355,9 +367,22 @@ __device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b,
 
 constexpr float kLog2e = 1.4426950408889634f;
 
-// Put `row` on the re-scoring list, once.
-__device__ __forceinline__ void flag_row(unsigned* flags, unsigned* list, unsigned* count, int64_t row) {
-    if (atomicExch(flags + row, 1u) == 0u) list[atomicAdd(count, 1u)] = (unsigned)row;
+// TMEM columns of main accumulator `seg` relative to the tile's first one (GemmParams::ksplit; split layout,
+// buffers 128 columns apart, the correction accumulator BN columns up).  `w` = 64 (N <= 64: the second sits
+// beside the first, the third beside the correction accumulator) or 32 (N <= 32: four in the main slot, three
+// more beside the correction accumulator).
+__device__ __forceinline__ uint32_t seg_offset(int seg, int w) {
+    const int per_slot = 128 / w;
+    return seg < per_slot ? (uint32_t)(seg * w) : (uint32_t)BN + (uint32_t)((seg - per_slot + 1) * w);
+}
+
+// Put `row` on the re-scoring list, once; `ez` = the logit error the row was judged against (every thread that
+// flags a row has the same value for it).
+__device__ __forceinline__ void flag_row(unsigned* flags, unsigned* list, unsigned* count, float* ezr, int64_t row, float ez) {
+    if (atomicExch(flags + row, 1u) == 0u) {
+        if (ezr) ezr[row] = ez;
+        list[atomicAdd(count, 1u)] = (unsigned)row;
+    }
 }
 
 // ---- cta_group::2 (CTA pair) forms ---------------------------------------------------------------
@@ -411,8 +436,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     // The arithmetic of a call is chosen on the device (x_scale_kernel: 3xFP16 unless the data's dynamic range
     // would cost precision); both kernels are enqueued and the one not chosen leaves here, every CTA alike.
     if (reinterpret_cast<const uint32_t*>(p.x_scale)[4] != (F16 ? 0u : 1u)) return;
-    if (!F16 && p.count_fallback && blockIdx.x == 0 && threadIdx.x == 0)
-        atomicAdd(p.status + 2, (unsigned long long)p.n_rows);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(p.status + 3, (unsigned long long)p.n_rows);          // rows this path has scored (layout feedback)
+        if (!F16 && p.count_fallback) atomicAdd(p.status + 2, (unsigned long long)p.n_rows);
+    }
     extern __shared__ unsigned char smem_dyn[];
     // 1024-byte alignment by pointer arithmetic on the shared array itself: going through uintptr_t made
     // every access below a generic LD/ST instead of LDS/STS
@@ -595,20 +622,25 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const uint32_t accph = (p.acc_bufs == 2 ? (it >> 1) : it) & 1u;         // its use count, as a parity
             if constexpr (PAIR) mbar_wait_cluster(acc_empty + buf, accph ^ 1); else mbar_wait(acc_empty + buf, accph ^ 1);
             tc_fence_after();
+            int prev_seg = -1;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 if constexpr (PAIR) mbar_wait_cluster(a_ready + as, aph); else mbar_wait(a_ready + as, aph);
                 // TF32: hi tiles and lo tiles are two arrays; FP16: stage = [hi 16 KB | lo 16 KB] contiguous
                 const uint64_t ahi = ahi0 + (uint64_t)(as * ((F16 ? A_STAGE : A_TILE_BYTES) >> 4));
                 const uint64_t alo = F16 ? ahi + (uint64_t)(A_TILE_BYTES >> 4)
                                          : alo0 + (uint64_t)(as * (A_TILE_BYTES >> 4));
-                const uint32_t first = kc > 0 ? 1u : 0u;
+                const int seg = p.ksplit > 1 ? kc * p.ksplit / p.num_k_chunks : 0;
+                const uint32_t first = seg == prev_seg ? 1u : 0u;           // a segment's first chunk overwrites
+                const uint32_t cfirst = kc > 0 ? 1u : 0u;                   // the correction accumulator spans all of K
+                prev_seg = seg;
                 for (int part = 0; part < 2; ++part) {
                     for (int nbk = 0; nbk < p.nb; ++nbk) {
                         mbar_wait(b_full + bs, bph);
                         tc_fence_after();
                         const uint64_t bd = b0 + (uint64_t)(bs * (B_TILE_BYTES >> 4));
-                        const uint32_t d_tmem = tmem_base + buf * (uint32_t)p.acc_stride + (uint32_t)(nbk * BN);
-                        const uint32_t c_tmem = d_tmem + c_off;
+                        const uint32_t t0 = tmem_base + buf * (uint32_t)p.acc_stride + (uint32_t)(nbk * BN);
+                        const uint32_t d_tmem = t0 + seg_offset(seg, p.seg_w);
+                        const uint32_t c_tmem = t0 + c_off;
                         if (leader) {
                             if (part == 0) {
                                 // x_hi.w_hi into the main accumulator, x_lo.w_hi into the correction one
@@ -616,7 +648,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)      // 32-byte steps inside the swizzled row
                                     mma_issue<F16, PAIR>(d_tmem, ahi + 2 * k, bd + 2 * k, idesc, 1u);
-                                mma_issue<F16, PAIR>(c_tmem, alo, bd, idesc, first | corr_first);
+                                mma_issue<F16, PAIR>(c_tmem, alo, bd, idesc, cfirst | corr_first);
 #pragma unroll
                                 for (int k = 1; k < BK / 8; ++k)
                                     mma_issue<F16, PAIR>(c_tmem, alo + 2 * k, bd + 2 * k, idesc, 1u);
@@ -761,6 +793,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         tmem_ld32(t_lane + (uint32_t)BN, u);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] += u[i];
+                        for (int sg = 1; sg < p.ksplit; ++sg) {
+                            tmem_ld32(t_lane + seg_offset(sg, p.seg_w), u);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) v[i] += u[i];
+                        }
                     }
                     float gm = -INFINITY;
 #pragma unroll
@@ -823,13 +860,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
                         const bool finite_row = finite_f(gm) && finite_f(gs);
                         if (!finite_row) {
-                            if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                            if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                             else atomicAdd(p.status, 1ull);
                         }
                         if (p.flags) {
                             p.lse[row] = gm + logf(gs);
                             if (finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
-                                flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                                flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                         }
                     }
                 } else {
@@ -850,6 +887,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 if (p.split) {                                                                         \
                     _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8)                               \
                         tmem_add8(t_lane + (uint32_t)(BN + (cb) + i8), (v) + i8);                      \
+                    for (int sg = 1; sg < p.ksplit; ++sg)                                              \
+                        _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8)                           \
+                            tmem_add8(t_lane + seg_offset(sg, p.seg_w) + (uint32_t)((cb) + i8), (v) + i8);      \
                 }                                                                                      \
                 /* eight columns at a time, fenced: with all 64 scale / bias values of a chunk loaded */ \
                 /* ahead of the FMAs the second (in-flight) TMEM buffer no longer fits in registers */    \
@@ -1020,7 +1060,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             if (live) {
                 // the thread whose columns hold the maximum always counts it; anything else above tau is a near-tie
                 const bool owner = garg >= col0 + cb_lo && garg < col0 + cb_hi;
-                if (p.flags && near >= (owner ? 2 : 1)) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                if (p.flags && near >= (owner ? 2 : 1)) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                 if (rank == 0 && h == 0) {
                     if (p.label) __stcs(p.label + row, garg);
                     if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
@@ -1028,14 +1068,14 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     if (!finite_row) {
                         // With a re-scoring pass the row is handed over (flag 2): an fp16 overflow of a
                         // finite input would otherwise be reported as non-finite data.
-                        if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                        if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                         else atomicAdd(p.status, 1ull);
                     }
                     if (p.flags) {
                         p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
                         // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, which is always the top
                         // one (p (1 - p) rises up to 1/2 and no class but the top one can pass it): p_top = inv
-                        if (finite_row && inv * (1.0f - inv) > risk_thr) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                        if (finite_row && inv * (1.0f - inv) > risk_thr) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                     }
                 }
             }
@@ -1104,7 +1144,7 @@ __global__ void __launch_bounds__(kFixWarps * 32)
 gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int c_pad,
                       const float* __restrict__ W, const float* __restrict__ b,
                       const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
-                      const float* __restrict__ lse, float* proba,
+                      const float* __restrict__ lse, const float* __restrict__ ezr, float* proba,
                       float* decision, int32_t* label, float* maxprob, unsigned long long* rescored,
                       unsigned long long* status) {
     extern __shared__ float fix_smem[];
@@ -1133,7 +1173,23 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
         __syncwarp();
-        const float thr = fminf(0.01f, 0.9f * pmax);    // classes that carry weight, or rival the maximum
+        // Which classes get an fp32 logit: the rivals of the maximum (near-ties), and every class whose own
+        // probability the error bound `ez` of this row could move by more than ~4e-6 (p (1 + mass) ez with
+        // p >= 2e-6 / ez).  What stays behind enters the row only through the renormalisation, as the
+        // probability-weighted MEAN of its logit errors: random parts average out over the many small classes,
+        // the systematic part of the truncation error is ~1/8 of the maximum `ez` is built on (measured mean /
+        // max, profiles/r02_gemm_accumulation_error.txt; 1/4 is assumed); the threshold is lowered until
+        // mass_left * ez / 4 * p_max <= 4e-6.
+        const float ez = ezr[row];
+        float thr = fminf(fmaxf(2e-6f / ez, 1e-4f), 0.9f * pmax);
+        for (int round = 0; round < 3; ++round) {
+            float left = 0.0f;
+            for (int c = lane; c < C; c += 32) left += prow[c] < thr ? prow[c] : 0.0f;
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) left += __shfl_xor_sync(0xffffffffu, left, off);
+            if (left * ez * 0.25f * pmax <= 4e-6f) break;
+            thr *= 0.25f;
+        }
         float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
         int best = 0, nq = 0;
         // queue of selected classes in ascending order, worked off four at a time
@@ -1308,6 +1364,7 @@ struct ShortParams {
     unsigned* flags;
     unsigned* flag_list;
     unsigned* n_flagged;
+    float* ezr;                 // unused here (whole rows are re-scored): nullptr
 };
 
 // A warp's 32 rows x C values, one row per lane in registers, to their place in an [n][C] matrix: staged in
@@ -1584,10 +1641,10 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
                 if (p.maxprob) __stcs(p.maxprob + row, inv);
                 const bool finite_row = finite_f(gm) && finite_f(gs);
                 if (!finite_row) {
-                    if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                    if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                     else atomicAdd(p.status, 1ull);
                 } else if (p.flags && (risk || gnear >= 2)) {
-                    flag_row(p.flags, p.flag_list, p.n_flagged, row);
+                    flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                 }
             }
         }
@@ -1910,6 +1967,11 @@ struct GemmPlan {
     bool adaptive = true;
     int c_pad = 0;
     uint64_t rows_seen = 0, rescored_seen = 0;     // since the layout was last chosen (lr_score_host holds the staging lock)
+    // Device-path feedback: after every launch the status block is copied (asynchronously) to this pinned mirror;
+    // the next launch reads whatever has arrived -- rows scored [3] and rows re-scored [1] as of the same point of
+    // the stream -- and applies the rule of gemm_feedback without a synchronisation.
+    unsigned long long* mirror = nullptr;
+    unsigned long long mirror_rows0 = 0, mirror_resc0 = 0;
     bool configured[64] = {false};
     bool fix_configured[64] = {false};
     bool fixup = true;          // re-score near-tie rows in fp32 (LRS_GEMM_FIXUP=0 turns it off)
@@ -2092,6 +2154,8 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     LRS_CUDA(cudaMalloc(&g->w_norm, g->c_pad * sizeof(float)));
     LRS_CUDA(cudaMalloc(&g->col_scale, g->d64 * sizeof(float)));
     LRS_CUDA(cudaMalloc(&g->w_mul, d * sizeof(double)));
+    LRS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g->mirror), 4 * sizeof(unsigned long long), cudaHostAllocDefault));
+    std::memset(g->mirror, 0, 4 * sizeof(unsigned long long));
     if (d4 != d) LRS_CUDA(cudaMalloc(&g->w32_pad, (size_t)C * d4 * sizeof(float)));
     // padding (classes beyond C, columns beyond d) stays zero across reloads
     LRS_CUDA(cudaMemset(g->w_hi, 0, b32));
@@ -2148,6 +2212,7 @@ void gemm_destroy(Model& m) {
     cudaFree(m.gemm->col_scale);
     cudaFree(m.gemm->w_mul);
     cudaFree(m.gemm->w_norm);
+    if (m.gemm->mirror) cudaFreeHost(m.gemm->mirror);
     delete m.gemm;
     m.gemm = nullptr;
 }
@@ -2188,6 +2253,17 @@ cudaError_t launch_gemm_kernel(const cudaLaunchConfig_t& cfg, bool pair, const C
 
 int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix) {
     GemmPlan* g = m.gemm;
+    if (g->adaptive && g->active.load() == 0 && g->has[1]) {
+        // what the mirror shows of earlier launches on this model (it may lag by a launch or two)
+        const unsigned long long rows = *reinterpret_cast<volatile unsigned long long*>(g->mirror + 3);
+        const unsigned long long resc = *reinterpret_cast<volatile unsigned long long*>(g->mirror + 1);
+        if (rows - g->mirror_rows0 >= 4096 && (resc - g->mirror_resc0) * 5 > rows - g->mirror_rows0) {
+            g->active = 1;
+        } else if (rows - g->mirror_rows0 > (1ull << 24)) {          // judge on recent data only
+            g->mirror_rows0 = rows;
+            g->mirror_resc0 = resc;
+        }
+    }
     GemmPlan::Layout& L = g->layout[g->active.load()];
     // X as the two arithmetics read it: fp32 boxes of 64 columns, unswizzled (3xFP16: converted in place) or of
     // 32 columns, 128-byte swizzle (3xTF32)
@@ -2215,17 +2291,19 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     unsigned* flags = nullptr;
     unsigned* flag_list = nullptr;
     float* lse = nullptr;
+    float* ezr = nullptr;
     AsyncScratch scratch;
     scratch.s = a.stream;
     const size_t stat_bytes = 2 * kMaxSample * sizeof(float);
     const size_t lse_bytes = fixup ? ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256 : 0;
-    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + 3 * lse_bytes, a.stream));
+    LRS_CUDA(cudaMallocAsync(&scratch.p, 256 + stat_bytes + 4 * lse_bytes, a.stream));
     float* x_scale = reinterpret_cast<float*>(scratch.p);
     float* rowstat = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256);
     if (fixup) {
         lse = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes);
         flags = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + lse_bytes);
         flag_list = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + 2 * lse_bytes);
+        ezr = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + 3 * lse_bytes);
         LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows * sizeof(unsigned), a.stream));
     }
     LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));          // ticket, decisions, [8] = length of the re-scoring list
@@ -2236,6 +2314,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     p.flags = flags;
     p.flag_list = flag_list;
     p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
+    p.ezr = ezr;
     p.lse = lse;
     p.n_rows = a.n_rows;
     p.n_features = d_eff;
@@ -2269,6 +2348,15 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     }
     p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
     p.acc_stride = 128;
+    // long rows of a model with at most 64 classes: up to three main accumulators, one per third of K (see GemmParams)
+    p.ksplit = 1;
+    if (L.split && L.mma_n <= 64 && !L.pair && L.nb == 1) {
+        const int most = L.mma_n <= 32 ? 7 : 3;
+        p.ksplit = (d_eff + 1364) / 1365;
+        p.ksplit = p.ksplit < 1 ? 1 : (p.ksplit > most ? most : p.ksplit);
+    }
+    p.seg_w = L.mma_n <= 32 ? 32 : 64;
+    if (const char* e = getenv("LRS_GEMM_KSPLIT")) p.ksplit = (atoi(e) >= 1 && atoi(e) <= p.ksplit) ? atoi(e) : p.ksplit;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
     p.bias = g->bias;
     p.col_inv_scale = g->col_inv_scale;
@@ -2323,7 +2411,8 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // 1.68e-5 / 6.5e-6 for 3xFP16 on one / split accumulators, 3.1e-5 / 1.08e-5 for 3xTF32), plus a fifth.  It
     // grows with the number of accumulation steps, i.e. linearly with the row length (measured at d = 256, 1024,
     // 4096, 16384: 6.3e-6, 1.68e-5, 6.7e-5, 2.4e-4), a little slower than that below 1024.
-    const float len = (float)(d_eff > 384 ? d_eff : 384) / 1024.0f;
+    const int d_acc = d_eff / p.ksplit;              // row length behind one main accumulator
+    const float len = (float)(d_acc > 384 ? d_acc : 384) / 1024.0f;
     // Both arithmetics are enqueued; the kernel x_scale_kernel did not choose returns at once (a few us).
     if (g->force != 2) {
         p.num_k_chunks = (d_eff + BK16 - 1) / BK16;
@@ -2348,7 +2437,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
                 g->fix_configured[dev] = true;
             }
             gemm_fixup_sel_kernel<<<m.num_sms * 3, kFixWarps * 32, fsm, a.stream>>>(
-                a.X, a.ldx, d_eff, m.n_scores, c_pad, w_fix, m.b, flag_list, p.n_flagged, lse, a.proba, a.decision,
+                a.X, a.ldx, d_eff, m.n_scores, c_pad, w_fix, m.b, flag_list, p.n_flagged, lse, ezr, a.proba, a.decision,
                 a.label, a.maxprob, m.status + 1, m.status);
         } else {
             gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_eff, m.n_scores, w_fix, m.b,
@@ -2358,6 +2447,8 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         count_launch();
         LRS_CUDA(cudaGetLastError());
     }
+    if (g->adaptive && g->active.load() == 0 && g->has[1])
+        LRS_CUDA(cudaMemcpyAsync(g->mirror, m.status, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, a.stream));
     return LR_OK;
 }
 
@@ -2428,6 +2519,7 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     p.flags = flags;
     p.flag_list = flag_list;
     p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
+    p.ezr = nullptr;
     const size_t smem = (size_t)SrSmem::op + (size_t)p.op_stages * kSrOpBytes + (size_t)p.raw_stages * p.stage_bytes + 1024;
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
     const int grid = (int)(n_tiles < m.num_sms ? n_tiles : m.num_sms);

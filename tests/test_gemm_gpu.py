@@ -321,10 +321,12 @@ def test_gemm_fitted_on_raw_measurements(eng):
     clf.close()
 
 
-@pytest.mark.parametrize("d,c,n", [(4096, 64, 6000), (4096, 1000, 3000), (16384, 64, 3000), (16384, 1000, 1500)])
+@pytest.mark.parametrize("d,c,n", [(4096, 64, 6000), (4096, 1000, 3000), (16384, 64, 3000), (16384, 1000, 1500),
+                                   (8192, 20, 3000), (2048, 48, 5000)])
 def test_gemm_long_rows(eng, d, c, n):
     """The truncating accumulation error grows with the number of k-steps: the re-scoring band has to grow
-    with the row length (it was measured at d = 1024)."""
+    with the row length (it was measured at d = 1024); models of at most 64 classes sum long rows in up to
+    three (seven: at most 32 classes) TMEM accumulators instead."""
     mlapi, lib = eng
     W, b = synth.make_model(d, c, 40 + c)
     X = synth.make_X(n, d, 41)
