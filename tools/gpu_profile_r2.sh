@@ -12,10 +12,14 @@ timeout 300 python bench.py --impl reference --steps 5 --warmup 2 > gpurun_out/r
 timeout 300 python bench.py --workload cfg0 --steps 20 --warmup 5 > gpurun_out/r2_bench_cfg0.json 2>/dev/null
 timeout 900 python tools/shape_sweep.py --out gpurun_out/r2_shape_sweep.json > gpurun_out/r2_shape_sweep.log 2>&1; echo "sweep exit $?"
 timeout 600 python tools/refit_bench_general.py --out gpurun_out/r2_refit_general.json > /dev/null 2>&1; echo "refit bench exit $?"
+timeout 300 python tools/rescoring_rate.py > gpurun_out/r2_rescoring_rate.txt 2>&1
+timeout 300 python tools/gemm_kappa.py > gpurun_out/r2_gemm_accumulation_error.txt 2>&1
+timeout 300 python tools/gemm_kappa.py --short >> gpurun_out/r2_gemm_accumulation_error.txt 2>&1
+timeout 300 python tools/latency_single.py > gpurun_out/r2_latency_single.json 2>/dev/null
 if [ "$1" != "skip-ncu" ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
   timeout 600 $CMD > gpurun_out/r2_plain.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:lrs -c 400 --csv \
       --log-file gpurun_out/r2_launches_default.csv $CMD > gpurun_out/r2_ncu_list.log 2>&1
   echo "ncu list exit $?"
   CMD3="python bench.py --workload cfg3 --rows 400000 --steps 2 --warmup 3 --no-e2e --no-cpu"
