@@ -317,6 +317,25 @@ def score_workload(ctx, name, rows, steps, warmup, want, logit_scale, e2e_steps,
         sync_all()
         copy_s = max_over_ranks(c0.elapsed_time(c1) / 2 * 1e-3)
         h2d_bytes = int(n_e * d * 4)
+        # ... and with the result going back at the same time on a second stream (what a step moves in all): where
+        # the host's memory fabric rather than one direction of the link is the limit, this is the figure to beat
+        bidir_s = None
+        if P is not None:
+            tp = torch.from_numpy(ph.array)
+            side = torch.cuda.Stream(dev)
+            sync_all()
+            b0, b1, b2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            b0.record(stream)
+            side.wait_stream(stream)
+            for _ in range(2):
+                Xd.copy_(th, non_blocking=True)
+                with torch.cuda.stream(side):
+                    tp.copy_(P[:n_e], non_blocking=True)
+            b1.record(stream)
+            with torch.cuda.stream(side):
+                b2.record(side)
+            sync_all()
+            bidir_s = max_over_ranks(max(b0.elapsed_time(b1), b0.elapsed_time(b2)) / 2 * 1e-3)
         e2e = {"value": world * n_e / dt, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                "d2h_bytes_per_step": int(n_e * n_out * 4), "rows_per_step_per_gpu": n_e,
                "steps": e2e_steps, "ms_per_step": dt * 1e3,
@@ -324,8 +343,11 @@ def score_workload(ctx, name, rows, steps, warmup, want, logit_scale, e2e_steps,
                "h2d_gbs": world * h2d_bytes / dt / 1e9,
                "h2d_ceiling_gbs": world * h2d_bytes / copy_s / 1e9,
                "frac_of_h2d_ceiling": copy_s / dt,
+               "copy_ceiling_bidir_gbs": (world * (h2d_bytes + n_e * n_out * 4) / bidir_s / 1e9) if bidir_s else None,
+               "frac_of_bidir_ceiling": (bidir_s / dt) if bidir_s else None,
                "h2d_ceiling_note": "all ranks at once, bare cudaMemcpyAsync of the same pinned X, aggregate GB/s, "
-                                   "max time over ranks",
+                                   "max time over ranks; bidir = the same with P copied back concurrently on a second "
+                                   "stream, all bytes counted",
                "host_cpus_bound_per_rank": ctx.numa_cpus,
                "matches_device_result": same}
         xh.free(); ph.free()
