@@ -83,6 +83,7 @@ static int select_path(const Model& m, const ScoreArgs& a) {
         return LR_PATH_NARROW;
     }
     if (gemm_supports(m, a)) return LR_PATH_GEMM;
+    if (!m.groups.empty() && a.n_rows < (int64_t)1 << 31) return LR_PATH_GEMM;     // > 2048 classes: class groups
     return LR_PATH_GENERIC;
 }
 
@@ -90,7 +91,7 @@ static int dispatch(const Model& m, const ScoreArgs& a) {
     switch (select_path(m, a)) {
         case LR_PATH_NARROW: return narrow_launch(m, a);
         case LR_PATH_WIDE: return wide_launch(m, a);
-        case LR_PATH_GEMM: return gemm_launch(m, a);
+        case LR_PATH_GEMM: return m.groups.empty() ? gemm_launch(m, a) : gemm_groups_launch(m, a);
         case LR_PATH_GENERIC: return generic_launch(m, a);
     }
     return fail(LR_ERR_INVALID, "unknown path id");
@@ -150,14 +151,15 @@ int lr_model_create(const double* coef, const double* intercept, int32_t n_score
     auto bail = [&](int code) { lr_model_destroy(reinterpret_cast<lr_model*>(m)); return code; };
     if (cudaMalloc(&m->W, nw * sizeof(float)) != cudaSuccess ||
         cudaMalloc(&m->b, n_scores * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&m->status, 4 * sizeof(unsigned long long)) != cudaSuccess)
+        cudaMalloc(&m->status, 8 * sizeof(unsigned long long)) != cudaSuccess)      // [4..7]: class groups' counters
         return bail(fail(LR_ERR_CUDA, std::string("cudaMalloc(model): ") + cudaGetErrorString(cudaGetLastError())));
     if (cudaMemcpy(m->W, w32.data(), nw * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMemcpy(m->b, b32.data(), n_scores * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
-        cudaMemset(m->status, 0, 4 * sizeof(unsigned long long)) != cudaSuccess)
+        cudaMemset(m->status, 0, 8 * sizeof(unsigned long long)) != cudaSuccess)
         return bail(fail(LR_ERR_CUDA, std::string("upload(model): ") + cudaGetErrorString(cudaGetLastError())));
     if ((rc = narrow_prepare(*m, w32.data(), b32.data())) != LR_OK) return bail(rc);
     if ((rc = gemm_prepare(*m, coef, intercept)) != LR_OK) return bail(rc);
+    if ((rc = gemm_groups_prepare(*m, coef, intercept)) != LR_OK) return bail(rc);
     m->stage = new HostStage();
     *out = reinterpret_cast<lr_model*>(m);
     return LR_OK;
@@ -178,6 +180,7 @@ int lr_model_update(lr_model* h, const double* coef, const double* intercept) {
     LRS_CUDA(cudaMemcpy(m->b, b32.data(), m->n_scores * sizeof(float), cudaMemcpyHostToDevice));
     int rc;
     if ((rc = narrow_prepare(*m, w32.data(), b32.data())) != LR_OK) return rc;
+    if ((rc = gemm_groups_load(*m, coef, intercept)) != LR_OK) return rc;
     return gemm_load(*m, coef, intercept);
 }
 
@@ -188,6 +191,7 @@ void lr_model_destroy(lr_model* h) {
     cudaDeviceSynchronize();
     if (m->stage) { m->stage->release(); delete m->stage; }
     gemm_destroy(*m);
+    gemm_groups_destroy(*m);
     cudaFree(m->W); cudaFree(m->b); cudaFree(m->Wn); cudaFree(m->bn); cudaFree(m->status);
     delete m;
 }
@@ -247,9 +251,10 @@ int lr_model_take_rescored(lr_model* h, void* stream, uint64_t* out) {
     Model* m = reinterpret_cast<Model*>(h);
     DeviceGuard guard(m->device);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    unsigned long long v = 0;                      // the device counter only ever grows
-    LRS_CUDA(cudaMemcpyAsync(&v, m->status + 1, sizeof(v), cudaMemcpyDeviceToHost, s));
+    unsigned long long w[8] = {};                  // the device counters only ever grow; [5] = the class groups' share
+    LRS_CUDA(cudaMemcpyAsync(w, m->status, sizeof(w), cudaMemcpyDeviceToHost, s));
     LRS_CUDA(cudaStreamSynchronize(s));
+    const unsigned long long v = w[1] + w[5];
     *out = v - m->rescored_taken.exchange(v);
     return LR_OK;
 }
@@ -259,9 +264,10 @@ int lr_model_take_fallback(lr_model* h, void* stream, uint64_t* out) {
     Model* m = reinterpret_cast<Model*>(h);
     DeviceGuard guard(m->device);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    unsigned long long v = 0;                      // the device counter only ever grows
-    LRS_CUDA(cudaMemcpyAsync(&v, m->status + 2, sizeof(v), cudaMemcpyDeviceToHost, s));
+    unsigned long long w[8] = {};
+    LRS_CUDA(cudaMemcpyAsync(w, m->status, sizeof(w), cudaMemcpyDeviceToHost, s));
     LRS_CUDA(cudaStreamSynchronize(s));
+    const unsigned long long v = w[2] + w[6];
     *out = v - m->fallback_taken.exchange(v);
     return LR_OK;
 }

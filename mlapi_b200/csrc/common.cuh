@@ -7,6 +7,7 @@
 
 #include <atomic>
 #include <string>
+#include <vector>
 
 #include "../../include/lrscore.h"
 
@@ -53,6 +54,10 @@ struct Model {
     std::atomic<unsigned long long> fallback_taken{0};
 
     GemmPlan* gemm = nullptr;
+    // more than 2048 classes: class groups of equal size, each an ordinary tensor-path model over a slice of W / b
+    // (which they do not own); see gemm_groups_launch
+    std::vector<Model*> groups;
+    int group_classes = 0;
     HostStage* stage = nullptr;
     int64_t host_chunk_rows = 0;
 };
@@ -66,6 +71,11 @@ struct ScoreArgs {
     int32_t* label;
     float* maxprob;
     cudaStream_t stream;
+    // a model that is one class group of a larger one (more than 2048 classes, gemm_groups_launch): where its columns
+    // sit in the caller's proba / decision rows, and where the log-sum-exp of its own classes goes
+    int64_t out_pitch = 0;      // 0: n_scores
+    int out_col0 = 0;
+    float* lse_out = nullptr;
 };
 
 // per-family entry points (each returns LR_OK / error code, sets last error)
@@ -85,7 +95,11 @@ void gemm_destroy(Model& m);
 void gemm_feedback(Model& m, int64_t rows, uint64_t rescored_total);
 int gemm_active_layout(const Model& m);
 int gemm_launch(const Model& m, const ScoreArgs& a);
-bool gemm_short_rows(const Model& m, const ScoreArgs& a);   // 13..32 classes, dense rows of <= 64 floats: the short-row tensor form
+bool gemm_short_rows(const Model& m, const ScoreArgs& a);
+int gemm_groups_prepare(Model& m, const double* coef, const double* intercept);    // > 2048 classes
+int gemm_groups_load(Model& m, const double* coef, const double* intercept);
+int gemm_groups_launch(const Model& m, const ScoreArgs& a);
+void gemm_groups_destroy(Model& m);   // 13..32 classes, dense rows of <= 64 floats: the short-row tensor form
 
 // ---- device helpers ----------------------------------------------------------------------------
 #ifdef __CUDACC__

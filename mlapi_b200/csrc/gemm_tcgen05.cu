@@ -133,6 +133,8 @@ struct GemmParams {
     unsigned* n_flagged;    // ... and how many there are
     float* ezr;             // [n_rows] per flagged row: the logit error bound it was flagged under
     float* lse;             // [n_rows] log-sum-exp of the row as the tensor path saw it (for the re-scoring pass)
+    int64_t out_pitch;      // floats between rows of proba / decision (n_classes, or the full class count when this
+    int out_col0;           // model is one class group of a larger one: then its columns start at out_col0)
     int vec_store;          // 1: rows of proba/decision are 16-byte aligned (C % 4 == 0, base aligned);
                             // 2: 32-byte aligned as well (C % 8 == 0): 256-bit stores, whole sectors per lane
 };
@@ -810,7 +812,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                     for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
                     if (p.decision && live) {
-                        float* zr = p.decision + row * p.n_classes;
+                        float* zr = p.decision + row * p.out_pitch + p.out_col0;
                         if (n_real == 32 && p.vec_store) {
 #pragma unroll
                             for (int i = 0; i < 32; i += 4)
@@ -838,7 +840,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] *= inv;
                         if (live) {
-                            float* pr = p.proba + row * p.n_classes;
+                            float* pr = p.proba + row * p.out_pitch + p.out_col0;
                             if (n_real == 32 && p.vec_store == 2) {
 #pragma unroll
                                 for (int i = 0; i < 32; i += 8) st_cs_v8(pr + i, v + i);
@@ -863,11 +865,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                             else atomicAdd(p.status, 1ull);
                         }
-                        if (p.flags) {
-                            p.lse[row] = gm + logf(gs);
-                            if (finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
-                                flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
-                        }
+                        if (p.lse) p.lse[row] = gm + logf(gs);
+                        if (p.flags && finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
+                            flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                     }
                 } else {
                     tc_fence_before();
@@ -905,7 +905,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             do {                                                                                       \
                 LRS_CHUNK_LOGITS(v, cb);                                                               \
                 if (p.decision && live) {                                                              \
-                    const int64_t off = row * p.n_classes + col0 + (cb);                               \
+                    const int64_t off = row * p.out_pitch + p.out_col0 + col0 + (cb);                  \
                     if ((cb) + 32 <= n_real && p.vec_store) {                                          \
                         _Pragma("unroll") for (int i = 0; i < 32; i += 4)                              \
                             __stcs(reinterpret_cast<float4*>(p.decision + off + i),                    \
@@ -1021,7 +1021,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     near += (v)[i] > near_thr ? 1 : 0;                                                 \
                 }                                                                                      \
                 if (p.proba && live) {                                                                 \
-                    const int64_t off = row * p.n_classes + col0 + (cb);                               \
+                    const int64_t off = row * p.out_pitch + p.out_col0 + col0 + (cb);                  \
                     if ((cb) + 32 <= n_real && p.vec_store == 2) {                                     \
                         _Pragma("unroll") for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, (v) + i); \
                     } else if ((cb) + 32 <= n_real && p.vec_store) {                                   \
@@ -1071,12 +1071,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                         else atomicAdd(p.status, 1ull);
                     }
-                    if (p.flags) {
-                        p.lse[row] = gm + logf(gs);           // non-finite rows store a non-finite value here
-                        // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, which is always the top
-                        // one (p (1 - p) rises up to 1/2 and no class but the top one can pass it): p_top = inv
-                        if (finite_row && inv * (1.0f - inv) > risk_thr) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
-                    }
+                    if (p.lse) p.lse[row] = gm + logf(gs);    // non-finite rows store a non-finite value here
+                    // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, which is always the top
+                    // one (p (1 - p) rises up to 1/2 and no class but the top one can pass it): p_top = inv
+                    if (p.flags && finite_row && inv * (1.0f - inv) > risk_thr)
+                        flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
                 }
             }
         }
@@ -1141,7 +1140,7 @@ constexpr int kFixQueue = 64;          // selected classes waiting for their dot
 // grid-stride over the list, one warp per flagged row.  Dynamic shared memory: [kFixWarps][c_pad] floats (the
 // row of P a warp works on) + [kFixWarps][kFixQueue] ints.
 __global__ void __launch_bounds__(kFixWarps * 32)
-gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int c_pad,
+gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int c_pad, int64_t out_pitch, int out_col0,
                       const float* __restrict__ W, const float* __restrict__ b,
                       const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
                       const float* __restrict__ lse, const float* __restrict__ ezr, float* proba,
@@ -1159,11 +1158,11 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
         if (!finite_f(L)) {
             // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
             // score the whole row in fp32, which also settles whether the input really is non-finite
-            score_row_warp(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status);
+            score_row_warp_pitched(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status, out_pitch, out_col0);
             if (lane == 0) atomicAdd(rescored, 1ull);
             continue;
         }
-        float* pr = proba + row * C;
+        float* pr = proba + row * out_pitch + out_col0;
         float pmax = 0.0f;
         for (int c = lane; c < C; c += 32) {             // independent loads: one trip to memory for the row
             const float v = __ldcg(pr + c);
@@ -1214,7 +1213,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
                     __syncwarp();
                     if (lane == 0) {
                         prow[cj] = q;
-                        if (decision) decision[row * C + cj] = z;
+                        if (decision) decision[row * out_pitch + out_col0 + cj] = z;
                     }
                 }
                 done += take;
@@ -1258,7 +1257,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
 // /predict pattern): there is no row of P to pick classes from, so a whole CTA re-scores every class
 // of the flagged row, eight warps splitting the classes, four classes per step.
 __global__ void __launch_bounds__(256)
-gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
+gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int64_t out_pitch, int out_col0,
                        const float* __restrict__ W, const float* __restrict__ b,
                        const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
                        float* decision, int32_t* label, float* maxprob,
@@ -1284,7 +1283,7 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C,
             for (int u = 0; u < 4; ++u) {
                 if (c + u >= c_hi) break;
                 const float z = z4[u] + __ldg(b + c + u);
-                if (decision && lane == 0) decision[row * C + c + u] = z;
+                if (decision && lane == 0) decision[row * out_pitch + out_col0 + c + u] = z;
                 if (z > m) { ssum = ssum * expf(m - z) + 1.0f; m = z; arg = c + u; }
                 else ssum += expf(z - m);
             }
@@ -2306,6 +2305,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         ezr = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch.p) + 256 + stat_bytes + 3 * lse_bytes);
         LRS_CUDA(cudaMemsetAsync(flags, 0, (size_t)a.n_rows * sizeof(unsigned), a.stream));
     }
+    if (a.lse_out) lse = a.lse_out;                 // a class group hands its log-sum-exp to the caller
     LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));          // ticket, decisions, [8] = length of the re-scoring list
     x_scale_kernel<true><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
                                                               g->inv_cscale_max, g->force, x_scale, rowstat);
@@ -2370,9 +2370,11 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     p.label = a.label;
     p.maxprob = a.maxprob;
     p.status = m.status;
-    const bool al = (m.n_scores % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) &&
+    p.out_pitch = a.out_pitch ? a.out_pitch : m.n_scores;
+    p.out_col0 = a.out_col0;
+    const bool al = (p.out_pitch % 4 == 0) && (p.out_col0 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 15u) == 0) &&
                     ((reinterpret_cast<uintptr_t>(a.decision) & 15u) == 0);
-    const bool al32 = al && (m.n_scores % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 31u) == 0);
+    const bool al32 = al && (p.out_pitch % 8 == 0) && (p.out_col0 % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 31u) == 0);
     p.vec_store = al32 ? 2 : (al ? 1 : 0);
 
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
@@ -2437,10 +2439,12 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
                 g->fix_configured[dev] = true;
             }
             gemm_fixup_sel_kernel<<<m.num_sms * 3, kFixWarps * 32, fsm, a.stream>>>(
-                a.X, a.ldx, d_eff, m.n_scores, c_pad, w_fix, m.b, flag_list, p.n_flagged, lse, ezr, a.proba, a.decision,
+                a.X, a.ldx, d_eff, m.n_scores, c_pad, p.out_pitch, p.out_col0, w_fix, m.b, flag_list, p.n_flagged, lse, ezr,
+                a.proba, a.decision,
                 a.label, a.maxprob, m.status + 1, m.status);
         } else {
-            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_eff, m.n_scores, w_fix, m.b,
+            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_eff, m.n_scores, p.out_pitch,
+                                                                       p.out_col0, w_fix, m.b,
                                                                        flag_list, p.n_flagged, a.decision, a.label,
                                                                        a.maxprob, m.status + 1, m.status);
         }
@@ -2587,13 +2591,202 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
         s.X = scratch;
         s.ldx = d4;
         s.n_rows = n;
-        if (a.proba) s.proba = a.proba + r0 * C;
-        if (a.decision) s.decision = a.decision + r0 * C;
+        const int64_t pitch = a.out_pitch ? a.out_pitch : C;
+        if (a.proba) s.proba = a.proba + r0 * pitch;
+        if (a.decision) s.decision = a.decision + r0 * pitch;
+        if (a.lse_out) s.lse_out = a.lse_out + r0;
         if (a.label) s.label = a.label + r0;
         if (a.maxprob) s.maxprob = a.maxprob + r0;
         rc = gemm_launch_aligned(m, s, d4, w_fix);
     }
     return rc;
+}
+
+// ---- more than 2048 classes: class groups --------------------------------------------------------------------
+// A model of C > 2048 classes is cut into G = ceil(C / 2048) groups of equal size (a multiple of 8 classes; the last
+// takes what is left), each an ordinary tensor-path model over its slice of W / b.  A call scores the batch once per
+// group -- each writes the softmax over its OWN classes into its columns of the caller's rows, and per row the
+// log-sum-exp, best class and best probability of the group -- then one kernel per row combines the groups: row
+// log-sum-exp L = logsumexp_g(lse_g), every group's columns scaled by exp(lse_g - L), the best class taken across
+// groups (lowest group on a tie; two groups whose best logits lie within the accumulation error band of each other
+// have those two logits recomputed in fp32).  X is read G times (it stays in L2 for batches of a few hundred MB);
+// P is written once and rescaled once.  Replaces the SIMT fallback these models ran on (one warp per row: ~0.03 TB/s).
+namespace {
+
+constexpr int kGroupClasses = 2048;
+
+__global__ void __launch_bounds__(256)
+groups_combine_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int C, int G, int S,
+                      const float* __restrict__ W, const float* __restrict__ b, float band,
+                      float* __restrict__ lse_g /* [G][n]: in: group log-sum-exp, out: scale of the group's columns */,
+                      const int32_t* __restrict__ label_g, const float* __restrict__ maxp_g,
+                      float* proba, int32_t* label, float* maxprob, unsigned long long* status) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
+        // lanes hold groups (G <= 32)
+        const float l = lane < G ? lse_g[(int64_t)lane * n_rows + row] : -CUDART_INF_F;
+        const float mp = lane < G ? maxp_g[(int64_t)lane * n_rows + row] : 1.0f;
+        const int lb = lane < G ? label_g[(int64_t)lane * n_rows + row] : 0;
+        float zbest = lane < G ? l + logf(mp) : -CUDART_INF_F;         // the group's largest logit
+        float m = l;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+        float e = lane < G ? expf(l - m) : 0.0f;
+        float ssum = e;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, off);
+        const float L = m + logf(ssum);
+        const float scale = e / ssum;                                  // exp(lse_g - L)
+        if (lane < G) lse_g[(int64_t)lane * n_rows + row] = scale;
+        // best group (lowest on a tie), runner-up
+        float z1 = zbest;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) z1 = fmaxf(z1, __shfl_xor_sync(0xffffffffu, z1, off));
+        unsigned win = __ballot_sync(0xffffffffu, zbest == z1);
+        int g1 = __ffs(win) - 1;
+        float z2 = lane == g1 ? -CUDART_INF_F : zbest;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) z2 = fmaxf(z2, __shfl_xor_sync(0xffffffffu, z2, off));
+        int best = __shfl_sync(0xffffffffu, lb, g1) + g1 * S;
+        float pbest = __shfl_sync(0xffffffffu, mp * scale, g1);
+        if (G > 1 && z1 - z2 <= band * fmaxf(1.0f, fabsf(z1))) {
+            // two groups' champions within the error band: their logits again, in fp32
+            const unsigned win2 = __ballot_sync(0xffffffffu, lane != g1 && zbest == z2);
+            const int g2 = __ffs(win2) - 1;
+            const int c1 = best, c2 = __shfl_sync(0xffffffffu, lb, g2) + g2 * S;
+            const float* x = X + row * ldx;
+            float a1 = 0.0f, a2 = 0.0f;
+            for (int k = lane; k < d; k += 32) {
+                const float xv = __ldg(x + k);
+                a1 = fmaf(xv, __ldg(W + (int64_t)c1 * d + k), a1);
+                a2 = fmaf(xv, __ldg(W + (int64_t)c2 * d + k), a2);
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) {
+                a1 += __shfl_xor_sync(0xffffffffu, a1, off);
+                a2 += __shfl_xor_sync(0xffffffffu, a2, off);
+            }
+            a1 += __ldg(b + c1);
+            a2 += __ldg(b + c2);
+            if (a2 > a1 || (a2 == a1 && c2 < c1)) { best = c2; pbest = expf(a2 - L); }
+            else pbest = expf(a1 - L);
+        }
+        if (lane == 0) {
+            if (label) label[row] = best;
+            if (maxprob) maxprob[row] = pbest;
+            if (!finite_f(L)) atomicAdd(status, 1ull);
+        }
+    }
+}
+
+// every group's columns of a row times that group's scale (groups_combine_kernel left it in lse_g)
+__global__ void __launch_bounds__(256)
+groups_scale_kernel(float* __restrict__ proba, int64_t n_rows, int C, int S, const float* __restrict__ scale_g) {
+    const int64_t total4 = n_rows * (int64_t)(C / 4);
+    if (C % 4 == 0 && (reinterpret_cast<uintptr_t>(proba) & 15u) == 0) {
+        for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total4; t += (int64_t)gridDim.x * 256) {
+            const int64_t row = t / (C / 4);
+            const int c = (int)(t - row * (C / 4)) * 4;               // S % 8 == 0: four columns never straddle groups
+            const float sc = __ldg(scale_g + (int64_t)(c / S) * n_rows + row);
+            float4 v = reinterpret_cast<float4*>(proba)[t];
+            v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+            reinterpret_cast<float4*>(proba)[t] = v;
+        }
+    } else {
+        const int64_t total = n_rows * (int64_t)C;
+        for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+            const int64_t row = t / C;
+            const int c = (int)(t - row * C);
+            proba[t] *= __ldg(scale_g + (int64_t)(c / S) * n_rows + row);
+        }
+    }
+}
+
+}  // namespace
+
+int gemm_groups_prepare(Model& m, const double* coef, const double* intercept) {
+    if (m.n_scores <= kGroupClasses || !encode_tiled()) return LR_OK;
+    const int C = m.n_scores, d = m.n_features;
+    const int G = (C + kGroupClasses - 1) / kGroupClasses;
+    if (G > 32) return LR_OK;                       // 65 536 classes and more: the generic path
+    const int S = ((C + G - 1) / G + 7) / 8 * 8;    // group size: columns of a group start 32-byte aligned
+    m.group_classes = S;
+    for (int g = 0; g < G; ++g) {
+        const int c0 = g * S, cnt = (c0 + S <= C ? S : C - c0);
+        if (cnt < 13) return fail(LR_ERR_INVALID, "internal: class group too small");
+        Model* sub = new Model();
+        sub->device = m.device;
+        sub->n_scores = cnt;
+        sub->n_features = d;
+        sub->n_out = cnt;
+        sub->num_sms = m.num_sms;
+        sub->W = m.W + (size_t)c0 * d;              // slices of the parent's device copies (not owned)
+        sub->b = m.b + c0;
+        sub->status = m.status + 4;                 // the groups' own counters; non-finite rows are counted once, by
+                                                    // groups_combine_kernel, into the model's
+        m.groups.push_back(sub);
+        const int rc = gemm_prepare(*sub, coef + (size_t)c0 * d, intercept + c0);
+        if (rc != LR_OK) return rc;
+        if (!sub->gemm) return fail(LR_ERR_CUDA, "internal: class group has no tensor-path plan");
+    }
+    return LR_OK;
+}
+
+int gemm_groups_load(Model& m, const double* coef, const double* intercept) {
+    for (size_t g = 0; g < m.groups.size(); ++g) {
+        const size_t c0 = g * (size_t)m.group_classes;
+        const int rc = gemm_load(*m.groups[g], coef + c0 * m.n_features, intercept + c0);
+        if (rc != LR_OK) return rc;
+    }
+    return LR_OK;
+}
+
+void gemm_groups_destroy(Model& m) {
+    for (Model* sub : m.groups) {
+        gemm_destroy(*sub);
+        delete sub;
+    }
+    m.groups.clear();
+}
+
+int gemm_groups_launch(const Model& m, const ScoreArgs& a) {
+    const int G = (int)m.groups.size(), C = m.n_scores, S = m.group_classes;
+    if (G == 0) return fail(LR_ERR_INVALID, "model has no class groups");
+    if (a.n_rows >= (int64_t)1 << 31) return fail(LR_ERR_INVALID, "gemm path needs fewer than 2^31 rows");
+    AsyncScratch scratch;
+    scratch.s = a.stream;
+    const size_t per = ((size_t)a.n_rows * sizeof(float) + 255) / 256 * 256;
+    LRS_CUDA(cudaMallocAsync(&scratch.p, 3 * (size_t)G * per, a.stream));
+    char* base = static_cast<char*>(scratch.p);
+    float* lse_g = reinterpret_cast<float*>(base);
+    int32_t* label_g = reinterpret_cast<int32_t*>(base + (size_t)G * per);
+    float* maxp_g = reinterpret_cast<float*>(base + 2 * (size_t)G * per);
+    // (the per-group arrays are [G][n_rows], dense; `per` is only the allocation granule)
+    for (int g = 0; g < G; ++g) {
+        ScoreArgs s = a;
+        s.out_pitch = C;
+        s.out_col0 = g * S;
+        s.lse_out = lse_g + (size_t)g * a.n_rows;
+        s.label = label_g + (size_t)g * a.n_rows;
+        s.maxprob = maxp_g + (size_t)g * a.n_rows;
+        const int rc = gemm_launch(*m.groups[g], s);
+        if (rc != LR_OK) return rc;
+    }
+    // what separates two groups' champions from a tie the tensor path cannot call: the band of its one-accumulator
+    // layout at this row length (gemm_launch_aligned)
+    const int d = m.n_features;
+    const float band = 2.0f * 2.0e-5f * (float)(d > 384 ? d : 384) / 1024.0f;
+    const int64_t want = (a.n_rows + 7) / 8;
+    const int grid = (int)(want < (int64_t)m.num_sms * 8 ? want : (int64_t)m.num_sms * 8);
+    groups_combine_kernel<<<grid, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d, C, G, S, m.W, m.b, band, lse_g, label_g, maxp_g,
+                                                      a.proba, a.label, a.maxprob, m.status);
+    count_launch();
+    if (a.proba) {
+        groups_scale_kernel<<<m.num_sms * 8, 256, 0, a.stream>>>(a.proba, a.n_rows, C, S, lse_g);
+        count_launch();
+    }
+    LRS_CUDA(cudaGetLastError());
+    return LR_OK;
 }
 
 }  // namespace lrs

@@ -10,11 +10,13 @@ namespace lrs {
 #ifdef __CUDACC__
 constexpr int kGenericCC = 4;   // score columns per sweep over the row
 
-__device__ __forceinline__ void score_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
-                                               const float* __restrict__ W, const float* __restrict__ b,
-                                               float* __restrict__ proba, float* __restrict__ decision,
-                                               int32_t* __restrict__ label, float* __restrict__ maxprob,
-                                               unsigned long long* status) {
+// `pitch` floats between rows of proba / decision, `col0` the first column this model's classes occupy (a class
+// group of a larger model; pitch = C, col0 = 0 otherwise)
+__device__ __forceinline__ void score_row_warp_pitched(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+                                                       const float* __restrict__ W, const float* __restrict__ b,
+                                                       float* __restrict__ proba, float* __restrict__ decision,
+                                                       int32_t* __restrict__ label, float* __restrict__ maxprob,
+                                                       unsigned long long* status, int64_t pitch, int col0) {
     constexpr int CC = kGenericCC;
     float run_max = -CUDART_INF_F, run_sum = 0.0f;
     int arg = 0;
@@ -49,8 +51,8 @@ __device__ __forceinline__ void score_row_warp(const float* __restrict__ x, int6
                     }
                 } else {
                     if (lane == 0) {
-                        if (decision) decision[row * C + c] = z;
-                        if (proba) proba[row * C + c] = z;     // normalised below
+                        if (decision) decision[row * pitch + col0 + c] = z;
+                        if (proba) proba[row * pitch + col0 + c] = z;     // normalised below
                     }
                     if (z > run_max) {                          // strict: first maximum wins
                         run_sum = run_sum * expf(run_max - z) + 1.0f;
@@ -73,11 +75,18 @@ __device__ __forceinline__ void score_row_warp(const float* __restrict__ x, int6
         if (proba) {
             __syncwarp();
             for (int c = lane; c < C; c += 32) {
-                const float z = proba[row * C + c];
-                proba[row * C + c] = expf(z - run_max) * inv;
+                const float z = proba[row * pitch + col0 + c];
+                proba[row * pitch + col0 + c] = expf(z - run_max) * inv;
             }
         }
     }
+}
+__device__ __forceinline__ void score_row_warp(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+                                               const float* __restrict__ W, const float* __restrict__ b,
+                                               float* __restrict__ proba, float* __restrict__ decision,
+                                               int32_t* __restrict__ label, float* __restrict__ maxprob,
+                                               unsigned long long* status) {
+    score_row_warp_pitched(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status, C, 0);
 }
 #endif
 

@@ -421,3 +421,43 @@ def test_short_rows_range_guard_falls_back_to_fp32(eng):
     parity.assert_parity(host, z, orc.softmax(z), z.argmax(1), "short rows, fp32 fallback")
     assert clf.take_fallback() == n
     clf.close()
+
+
+# ---- more than 2048 classes: class groups on the tensor path -------------------------------------------
+@pytest.mark.parametrize("d,c", [(64, 2049), (256, 3000), (32, 5000), (130, 4100)])
+def test_more_than_2048_classes(eng, d, c):
+    """Class groups of equal size, each scored by the tensor path into its columns of the caller's rows, then
+    combined per row (log-sum-exp across groups, best class across groups, a tie between two groups' champions)."""
+    import ctypes as C
+    import torch
+    mlapi, lib = eng
+    L = lib.load()
+    W, b = synth.make_model(d, c, 1200 + c)
+    W[c - 1] = W[5]                                     # an exact tie between a class of the first and of the last group
+    b[c - 1] = b[5]
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    rng = np.random.default_rng(d + c)
+    for n in (1, 129, 2500):
+        X = rng.standard_normal((n, d), dtype=np.float32)
+        X[0] = (W[5] * 6.0).astype(np.float32)          # row 0 is pulled towards the tied pair: the lower class wins
+        Xt = torch.from_numpy(X).cuda()
+        path = C.c_int32(0)
+        lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d, C.byref(path)))
+        assert path.value == lib.PATH_GEMM
+        z = orc.decision_function(X, W, b)
+        P = orc.softmax(z)
+        idx = z.argmax(1)
+        out = clf.score_rows(X, **ALL)                  # host path (staged chunks)
+        parity.assert_parity(out, z, P, idx, f"class groups d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+        assert out["label"][0] == 5
+        out2 = clf.score_rows(Xt, label=True, maxprob=True)     # device path, the /predict pattern
+        torch.cuda.synchronize()
+        parity.assert_parity({k: v.cpu().numpy() for k, v in out2.items() if v is not None}, z, P, idx,
+                             f"class groups d={d} C={c} n={n} (label+maxprob)")
+    Xb = rng.standard_normal((300, d), dtype=np.float32)
+    Xb[7, 1] = np.nan
+    with pytest.raises(ValueError, match="NaN or infinity"):
+        clf.predict_proba(Xb)
+    clf.score_rows(torch.from_numpy(Xb).cuda(), proba=True)
+    assert clf.take_nonfinite() == 1                    # one row, counted once whatever the number of groups
+    clf.close()
