@@ -433,13 +433,12 @@ def test_more_than_2048_classes(eng, d, c):
     mlapi, lib = eng
     L = lib.load()
     W, b = synth.make_model(d, c, 1200 + c)
-    W[c - 1] = W[5]                                     # an exact tie between a class of the first and of the last group
-    b[c - 1] = b[5]
+    W[c - 1] = W[5]                                     # an exact tie between a class of the first and of the last group,
+    b[c - 1] = b[5] = 12.0                              # far above every other class: the lower one must win every row
     clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
     rng = np.random.default_rng(d + c)
     for n in (1, 129, 2500):
         X = rng.standard_normal((n, d), dtype=np.float32)
-        X[0] = (W[5] * 6.0).astype(np.float32)          # row 0 is pulled towards the tied pair: the lower class wins
         Xt = torch.from_numpy(X).cuda()
         path = C.c_int32(0)
         lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d, C.byref(path)))
@@ -449,8 +448,9 @@ def test_more_than_2048_classes(eng, d, c):
         idx = z.argmax(1)
         out = clf.score_rows(X, **ALL)                  # host path (staged chunks)
         parity.assert_parity(out, z, P, idx, f"class groups d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
-        assert out["label"][0] == 5
+        assert (out["label"] == 5).all()
         out2 = clf.score_rows(Xt, label=True, maxprob=True)     # device path, the /predict pattern
+        assert (out2["label"].cpu().numpy() == 5).all()
         torch.cuda.synchronize()
         parity.assert_parity({k: v.cpu().numpy() for k, v in out2.items() if v is not None}, z, P, idx,
                              f"class groups d={d} C={c} n={n} (label+maxprob)")
