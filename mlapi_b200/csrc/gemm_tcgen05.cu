@@ -915,8 +915,14 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             if ((cb) + i < n_real) __stcs(p.decision + off + i, (v)[i]);               \
                     }                                                                                  \
                 }                                                                                      \
-                float cm = -INFINITY;                                                                  \
-                _Pragma("unroll") for (int i = 0; i < 32; ++i) cm = fmaxf(cm, (v)[i]);                 \
+                /* four independent chains for the maximum (and for the sum below): one 32-long chain of */ \
+                /* dependent operations per chunk is latency this warp has nobody to hide behind         */ \
+                float cm0 = -INFINITY, cm1 = -INFINITY, cm2 = -INFINITY, cm3 = -INFINITY;              \
+                _Pragma("unroll") for (int i = 0; i < 32; i += 4) {                                    \
+                    cm0 = fmaxf(cm0, (v)[i]); cm1 = fmaxf(cm1, (v)[i + 1]);                            \
+                    cm2 = fmaxf(cm2, (v)[i + 2]); cm3 = fmaxf(cm3, (v)[i + 3]);                        \
+                }                                                                                      \
+                const float cm = fmaxf(fmaxf(cm0, cm1), fmaxf(cm2, cm3));                              \
                 if (cm > m) { /* strict: an earlier chunk keeps a tie */                               \
                     int idx = 31;                                                                      \
                     _Pragma("unroll") for (int i = 30; i >= 0; --i) idx = ((v)[i] == cm) ? i : idx;    \
@@ -925,11 +931,14 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 /* exponentials relative to the chunk's own maximum (<= 1), kept in TMEM for pass 2 */ \
                 /* (z - cm) first: exactly 0 for the maximum itself, whatever its size (an fma against a */ \
                 /* pre-multiplied cm * log2e leaves the product's rounding error in the exponent)        */ \
-                float cs = 0.0f;                                                                       \
-                _Pragma("unroll") for (int i = 0; i < 32; ++i) {                                       \
-                    (v)[i] = ex2(((v)[i] - cm) * kLog2e);                                              \
-                    cs += (v)[i];                                                                      \
+                float cs0 = 0.0f, cs1 = 0.0f, cs2 = 0.0f, cs3 = 0.0f;                                  \
+                _Pragma("unroll") for (int i = 0; i < 32; i += 4) {                                    \
+                    (v)[i] = ex2(((v)[i] - cm) * kLog2e); cs0 += (v)[i];                               \
+                    (v)[i + 1] = ex2(((v)[i + 1] - cm) * kLog2e); cs1 += (v)[i + 1];                   \
+                    (v)[i + 2] = ex2(((v)[i + 2] - cm) * kLog2e); cs2 += (v)[i + 2];                   \
+                    (v)[i + 3] = ex2(((v)[i + 3] - cm) * kLog2e); cs3 += (v)[i + 3];                   \
                 }                                                                                      \
+                const float cs = (cs0 + cs1) + (cs2 + cs3);                                            \
                 tmem_st32(t_lane + (uint32_t)(cb), v);                                                 \
                 chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid] = cm;                            \
                 if (cm > -INFINITY) { /* an all-padding chunk: -inf - -inf */                          \

@@ -436,9 +436,11 @@ def test_request_sized_pinned_batches_are_scored_in_place(eng, golden):
     from mlapi_b200.estimator import PinnedArray
     L = lib.load()
     rng = np.random.default_rng(12)
-    for d, ns in ((4, 3), (32, 1), (2000, 1), (16, 2100)):      # narrow, narrow, wide, generic (> 2048 classes)
+    for d, ns, path in ((4, 3, None), (32, 1, None), (2000, 1, None), (16, 40, lib.PATH_GENERIC)):   # narrow, narrow, wide, generic
         W, b = synth.make_model(d, ns, 70 + d)
         clf = _model(eng, W, b)
+        if path is not None:
+            clf.set_path(path)                                   # (the generic kernel serves any shape when asked to)
         rep = clf._replicas[0]
         for n in (1, 7, 8):
             X = rng.standard_normal((n, d), dtype=np.float32)
