@@ -302,9 +302,6 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) 
 }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
-__device__ __forceinline__ void st_cluster_v2(uint32_t addr, float a, float b) {
-    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
-}
 // 256-bit streaming store (sm_100): one full 32-byte sector per lane and instruction
 __device__ __forceinline__ void st_cs_v8(float* p, const float* v) {
     asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
@@ -686,7 +683,6 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         int as = 0;
         uint32_t aph = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
-            const int64_t tile = grp * gsz + rt;
             for (int kc = 0; kc < p.num_k_chunks; ++kc) {
                 float4 cs = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
                 if constexpr (F16) {
@@ -1597,7 +1593,6 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
         const int ew = warp - (kMmaWarp + 1);                    // 0..11
         const int set = ew >> 2;
         const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
-        const int r_in_tile = q * 32 + lane;
         float* stage = reinterpret_cast<float*>(smem + SrSmem::out) + ew * 32 * 32;
         const float psum_scale = p.x_scale[5];
         const float floor_err = p.x_scale[6];

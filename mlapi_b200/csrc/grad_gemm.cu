@@ -114,7 +114,7 @@ constexpr uint32_t kGradIdesc = (1u << 4)                    // D = f32, A = B =
                                 | ((uint32_t)(GN >> 3) << 17) | ((uint32_t)(GM >> 4) << 24);
 
 struct GradSmem {
-    static constexpr int stages = 0;                                   // [kStages][kStageBytes], 1024-aligned
+    // [kStages][kStageBytes] from the 1024-aligned base, then:
     static constexpr int bars = kStages * kStageBytes;                 // full[kStages], empty[kStages], acc_full[2], acc_empty[2]
     static constexpr int tmem_slot = bars + (2 * kStages + 4) * 8;
     static constexpr int total = tmem_slot + 16;
