@@ -404,8 +404,9 @@ __device__ __forceinline__ void tc_commit_2sm(uint64_t* bar, uint16_t mask) {
                  : "memory");
 }
 template <bool F16>
-__device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
-    constexpr uint32_t idesc = (F16 ? kIdesc16 : kIdesc) + ((uint32_t)(BM >> 4) << 24);   // M = 256 across the pair
+__device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc1,
+                                           uint32_t accumulate) {
+    const uint32_t idesc = idesc1 + ((uint32_t)(BM >> 4) << 24);   // M = 256 across the pair
     if constexpr (F16)
         asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
@@ -420,7 +421,7 @@ __device__ __forceinline__ void tc_mma_2sm(uint32_t d_tmem, uint64_t a_desc, uin
 // `idesc` (unpaired form only): instruction descriptor with the model's N, see GemmParams::mma_n
 template <bool F16, bool PAIR>
 __device__ __forceinline__ void mma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
-    if constexpr (PAIR) tc_mma_2sm<F16>(d, a, b, acc);
+    if constexpr (PAIR) tc_mma_2sm<F16>(d, a, b, idesc, acc);
     else tc_mma<F16>(d, a, b, idesc, acc);
 }
 
@@ -488,12 +489,14 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     // multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
     // GPU's memory hung the GPU -- and nothing stops a caller from handing in a peer's buffer.)
     const bool w_mc = !PAIR && p.nrt > 1;               // W (the library's own copy, on this GPU) multicast across row tiles
-    const int n_cols_cta = p.nb * BN;
+    // classes of this CTA: nb blocks of mma_n (the class count is spread evenly over the blocks of all slices, in
+    // whole 32-column chunks: 300 classes are 2 x 160, not 2 x 256); block k's accumulator starts at TMEM column k * BN
+    const int n_cols_cta = p.nb * p.mma_n;
     const int col0 = (int)rank * n_cols_cta;       // first class handled by this CTA
     // Multicast group of W: the nrt CTAs of a class slice need the same W tiles, each fetches 1/nrt of the rows.
     uint16_t w_mask = 0;
     for (int j = 0; j < p.nrt; ++j) w_mask |= (uint16_t)(1u << (rank + j * p.ncc));
-    const int w_rows = PAIR ? BN / 2 : p.mma_n / p.nrt;  // rows of each W tile this CTA fetches
+    const int w_rows = PAIR ? p.mma_n / 2 : p.mma_n / p.nrt;  // rows of each W tile this CTA fetches
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kMaxAStages; ++i) {     // (operand ring and raw ring may differ in depth)
@@ -559,19 +562,19 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (leader && PAIR) {
                             // each CTA of the pair fetches its half of the tile into its own shared
                             // memory; both transfers are counted on the issuing CTA's barrier
-                            if (lead) mbar_expect_tx(b_full + bs, 2 * B_TILE_BYTES);
+                            if (lead) mbar_expect_tx(b_full + bs, p.mma_n * 128);
                             tma_load_2d_2sm(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
-                                            col0 + nbk * BN + (int)rt * w_rows,
+                                            col0 + nbk * p.mma_n + (int)rt * w_rows,
                                             map_to_cta(smem_u32(b_full + bs), lead_rank));
                         } else if (leader) {
-                            mbar_expect_tx(b_full + bs, PAIR ? B_TILE_BYTES : p.mma_n * 128);
+                            mbar_expect_tx(b_full + bs, p.mma_n * 128);
                             if (w_mc)
                                 tma_load_2d_mc(b_t + bs * B_TILE_BYTES + rt * w_rows * 128,
                                                part == 0 ? &map_whi : &map_wlo, kc * BKx,
-                                               col0 + nbk * BN + (int)rt * w_rows, b_full + bs, w_mask);
+                                               col0 + nbk * p.mma_n + (int)rt * w_rows, b_full + bs, w_mask);
                             else
                                 tma_load_2d(b_t + bs * B_TILE_BYTES, part == 0 ? &map_whi : &map_wlo, kc * BKx,
-                                            col0 + nbk * BN, b_full + bs);
+                                            col0 + nbk * p.mma_n, b_full + bs);
                         }
                         __syncwarp();
                         if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
@@ -757,6 +760,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const float floor_err = p.x_scale[6];
         const int ew = warp - (2 + kConvWarps);      // 0..7
         const int etid = ew * 32 + lane;             // 0..255
+        // TMEM column of class `cb` of this CTA (see n_cols_cta): blocks of mma_n classes, BN columns apart
+        const int mma_n = p.mma_n;
+#define LRS_TCOL(cb) ((uint32_t)(mma_n == BN ? (cb) : ((cb) / mma_n) * BN + (cb) % mma_n))
         float* chunk_ref = reinterpret_cast<float*>(smem + SmemLayout::chunk_ref);   // [8 chunks][256 threads]
         const int q = warp & 3;                      // TMEM lane quadrant this warp may read
         const int h = ew >> 2;                       // column half
@@ -935,7 +941,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     (v)[i + 3] = ex2(((v)[i + 3] - cm) * kLog2e); cs3 += (v)[i + 3];                   \
                 }                                                                                      \
                 const float cs = (cs0 + cs1) + (cs2 + cs3);                                            \
-                tmem_st32(t_lane + (uint32_t)(cb), v);                                                 \
+                tmem_st32(t_lane + LRS_TCOL(cb), v);                                                   \
                 chunk_ref[(((cb) - cb_lo) >> 5) * kEpiThreads + etid] = cm;                            \
                 if (cm > -INFINITY) { /* an all-padding chunk: -inf - -inf */                          \
                     const float nm = fmaxf(m, cm);                                                     \
@@ -948,13 +954,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 // again, unused -- a load under a condition made the compiler keep copies of both buffers)
                 float ra[32], rb[32];
                 const int cb_last = cb_hi1 - 32;
-                tmem_ld32_issue(t_lane + (uint32_t)cb_lo, ra);
+                tmem_ld32_issue(t_lane + LRS_TCOL(cb_lo), ra);
                 for (int cb = cb_lo; cb < cb_hi1; cb += 64) {
                     tmem_ld_wait(ra);
-                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 32, cb_last), rb);
+                    tmem_ld32_issue(t_lane + LRS_TCOL(min(cb + 32, cb_last)), rb);
                     LRS_PASS1_CHUNK(ra, cb);
                     tmem_ld_wait(rb);
-                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 64, cb_last), ra);
+                    tmem_ld32_issue(t_lane + LRS_TCOL(min(cb + 64, cb_last)), ra);
                     if (cb + 32 < cb_hi1) LRS_PASS1_CHUNK(rb, cb + 32);
                 }
                 tmem_ld_wait(ra);
@@ -1044,13 +1050,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 // again, unused -- a load under a condition made the compiler keep copies of both buffers)
                 float ra[32], rb[32];
                 const int cb_last = cb_hi1 - 32;
-                tmem_ld32_issue(t_lane + (uint32_t)cb_lo, ra);
+                tmem_ld32_issue(t_lane + LRS_TCOL(cb_lo), ra);
                 for (int cb = cb_lo; cb < cb_hi1; cb += 64) {
                     tmem_ld_wait(ra);
-                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 32, cb_last), rb);
+                    tmem_ld32_issue(t_lane + LRS_TCOL(min(cb + 32, cb_last)), rb);
                     LRS_PASS2_CHUNK(ra, cb);
                     tmem_ld_wait(rb);
-                    tmem_ld32_issue(t_lane + (uint32_t)min(cb + 64, cb_last), ra);
+                    tmem_ld32_issue(t_lane + LRS_TCOL(min(cb + 64, cb_last)), ra);
                     if (cb + 32 < cb_hi1) LRS_PASS2_CHUNK(rb, cb + 32);
                 }
                 tmem_ld_wait(ra);
@@ -1058,6 +1064,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #undef LRS_PASS2_CHUNK
 #undef LRS_PASS1_CHUNK
 #undef LRS_CHUNK_LOGITS
+#undef LRS_TCOL
             tc_fence_before();
             if (lead) mbar_arrive(acc_empty + buf);   // this buffer may be overwritten
             else mbar_arrive_cluster(map_to_cta(smem_u32(acc_empty + buf), lead_rank));
@@ -2129,6 +2136,19 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         acc.mma_n = (C + 31) / 32 * 32;
         if (const char* e = getenv("LRS_GEMM_MMA_N")) acc.mma_n = atoi(e) >= acc.mma_n ? BN : acc.mma_n;   // debug: any value >= N restores 256
     }
+    // More than one class block: the classes are spread evenly over the blocks of all slices, in whole 32-column
+    // chunks, instead of filling 256-wide blocks and padding the last ones with zeros (300 classes: 2 x 160 instead
+    // of 2 x 256; 1100: 8 x 160 instead of 8 x 256).  cfg 3 (1000 classes: 4 x 256) is unchanged.
+    if (!getenv("LRS_GEMM_MMA_N")) {
+        for (int i = 0; i < GemmPlan::kLayouts; ++i) {
+            auto& L = g->layout[i];
+            if (!g->has[i] || L.ncc * L.nb == 1) continue;
+            const int blocks = L.ncc * L.nb;
+            int n = ((C + blocks - 1) / blocks + 31) / 32 * 32;
+            if (L.nrt > 1) n = (n + 63) / 64 * 64;      // (opt-in W multicast: every CTA fetches mma_n / nrt rows)
+            L.mma_n = n < BN ? n : BN;
+        }
+    }
     g->active = g->has[0] ? 0 : 1;                  // C <= 256: the accurate layout costs nothing extra
     if (const char* e = getenv("LRS_GEMM_SPLIT")) {  // pin a layout: 1 = accurate, 0 = fast
         const int want = atoi(e) != 0 ? 1 : 0;
@@ -2174,7 +2194,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     for (int i = 0; i < GemmPlan::kLayouts; ++i) {
         if (!g->has[i]) continue;
         auto& L = g->layout[i];
-        const int wbox = L.pair ? BN / 2 : L.mma_n / L.nrt;
+        const int wbox = L.pair ? L.mma_n / 2 : L.mma_n / L.nrt;
         if ((rc = make_map(&L.map_whi, g->w_hi, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
         if ((rc = make_map(&L.map_wlo, g->w_lo, g->c_pad, d, d4, wbox)) != LR_OK) return rc;
         if ((rc = make_map_ex(&L.map_w16hi, g->w16_hi, g->c_pad, d, g->d16, wbox, BK16, 2, true)) != LR_OK) return rc;
