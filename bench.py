@@ -17,8 +17,8 @@ reference's implementation of the path) on this box's host cores.  With the defa
 line carries `configs.cfg2` and `configs.cfg3`: BASELINE configs[2] (d=100k binary, 250 000 rows =
 100 GB per GPU: the whole 2M-row config in one resident round at 8 GPUs) and configs[3] (d=1024,
 C=1000, 2.5M rows per GPU: 20M rows at 8 GPUs), each with its own timing, roofline, clocks and
-launch count; and, under torchrun, `refit`: one distributed loss/gradient evaluation with its NCCL
-all-reduce (the design's only collective).
+launch count; and `refit`: one loss/gradient evaluation of the batch-gradient refit per shape -- under torchrun
+distributed, with its NCCL all-reduce (the design's only collective).
 `--impl reference` times only the CPU implementation and prints the same line shape.
 """
 from __future__ import annotations
@@ -194,7 +194,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": config_of(args.workload, 0, want, args.logit_scale, args.gpus),
+        "config": config_of(args.workload, args.rows, want, args.logit_scale, args.gpus),
         "run": {"rows_scored_per_step": c["rows"], "kernel_path": "scikit-learn predict_proba on host cores",
                 "note": "rank 0 only; rows/s of the CPU path does not depend on the batch size at this scale"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": c["cores"], "kind": "reference",
@@ -431,28 +431,34 @@ def refit_record(ctx):
 
         def evaluate():
             vec = ev.sums(w0)
-            dist.all_reduce(vec, op=dist.ReduceOp.SUM)        # the design's only collective
+            if world > 1:
+                dist.all_reduce(vec, op=dist.ReduceOp.SUM)    # the design's only collective
             return vec.cpu()
 
         for _ in range(2):
             evaluate()
         torch.cuda.synchronize(dev)
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
         k = 5
         for _ in range(k):
             evaluate()
         dt = torch.tensor([(time.perf_counter() - t0) / k], dtype=torch.float64, device=dev)
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         ev.close()
         res = refit.fit(X, y.cpu().numpy(), classes=np.arange(c), max_iter=5)
         mine = torch.from_numpy(np.concatenate([res.coef_.ravel(), res.intercept_.ravel()])).to(dev)
         ref = mine.clone()
-        dist.broadcast(ref, src=0)
         dev_max = (mine - ref).abs().max()
-        dist.all_reduce(dev_max, op=dist.ReduceOp.MAX)
+        if world > 1:
+            dist.broadcast(ref, src=0)
+            dev_max = (mine - ref).abs().max()
+            dist.all_reduce(dev_max, op=dist.ReduceOp.MAX)
         out[tag] = {"rows_per_gpu": n, "n_features": d, "n_classes": c, "ms_per_evaluation": float(dt.item()) * 1e3,
-                    "allreduce_bytes": int(8 * (1 + rows * (d + 1))), "collective": "NCCL all-reduce (sum, float64)",
+                    "allreduce_bytes": int(8 * (1 + rows * (d + 1))) if world > 1 else 0,
+                    "collective": "NCCL all-reduce (sum, float64)" if world > 1 else "none (one rank)",
                     "lbfgs_iterations": int(res.n_iter_[0]),
                     "max_abs_coef_diff_vs_rank0": float(dev_max.item())}
         del X, y, ev
@@ -520,11 +526,10 @@ def main():
             except Exception as exc:        # the headline line must still be printed
                 extras[name] = {"error": f"{type(exc).__name__}: {exc}"}
                 torch.cuda.empty_cache()
-        if world > 1:
-            try:
-                refit = refit_record(ctx)
-            except Exception as exc:
-                refit = {"error": f"{type(exc).__name__}: {exc}"}
+        try:
+            refit = refit_record(ctx)
+        except Exception as exc:
+            refit = {"error": f"{type(exc).__name__}: {exc}"}
     if rank == 0:
         line = {"metric": METRIC, "n_gpus": world, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "fp32", "data": "synthetic"}
