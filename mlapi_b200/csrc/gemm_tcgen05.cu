@@ -78,6 +78,7 @@ struct SmemLayoutT {
     static constexpr int bias = b + b_stages * b_tile;               // [512] floats
     static constexpr int cscale = bias + 512 * 4;                    // [512] floats: 1 / (x scale * class scale), FP16 mode
     static constexpr int xchg = cscale + 512 * 4;                    // [2 tile parities][kMaxCluster][BM] float4 (max, class, sum, -)
+    static_assert(2 * kMaxCluster * BM * 16 >= 8 * 32 * 16 * 4, "xchg doubles as the register epilogue's store tiles");
     static constexpr int halves = xchg + 2 * kMaxCluster * BM * 16;  // [BM] float4: column half 1 -> column half 0, CTA-local
     static constexpr int glob = halves + BM * 16;                    // [BM] float4: row statistics of the whole cluster
     static constexpr int chunk_ref = glob + BM * 16;                 // [8][kEpiThreads] floats: the maximum each 32-column
@@ -96,6 +97,7 @@ struct GemmParams {
     int n_classes;
     int nb;                 // 256-class blocks per CTA (1 or 2)
     int split;              // 1: nb == 1 and the correction products accumulate in TMEM columns 256..511
+    int stage_off;          // byte offset of the epilogue's 8 x 2 KB store tiles inside the ring area (0: none; see store_block_by_rows)
     int ncc;                // class slices per cluster: CTAs that share a row tile
     int nrt;                // row tiles per cluster (1 or 2): CTAs that share a class slice
                             // cluster = ncc * nrt CTAs, rank = slice + ncc * row_tile
@@ -307,6 +309,31 @@ __device__ __forceinline__ void st_cs_v8(float* p, const float* v) {
     asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
                  "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
                  : "memory");
+}
+// A warp's 32 rows x 32 columns (lane = row, v = its columns) to global memory through a tile in shared memory,
+// so that a store instruction writes the columns of two rows side by side (2 x 64 contiguous bytes) instead of one
+// column of 32 rows (32 sectors per instruction, which is what scalar per-row stores cost when the row pitch rules
+// vectors out: 1.4-1.8x on the whole step, measured on 101 / 150 / 255 / 1001 classes).  Two sweeps of 16 columns;
+// `stage` = 32 x 16 floats per warp (2 KB), column index xor-ed with the row so that the reads are conflict-free
+// and the writes two-way.  `dst` = column 0 of the warp's first row.
+constexpr int kStoreTileBytes = 32 * 16 * 4;
+__device__ __forceinline__ void store_block_by_rows(float* __restrict__ stage, const float (&v)[32], int lane,
+                                                    float* __restrict__ dst, int64_t pitch, int rows_valid, int n_cols) {
+    const int col = lane & 15, rsel = lane >> 4;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        if (half * 16 < n_cols) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) stage[lane * 16 + (i ^ (lane & 15))] = v[half * 16 + i];
+            __syncwarp();
+            if (half * 16 + col < n_cols) {
+                float* o = dst + half * 16 + col;
+#pragma unroll 4
+                for (int r = rsel; r < rows_valid; r += 2) __stcs(o + r * pitch, stage[r * 16 + (col ^ (r & 15))]);
+            }
+            __syncwarp();
+        }
+    }
 }
 __device__ __forceinline__ float ex2(float x) {
     float y;
@@ -773,6 +800,9 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const int n_chunks = (n_real + 31) / 32;
         const int cb_lo = h == 0 ? 0 : ((n_chunks + 1) / 2) * 32;
         const int cb_hi = h == 0 ? ((n_chunks + 1) / 2) * 32 : n_chunks * 32;
+        // store tiles of the general form (rows whose pitch rules vector stores out): the host left the last 16 KB of
+        // the ring area free for them (GemmParams::stage_off)
+        float* const stg_general = p.stage_off ? reinterpret_cast<float*>(smem + p.stage_off) + ew * (kStoreTileBytes / 4) : nullptr;
         uint32_t it = 0;
         for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters, ++it) {
             const int64_t tile = grp * gsz + rt;      // may lie past the end: TMA zero-fills, nothing is stored
@@ -781,48 +811,74 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             const uint32_t par = it & 1;
             const uint32_t buf = p.acc_bufs == 2 ? (it & 1u) : 0u;
             const uint32_t t_lane = t_lane0 + buf * (uint32_t)p.acc_stride;
+            // rows of this warp that exist, and where its block starts in the (n_rows x pitch) outputs
+            const int64_t row_w = tile * BM + q * 32;
+            const int rows_valid = p.n_rows - row_w >= 32 ? 32 : (p.n_rows > row_w ? (int)(p.n_rows - row_w) : 0);
+            const int64_t blk_w = row_w * p.out_pitch + p.out_col0 + col0;
             mbar_wait(acc_full + buf, (p.acc_bufs == 2 ? (it >> 1) : it) & 1u);
             tc_fence_after();
 
-            // ---- at most 32 classes: the four warps of column half 0 hold whole rows, one lane per row ----
-            // One read of TMEM, everything else in registers: no write-back, no second and third pass, no
-            // meeting of halves in shared memory (the three-pass form spent 2.4 us per 128-row tile on a
-            // 32-class model, which is what bounded it).  Same arithmetic and the same re-scoring flags.
-            if (!PAIR && n_chunks == 1 && p.ncc == 1 && !(p.debug_skip & 2)) {
-                if (h == 0) {
+            // ---- at most 64 classes: whole rows stay in registers, one lane per row ----
+            // One read of TMEM, everything else in registers: no write-back, no second pass over TMEM (the general
+            // form below spent 2.4 us per 128-row tile on a 32-class model and 5.5 us on a 50-class one, which is
+            // what bounded them).  Up to 32 classes the four warps of column half 0 do it alone; with 33..64 the
+            // warps of half 1 take columns 32..63 of the same rows and the two warps of a lane quadrant meet twice
+            // in shared memory (row maximum, then sum), 64 threads per named barrier.  Same arithmetic and the
+            // same re-scoring flags as the general form.
+            if (!PAIR && n_chunks <= 2 && p.ncc == 1 && !(p.debug_skip & 2)) {
+                const bool two = n_chunks == 2;
+                if (h == 0 || two) {
+                    const int cbase = h * 32;
+                    const int n_here = n_real - cbase < 32 ? n_real - cbase : 32;   // real classes in this warp's columns
+                    const uint32_t t_col = t_lane + (uint32_t)cbase;
                     float v[32];
-                    tmem_ld32(t_lane, v);
+                    tmem_ld32(t_col, v);
                     if (p.split) {
                         float u[32];
-                        tmem_ld32(t_lane + (uint32_t)BN, u);
+                        tmem_ld32(t_col + (uint32_t)BN, u);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] += u[i];
                         for (int sg = 1; sg < p.ksplit; ++sg) {
-                            tmem_ld32(t_lane + seg_offset(sg, p.seg_w), u);
+                            tmem_ld32(t_col + seg_offset(sg, p.seg_w), u);
 #pragma unroll
                             for (int i = 0; i < 32; ++i) v[i] += u[i];
                         }
                     }
+                    tc_fence_before();
+                    mbar_arrive(acc_empty + buf);                     // the accumulators are in registers now
                     float gm = -INFINITY;
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        if constexpr (F16) v[i] = fmaf(v[i], cscale_s[i], bias_s[i]);
-                        else v[i] += bias_s[i];                       // padding carries -inf
+                        if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cbase + i], bias_s[cbase + i]);
+                        else v[i] += bias_s[cbase + i];               // padding carries -inf
                         gm = fmaxf(gm, v[i]);
                     }
                     int garg = 31;
 #pragma unroll
                     for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
-                    if (p.decision && live) {
-                        float* zr = p.decision + row * p.out_pitch + p.out_col0;
-                        if (n_real == 32 && p.vec_store) {
+                    garg += cbase;
+                    if (two) {
+                        float* xm = chunk_ref;                        // [2 halves][128 rows] maxima, then classes
+                        int* xa = reinterpret_cast<int*>(chunk_ref + 2 * BM);
+                        xm[h * BM + r_in_tile] = gm;
+                        xa[h * BM + r_in_tile] = garg;
+                        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+                        const float om = xm[(h ^ 1) * BM + r_in_tile];
+                        const int oa = xa[(h ^ 1) * BM + r_in_tile];
+                        if (h == 0 ? om > gm : om >= gm) { gm = om; garg = oa; }   // ties: the lower class, i.e. half 0
+                    }
+                    const int64_t blk = blk_w + cbase;
+                    float* stg = reinterpret_cast<float*>(smem + SmemLayout::xchg) + ew * (kStoreTileBytes / 4);   // (no cluster exchange here)
+                    if (p.decision) {
+                        if (n_here == 32 && p.vec_store) {
+                            if (live) {
+                                float* zr = p.decision + row * p.out_pitch + p.out_col0 + cbase;
 #pragma unroll
-                            for (int i = 0; i < 32; i += 4)
-                                __stcs(reinterpret_cast<float4*>(zr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                                for (int i = 0; i < 32; i += 4)
+                                    __stcs(reinterpret_cast<float4*>(zr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+                            }
                         } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (i < n_real) __stcs(zr + i, v[i]);
+                            store_block_by_rows(stg, v, lane, p.decision + blk, p.out_pitch, rows_valid, n_here);
                         }
                     }
                     const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
@@ -836,30 +892,31 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         v[i] = ex2(fmaf(v[i], kLog2e, -gml));
                         gs += v[i];
                     }
+                    if (two) {
+                        float* xs = chunk_ref + 4 * BM;               // [2 halves][128 rows] sums, then near-tie counts
+                        int* xn = reinterpret_cast<int*>(chunk_ref + 6 * BM);
+                        xs[h * BM + r_in_tile] = gs;
+                        xn[h * BM + r_in_tile] = gnear;
+                        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+                        gs += xs[(h ^ 1) * BM + r_in_tile];           // a + b == b + a: both warps hold the same sum
+                        gnear += xn[(h ^ 1) * BM + r_in_tile];
+                    }
                     const float inv = __frcp_rn(gs);
                     const float risk_thr = 8e-6f / ez;
                     if (p.proba) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] *= inv;
-                        if (live) {
-                            float* pr = p.proba + row * p.out_pitch + p.out_col0;
-                            if (n_real == 32 && p.vec_store == 2) {
+                        if (n_here == 32 && p.vec_store == 2) {
+                            if (live) {
+                                float* pr = p.proba + row * p.out_pitch + p.out_col0 + cbase;
 #pragma unroll
                                 for (int i = 0; i < 32; i += 8) st_cs_v8(pr + i, v + i);
-                            } else if (n_real == 32 && p.vec_store) {
-#pragma unroll
-                                for (int i = 0; i < 32; i += 4)
-                                    __stcs(reinterpret_cast<float4*>(pr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                            } else {
-#pragma unroll
-                                for (int i = 0; i < 32; ++i)
-                                    if (i < n_real) __stcs(pr + i, v[i]);
                             }
+                        } else {
+                            store_block_by_rows(stg, v, lane, p.proba + blk, p.out_pitch, rows_valid, n_here);
                         }
                     }
-                    tc_fence_before();
-                    mbar_arrive(acc_empty + buf);
-                    if (live) {
+                    if (live && h == 0) {
                         if (p.label) __stcs(p.label + row, garg);
                         if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
                         const bool finite_row = finite_f(gm) && finite_f(gs);
@@ -881,6 +938,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // ---- pass 1: running maximum (first argmax) and sum of exp(z - running maximum) over my columns.
             // The load of the next 32-column chunk is in flight while this one is worked on.
             const int cb_hi1 = (p.debug_skip & 2) ? cb_lo : cb_hi;
+            float* const stg = stg_general;
             float m = -INFINITY, ssum = 0.0f;
             int arg = col0 + cb_lo;
             // raw accumulator chunk -> logits, in place
@@ -906,7 +964,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #define LRS_PASS1_CHUNK(v, cb)                                                                         \
             do {                                                                                       \
                 LRS_CHUNK_LOGITS(v, cb);                                                               \
-                if (p.decision && live) {                                                              \
+                if (p.decision && stg) {                                                               \
+                    store_block_by_rows(stg, v, lane, p.decision + blk_w + (cb), p.out_pitch, rows_valid, \
+                                        n_real - (cb) < 32 ? n_real - (cb) : 32);                      \
+                } else if (p.decision && live) {                                                       \
                     const int64_t off = row * p.out_pitch + p.out_col0 + col0 + (cb);                  \
                     if ((cb) + 32 <= n_real && p.vec_store) {                                          \
                         _Pragma("unroll") for (int i = 0; i < 32; i += 4)                              \
@@ -1031,7 +1092,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     (v)[i] *= fj;                                                                      \
                     near += (v)[i] > near_thr ? 1 : 0;                                                 \
                 }                                                                                      \
-                if (p.proba && live) {                                                                 \
+                if (p.proba && stg) {                                                                  \
+                    store_block_by_rows(stg, v, lane, p.proba + blk_w + (cb), p.out_pitch, rows_valid, \
+                                        n_real - (cb) < 32 ? n_real - (cb) : 32);                      \
+                } else if (p.proba && live) {                                                          \
                     const int64_t off = row * p.out_pitch + p.out_col0 + col0 + (cb);                  \
                     if ((cb) + 32 <= n_real && p.vec_store == 2) {                                     \
                         _Pragma("unroll") for (int i = 0; i < 32; i += 8) st_cs_v8(p.proba + off + i, (v) + i); \
@@ -2124,7 +2188,9 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     const bool force_pair = getenv("LRS_GEMM_PAIR") && pair, force_mc = getenv("LRS_GEMM_MC") && mc;
     for (int i = 0; i < 2; ++i) {
         auto& L = g->layout[i];
-        L.pair = pair && (L.ncc * 2 <= 4 || (force_pair && L.ncc * 2 <= 8));
+        // (the accurate layout with two class slices: 3.39 ms unpaired against 4.40 paired on d=1024, 300 classes,
+        // 3.93 / 4.19 on 500, 4.77 / 5.25 on d=512, 400 -- a cluster of 4 leaves 16 SMs idle and its X ring is shorter)
+        L.pair = pair && ((i == 0 ? L.ncc * 2 <= 4 : L.ncc == 1) || (force_pair && L.ncc * 2 <= 8));
         L.nrt = (!L.pair && force_mc && L.ncc * 2 <= 8) ? 2 : 1;
     }
     // A model whose classes fit one W tile multiplies by exactly that many columns (in whole 32-column
@@ -2356,12 +2422,13 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // d=256, C=32, 3214 against 3457 at d=4096, C=64 -- the rings it leaves room for are shallower.)
     if (L.pair) {
         p.b_tile_bytes = SmemLayoutT<true>::b_tile; p.a_stages = SmemLayoutT<true>::a_stages; p.b_stages = SmemLayoutT<true>::b_stages;
-    } else if (L.mma_n <= 64) {
-        p.b_tile_bytes = 8 * 1024; p.a_stages = 3; p.b_stages = 12;
-    } else if (L.mma_n <= 128) {
-        p.b_tile_bytes = 16 * 1024; p.a_stages = 3; p.b_stages = 6;
     } else {
-        p.b_tile_bytes = 32 * 1024; p.a_stages = 2; p.b_stages = 4;
+        // W stages of exactly mma_n rows (multiples of 4 KB, so every tile keeps the 1 KB alignment the swizzle
+        // wants); a third X stage whenever four W stages still fit beside it
+        p.b_tile_bytes = L.mma_n * 128;
+        p.a_stages = 3 * 32 * 1024 + 4 * p.b_tile_bytes <= 192 * 1024 ? 3 : 2;
+        p.b_stages = (192 * 1024 - p.a_stages * 32 * 1024) / p.b_tile_bytes;
+        if (p.b_stages > kMaxBStages) p.b_stages = kMaxBStages;
     }
     if (const char* e = getenv("LRS_GEMM_RINGS")) {          // tuning: "a_stages,b_stages"
         int as = 0, bs = 0;
@@ -2400,6 +2467,19 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
                     ((reinterpret_cast<uintptr_t>(a.decision) & 15u) == 0);
     const bool al32 = al && (p.out_pitch % 8 == 0) && (p.out_col0 % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.proba) & 31u) == 0);
     p.vec_store = al32 ? 2 : (al ? 1 : 0);
+    // Rows that cannot take 32-byte vector stores leave through 16 KB of store tiles at the end of the ring area, paid
+    // for with a W stage where the rings fill it (the register epilogue of <= 64 classes has its tiles elsewhere).
+    // Measured (d=512, 2M rows): 101 classes through the tiles 1.31 ms, 100 classes with 16-byte stores 1.40 ms.
+    p.stage_off = 0;
+    if (p.vec_store < 2 && (a.proba || a.decision) && (L.pair || L.ncc > 1 || L.nb * L.mma_n > 64)) {
+        const int ring_end = 192 * 1024 - 8 * kStoreTileBytes;
+        int bs = p.b_stages;
+        while (bs > 2 && p.a_stages * 32 * 1024 + bs * p.b_tile_bytes > ring_end) --bs;
+        if (p.a_stages * 32 * 1024 + bs * p.b_tile_bytes <= ring_end) {
+            p.b_stages = bs;
+            p.stage_off = ring_end;
+        }
+    }
 
     const int64_t n_tiles = (a.n_rows + BM - 1) / BM;
     cudaLaunchConfig_t cfg = {};

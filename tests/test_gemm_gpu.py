@@ -192,7 +192,7 @@ def test_gemm_unaligned_device_rows_are_repitched(eng):
     clf.close()
 
 
-@pytest.mark.parametrize("d,c", [(64, 17), (64, 32), (200, 33), (256, 64), (512, 100), (96, 128), (128, 160), (64, 224), (64, 225)])
+@pytest.mark.parametrize("d,c", [(64, 17), (64, 32), (200, 33), (300, 50), (256, 64), (2048, 40), (512, 100), (96, 101), (512, 150), (96, 128), (128, 160), (64, 224), (64, 225)])
 def test_gemm_small_class_counts(eng, d, c):
     """17..224 classes: the unpaired small-N form (N = classes rounded up to 32, two accumulator buffers
     up to N = 128); 225..256 keep the 256-wide tile.  Several row tiles per CTA so both buffers cycle."""
@@ -207,6 +207,45 @@ def test_gemm_small_class_counts(eng, d, c):
         parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
                              orc.predict_index(X, W, b), f"gemm small-N d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
     clf.close()
+
+
+@pytest.mark.parametrize("fixup", ["1", "0"])
+def test_gemm_33_to_64_classes_ties_across_column_halves(eng, fixup, monkeypatch):
+    """33..64 classes: two warps per row keep 32 columns each in registers and meet in shared memory.  Exact ties
+    between a class of the lower half and one of the upper half (5 / 40), inside the upper half (35 / 45) and over
+    all classes go to the lowest index -- with the fp32 re-scoring pass and without it (the tied logits come from
+    identical W rows, so the tensor arithmetic gives identical values too)."""
+    mlapi, lib = eng
+    monkeypatch.setenv("LRS_GEMM_FIXUP", fixup)
+    d, c = 96, 50
+    rng = np.random.default_rng(50)
+    W = rng.standard_normal((c, d)) / np.sqrt(d)
+    b = rng.standard_normal(c)
+    W[40], b[40] = W[5], b[5]
+    W[45], b[45] = W[35], b[35]
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    n = 3000
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    X[:700] += (6.0 * W[5] / np.linalg.norm(W[5])).astype(np.float32)       # classes 5 and 40 lead, tied
+    X[700:1400] += (6.0 * W[35] / np.linalg.norm(W[35])).astype(np.float32)  # 35 and 45
+    X[-1] = 0.0
+    z = orc.decision_function(X, W, b)
+    for pattern in (ALL, dict(label=True, maxprob=True)):
+        out = clf.score_rows(X, **pattern)
+        parity.assert_parity({k: v for k, v in out.items() if v is not None}, z, orc.softmax(z), z.argmax(1),
+                             f"two column halves, fixup={fixup}", z_atol=parity.Z_ATOL_TENSOR)
+        lab = out["label"]
+        assert not np.isin(lab, (40, 45)).any()                  # the higher twin never wins
+        assert (lab[:700] == 5).sum() > 500 and (lab[700:1400] == 35).sum() > 500
+    # all classes tied on every row: class 0
+    clf0 = mlapi.B200LogisticRegression(np.zeros((c, d)), np.full(c, 0.25), np.arange(c))
+    clf0.set_path(lib.PATH_GEMM)
+    out = clf0.score_rows(X[:300], **ALL)
+    assert (out["label"] == 0).all()
+    np.testing.assert_allclose(out["proba"], 1.0 / c, rtol=1e-6)
+    clf.close()
+    clf0.close()
 
 
 # ---- dynamic range: what the 3xFP16 split must survive ---------------------------------------------
