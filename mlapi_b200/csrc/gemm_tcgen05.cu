@@ -287,6 +287,19 @@ __device__ __forceinline__ void tmem_add8(uint32_t taddr, float* v) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] += __uint_as_float(r[i]);
 }
+// sixteen at a time: half the round trips of tmem_add8 where the registers allow it
+__device__ __forceinline__ void tmem_add16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] += __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
@@ -450,6 +463,128 @@ template <bool F16, bool PAIR>
 __device__ __forceinline__ void mma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
     if constexpr (PAIR) tc_mma_2sm<F16>(d, a, b, idesc, acc);
     else tc_mma<F16>(d, a, b, idesc, acc);
+}
+
+// The epilogue of a model with at most 64 classes: whole rows stay in registers, one lane per row.
+// One read of TMEM, everything else in registers: no write-back, no second pass over TMEM (the general form spent
+// 2.4 us per 128-row tile on a 32-class model, which is what bounded it).  A warp holds one 32-column chunk of its
+// 32 rows (TMEM lets only the two warps of a lane quadrant read those rows): up to 32 classes the four warps of
+// column half 0 do it alone, with 33..64 the warps of half 1 take columns 32..63 of the same rows and the two warps
+// of a quadrant meet twice in shared memory (row maximum, then sum), 64 threads per named barrier.  Same arithmetic
+// and the same re-scoring flags as the general form.  (Two chunks per warp, for up to 128 classes, were tried: the
+// 64 live values spill against the 128-register cap and it ran 10-20 % slower than the general form.)
+// `xch` = 8 x 128 floats of scratch, `stg` = the warp's store tile (store_block_by_rows).
+template <bool F16>
+__device__ __forceinline__ void epilogue_in_registers(const GemmParams& p, uint32_t t_lane, int h, int q, int lane, int n_real,
+                                                      int64_t row, bool live, int rows_valid, int64_t blk_w,
+                                                      const float* cscale_s, const float* bias_s, float* xch, float* stg,
+                                                      uint64_t* acc_empty_bar, float psum_scale, float floor_err) {
+    const bool two = n_real > 32;                     // the warps of column half 1 take part
+    if (h == 1 && !two) {
+        tc_fence_before();
+        mbar_arrive(acc_empty_bar);
+        return;
+    }
+    const int r_in_tile = q * 32 + lane;
+    const int cbase = h * 32;
+    const int n_here = n_real - cbase < 32 ? n_real - cbase : 32;   // real classes in this warp's columns
+    const uint32_t t_col = t_lane + (uint32_t)cbase;
+    float v[32];
+    tmem_ld32(t_col, v);
+    if (p.split) {
+        float u[32];
+        tmem_ld32(t_col + (uint32_t)BN, u);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += u[i];
+        for (int sg = 1; sg < p.ksplit; ++sg) {
+            tmem_ld32(t_col + seg_offset(sg, p.seg_w), u);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += u[i];
+        }
+    }
+    tc_fence_before();
+    mbar_arrive(acc_empty_bar);                       // the accumulators are in registers now
+    float gm = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cbase + i], bias_s[cbase + i]);
+        else v[i] += bias_s[cbase + i];               // padding carries -inf
+        gm = fmaxf(gm, v[i]);
+    }
+    int garg = 31;
+#pragma unroll
+    for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
+    garg += cbase;
+    if (two) {
+        float* xm = xch;                              // [2 halves][128 rows] maxima, then classes
+        int* xa = reinterpret_cast<int*>(xch + 2 * BM);
+        xm[h * BM + r_in_tile] = gm;
+        xa[h * BM + r_in_tile] = garg;
+        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+        const float om = xm[(h ^ 1) * BM + r_in_tile];
+        const int oa = xa[(h ^ 1) * BM + r_in_tile];
+        if (h == 0 ? om > gm : om >= gm) { gm = om; garg = oa; }   // ties: the lower class, i.e. half 0
+    }
+    const int64_t blk = blk_w + cbase;
+    if (p.decision) {
+        if (n_here == 32 && p.vec_store) {
+            if (live) {
+                float* zr = p.decision + row * p.out_pitch + p.out_col0 + cbase;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                    __stcs(reinterpret_cast<float4*>(zr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+            }
+        } else {
+            store_block_by_rows(stg, v, lane, p.decision + blk, p.out_pitch, rows_valid, n_here);
+        }
+    }
+    const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
+    const float tau = gm - 2.0f * ez;
+    const float gml = gm * kLog2e;
+    float gs = 0.0f;
+    int gnear = 0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        gnear += v[i] > tau ? 1 : 0;
+        v[i] = ex2(fmaf(v[i], kLog2e, -gml));
+        gs += v[i];
+    }
+    if (two) {
+        float* xs = xch + 4 * BM;                     // [2 halves][128 rows] sums, then near-tie counts
+        int* xn = reinterpret_cast<int*>(xch + 6 * BM);
+        xs[h * BM + r_in_tile] = gs;
+        xn[h * BM + r_in_tile] = gnear;
+        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
+        gs += xs[(h ^ 1) * BM + r_in_tile];           // a + b == b + a: both warps hold the same sum
+        gnear += xn[(h ^ 1) * BM + r_in_tile];
+    }
+    const float inv = __frcp_rn(gs);
+    const float risk_thr = 8e-6f / ez;
+    if (p.proba) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] *= inv;
+        if (n_here == 32 && p.vec_store == 2) {
+            if (live) {
+                float* pr = p.proba + row * p.out_pitch + p.out_col0 + cbase;
+#pragma unroll
+                for (int i = 0; i < 32; i += 8) st_cs_v8(pr + i, v + i);
+            }
+        } else {
+            store_block_by_rows(stg, v, lane, p.proba + blk, p.out_pitch, rows_valid, n_here);
+        }
+    }
+    if (live && h == 0) {
+        if (p.label) __stcs(p.label + row, garg);
+        if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
+        const bool finite_row = finite_f(gm) && finite_f(gs);
+        if (!finite_row) {
+            if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
+            else atomicAdd(p.status, 1ull);
+        }
+        if (p.lse) p.lse[row] = gm + logf(gs);
+        if (p.flags && finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
+            flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
+    }
 }
 
 // F16 = false: 3xTF32 (operands are fp32 containers, 8 K-elements per MMA).
@@ -763,7 +898,10 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         *reinterpret_cast<uint2*>(stage + A_TILE_BYTES + off) = make_uint2(l0, l1);
                     }
                 }
-                fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core
+                // generic-proxy writes -> visible to the tensor core.  (One arrival per thread: electing one lane per
+                // warp behind a __syncwarp -- 4 arrivals per k-chunk instead of 128, remote ones in a pair's second
+                // CTA -- measured 3-4 % slower on cfg 3 and on every other shape tried.)
+                fence_proxy_async();
                 if (lead) mbar_arrive(a_ready + as);
                 else mbar_arrive_cluster(map_to_cta(smem_u32(a_ready + as), lead_rank));
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
@@ -818,120 +956,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_wait(acc_full + buf, (p.acc_bufs == 2 ? (it >> 1) : it) & 1u);
             tc_fence_after();
 
-            // ---- at most 64 classes: whole rows stay in registers, one lane per row ----
-            // One read of TMEM, everything else in registers: no write-back, no second pass over TMEM (the general
-            // form below spent 2.4 us per 128-row tile on a 32-class model and 5.5 us on a 50-class one, which is
-            // what bounded them).  Up to 32 classes the four warps of column half 0 do it alone; with 33..64 the
-            // warps of half 1 take columns 32..63 of the same rows and the two warps of a lane quadrant meet twice
-            // in shared memory (row maximum, then sum), 64 threads per named barrier.  Same arithmetic and the
-            // same re-scoring flags as the general form.
+            // ---- at most 64 classes: whole rows stay in registers (epilogue_in_registers) ----
             if (!PAIR && n_chunks <= 2 && p.ncc == 1 && !(p.debug_skip & 2)) {
-                const bool two = n_chunks == 2;
-                if (h == 0 || two) {
-                    const int cbase = h * 32;
-                    const int n_here = n_real - cbase < 32 ? n_real - cbase : 32;   // real classes in this warp's columns
-                    const uint32_t t_col = t_lane + (uint32_t)cbase;
-                    float v[32];
-                    tmem_ld32(t_col, v);
-                    if (p.split) {
-                        float u[32];
-                        tmem_ld32(t_col + (uint32_t)BN, u);
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] += u[i];
-                        for (int sg = 1; sg < p.ksplit; ++sg) {
-                            tmem_ld32(t_col + seg_offset(sg, p.seg_w), u);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) v[i] += u[i];
-                        }
-                    }
-                    tc_fence_before();
-                    mbar_arrive(acc_empty + buf);                     // the accumulators are in registers now
-                    float gm = -INFINITY;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if constexpr (F16) v[i] = fmaf(v[i], cscale_s[cbase + i], bias_s[cbase + i]);
-                        else v[i] += bias_s[cbase + i];               // padding carries -inf
-                        gm = fmaxf(gm, v[i]);
-                    }
-                    int garg = 31;
-#pragma unroll
-                    for (int i = 30; i >= 0; --i) garg = (v[i] == gm) ? i : garg;   // first index wins
-                    garg += cbase;
-                    if (two) {
-                        float* xm = chunk_ref;                        // [2 halves][128 rows] maxima, then classes
-                        int* xa = reinterpret_cast<int*>(chunk_ref + 2 * BM);
-                        xm[h * BM + r_in_tile] = gm;
-                        xa[h * BM + r_in_tile] = garg;
-                        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
-                        const float om = xm[(h ^ 1) * BM + r_in_tile];
-                        const int oa = xa[(h ^ 1) * BM + r_in_tile];
-                        if (h == 0 ? om > gm : om >= gm) { gm = om; garg = oa; }   // ties: the lower class, i.e. half 0
-                    }
-                    const int64_t blk = blk_w + cbase;
-                    float* stg = reinterpret_cast<float*>(smem + SmemLayout::xchg) + ew * (kStoreTileBytes / 4);   // (no cluster exchange here)
-                    if (p.decision) {
-                        if (n_here == 32 && p.vec_store) {
-                            if (live) {
-                                float* zr = p.decision + row * p.out_pitch + p.out_col0 + cbase;
-#pragma unroll
-                                for (int i = 0; i < 32; i += 4)
-                                    __stcs(reinterpret_cast<float4*>(zr + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                            }
-                        } else {
-                            store_block_by_rows(stg, v, lane, p.decision + blk, p.out_pitch, rows_valid, n_here);
-                        }
-                    }
-                    const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
-                    const float tau = gm - 2.0f * ez;
-                    const float gml = gm * kLog2e;
-                    float gs = 0.0f;
-                    int gnear = 0;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        gnear += v[i] > tau ? 1 : 0;
-                        v[i] = ex2(fmaf(v[i], kLog2e, -gml));
-                        gs += v[i];
-                    }
-                    if (two) {
-                        float* xs = chunk_ref + 4 * BM;               // [2 halves][128 rows] sums, then near-tie counts
-                        int* xn = reinterpret_cast<int*>(chunk_ref + 6 * BM);
-                        xs[h * BM + r_in_tile] = gs;
-                        xn[h * BM + r_in_tile] = gnear;
-                        asm volatile("bar.sync %0, 64;" ::"r"(3 + q) : "memory");
-                        gs += xs[(h ^ 1) * BM + r_in_tile];           // a + b == b + a: both warps hold the same sum
-                        gnear += xn[(h ^ 1) * BM + r_in_tile];
-                    }
-                    const float inv = __frcp_rn(gs);
-                    const float risk_thr = 8e-6f / ez;
-                    if (p.proba) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] *= inv;
-                        if (n_here == 32 && p.vec_store == 2) {
-                            if (live) {
-                                float* pr = p.proba + row * p.out_pitch + p.out_col0 + cbase;
-#pragma unroll
-                                for (int i = 0; i < 32; i += 8) st_cs_v8(pr + i, v + i);
-                            }
-                        } else {
-                            store_block_by_rows(stg, v, lane, p.proba + blk, p.out_pitch, rows_valid, n_here);
-                        }
-                    }
-                    if (live && h == 0) {
-                        if (p.label) __stcs(p.label + row, garg);
-                        if (p.maxprob) __stcs(p.maxprob + row, inv);      // exp(gm - gm) == 1
-                        const bool finite_row = finite_f(gm) && finite_f(gs);
-                        if (!finite_row) {
-                            if (p.flags && !p.count_nonfinite) flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
-                            else atomicAdd(p.status, 1ull);
-                        }
-                        if (p.lse) p.lse[row] = gm + logf(gs);
-                        if (p.flags && finite_row && (gnear >= 2 || inv * (1.0f - inv) > risk_thr))
-                            flag_row(p.flags, p.flag_list, p.n_flagged, p.ezr, row, ez);
-                    }
-                } else {
-                    tc_fence_before();
-                    mbar_arrive(acc_empty + buf);
-                }
+                float* stg_r = reinterpret_cast<float*>(smem + SmemLayout::xchg) + ew * (kStoreTileBytes / 4);   // (no cluster exchange here)
+                epilogue_in_registers<F16>(p, t_lane, h, q, lane, n_real, row, live, rows_valid, blk_w, cscale_s, bias_s,
+                                           chunk_ref, stg_r, acc_empty + buf, psum_scale, floor_err);
                 continue;
             }
 
@@ -945,11 +974,11 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #define LRS_CHUNK_LOGITS(v, cb)                                                                        \
             do {                                                                                       \
                 if (p.split) {                                                                         \
-                    _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8)                               \
-                        tmem_add8(t_lane + (uint32_t)(BN + (cb) + i8), (v) + i8);                      \
+                    _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 16)                              \
+                        tmem_add16(t_lane + (uint32_t)(BN + (cb) + i8), (v) + i8);                     \
                     for (int sg = 1; sg < p.ksplit; ++sg)                                              \
-                        _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 8)                           \
-                            tmem_add8(t_lane + seg_offset(sg, p.seg_w) + (uint32_t)((cb) + i8), (v) + i8);      \
+                        _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 16)                          \
+                            tmem_add16(t_lane + seg_offset(sg, p.seg_w) + (uint32_t)((cb) + i8), (v) + i8);     \
                 }                                                                                      \
                 /* eight columns at a time, fenced: with all 64 scale / bias values of a chunk loaded */ \
                 /* ahead of the FMAs the second (in-flight) TMEM buffer no longer fits in registers */    \

@@ -24,8 +24,8 @@ PATH_NAMES = {1: "narrow", 2: "wide", 3: "gemm", 4: "generic"}
 BINARY_D = [4, 5, 8, 16, 30, 32, 33, 64, 100, 101, 128, 256, 257, 512, 1000, 1001, 1024, 2048, 2049, 4096, 5001, 20000,
             100000, 100001]
 MULTI = [(4, 3), (16, 4), (30, 3), (33, 4), (256, 3), (1000, 3), (54, 7), (64, 7), (784, 6), (64, 10), (61, 10), (784, 10),
-         (785, 10), (3072, 10), (4096, 10), (8000, 10), (8000, 3), (1024, 12), (128, 16), (784, 16), (32, 20), (54, 20), (16, 26), (64, 32), (256, 32), (300, 50), (512, 100),
-         (1024, 128), (4096, 64), (768, 256), (1024, 300), (1024, 1000), (1022, 1000), (128, 1000), (2048, 2000)]
+         (785, 10), (3072, 10), (4096, 10), (8000, 10), (8000, 3), (1024, 12), (128, 16), (784, 16), (32, 20), (54, 20), (16, 26), (64, 32), (256, 32), (64, 50), (300, 50), (96, 96), (512, 100), (512, 101),
+         (1024, 128), (4096, 64), (768, 255), (768, 256), (1024, 300), (1024, 1000), (1024, 1001), (1022, 1000), (128, 1000), (2048, 2000)]
 
 
 def main():
