@@ -40,7 +40,7 @@ extern "C" {
                                  (large batches of 13..16 classes on rows of >= 64 floats take LR_PATH_GEMM)        */
 #define LR_PATH_WIDE     2    /* binary, rows of 1024 floats and more: row-block streaming, W re-used across 8 rows */
 #define LR_PATH_GEMM     3    /* 13..2048 classes: TMA-fed tcgen05 GEMM (3xFP16 split, 3xTF32 when the batch's dynamic
-                                 range demands it) + fused softmax; unaligned rows are re-pitched first; dense rows of
+                                 range demands it) + fused softmax; rows TMA cannot address arrive by cp.async; dense rows of
                                  <= 64 floats with <= 32 classes take its short-row form; 2049..65536 classes run as
                                  class groups of <= 2048, combined per row                                        */
 #define LR_PATH_GENERIC  4    /* any shape: SIMT row-per-warp fallback (what is left: > 65536 classes)           */

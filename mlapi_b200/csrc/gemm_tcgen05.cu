@@ -57,7 +57,10 @@ constexpr int BN = 256;          // classes per MMA / per W stage
 constexpr int A_TILE_BYTES = BM * BK * 4;     // 16 KB: one operand tile of X (hi or lo), either mode
 constexpr int kConvWarps = 4;                 // converter warps (all on one k-chunk)
 constexpr int kConvThreads = kConvWarps * 32;
-constexpr int kThreads = (2 + kConvWarps + 8 + 1) * 32;   // warps: TMA (W), MMA, converters, 8 epilogue, TMA (X)
+constexpr int kLoadWarps = 1;                 // X producer: drives TMA, or copies the rows TMA cannot address itself (a second
+                                              // loader warp helps odd pitches, 2.0 -> 2.5 TB/s, but 512 threads leave the
+                                              // epilogue short of registers: 56-byte spill frames instead of 24)
+constexpr int kThreads = (2 + kConvWarps + 8 + kLoadWarps) * 32;   // warps: TMA (W), MMA, converters, 8 epilogue, X producers
 constexpr int kEpiThreads = 256;
 constexpr int kMaxCluster = 4;          // class slices per cluster -> up to 2048 classes
 constexpr int kMaxAStages = 6;          // X ring depth the barrier block has room for
@@ -98,6 +101,12 @@ struct GemmParams {
     int nb;                 // 256-class blocks per CTA (1 or 2)
     int split;              // 1: nb == 1 and the correction products accumulate in TMEM columns 256..511
     int stage_off;          // byte offset of the epilogue's 8 x 2 KB store tiles inside the ring area (0: none; see store_block_by_rows)
+    int sw_load;            // 1, 2: TMA cannot address X (row pitch or base not a multiple of 16 bytes -- and the innermost box
+                            // coordinate has to be one too, so no tensor map over every fourth row helps): the X producer
+                            // warp fills the raw tiles with 4-byte (1) or 8-byte (2) cp.async copies from x_raw instead
+    const float* x_raw;     // X and its pitch (floats) for that
+    int64_t ldx;
+    int d_x;                // real row length of X (n_features is the length the W copies are padded to)
     int ncc;                // class slices per cluster: CTAs that share a row tile
     int nrt;                // row tiles per cluster (1 or 2): CTAs that share a class slice
                             // cluster = ncc * nrt CTAs, rank = slice + ncc * row_tile
@@ -186,6 +195,14 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
             smem_u32(dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// 4-byte asynchronous copy global -> shared (src_bytes = 0: four zero bytes), and "all my copies so far have landed"
+// as an arrival on an mbarrier whose count already includes it
+__device__ __forceinline__ void cp_async4(uint32_t dst, const float* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
@@ -662,7 +679,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kMaxAStages; ++i) {     // (operand ring and raw ring may differ in depth)
-            mbar_init(x_full + i, 1);
+            mbar_init(x_full + i, p.sw_load ? kLoadWarps * 32 : 1);
             mbar_init(a_ready + i, PAIR ? 2 * kConvThreads : kConvThreads);    // PAIR: both CTAs' converters report to the issuing CTA
             mbar_init(a_empty + i, 1);
         }
@@ -742,6 +759,73 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         if (++bs == B_STAGES) { bs = 0; bph ^= 1; }
                     }
                 }
+            }
+        }
+    } else if (warp >= 2 + kConvWarps + 8 && p.sw_load) {
+        // ===================== X producers, rows TMA cannot address =====================
+        // The warp copies the 128 rows of the tile; a warp instruction = consecutive floats of one row
+        // (coalesced), 4 bytes per lane -- 8 where every row is 8-byte aligned (sw_load == 2: even pitch, e.g. the
+        // dense rows of an even feature count).  Rows past the end and columns past the row length arrive as zeros,
+        // like TMA's out-of-bounds fill.  The copies are asynchronous: a stage's instructions are issued back to
+        // back and the stage's barrier counts every lane's "all landed".  A tile and k-chunk that lie fully inside
+        // the batch take a loop without predicates or pointer selects: one warp issues dependent integer work at
+        // one instruction per ~4 cycles, and with ~10 instructions per copy the loader managed 1.8 TB/s.
+        const int lw = warp - (2 + kConvWarps + 8);
+        constexpr int ROWS = BM / kLoadWarps;
+        int as = 0;
+        uint32_t aph = 0;
+        for (int64_t grp = cluster_id; grp < n_groups; grp += n_clusters) {
+            const int64_t tile = grp * gsz + rt;
+            const int64_t row_lo = tile * BM + lw * ROWS;
+            for (int kc = 0; kc < p.num_k_chunks; ++kc) {
+                mbar_wait(a_empty + as, aph ^ 1);
+                const int k0 = kc * BKx;
+                const uint32_t xdst = smem_u32(F16 ? a_hi + as * A_STAGE : a_hi + as * A_TILE_BYTES) +
+                                      (uint32_t)(lw * ROWS * BKx * 4);
+                if (row_lo + ROWS <= p.n_rows && k0 + BKx <= p.d_x) {
+                    const float* src = p.x_raw + row_lo * p.ldx + k0;
+                    if constexpr (F16) {                 // raw tile: [128][64] floats, linear
+                        if (p.sw_load == 2) {
+                            src += 2 * lane;
+                            const uint32_t dst = xdst + (uint32_t)(lane * 8);
+#pragma unroll 8
+                            for (int r = 0; r < ROWS; ++r, src += p.ldx)
+                                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + (uint32_t)(r * 256)), "l"(src) : "memory");
+                        } else {
+                            src += lane;
+                            const uint32_t dst = xdst + (uint32_t)(lane * 4);
+#pragma unroll 8
+                            for (int r = 0; r < ROWS; ++r, src += p.ldx) {
+                                cp_async4(dst + (uint32_t)(r * 256), src, 4u);
+                                cp_async4(dst + (uint32_t)(r * 256 + 128), src + 32, 4u);
+                            }
+                        }
+                    } else {                             // [128][32] floats in the operand's 128-byte swizzle
+                        src += lane;
+                        const uint32_t dst = xdst + (uint32_t)((lane & 3) * 4);
+#pragma unroll 8
+                        for (int r = 0; r < ROWS; ++r, src += p.ldx)      // (ROWS % 8 == 0: r & 7 is the tile row's)
+                            cp_async4(dst + (uint32_t)(r * 128 + (((lane >> 2) ^ (r & 7)) << 4)), src, 4u);
+                    }
+                } else {
+                    for (int r = 0; r < ROWS; ++r) {
+                        const bool rv = row_lo + r < p.n_rows;
+                        const float* src = p.x_raw + (rv ? row_lo + r : 0) * p.ldx + k0;
+                        if constexpr (F16) {
+#pragma unroll
+                            for (int c = lane; c < BKx; c += 32) {
+                                const bool ok = rv && k0 + c < p.d_x;
+                                cp_async4(xdst + (uint32_t)(r * (BKx * 4) + c * 4), ok ? src + c : p.x_raw, ok ? 4u : 0u);
+                            }
+                        } else {
+                            const bool ok = rv && k0 + lane < p.d_x;
+                            cp_async4(xdst + (uint32_t)(r * 128 + (((lane >> 2) ^ (r & 7)) << 4) + (lane & 3) * 4),
+                                      ok ? src + lane : p.x_raw, ok ? 4u : 0u);
+                        }
+                    }
+                }
+                cp_async_arrive_noinc(x_full + as);
+                if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
         }
     } else if (warp == 2 + kConvWarps + 8) {
@@ -907,7 +991,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 if (++as == A_STAGES) { as = 0; aph ^= 1; }
             }
         }
-    } else {
+    } else if (warp < 2 + kConvWarps + 8) {
         // ===================== epilogue (8 warps) =====================
         // Warp w may read TMEM lanes 32*(w%4)..+31 only, so the eight warps form two groups of four:
         // group h covers half of this CTA's class columns for all 128 rows.  Two passes over TMEM:
@@ -1206,29 +1290,39 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 // the row of P and a few rows of W instead of all of W.  The epilogue leaves a compact list of the flagged
 // rows, so the warps of this pass share them evenly whatever their density.
 //
-// Four dot products at once (rows c[0..3] of W against the same row of X; both are 16-byte aligned on this
-// path): the pieces of X are loaded once and sixteen independent loads are in flight per lane -- taken one
-// class at a time, a row's ~20 selected classes were ~20 dependent trips to L2.
+// Four dot products at once (rows c[0..3] of W, `ldw` floats apart, against the same row of X): the pieces of X
+// are loaded once and sixteen independent loads are in flight per lane -- taken one class at a time, a row's ~20
+// selected classes were ~20 dependent trips to L2.  `xal`: the row of X is 16-byte aligned and d % 4 == 0
+// (128-bit loads of both); otherwise 4-byte loads over exactly d elements.
 __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const float* __restrict__ W, const int (&c)[4],
-                                             int d, int lane, float (&z)[4]) {
-    const float4* x4 = reinterpret_cast<const float4*>(x);
-    const float4* w4[4];
-    float acc[4];
+                                             int d, int ldw, bool xal, int lane, float (&z)[4]) {
+    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (xal) {
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const float4* w4[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-        w4[u] = reinterpret_cast<const float4*>(W + (int64_t)c[u] * d);
-        acc[u] = 0.0f;
-    }
+        for (int u = 0; u < 4; ++u) w4[u] = reinterpret_cast<const float4*>(W + (int64_t)c[u] * ldw);
 #pragma unroll 4
-    for (int k = lane; k < d / 4; k += 32) {
-        const float4 xv = __ldg(x4 + k);
+        for (int k = lane; k < d / 4; k += 32) {
+            const float4 xv = __ldg(x4 + k);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const float4 wv = __ldg(w4[u] + k);
-            acc[u] = fmaf(xv.x, wv.x, acc[u]);
-            acc[u] = fmaf(xv.y, wv.y, acc[u]);
-            acc[u] = fmaf(xv.z, wv.z, acc[u]);
-            acc[u] = fmaf(xv.w, wv.w, acc[u]);
+            for (int u = 0; u < 4; ++u) {
+                const float4 wv = __ldg(w4[u] + k);
+                acc[u] = fmaf(xv.x, wv.x, acc[u]);
+                acc[u] = fmaf(xv.y, wv.y, acc[u]);
+                acc[u] = fmaf(xv.z, wv.z, acc[u]);
+                acc[u] = fmaf(xv.w, wv.w, acc[u]);
+            }
+        }
+    } else {
+        const float* w1[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) w1[u] = W + (int64_t)c[u] * ldw;
+#pragma unroll 4
+        for (int k = lane; k < d; k += 32) {
+            const float xv = __ldg(x + k);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) acc[u] = fmaf(xv, __ldg(w1[u] + k), acc[u]);
         }
     }
 #pragma unroll
@@ -1245,7 +1339,7 @@ constexpr int kFixQueue = 64;          // selected classes waiting for their dot
 // grid-stride over the list, one warp per flagged row.  Dynamic shared memory: [kFixWarps][c_pad] floats (the
 // row of P a warp works on) + [kFixWarps][kFixQueue] ints.
 __global__ void __launch_bounds__(kFixWarps * 32)
-gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int c_pad, int64_t out_pitch, int out_col0,
+gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int ldw, int xal, int C, int c_pad, int64_t out_pitch, int out_col0,
                       const float* __restrict__ W, const float* __restrict__ b,
                       const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
                       const float* __restrict__ lse, const float* __restrict__ ezr, float* proba,
@@ -1263,7 +1357,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
         if (!finite_f(L)) {
             // the tensor pass saw NaN/inf here (bad input, or an fp16 overflow of a finite one):
             // score the whole row in fp32, which also settles whether the input really is non-finite
-            score_row_warp_pitched(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status, out_pitch, out_col0);
+            score_row_warp_pitched(x, row, lane, d, ldw, C, W, b, proba, decision, label, maxprob, status, out_pitch, out_col0);
             if (lane == 0) atomicAdd(rescored, 1ull);
             continue;
         }
@@ -1305,7 +1399,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
 #pragma unroll
                 for (int u = 0; u < 4; ++u) cls[u] = queue[done + (u < take ? u : 0)];
                 float z4[4];
-                warp_dot4_x4(x, W, cls, d, lane, z4);
+                warp_dot4_x4(x, W, cls, d, ldw, xal != 0, lane, z4);
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (u >= take) break;
@@ -1362,7 +1456,7 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, in
 // /predict pattern): there is no row of P to pick classes from, so a whole CTA re-scores every class
 // of the flagged row, eight warps splitting the classes, four classes per step.
 __global__ void __launch_bounds__(256)
-gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, int64_t out_pitch, int out_col0,
+gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int ldw, int xal, int C, int64_t out_pitch, int out_col0,
                        const float* __restrict__ W, const float* __restrict__ b,
                        const unsigned* __restrict__ list, const unsigned* __restrict__ n_list,
                        float* decision, int32_t* label, float* maxprob,
@@ -1383,7 +1477,7 @@ gemm_fixup_full_kernel(const float* __restrict__ X, int64_t ldx, int d, int C, i
 #pragma unroll
             for (int u = 0; u < 4; ++u) cls[u] = min(c + u, c_hi - 1);
             float z4[4];
-            warp_dot4_x4(x, W, cls, d, lane, z4);
+            warp_dot4_x4(x, W, cls, d, ldw, xal != 0, lane, z4);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 if (c + u >= c_hi) break;
@@ -2122,9 +2216,8 @@ int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, u
 
 }  // namespace
 
-// Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048.  TMA wants
-// 16-byte aligned rows: batches whose base or pitch is not (odd feature counts among them) are re-pitched
-// into an aligned scratch first, see gemm_launch.
+// Shapes the tensor-core path serves: more classes than the narrow path holds, up to 2048.  TMA wants a
+// 16-byte aligned base and pitch: batches without are fetched by the kernel's own loader, see gemm_launch.
 bool gemm_supports(const Model& m, const ScoreArgs& a) {
     return m.gemm != nullptr && a.n_rows < (int64_t)1 << 31;
 }
@@ -2140,7 +2233,7 @@ int gemm_load(Model& m, const double* coef, const double* intercept) {
     LRS_CUDA(cudaMemcpy(g->bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
     LRS_CUDA(cudaMemcpy(g->coef64, coef, (size_t)C * d * sizeof(double), cudaMemcpyHostToDevice));
     if (g->w32_pad) {
-        // fp32 coefficients at the padded pitch, for the re-scoring pass over re-pitched rows (see gemm_launch)
+        // fp32 coefficients at the padded pitch, for the re-scoring pass (its W rows are read with 128-bit loads)
         std::vector<float> w32((size_t)C * d4, 0.0f);
         for (int c = 0; c < C; ++c)
             for (int k = 0; k < d; ++k) w32[(size_t)c * d4 + k] = (float)coef[(size_t)c * d + k];
@@ -2170,7 +2263,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     if (m.n_scores < 13 || m.n_scores > kMaxCluster * 2 * BN) return LR_OK;
     if (!encode_tiled()) return LR_OK;            // no TMA descriptor API: generic path serves the model
     {
-        // The per-call scratch of this path (X scale, flags, log-sum-exp, re-pitched rows) comes from the device's
+        // The per-call scratch of this path (X scale, flags, log-sum-exp) comes from the device's
         // default stream-ordered pool.  Left at its default threshold of 0 the pool hands its memory back to the
         // driver at every synchronisation, i.e. once per lr_score_host call: let it keep up to 1 GiB.
         cudaMemPool_t pool = nullptr;
@@ -2337,19 +2430,6 @@ void gemm_destroy(Model& m) {
 
 namespace {
 
-// Rows of X copied to a 16-byte pitch (d4 floats, zero-filled beyond d): one warp per row.
-__global__ void __launch_bounds__(256)
-repitch_kernel(const float* __restrict__ X, int64_t n_rows, int64_t ldx, int d, int d4, float* __restrict__ out) {
-    const int lane = threadIdx.x & 31;
-    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (int64_t)gridDim.x * 8) {
-        const float* x = X + row * ldx;
-        float* o = out + row * d4;
-        for (int k = lane; k < d4; k += 32) o[k] = k < d ? ldg_stream1(x + k) : 0.0f;
-    }
-}
-
-// The tensor-core pass over rows that TMA can address: 16-byte aligned base and pitch, `d_eff` columns
-// (a multiple of 4); `w_fix` = fp32 coefficients at pitch d_eff for the re-scoring pass.
 // Stream-ordered scratch that is handed back on every way out of the launch code.
 struct AsyncScratch {
     void* p = nullptr;
@@ -2369,8 +2449,12 @@ cudaError_t launch_gemm_kernel(const cudaLaunchConfig_t& cfg, bool pair, const C
     }
 }
 
-int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix) {
+// `d_eff`: row length as the W copies see it (n_features rounded up to 4); `w_fix`: fp32 W at pitch d_eff for the
+// re-scoring pass; `sw_load`: TMA cannot address X (GemmParams::sw_load).
+int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix, bool sw_load) {
     GemmPlan* g = m.gemm;
+    const int d_x = m.n_features;
+    const bool xal = !sw_load && d_x % 4 == 0;      // 128-bit loads of X rows in the side kernels
     if (g->adaptive && g->active.load() == 0 && g->has[1]) {
         // what the mirror shows of earlier launches on this model (it may lag by a launch or two)
         const unsigned long long rows = *reinterpret_cast<volatile unsigned long long*>(g->mirror + 3);
@@ -2385,12 +2469,14 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     GemmPlan::Layout& L = g->layout[g->active.load()];
     // X as the two arithmetics read it: fp32 boxes of 64 columns, unswizzled (3xFP16: converted in place) or of
     // 32 columns, 128-byte swizzle (3xTF32)
-    CUtensorMap map_x16, map_x32;
+    // (columns past the real row length and rows past the batch read as zeros; with sw_load the kernel takes no X map,
+    // a W map stands in)
+    CUtensorMap map_x16 = L.map_w16hi, map_x32 = L.map_whi;
     int rc;
-    if (g->force != 2 &&
-        (rc = make_map_ex(&map_x16, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, BM, BK16, 4, false)) != LR_OK)
+    if (!sw_load && g->force != 2 &&
+        (rc = make_map_ex(&map_x16, a.X, (uint64_t)a.n_rows, (uint64_t)d_x, (uint64_t)a.ldx, BM, BK16, 4, false)) != LR_OK)
         return rc;
-    if (g->force != 1 && (rc = make_map(&map_x32, a.X, (uint64_t)a.n_rows, (uint64_t)d_eff, (uint64_t)a.ldx, BM)) != LR_OK)
+    if (!sw_load && g->force != 1 && (rc = make_map(&map_x32, a.X, (uint64_t)a.n_rows, (uint64_t)d_x, (uint64_t)a.ldx, BM)) != LR_OK)
         return rc;
     const size_t smem = (L.pair ? SmemLayoutT<true>::total : SmemLayoutT<false>::total) + 1024;
     const int dev = m.device & 63;
@@ -2426,10 +2512,19 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     }
     if (a.lse_out) lse = a.lse_out;                 // a class group hands its log-sum-exp to the caller
     LRS_CUDA(cudaMemsetAsync(x_scale, 0, 64, a.stream));          // ticket, decisions, [8] = length of the re-scoring list
-    x_scale_kernel<true><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_eff, g->col_scale, g->w_norm_max,
-                                                              g->inv_cscale_max, g->force, x_scale, rowstat);
+    if (xal)
+        x_scale_kernel<true><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_x, g->col_scale, g->w_norm_max,
+                                                                  g->inv_cscale_max, g->force, x_scale, rowstat);
+    else
+        x_scale_kernel<false><<<kXScaleBlocks, 256, 0, a.stream>>>(a.X, a.n_rows, a.ldx, d_x, g->col_scale, g->w_norm_max,
+                                                                   g->inv_cscale_max, g->force, x_scale, rowstat);
     count_launch();
     GemmParams p;
+    // (8-byte copies where every row starts on an 8-byte boundary)
+    p.sw_load = !sw_load ? 0 : ((a.ldx % 2 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 7u) == 0) ? 2 : 1);
+    p.x_raw = a.X;
+    p.ldx = a.ldx;
+    p.d_x = d_x;
     p.flags = flags;
     p.flag_list = flag_list;
     p.n_flagged = reinterpret_cast<unsigned*>(x_scale) + 8;
@@ -2572,11 +2667,11 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
                 g->fix_configured[dev] = true;
             }
             gemm_fixup_sel_kernel<<<m.num_sms * 3, kFixWarps * 32, fsm, a.stream>>>(
-                a.X, a.ldx, d_eff, m.n_scores, c_pad, p.out_pitch, p.out_col0, w_fix, m.b, flag_list, p.n_flagged, lse, ezr,
+                a.X, a.ldx, d_x, d_eff, xal ? 1 : 0, m.n_scores, c_pad, p.out_pitch, p.out_col0, w_fix, m.b, flag_list, p.n_flagged, lse, ezr,
                 a.proba, a.decision,
                 a.label, a.maxprob, m.status + 1, m.status);
         } else {
-            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_eff, m.n_scores, p.out_pitch,
+            gemm_fixup_full_kernel<<<m.num_sms * 4, 256, 0, a.stream>>>(a.X, a.ldx, d_x, d_eff, xal ? 1 : 0, m.n_scores, p.out_pitch,
                                                                        p.out_col0, w_fix, m.b,
                                                                        flag_list, p.n_flagged, a.decision, a.label,
                                                                        a.maxprob, m.status + 1, m.status);
@@ -2698,41 +2793,14 @@ int gemm_launch(const Model& m, const ScoreArgs& a) {
     GemmPlan* g = m.gemm;
     const int d = m.n_features;
     if (short_rows_serve(m, a)) return short_launch(m, a);
-    const bool aligned = d % 4 == 0 && a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
-    if (aligned) return gemm_launch_aligned(m, a, d, m.W);
-    // Odd feature counts, odd pitches, unaligned bases: TMA cannot address those rows.  They are copied in
-    // blocks of rows to an aligned scratch (stream-ordered, <= 512 MB) and the block is scored from there --
-    // one extra read and write of X, against a SIMT fallback that ran 40x slower on d=1022, C=1000.
+    // TMA wants a 16-byte aligned base and row pitch (any row length: columns past it are out of bounds and read as
+    // zeros, which is what the zero-padded W copies multiply them with).  Everything else -- odd pitches, the dense
+    // rows of an odd feature count, a base off by a few floats -- is fetched by the kernel's X producer warps with
+    // 4-byte asynchronous copies (GemmParams::sw_load).  (Until late in round 2 such batches were first copied to an
+    // aligned scratch: one extra write and read of X, 9.9 ms against 6.4 on d=1022 / 1024 with 1000 classes.)
+    const bool tma_ok = a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
     const int d4 = g->d4;
-    const float* w_fix = d4 == d ? m.W : g->w32_pad;
-    int64_t block = ((int64_t)512 << 20) / ((int64_t)d4 * 4);
-    block = block < 1024 ? 1024 : block / 1024 * 1024;
-    if (block > a.n_rows) block = a.n_rows;
-    AsyncScratch rows;
-    rows.s = a.stream;
-    LRS_CUDA(cudaMallocAsync(&rows.p, (size_t)block * d4 * sizeof(float), a.stream));
-    float* scratch = static_cast<float*>(rows.p);
-    int rc = LR_OK;
-    const int C = m.n_scores;
-    for (int64_t r0 = 0; r0 < a.n_rows && rc == LR_OK; r0 += block) {
-        const int64_t n = a.n_rows - r0 < block ? a.n_rows - r0 : block;
-        const int64_t want = (n + 7) / 8;
-        const int grid = (int)(want < (int64_t)m.num_sms * 8 ? want : (int64_t)m.num_sms * 8);
-        repitch_kernel<<<grid, 256, 0, a.stream>>>(a.X + r0 * a.ldx, n, a.ldx, d, d4, scratch);
-        count_launch();
-        ScoreArgs s = a;
-        s.X = scratch;
-        s.ldx = d4;
-        s.n_rows = n;
-        const int64_t pitch = a.out_pitch ? a.out_pitch : C;
-        if (a.proba) s.proba = a.proba + r0 * pitch;
-        if (a.decision) s.decision = a.decision + r0 * pitch;
-        if (a.lse_out) s.lse_out = a.lse_out + r0;
-        if (a.label) s.label = a.label + r0;
-        if (a.maxprob) s.maxprob = a.maxprob + r0;
-        rc = gemm_launch_aligned(m, s, d4, w_fix);
-    }
-    return rc;
+    return gemm_launch_aligned(m, a, d4, d4 == d ? m.W : g->w32_pad, !tma_ok);
 }
 
 // ---- more than 2048 classes: class groups --------------------------------------------------------------------

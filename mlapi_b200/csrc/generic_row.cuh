@@ -11,8 +11,8 @@ namespace lrs {
 constexpr int kGenericCC = 4;   // score columns per sweep over the row
 
 // `pitch` floats between rows of proba / decision, `col0` the first column this model's classes occupy (a class
-// group of a larger model; pitch = C, col0 = 0 otherwise)
-__device__ __forceinline__ void score_row_warp_pitched(const float* __restrict__ x, int64_t row, int lane, int d, int C,
+// group of a larger model; pitch = C, col0 = 0 otherwise); `ldw` floats between rows of W (>= d)
+__device__ __forceinline__ void score_row_warp_pitched(const float* __restrict__ x, int64_t row, int lane, int d, int ldw, int C,
                                                        const float* __restrict__ W, const float* __restrict__ b,
                                                        float* __restrict__ proba, float* __restrict__ decision,
                                                        int32_t* __restrict__ label, float* __restrict__ maxprob,
@@ -29,7 +29,7 @@ __device__ __forceinline__ void score_row_warp_pitched(const float* __restrict__
             const float xv = __ldg(x + k);
 #pragma unroll
             for (int i = 0; i < CC; ++i)
-                if (c0 + i < C) acc[i] = fmaf(xv, __ldg(W + (int64_t)(c0 + i) * d + k), acc[i]);
+                if (c0 + i < C) acc[i] = fmaf(xv, __ldg(W + (int64_t)(c0 + i) * ldw + k), acc[i]);
         }
 #pragma unroll
         for (int i = 0; i < CC; ++i)
@@ -86,7 +86,7 @@ __device__ __forceinline__ void score_row_warp(const float* __restrict__ x, int6
                                                float* __restrict__ proba, float* __restrict__ decision,
                                                int32_t* __restrict__ label, float* __restrict__ maxprob,
                                                unsigned long long* status) {
-    score_row_warp_pitched(x, row, lane, d, C, W, b, proba, decision, label, maxprob, status, C, 0);
+    score_row_warp_pitched(x, row, lane, d, d, C, W, b, proba, decision, label, maxprob, status, C, 0);
 }
 #endif
 

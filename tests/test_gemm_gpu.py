@@ -150,18 +150,18 @@ def test_gemm_device_pitch(eng):
 
 
 @pytest.mark.parametrize("d,c", [(5, 17), (33, 40), (131, 100), (1022, 300), (250, 1000), (1023, 2048)])
-def test_gemm_odd_feature_counts_are_repitched(eng, d, c):
-    """n_features % 4 != 0: TMA cannot address the rows, the library copies them to an aligned scratch
-    and stays on the tensor-core path (the SIMT fallback was 40x slower on d=1022, C=1000)."""
+def test_gemm_odd_feature_counts(eng, d, c):
+    """n_features % 4 != 0 from host arrays: the staging buffers keep a 16-byte pitch, the tensor map's row length
+    is the real one (columns past it read as zeros) and the batch stays on the tensor-core path."""
     mlapi, lib = eng
     W, b = synth.make_model(d, c, 500 + c)
     clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
     rng = np.random.default_rng(d * 3 + c)
     for n in (1, 130, 1111):
         X = rng.standard_normal((n, d), dtype=np.float32)
-        out = clf.score_rows(X, **ALL)                      # dispatcher: gemm (re-pitched)
+        out = clf.score_rows(X, **ALL)                      # dispatcher: gemm
         parity.assert_parity(out, orc.decision_function(X, W, b), orc.predict_proba(X, W, b),
-                             orc.predict_index(X, W, b), f"gemm repitch d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+                             orc.predict_index(X, W, b), f"gemm odd d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
     Xb = rng.standard_normal((300, d), dtype=np.float32)
     Xb[7, d - 1] = np.nan                                   # last (odd) column must be seen
     with pytest.raises(ValueError, match="NaN or infinity"):
@@ -169,26 +169,39 @@ def test_gemm_odd_feature_counts_are_repitched(eng, d, c):
     clf.close()
 
 
-def test_gemm_unaligned_device_rows_are_repitched(eng):
+@pytest.mark.parametrize("f16", ["1", "0"])
+@pytest.mark.parametrize("d,pitch,off,c,n", [(64, 67, 0, 300, 700),      # odd pitch
+                                             (64, 67, 1, 300, 700),      # odd pitch, base 4 bytes past a 16-byte boundary
+                                             (64, 68, 2, 40, 5000),      # aligned pitch, base 8 bytes off (8-byte copies)
+                                             (1022, 1022, 0, 100, 3000), # dense rows of an even feature count (8-byte copies)
+                                             (617, 617, 0, 26, 2500),    # dense rows of an odd feature count (4-byte copies)
+                                             (131, 135, 3, 1000, 900),   # several class blocks, K tail, ragged last tile
+                                             (70, 70, 2, 17, 129)])
+def test_gemm_device_rows_tma_cannot_address(eng, d, pitch, off, c, n, f16, monkeypatch):
+    """Row pitch or base not a multiple of 16 bytes: no tensor map can describe X (and the innermost box coordinate
+    must be 16-byte aligned too), so the kernel's X producer warps copy the rows with 4- or 8-byte cp.async -- in
+    both arithmetics (3xFP16: linear raw tile; 3xTF32: the operand's swizzled layout), with a P matrix and with
+    labels + max probability only, whose re-scoring kernels read the same unaligned rows."""
     import ctypes as C
     import torch
     mlapi, lib = eng
+    monkeypatch.setenv("LRS_GEMM_F16", f16)
     L = lib.load()
-    d, c, n = 64, 300, 700
-    W, b = synth.make_model(d, c, 11)
+    W, b = synth.make_model(d, c, 11 + d)
     clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
-    buf = np.random.default_rng(5).standard_normal((n, d + 3), dtype=np.float32)
-    for off in (0, 1):                                      # odd pitch; odd pitch + 4-byte aligned base
-        Xh = buf[:, off:off + d]
-        Xt = torch.from_numpy(buf).cuda()[:, off:off + d]
-        path = C.c_int32(0)
-        lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, d + 3, C.byref(path)))
-        assert path.value == lib.PATH_GEMM
-        out = clf.score_rows(Xt, **ALL)
+    buf = np.random.default_rng(5 + d).standard_normal(n * pitch + 8, dtype=np.float32)
+    Xh = buf[off:off + n * pitch].reshape(n, pitch)[:, :d]
+    Xt = torch.from_numpy(buf).cuda()[off:off + n * pitch].view(n, pitch)[:, :d]
+    path = C.c_int32(0)
+    lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, pitch, C.byref(path)))
+    assert path.value == lib.PATH_GEMM
+    z = orc.decision_function(Xh, W, b)
+    for pattern in (ALL, dict(label=True, maxprob=True)):
+        out = clf.score_rows(Xt, **pattern)
         torch.cuda.synchronize()
-        host = {k: v.cpu().numpy() for k, v in out.items()}
-        parity.assert_parity(host, orc.decision_function(Xh, W, b), orc.predict_proba(Xh, W, b),
-                             orc.predict_index(Xh, W, b), f"gemm unaligned off={off}", z_atol=parity.Z_ATOL_TENSOR)
+        host = {k: v.cpu().numpy() for k, v in out.items() if v is not None}
+        parity.assert_parity(host, z, orc.softmax(z), z.argmax(1), f"gemm unaligned d={d} pitch={pitch} off={off} f16={f16}",
+                             z_atol=parity.Z_ATOL_TENSOR)
     clf.close()
 
 

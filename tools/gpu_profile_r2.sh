@@ -19,7 +19,7 @@ timeout 300 python tools/latency_single.py > gpurun_out/r2_latency_single.json 2
 if [ "$1" != "skip-ncu" ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
   timeout 600 $CMD > gpurun_out/r2_plain.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:narrow|wide_|gemm_|x_scale|short_|fixup|w_split|w_colscale|repitch|groups_" -c 400 --csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:narrow|wide_|gemm_|x_scale|short_|fixup|w_split|w_colscale|groups_" -c 400 --csv \
       --log-file gpurun_out/r2_launches_default.csv $CMD > gpurun_out/r2_ncu_list.log 2>&1
   echo "ncu list exit $?"
   CMD3="python bench.py --workload cfg3 --rows 400000 --steps 2 --warmup 3 --no-e2e --no-cpu"

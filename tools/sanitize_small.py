@@ -35,7 +35,7 @@ for d, ns, n, path in ((32, 1, 1000, _lib.PATH_NARROW), (4, 3, 333, _lib.PATH_NA
     check(f"path {_lib.PATH_NAMES[path]} d={d} C={ns} n={n}", clf, X, W, b)
 
 # this round's kernels: 5..16 classes (W in shared memory / through L1), flat tiles (unaligned and long aligned
-# rows, >= 4096 rows), small-N tensor form, re-pitched tensor path
+# rows, >= 4096 rows), small-N tensor form, unaligned rows on the tensor path
 for d, ns, n in ((40, 10, 500), (61, 7, 300), (2600, 12, 200), (33, 1, 5000), (5, 1, 4100), (257, 3, 4100), (512, 1, 4100),
                  (1001, 4, 4100), (64, 32, 1000), (200, 100, 700), (131, 100, 500), (1022, 300, 260)):
     W, b = synth.make_model(d, ns, d + ns)
