@@ -261,6 +261,43 @@ def test_gemm_33_to_64_classes_ties_across_column_halves(eng, fixup, monkeypatch
     clf0.close()
 
 
+@pytest.mark.parametrize("d,c,n", [(96, 101, 129), (64, 50, 1000), (128, 1001, 300), (64, 150, 257), (40, 17, 130),
+                                   (512, 100, 333)])
+def test_gemm_outputs_stay_inside_their_rows(eng, d, c, n):
+    """The epilogue's shared-memory store tiles write whole row segments: guard rows before and after P, the
+    decision values, the labels and the max probabilities keep their canary, for class counts that take the tiles
+    (not multiples of 8), ragged last tiles included.  Straight through the C ABI on caller-owned device buffers."""
+    import ctypes as C
+    import torch
+    mlapi, lib = eng
+    L = lib.load()
+    W, b = synth.make_model(d, c, 3 * d + c)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    X = torch.randn(n, d, device="cuda")
+    canary = -7.25
+    P = torch.full(((n + 2) * c,), canary, device="cuda")
+    Z = torch.full(((n + 2) * c,), canary, device="cuda")
+    lab = torch.full((n + 2,), -7, dtype=torch.int32, device="cuda")
+    mp = torch.full((n + 2,), canary, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    lib.check(L.lr_score(clf._replicas[0].handle, C.c_void_p(X.data_ptr()), n, d, C.c_void_p(P.data_ptr() + 4 * c),
+                         C.c_void_p(Z.data_ptr() + 4 * c), C.c_void_p(lab.data_ptr() + 4), C.c_void_p(mp.data_ptr() + 4),
+                         C.c_void_p(st)))
+    torch.cuda.synchronize()
+    for t in (P, Z):
+        t = t.view(n + 2, c)
+        assert (t[0] == canary).all() and (t[-1] == canary).all()
+        assert (t[1:-1] != canary).all()
+    assert lab[0] == -7 and lab[-1] == -7 and mp[0] == canary and mp[-1] == canary
+    Xh = X.cpu().numpy()
+    z = orc.decision_function(Xh, W, b)
+    parity.assert_parity({"proba": P.view(n + 2, c)[1:-1].cpu().numpy(), "decision": Z.view(n + 2, c)[1:-1].cpu().numpy(),
+                          "label": lab[1:-1].cpu().numpy(), "maxprob": mp[1:-1].cpu().numpy()},
+                         z, orc.softmax(z), z.argmax(1), f"guard rows d={d} C={c} n={n}", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
+
+
 # ---- dynamic range: what the 3xFP16 split must survive ---------------------------------------------
 # fp16 halves hold 22 bits only while the `lo` half stays out of subnormals.  The engine balances W per
 # feature at load time, puts each class row at the top of fp16's range, scales X per call from a robust

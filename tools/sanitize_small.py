@@ -43,6 +43,31 @@ for d, ns, n in ((40, 10, 500), (61, 7, 300), (2600, 12, 200), (33, 1, 5000), (5
     clf = B200LogisticRegression(W, b, np.arange(max(ns, 2)), out_dtype=np.float32)
     check(f"auto d={d} C={ns} n={n}", clf, X, W, b)
 
+# late round 2: 33..64 classes in registers, class counts that leave through the store tiles, and device rows TMA
+# cannot address (the kernel's cp.async loader: 4- and 8-byte copies, both arithmetics)
+for d, ns, n in ((96, 50, 700), (300, 64, 300), (96, 101, 400), (64, 255, 300), (128, 1001, 200), (64, 150, 129)):
+    W, b = synth.make_model(d, ns, d + ns)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    clf = B200LogisticRegression(W, b, np.arange(ns), out_dtype=np.float32)
+    check(f"auto d={d} C={ns} n={n}", clf, X, W, b)
+import torch  # noqa: E402
+for f16 in ("1", "0"):
+    os.environ["LRS_GEMM_F16"] = f16
+    for d, pitch, off, ns, n in ((64, 67, 1, 300, 300), (1022, 1022, 0, 100, 200), (617, 617, 0, 26, 150), (70, 72, 2, 40, 129)):
+        W, b = synth.make_model(d, ns, d + ns)
+        buf = rng.standard_normal(n * pitch + 8, dtype=np.float32)
+        Xh = buf[off:off + n * pitch].reshape(n, pitch)[:, :d]
+        Xt = torch.from_numpy(buf).cuda()[off:off + n * pitch].view(n, pitch)[:, :d]
+        clf = B200LogisticRegression(W, b, np.arange(ns))
+        out = clf.score_rows(Xt, proba=True, label=True)
+        torch.cuda.synchronize()
+        err = np.abs(out["proba"].cpu().numpy() - orc.predict_proba(Xh, W, b)).max()
+        lab = clf.score_rows(Xt, label=True, maxprob=True)["label"].cpu().numpy()
+        print(f"device rows d={d} pitch={pitch} off={off} C={ns} f16={f16}: max|dP| = {err:.2e}", flush=True)
+        assert err < 1e-5 and lab.shape == (n,)
+        clf.close()
+del os.environ["LRS_GEMM_F16"]
+
 os.environ["LRS_NARROW_BULK"] = "1"
 os.environ["LRS_NARROW_BULK_MIN_ROWS"] = "1"
 W, b = synth.make_model(32, 1, 3)
@@ -58,7 +83,6 @@ for env in ({"LRS_GEMM_F16": "0"}, {"LRS_GEMM_PAIR": "0"}, {"LRS_GEMM_SPLIT": "1
     for k in env:
         del os.environ[k]
 
-import torch  # noqa: E402
 from mlapi_b200 import refit  # noqa: E402
 X = torch.randn(5000, 32, device="cuda")
 y = (torch.rand(5000, device="cuda") < 0.5).int()
