@@ -120,10 +120,12 @@ struct GemmParams {
                                   // with zeros to whole k-chunks
     float kappa;                  // relative logit error of the truncating TMEM accumulation (layout, arithmetic, row length)
     int acc_stride;               // TMEM columns between the two accumulator buffers (acc_bufs == 2)
-    int seg_w;                    // columns reserved per main accumulator when ksplit > 1: 32 or 64
-    int ksplit;                   // 1..7 main accumulators per tile, each over a contiguous third of the k-chunks (split
-                                  // layout, N <= 64 only: there is room in TMEM for 3, for 7 when N <= 32): the truncation error of a logit grows
-                                  // with the accumulation steps behind it, so long rows are summed in pieces
+    int seg_w;                    // columns reserved per main accumulator when ksplit > 1: 32, 64 or 128
+    int seg_slot;                 // TMEM columns a buffer owns in each half: 128 (two buffers) or 256 (one), see seg_offset
+    int ksplit;                   // 1..15 main accumulators per tile, each over a contiguous piece of the k-chunks (split
+                                  // layout, N <= 128 only: TMEM has room for 3 beside a second buffer when N <= 64, 7 without;
+                                  // 7 / 15 when N <= 32; 1 / 3 when N <= 128): the truncation error of a logit grows with
+                                  // the accumulation steps behind it, so long rows are summed in pieces
     int count_fallback;           // 3xTF32 kernel launched as the fallback of a 3xFP16 model: add n_rows to status[2]
     int a_stages;           // unpaired kernel: X ring depth (32 KB stages) ...
     int b_tile_bytes;       // ... bytes reserved per W stage ...
@@ -423,12 +425,13 @@ __device__ __forceinline__ void tc_mma<true>(uint32_t d, uint64_t a, uint64_t b,
 
 constexpr float kLog2e = 1.4426950408889634f;
 
-// TMEM columns of main accumulator `seg` relative to the tile's first one (GemmParams::ksplit; split layout,
-// buffers 128 columns apart, the correction accumulator BN columns up).  `w` = 64 (N <= 64: the second sits
-// beside the first, the third beside the correction accumulator) or 32 (N <= 32: four in the main slot, three
-// more beside the correction accumulator).
-__device__ __forceinline__ uint32_t seg_offset(int seg, int w) {
-    const int per_slot = 128 / w;
+// TMEM columns of main accumulator `seg` relative to the tile's first one (GemmParams::ksplit; split layout, the
+// correction accumulator BN columns up).  `slot` = columns a buffer owns in each half of TMEM: 128 with two
+// accumulator buffers, 256 with one.  `w` = 128, 64 or 32 columns per accumulator (N <= 128 / 64 / 32): slot / w of
+// them in the main half, slot / w - 1 more beside the correction accumulator (two buffers: 1, 3 or 7 in all; one
+// buffer: 3, 7 or 15).
+__device__ __forceinline__ uint32_t seg_offset(int seg, int w, int slot) {
+    const int per_slot = slot / w;
     return seg < per_slot ? (uint32_t)(seg * w) : (uint32_t)BN + (uint32_t)((seg - per_slot + 1) * w);
 }
 
@@ -514,7 +517,7 @@ __device__ __forceinline__ void epilogue_in_registers(const GemmParams& p, uint3
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] += u[i];
         for (int sg = 1; sg < p.ksplit; ++sg) {
-            tmem_ld32(t_col + seg_offset(sg, p.seg_w), u);
+            tmem_ld32(t_col + seg_offset(sg, p.seg_w, p.seg_slot), u);
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] += u[i];
         }
@@ -887,7 +890,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         tc_fence_after();
                         const uint64_t bd = b0 + (uint64_t)(bs * (B_TILE_BYTES >> 4));
                         const uint32_t t0 = tmem_base + buf * (uint32_t)p.acc_stride + (uint32_t)(nbk * BN);
-                        const uint32_t d_tmem = t0 + seg_offset(seg, p.seg_w);
+                        const uint32_t d_tmem = t0 + seg_offset(seg, p.seg_w, p.seg_slot);
                         const uint32_t c_tmem = t0 + c_off;
                         if (leader) {
                             if (part == 0) {
@@ -1062,7 +1065,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         tmem_add16(t_lane + (uint32_t)(BN + (cb) + i8), (v) + i8);                     \
                     for (int sg = 1; sg < p.ksplit; ++sg)                                              \
                         _Pragma("unroll") for (int i8 = 0; i8 < 32; i8 += 16)                          \
-                            tmem_add16(t_lane + seg_offset(sg, p.seg_w) + (uint32_t)((cb) + i8), (v) + i8);     \
+                            tmem_add16(t_lane + seg_offset(sg, p.seg_w, p.seg_slot) + (uint32_t)((cb) + i8), (v) + i8);     \
                 }                                                                                      \
                 /* eight columns at a time, fenced: with all 64 scale / bias values of a chunk loaded */ \
                 /* ahead of the FMAs the second (in-flight) TMEM buffer no longer fits in registers */    \
@@ -2563,14 +2566,32 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     }
     p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
     p.acc_stride = 128;
-    // long rows of a model with at most 64 classes: up to three main accumulators, one per third of K (see GemmParams)
+    // Long rows of a model with at most 128 classes: several main accumulators, each over a contiguous piece of K of
+    // at most 800 columns (see GemmParams::ksplit).  Beside two accumulator buffers there is room for 3 (7 when N <= 32).
+    // Rows that want more give up the second buffer -- a tile of such rows takes HBM several times longer to
+    // deliver than the MMAs and the (now serial) epilogue need together -- for up to 7 (15): d=4096, 64 classes
+    // re-scored 13.5 % of its rows with 3 pieces (1.27 ms per 262k rows) and 0.006 % with 7 (1.08 ms).
     p.ksplit = 1;
-    if (L.split && L.mma_n <= 64 && !L.pair && L.nb == 1) {
-        const int most = L.mma_n <= 32 ? 7 : 3;
-        p.ksplit = (d_eff + 1364) / 1365;
-        p.ksplit = p.ksplit < 1 ? 1 : (p.ksplit > most ? most : p.ksplit);
+    p.seg_w = L.mma_n <= 32 ? 32 : (L.mma_n <= 64 ? 64 : 128);
+    p.seg_slot = 128;
+    if (L.split && L.mma_n <= 128 && !L.pair && L.nb == 1) {
+        const int most2 = 2 * (128 / p.seg_w) - 1, most1 = 2 * (256 / p.seg_w) - 1;
+        // (a row is flagged for its top probability once the error bound passes 3.2e-5: pieces of up to 800 columns
+        // keep it under that for logits up to ~5; shorter pieces only add TMEM reads -- d=784, 16 classes lost 8 % to
+        // a second piece it had no use for)
+        const int want = (d_eff + 799) / 800;
+        // 65..128 classes: one main accumulator beside a second buffer, three without.  Their epilogue is long
+        // enough to miss the overlap on rows of ~1000 floats (d=1024, 128 classes: 1.34 ms with 3.1 % re-scored
+        // against 1.49 with none), so they switch later: d=1536, 96 classes 1.82 -> 1.34 ms (33 % -> 2.3 % re-scored),
+        // d=2048, 100 classes 1.75 -> 1.32, d=4096, 128 classes 4.5 -> 1.4 (70 % -> 7 %).
+        if (want > most2 && (p.seg_w < 128 || d_eff > 1280) && !getenv("LRS_GEMM_TWO_BUFFERS")) {   // (64 classes: d > 2400; 32: d > 5600)
+            p.acc_bufs = 1;
+            p.seg_slot = 256;
+            p.ksplit = want > most1 ? most1 : want;
+        } else {
+            p.ksplit = want > most2 ? most2 : want;
+        }
     }
-    p.seg_w = L.mma_n <= 32 ? 32 : 64;
     if (const char* e = getenv("LRS_GEMM_KSPLIT")) p.ksplit = (atoi(e) >= 1 && atoi(e) <= p.ksplit) ? atoi(e) : p.ksplit;
     if (const char* e = getenv("LRS_GEMM_ACC_BUFS")) p.acc_bufs = (atoi(e) == 2 && p.acc_bufs == 2) ? 2 : 1;   // debug: 1 turns the overlap off
     p.bias = g->bias;

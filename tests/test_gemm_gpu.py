@@ -411,11 +411,14 @@ def test_gemm_fitted_on_raw_measurements(eng):
 
 
 @pytest.mark.parametrize("d,c,n", [(4096, 64, 6000), (4096, 1000, 3000), (16384, 64, 3000), (16384, 1000, 1500),
-                                   (8192, 20, 3000), (2048, 48, 5000)])
+                                   (8192, 20, 3000), (2048, 48, 5000), (2500, 40, 3000), (5000, 17, 2000), (6000, 32, 2000),
+                                   (12000, 30, 1500), (1536, 96, 3000), (4096, 128, 2000), (2048, 100, 2500), (1300, 65, 3000)])
 def test_gemm_long_rows(eng, d, c, n):
     """The truncating accumulation error grows with the number of k-steps: the re-scoring band has to grow
     with the row length (it was measured at d = 1024); models of at most 64 classes sum long rows in up to
-    three (seven: at most 32 classes) TMEM accumulators instead."""
+    three (seven: at most 32 classes) TMEM accumulators instead, and in seven (fifteen) without a second
+    accumulator buffer when the rows are longer still (d > 2400 / 5600); 65..128 classes in up to three
+    from d > 1280."""
     mlapi, lib = eng
     W, b = synth.make_model(d, c, 40 + c)
     X = synth.make_X(n, d, 41)
