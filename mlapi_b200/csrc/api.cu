@@ -77,7 +77,7 @@ static int select_path(const Model& m, const ScoreArgs& a) {
         // 13..16 classes on rows of 64 floats and more: the register-tile kernel is issue-bound there (~27 fp32
         // TFLOP/s: 3.4 TB/s at 16 classes), the tensor path's small-N form is not (4.4-5.1 TB/s measured at 32).
         // Batches large enough to amortise its extra launches, rows TMA can address.
-        const bool aligned = m.n_features % 4 == 0 && a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
+        const bool aligned = a.ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(a.X) & 15u) == 0;
         if (m.n_scores >= 13 && m.n_features >= 64 && a.n_rows >= 16384 && aligned && gemm_supports(m, a))
             return LR_PATH_GEMM;
         return LR_PATH_NARROW;
