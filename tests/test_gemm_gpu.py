@@ -298,6 +298,49 @@ def test_gemm_outputs_stay_inside_their_rows(eng, d, c, n):
     clf.close()
 
 
+def test_concurrent_calls_on_one_model(eng):
+    """include/lrscore.h: a model is read-only between create and update, concurrent lr_score calls on distinct
+    streams are safe.  Six threads, each with its own stream, batch and outputs, share one tensor-path model (per-call
+    scratch is stream-ordered, the layout feedback and the counters are atomics) and one narrow-path model."""
+    import threading
+    import torch
+    mlapi, lib = eng
+    models = []
+    for d, c in ((256, 300), (40, 3)):
+        W, b = synth.make_model(d, c, 90 + c)
+        models.append((mlapi.B200LogisticRegression(W, b, np.arange(c)), W, b, d))
+    errors = []
+
+    def worker(k):
+        try:
+            torch.cuda.set_device(0)
+            stream = torch.cuda.Stream()
+            rng = np.random.default_rng(1000 + k)
+            with torch.cuda.stream(stream):
+                for it in range(6):
+                    clf, W, b, d = models[(k + it) % 2]
+                    n = 700 + 97 * k + 13 * it
+                    Xh = rng.standard_normal((n, d), dtype=np.float32)
+                    Xt = torch.from_numpy(Xh).cuda(non_blocking=False)
+                    out = clf.score_rows(Xt, **ALL)
+                    stream.synchronize()
+                    host = {key: v.cpu().numpy() for key, v in out.items()}
+                    z = orc.decision_function(Xh, W, b)
+                    parity.assert_parity(host, z, orc.softmax(z), z.argmax(1), f"thread {k} call {it}",
+                                         z_atol=parity.Z_ATOL_TENSOR)
+        except Exception as e:  # noqa: BLE001 - reported by the main thread
+            errors.append(repr(e))
+
+    ts = [threading.Thread(target=worker, args=(k,)) for k in range(6)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors
+    for clf, *_ in models:
+        clf.close()
+
+
 # ---- dynamic range: what the 3xFP16 split must survive ---------------------------------------------
 # fp16 halves hold 22 bits only while the `lo` half stays out of subnormals.  The engine balances W per
 # feature at load time, puts each class row at the top of fp16's range, scales X per call from a robust
