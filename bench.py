@@ -423,9 +423,11 @@ def refit_record(ctx):
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         X = torch.randn((n, d), device=dev, generator=g)
         Wt, bt = make_model(d, rows, 7)
-        z = X @ torch.from_numpy(Wt.T.astype(np.float32)).to(dev) + torch.from_numpy(bt.astype(np.float32)).to(dev)
-        y = (z[:, 0] > 0).int() if rows == 1 else z.argmax(1).int()
-        del z
+        # labels of a planted model, by the library's own scorer (no library GEMM anywhere in this process)
+        from mlapi_b200.estimator import B200LogisticRegression
+        planted = B200LogisticRegression(Wt, bt, np.arange(c), devices=[dev.index if dev.index is not None else 0])
+        y = planted.score_rows(X, label=True)["label"].int()
+        planted.close()
         ev = refit.Evaluator(X, y, rows)
         w0 = np.zeros((rows, d + 1))
 

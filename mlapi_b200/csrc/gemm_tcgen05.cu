@@ -142,6 +142,8 @@ struct GemmParams {
     unsigned long long* status;
     unsigned* flags;        // [n_rows] one word per row, non-zero once the row is on the re-scoring list (several threads
                             // may find a reason to flag the same row)
+    int need_prob;          // 0: the caller takes labels / decision values only -- a row is then flagged for near-ties alone,
+                            // not for what the error bound could do to its probabilities
     unsigned* flag_list;    // [n_rows] the rows to re-score in fp32 (near-ties, risky probabilities, overflowed rows) ...
     unsigned* n_flagged;    // ... and how many there are
     float* ezr;             // [n_rows] per flagged row: the logit error bound it was flagged under
@@ -579,7 +581,7 @@ __device__ __forceinline__ void epilogue_in_registers(const GemmParams& p, uint3
         gnear += xn[(h ^ 1) * BM + r_in_tile];
     }
     const float inv = __frcp_rn(gs);
-    const float risk_thr = 8e-6f / ez;
+    const float risk_thr = p.need_prob ? 8e-6f / ez : 1.0f;      // (p (1 - p) <= 1/4: never)
     if (p.proba) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] *= inv;
@@ -1197,7 +1199,7 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             // A runner-up this close to the maximum may be the true winner, and |dp| ~ p(1-p)|dz|: the row is
             // flagged when a class of middling probability could move by ~8e-6 (see `ez` above the loop).
             const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
-            const float risk_thr = 8e-6f / ez;
+            const float risk_thr = p.need_prob ? 8e-6f / ez : 1.0f;      // (p (1 - p) <= 1/4: never)
             const float near_thr = inv * ex2(-2.0f * ez * kLog2e);   // z > max - 2 ez, as a probability
             int near = 0;
             const bool want_rows = p.proba != nullptr;
@@ -1544,6 +1546,7 @@ struct SrSmem {
     static constexpr int op = (tmem_slot + 16 + 1023) / 1024 * 1024;     // [op_stages][32 KB], then [raw_stages][stage_bytes]
 };
 struct ShortParams {
+    int need_prob;          // see GemmParams::need_prob
     const float* X;
     int64_t n_rows;
     int d;                      // features (dk = features rounded up to 16 is the kernel's template argument)
@@ -1832,7 +1835,7 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             const float inv = __frcp_rn(gs);
             // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, and that is always the top one
             // (p (1 - p) rises up to 1/2, and no class but the top one can pass it): its probability is `inv`
-            const bool risk = inv * (1.0f - inv) > 8e-6f / ez;
+            const bool risk = p.need_prob && inv * (1.0f - inv) > 8e-6f / ez;
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= inv;
             if (p.proba) store_rows_coalesced(stage, v, C, lane, p.proba + row0 * C, rows_valid, p_al);
@@ -2456,6 +2459,37 @@ cudaError_t launch_gemm_kernel(const cudaLaunchConfig_t& cfg, bool pair, const C
 // re-scoring pass; `sw_load`: TMA cannot address X (GemmParams::sw_load).
 int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const float* w_fix, bool sw_load) {
     GemmPlan* g = m.gemm;
+    // Labels + max probability without a P matrix (REF/main.py:21-22's pair of calls, in bulk): the rows whose top
+    // probability the error bound could move are re-scored, and with no row of P to pick the classes that matter
+    // from, that pass recomputes every class of such a row -- 4 MB of W per row of a 1000-class model, 21.9 ms per
+    // 1M rows of cfg 3's shape where the whole P matrix takes 6.4.  So the batch is scored in blocks of rows into a
+    // scratch P of at most 512 MB (stream-ordered; blocks of 64k rows left a quarter of the last wave idle: 9.8 ms)
+    // and re-scored class by class like any other.  No memory for the scratch: the old way.
+    if (!a.proba && a.maxprob && g->fixup && m.n_scores > 128 && !a.out_pitch && !a.lse_out && !getenv("LRS_GEMM_NO_SCRATCH_P")) {
+        const int C = m.n_scores;
+        const char* mb = getenv("LRS_GEMM_SCRATCH_P_MB");           // (tests shrink it to see several blocks)
+        int64_t block = ((int64_t)(mb && atoi(mb) > 0 ? atoi(mb) : 512) << 20) / ((int64_t)C * 4) / 1024 * 1024;
+        block = block < 4096 ? 4096 : block;
+        if (block > a.n_rows) block = a.n_rows;
+        AsyncScratch sp;
+        sp.s = a.stream;
+        if (cudaMallocAsync(&sp.p, (size_t)block * C * sizeof(float), a.stream) != cudaSuccess) {
+            cudaGetLastError();
+            sp.p = nullptr;
+        }
+        int rc = LR_OK;
+        for (int64_t r0 = 0; sp.p && r0 < a.n_rows && rc == LR_OK; r0 += block) {
+            ScoreArgs s = a;
+            s.X = a.X + r0 * a.ldx;
+            s.n_rows = a.n_rows - r0 < block ? a.n_rows - r0 : block;
+            s.proba = static_cast<float*>(sp.p);
+            if (a.decision) s.decision = a.decision + r0 * C;
+            if (a.label) s.label = a.label + r0;
+            s.maxprob = a.maxprob + r0;
+            rc = gemm_launch_aligned(m, s, d_eff, w_fix, sw_load);
+        }
+        if (sp.p) return rc;
+    }
     const int d_x = m.n_features;
     const bool xal = !sw_load && d_x % 4 == 0;      // 128-bit loads of X rows in the side kernels
     if (g->adaptive && g->active.load() == 0 && g->has[1]) {
@@ -2599,6 +2633,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     p.col_scale = g->col_scale;
     p.x_scale = x_scale;
     p.count_nonfinite = fixup ? 0 : 1;
+    p.need_prob = (a.proba || a.maxprob) ? 1 : 0;
     p.debug_skip = 0;
     if (const char* e = getenv("LRS_GEMM_DEBUG_SKIP")) p.debug_skip = atoi(e);
     p.proba = a.proba;
@@ -2763,6 +2798,7 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     // 26..32-class model for nothing
     p.kappa = float(getenv("LRS_SHORT_KAPPA") ? atof(getenv("LRS_SHORT_KAPPA")) : 1.0e-6 + 2.5e-6 * ((d + 15) / 16) / 4.0);
     p.count_nonfinite = fixup ? 0 : 1;
+    p.need_prob = (a.proba || a.maxprob) ? 1 : 0;
     p.vec_store = 0;
     p.proba = a.proba;
     p.decision = a.decision;

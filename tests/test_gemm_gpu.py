@@ -298,6 +298,39 @@ def test_gemm_outputs_stay_inside_their_rows(eng, d, c, n):
     clf.close()
 
 
+def test_labels_and_max_probability_without_a_p_matrix(eng, monkeypatch):
+    """predict + predict_proba().max() in bulk (REF/main.py:21-22) on a many-class model: the batch goes through a
+    scratch P in blocks of rows so that the re-scoring pass can pick the classes that matter; labels alone flag
+    near-ties only.  Three blocks here (the scratch is shrunk to 1 MB), a ragged last one."""
+    import torch
+    mlapi, lib = eng
+    monkeypatch.setenv("LRS_GEMM_SCRATCH_P_MB", "1")
+    d, c, n = 128, 300, 10_000
+    W, b = synth.make_model(d, c, 77)
+    clf = mlapi.B200LogisticRegression(W, b, np.arange(c))
+    clf.set_path(lib.PATH_GEMM)
+    Xh = synth.make_X(n, d, 78)
+    Xh[:200] *= 3.0                                   # confident rows next to flat ones
+    Xt = torch.from_numpy(Xh).cuda()
+    z = orc.decision_function(Xh, W, b)
+    P = orc.softmax(z)
+    before = lib.load().lr_launch_count()
+    out = clf.score_rows(Xt, label=True, maxprob=True)
+    torch.cuda.synchronize()
+    assert lib.load().lr_launch_count() - before >= 3 * 3          # three blocks, at least three kernels each
+    parity.assert_parity({k: v.cpu().numpy() for k, v in out.items() if v is not None}, z, P, z.argmax(1), "label+maxprob, blocks")
+    clf.take_rescored()
+    out = clf.score_rows(Xt, label=True)
+    torch.cuda.synchronize()
+    parity.assert_parity({"label": out["label"].cpu().numpy()}, z, P, z.argmax(1), "labels alone")
+    assert clf.take_rescored() < n // 100                          # near-ties only
+    out = clf.score_rows(Xt, label=True, maxprob=True, decision=True)
+    torch.cuda.synchronize()
+    parity.assert_parity({k: v.cpu().numpy() for k, v in out.items() if v is not None}, z, P, z.argmax(1),
+                         "label+maxprob+decision, blocks", z_atol=parity.Z_ATOL_TENSOR)
+    clf.close()
+
+
 def test_concurrent_calls_on_one_model(eng):
     """include/lrscore.h: a model is read-only between create and update, concurrent lr_score calls on distinct
     streams are safe.  Six threads, each with its own stream, batch and outputs, share one tensor-path model (per-call
