@@ -2465,7 +2465,9 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // 1M rows of cfg 3's shape where the whole P matrix takes 6.4.  So the batch is scored in blocks of rows into a
     // scratch P of at most 512 MB (stream-ordered; blocks of 64k rows left a quarter of the last wave idle: 9.8 ms)
     // and re-scored class by class like any other.  No memory for the scratch: the old way.
-    if (!a.proba && a.maxprob && g->fixup && m.n_scores > 128 && !a.out_pitch && !a.lse_out && !getenv("LRS_GEMM_NO_SCRATCH_P")) {
+    // (A class group of a larger model comes with a pitch for the caller's rows: the scratch has its own, so a group
+    // that also has decision values to write at the caller's pitch stays on the old way.)
+    if (!a.proba && a.maxprob && g->fixup && m.n_scores > 128 && (!a.out_pitch || !a.decision) && !getenv("LRS_GEMM_NO_SCRATCH_P")) {
         const int C = m.n_scores;
         const char* mb = getenv("LRS_GEMM_SCRATCH_P_MB");           // (tests shrink it to see several blocks)
         int64_t block = ((int64_t)(mb && atoi(mb) > 0 ? atoi(mb) : 512) << 20) / ((int64_t)C * 4) / 1024 * 1024;
@@ -2483,6 +2485,9 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
             s.X = a.X + r0 * a.ldx;
             s.n_rows = a.n_rows - r0 < block ? a.n_rows - r0 : block;
             s.proba = static_cast<float*>(sp.p);
+            s.out_pitch = 0;
+            s.out_col0 = 0;
+            if (a.lse_out) s.lse_out = a.lse_out + r0;
             if (a.decision) s.decision = a.decision + r0 * C;
             if (a.label) s.label = a.label + r0;
             s.maxprob = a.maxprob + r0;
