@@ -2467,7 +2467,7 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
     // and re-scored class by class like any other.  No memory for the scratch: the old way.
     // (A class group of a larger model comes with a pitch for the caller's rows: the scratch has its own, so a group
     // that also has decision values to write at the caller's pitch stays on the old way.)
-    if (!a.proba && a.maxprob && g->fixup && m.n_scores > 128 && (!a.out_pitch || !a.decision) && !getenv("LRS_GEMM_NO_SCRATCH_P")) {
+    if (!a.proba && a.maxprob && g->fixup && m.n_scores > 32 && (!a.out_pitch || !a.decision) && !getenv("LRS_GEMM_NO_SCRATCH_P")) {
         const int C = m.n_scores;
         const char* mb = getenv("LRS_GEMM_SCRATCH_P_MB");           // (tests shrink it to see several blocks)
         int64_t block = ((int64_t)(mb && atoi(mb) > 0 ? atoi(mb) : 512) << 20) / ((int64_t)C * 4) / 1024 * 1024;
