@@ -82,6 +82,11 @@ static int select_path(const Model& m, const ScoreArgs& a) {
             return LR_PATH_GEMM;
         return LR_PATH_NARROW;
     }
+    // A handful of rows of a small model: the tensor path's fixed cost (batch statistics, two kernels, the re-scoring
+    // pass: ~30 us) is three times what one warp per row needs for rows of <= 4096 multiply-adds and <= 32 classes
+    // (d=64, 20 classes: 10-14 us up to 4096 rows, d=128, 30 classes: 13-21; with 100 classes of d=32 the warp's serial
+    // walk over the classes takes as long as the tensor path).
+    if (m.n_scores <= 32 && (int64_t)m.n_features * m.n_scores <= 4096 && a.n_rows <= 4096) return LR_PATH_GENERIC;
     if (gemm_supports(m, a)) return LR_PATH_GEMM;
     if (!m.groups.empty() && a.n_rows < (int64_t)1 << 31) return LR_PATH_GEMM;     // > 2048 classes: class groups
     return LR_PATH_GENERIC;

@@ -1341,8 +1341,93 @@ __device__ __forceinline__ void warp_dot4_x4(const float* __restrict__ x, const 
 constexpr int kFixWarps = 8;
 constexpr int kFixQueue = 64;          // selected classes waiting for their dot products (per warp)
 
-// grid-stride over the list, one warp per flagged row.  Dynamic shared memory: [kFixWarps][c_pad] floats (the
-// row of P a warp works on) + [kFixWarps][kFixQueue] ints.
+// What a warp adds up over the classes it re-scores for a row.
+struct FixPart {
+    float old_mass = 0.0f, new_mass = 0.0f, best_z = -INFINITY, best_q = 0.0f;
+    int best = 0;
+};
+
+// The selected classes of [c_lo, c_hi) -- those with prow[c] >= thr -- get an fp32 logit: queued in ascending order,
+// worked off four at a time.  prow[c] becomes exp(z - L), the class's weight in units of the old row sum.
+__device__ __forceinline__ void fix_row_classes(const float* __restrict__ x, int d, int ldw, bool xal, const float* __restrict__ W,
+                                                const float* __restrict__ b, float* prow, int* queue, int c_lo, int c_hi,
+                                                float thr, float L, float* decision_row, int lane, FixPart& part) {
+    int nq = 0;
+    auto drain = [&](bool all) {
+        int done = 0;
+        while (nq - done >= 4 || (all && done < nq)) {
+            const int take = min(4, nq - done);
+            int cls[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) cls[u] = queue[done + (u < take ? u : 0)];
+            float z4[4];
+            warp_dot4_x4(x, W, cls, d, ldw, xal, lane, z4);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (u >= take) break;
+                const int cj = cls[u];
+                const float z = z4[u] + __ldg(b + cj);
+                const float q = expf(z - L);                    // in units of the old row sum
+                part.old_mass += prow[cj];
+                part.new_mass += q;
+                if (z > part.best_z) { part.best_z = z; part.best = cj; part.best_q = q; }   // ascending classes: first max wins
+                __syncwarp();
+                if (lane == 0) {
+                    prow[cj] = q;
+                    if (decision_row) decision_row[cj] = z;
+                }
+            }
+            done += take;
+        }
+        __syncwarp();
+        // what is left (fewer than four) moves to the front
+        const int left = nq - done;
+        const int keep = lane < left ? queue[done + lane] : 0;
+        __syncwarp();
+        if (lane < left) queue[lane] = keep;
+        nq = left;
+        __syncwarp();
+    };
+    for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
+        const int c = c0 + lane;
+        const bool sel = c < c_hi && prow[c] >= thr;
+        const unsigned mask = __ballot_sync(0xffffffffu, sel);
+        if (mask) {
+            if (nq + __popc(mask) > kFixQueue) drain(false);          // leaves at most 3
+            if (sel) queue[nq + __popc(mask & ((1u << lane) - 1u))] = c;
+            nq += __popc(mask);
+            __syncwarp();
+            if (nq >= 16) drain(false);
+        }
+    }
+    drain(true);
+}
+
+// Which classes get an fp32 logit: the rivals of the maximum (near-ties), and every class whose own probability the
+// error bound `ez` of this row could move by more than ~4e-6 (p (1 + mass) ez with p >= 2e-6 / ez).  What stays
+// behind enters the row only through the renormalisation, as the probability-weighted MEAN of its logit errors:
+// random parts average out over the many small classes, the systematic part of the truncation error is ~1/8 of the
+// maximum `ez` is built on (measured mean / max, profiles/r02_gemm_accumulation_error.txt; 1/4 is assumed); the
+// threshold is lowered until mass_left * ez / 4 * p_max <= 4e-6.  (Every lane of the calling warp gets the same value.)
+__device__ __forceinline__ float fix_row_threshold(const float* prow, int C, float pmax, float ez, int lane) {
+    float thr = fminf(fmaxf(2e-6f / ez, 1e-4f), 0.9f * pmax);
+    for (int round = 0; round < 3; ++round) {
+        float left = 0.0f;
+        for (int c = lane; c < C; c += 32) left += prow[c] < thr ? prow[c] : 0.0f;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) left += __shfl_xor_sync(0xffffffffu, left, off);
+        if (left * ez * 0.25f * pmax <= 4e-6f) break;
+        thr *= 0.25f;
+    }
+    return thr;
+}
+
+// Grid-stride over the list of flagged rows.  Many rows: one warp per row.  Few (at most eight per CTA): one CTA per
+// row, its eight warps each taking an eighth of the classes -- a row with a sizeable top probability over a long
+// flat tail has hundreds of classes re-scored (four dot products of d per ~2 us trip to L2 for one warp), and a
+// request-sized batch waited for its slowest such row: 2048 rows of cfg 3's shape took 131 or 270 us with the
+// batch's luck.  Dynamic shared memory: [kFixWarps][c_pad] floats (the rows of P the warps work on; the CTA form
+// uses the first) + [kFixWarps][kFixQueue] ints.
 __global__ void __launch_bounds__(kFixWarps * 32)
 gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int ldw, int xal, int C, int c_pad, int64_t out_pitch, int out_col0,
                       const float* __restrict__ W, const float* __restrict__ b,
@@ -1351,10 +1436,74 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int ldw, 
                       float* decision, int32_t* label, float* maxprob, unsigned long long* rescored,
                       unsigned long long* status) {
     extern __shared__ float fix_smem[];
+    __shared__ float s_f[4][kFixWarps];
+    __shared__ int s_best[kFixWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float* prow = fix_smem + (size_t)warp * c_pad;
     int* queue = reinterpret_cast<int*>(fix_smem + (size_t)kFixWarps * c_pad) + warp * kFixQueue;
     const unsigned n = *n_list;
+    if (n <= 8u * gridDim.x) {
+        // ---- one CTA per row ----
+        float* prow = fix_smem;
+        const int per = ((C + kFixWarps - 1) / kFixWarps + 31) / 32 * 32;      // classes per warp, whole 32-lane sweeps
+        for (unsigned li = blockIdx.x; li < n; li += gridDim.x) {
+            const int64_t row = list[li];
+            const float* x = X + row * ldx;
+            const float L = lse[row];
+            if (!finite_f(L)) {                          // (see the warp form below)
+                if (warp == 0) {
+                    score_row_warp_pitched(x, row, lane, d, ldw, C, W, b, proba, decision, label, maxprob, status, out_pitch, out_col0);
+                    if (lane == 0) atomicAdd(rescored, 1ull);
+                }
+                continue;
+            }
+            float* pr = proba + row * out_pitch + out_col0;
+            float pmax = 0.0f;
+            for (int c = threadIdx.x; c < C; c += kFixWarps * 32) {
+                const float v = __ldcg(pr + c);
+                prow[c] = v;
+                pmax = fmaxf(pmax, v);
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
+            if (lane == 0) s_f[0][warp] = pmax;
+            __syncthreads();
+#pragma unroll
+            for (int w = 0; w < kFixWarps; ++w) pmax = fmaxf(pmax, s_f[0][w]);
+            const float thr = fix_row_threshold(prow, C, pmax, ezr[row], lane);      // (every warp: the same scan)
+            __syncthreads();                             // nobody overwrites prow before every warp has its threshold
+            FixPart part;
+            const int c_lo = warp * per, c_hi = min(C, (warp + 1) * per);
+            if (c_lo < c_hi)
+                fix_row_classes(x, d, ldw, xal != 0, W, b, prow, queue, c_lo, c_hi, thr, L,
+                                decision ? decision + row * out_pitch + out_col0 : nullptr, lane, part);
+            if (lane == 0) {
+                s_f[1][warp] = part.old_mass; s_f[2][warp] = part.new_mass; s_f[3][warp] = part.best_z;
+                s_f[0][warp] = part.best_q; s_best[warp] = part.best;
+            }
+            __syncthreads();
+            float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
+            int best = 0;
+#pragma unroll
+            for (int w = 0; w < kFixWarps; ++w) {        // ascending class ranges: the first maximum wins
+                old_mass += s_f[1][w];
+                new_mass += s_f[2][w];
+                if (s_f[3][w] > best_z) { best_z = s_f[3][w]; best = s_best[w]; best_q = s_f[0][w]; }
+            }
+            const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+            const float invT = __frcp_rn(T);
+            const float sc = fabsf(T - 1.0f) > 1e-7f ? invT : 1.0f;
+            for (int c = threadIdx.x; c < C; c += kFixWarps * 32) __stcs(pr + c, prow[c] * sc);
+            if (threadIdx.x == 0) {
+                if (label) label[row] = best;
+                if (maxprob) maxprob[row] = best_q * invT;
+                atomicAdd(rescored, 1ull);
+            }
+            __syncthreads();
+        }
+        return;
+    }
+    // ---- one warp per row ----
+    float* prow = fix_smem + (size_t)warp * c_pad;
     for (unsigned li = blockIdx.x * kFixWarps + warp; li < n; li += gridDim.x * kFixWarps) {
         const int64_t row = list[li];
         const float* x = X + row * ldx;
@@ -1376,81 +1525,17 @@ gemm_fixup_sel_kernel(const float* __restrict__ X, int64_t ldx, int d, int ldw, 
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) pmax = fmaxf(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
         __syncwarp();
-        // Which classes get an fp32 logit: the rivals of the maximum (near-ties), and every class whose own
-        // probability the error bound `ez` of this row could move by more than ~4e-6 (p (1 + mass) ez with
-        // p >= 2e-6 / ez).  What stays behind enters the row only through the renormalisation, as the
-        // probability-weighted MEAN of its logit errors: random parts average out over the many small classes,
-        // the systematic part of the truncation error is ~1/8 of the maximum `ez` is built on (measured mean /
-        // max, profiles/r02_gemm_accumulation_error.txt; 1/4 is assumed); the threshold is lowered until
-        // mass_left * ez / 4 * p_max <= 4e-6.
-        const float ez = ezr[row];
-        float thr = fminf(fmaxf(2e-6f / ez, 1e-4f), 0.9f * pmax);
-        for (int round = 0; round < 3; ++round) {
-            float left = 0.0f;
-            for (int c = lane; c < C; c += 32) left += prow[c] < thr ? prow[c] : 0.0f;
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) left += __shfl_xor_sync(0xffffffffu, left, off);
-            if (left * ez * 0.25f * pmax <= 4e-6f) break;
-            thr *= 0.25f;
-        }
-        float old_mass = 0.0f, new_mass = 0.0f, best_z = -CUDART_INF_F, best_q = 0.0f;
-        int best = 0, nq = 0;
-        // queue of selected classes in ascending order, worked off four at a time
-        auto drain = [&](bool all) {
-            int done = 0;
-            while (nq - done >= 4 || (all && done < nq)) {
-                const int take = min(4, nq - done);
-                int cls[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) cls[u] = queue[done + (u < take ? u : 0)];
-                float z4[4];
-                warp_dot4_x4(x, W, cls, d, ldw, xal != 0, lane, z4);
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (u >= take) break;
-                    const int cj = cls[u];
-                    const float z = z4[u] + __ldg(b + cj);
-                    const float q = expf(z - L);                    // in units of the old row sum
-                    old_mass += prow[cj];
-                    new_mass += q;
-                    if (z > best_z) { best_z = z; best = cj; best_q = q; }   // ascending classes: first max wins
-                    __syncwarp();
-                    if (lane == 0) {
-                        prow[cj] = q;
-                        if (decision) decision[row * out_pitch + out_col0 + cj] = z;
-                    }
-                }
-                done += take;
-            }
-            __syncwarp();
-            // what is left (fewer than four) moves to the front
-            const int left = nq - done;
-            const int keep = lane < left ? queue[done + lane] : 0;
-            __syncwarp();
-            if (lane < left) queue[lane] = keep;
-            nq = left;
-            __syncwarp();
-        };
-        for (int c0 = 0; c0 < C; c0 += 32) {
-            const int c = c0 + lane;
-            const bool sel = c < C && prow[c] >= thr;
-            const unsigned mask = __ballot_sync(0xffffffffu, sel);
-            if (mask) {
-                if (nq + __popc(mask) > kFixQueue) drain(false);          // leaves at most 3
-                if (sel) queue[nq + __popc(mask & ((1u << lane) - 1u))] = c;
-                nq += __popc(mask);
-                __syncwarp();
-                if (nq >= 16) drain(false);
-            }
-        }
-        drain(true);
-        const float T = 1.0f - old_mass + new_mass;             // new row sum in units of the old one
+        const float thr = fix_row_threshold(prow, C, pmax, ezr[row], lane);
+        FixPart part;
+        fix_row_classes(x, d, ldw, xal != 0, W, b, prow, queue, 0, C, thr, L,
+                        decision ? decision + row * out_pitch + out_col0 : nullptr, lane, part);
+        const float T = 1.0f - part.old_mass + part.new_mass;   // new row sum in units of the old one
         const float invT = __frcp_rn(T);
         const float sc = fabsf(T - 1.0f) > 1e-7f ? invT : 1.0f;
         for (int c = lane; c < C; c += 32) __stcs(pr + c, prow[c] * sc);
         if (lane == 0) {
-            if (label) label[row] = best;
-            if (maxprob) maxprob[row] = best_q * invT;
+            if (label) label[row] = part.best;
+            if (maxprob) maxprob[row] = part.best_q * invT;
             atomicAdd(rescored, 1ull);
         }
         __syncwarp();

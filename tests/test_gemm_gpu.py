@@ -194,7 +194,9 @@ def test_gemm_device_rows_tma_cannot_address(eng, d, pitch, off, c, n, f16, monk
     Xt = torch.from_numpy(buf).cuda()[off:off + n * pitch].view(n, pitch)[:, :d]
     path = C.c_int32(0)
     lib.check(L.lr_model_select_path(clf._replicas[0].handle, C.c_void_p(Xt.data_ptr()), n, pitch, C.byref(path)))
-    assert path.value == lib.PATH_GEMM
+    # (a few rows of a small model go to the one-warp-per-row kernel on their own: forced here)
+    assert path.value == (lib.PATH_GEMM if d * c > 4096 or c > 32 or n > 4096 else lib.PATH_GENERIC)
+    clf.set_path(lib.PATH_GEMM)
     z = orc.decision_function(Xh, W, b)
     for pattern in (ALL, dict(label=True, maxprob=True)):
         out = clf.score_rows(Xt, **pattern)
