@@ -99,6 +99,9 @@ int lr_model_select_path(const lr_model* m, const float* X_dev, int64_t n_rows, 
  * Asynchronous: returns once the work is enqueued.  n_rows == 0 is a no-op.  Rows whose score is
  * not finite (NaN/inf in X -- sklearn raises ValueError for those, _base.py:385-389) are counted in
  * a device-side status word, read with lr_model_take_nonfinite().
+ * Device memory: the tensor-core path (LR_PATH_GEMM) takes per-call scratch from the device's default
+ * stream-ordered pool (cudaMallocAsync on `stream`): ~16 bytes per row, plus -- when max probabilities are wanted
+ * without a P matrix on a model of more than 32 classes -- a P block of at most 512 MB.  The other paths take none.
  */
 int lr_score(lr_model* m, const float* X_dev, int64_t n_rows, int64_t ldx,
              float* proba_dev, float* decision_dev, int32_t* label_dev, float* maxprob_dev,
