@@ -2376,7 +2376,15 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
     g->d64 = (d + BK16 - 1) / BK16 * BK16;
     auto& fast = g->layout[0];
     auto& acc = g->layout[1];
-    if (C > BN) {                                   // fast layout: 512 classes per CTA
+    // Short rows against 129..256 classes: a tile's MMAs are over in no time and the epilogue is most of the work
+    // (d=200, 160 classes: 3.4 ms per 5.4M rows, 2.1 without the epilogue), so it should at least overlap the next
+    // tile's MMAs.  Rows this short leave a single accumulator as accurate as split ones are at d=1024, so the layout
+    // drops the split and keeps TWO 256-column accumulator buffers instead, unpaired: d=200, 160 classes 3.49 ->
+    // 3.07 ms, d=384, 256 classes 2.53 -> 2.35, d=128, 200 classes 4.63 -> 4.41.  (With more than one class slice --
+    // tried up to 1024 classes -- the same trade loses: four CTAs meeting at every tile's exchange cost more than
+    // the overlap returns, d=128, 1000 classes 3.59 -> 3.79 ms, d=64, 300 classes 4.28 -> 5.60.)
+    const bool overlap256 = d4 <= 384 && C > 128 && C <= BN && !getenv("LRS_GEMM_NO_OVERLAP256");
+    if (C > BN && !overlap256) {                    // fast layout: 512 classes per CTA
         fast.nb = 2;
         fast.ncc = (C + 2 * BN - 1) / (2 * BN);
         if (fast.ncc == 3) fast.ncc = 4;
@@ -2386,7 +2394,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         acc.nb = 1;
         acc.ncc = (C + BN - 1) / BN;
         if (acc.ncc == 3) acc.ncc = 4;
-        acc.split = true;
+        acc.split = !overlap256;
         g->has[1] = true;
     }
     // two row tiles per cluster share every W tile through TMA multicast (cluster <= 8 CTAs)
@@ -2403,7 +2411,7 @@ int gemm_prepare(Model& m, const double* coef, const double* intercept) {
         auto& L = g->layout[i];
         // (the accurate layout with two class slices: 3.39 ms unpaired against 4.40 paired on d=1024, 300 classes,
         // 3.93 / 4.19 on 500, 4.77 / 5.25 on d=512, 400 -- a cluster of 4 leaves 16 SMs idle and its X ring is shorter)
-        L.pair = pair && ((i == 0 ? L.ncc * 2 <= 4 : L.ncc == 1) || (force_pair && L.ncc * 2 <= 8));
+        L.pair = pair && !(overlap256 && i == 1) && ((i == 0 ? L.ncc * 2 <= 4 : L.ncc == 1) || (force_pair && L.ncc * 2 <= 8));
         L.nrt = (!L.pair && force_mc && L.ncc * 2 <= 8) ? 2 : 1;
     }
     // A model whose classes fit one W tile multiplies by exactly that many columns (in whole 32-column
@@ -2688,8 +2696,10 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
             p.a_stages = as; p.b_stages = bs;
         }
     }
-    p.acc_bufs = (L.mma_n <= 128 && L.nb == 1 && !L.pair) ? 2 : 1;
-    p.acc_stride = 128;
+    // two accumulator buffers where TMEM holds them: split layout (main + correction) up to N = 128, 128 columns
+    // apart in each half; single accumulators up to N = 256, 256 apart
+    p.acc_bufs = (L.nb == 1 && !L.pair && L.mma_n <= (L.split ? 128 : 256)) ? 2 : 1;
+    p.acc_stride = (!L.split && L.mma_n > 128) ? 256 : 128;
     // Long rows of a model with at most 128 classes: several main accumulators, each over a contiguous piece of K of
     // at most 800 columns (see GemmParams::ksplit).  Beside two accumulator buffers there is room for 3 (7 when N <= 32).
     // Rows that want more give up the second buffer -- a tile of such rows takes HBM several times longer to
