@@ -612,6 +612,9 @@ __device__ __forceinline__ void epilogue_in_registers(const GemmParams& p, uint3
 // the other so that at most one chunk's raw accumulators and sixteen columns of the correction accumulator are live
 // beside the first chunk's logits (both chunks loaded at once spilled 270 bytes per thread and lost to the general
 // form).  Everything else as in epilogue_in_registers.
+// (A kernel instantiation of its own, EPI2: compiled into the common kernel its 64 live values pushed ptxas into
+// spilling loop-carried state of the OTHER epilogue forms -- d=128, 16 classes lost 9 % -- and as a non-inlined
+// function it forced the kernel's parameter block into local memory, which cost everybody 5-40 %.)
 template <bool F16>
 __device__ __forceinline__ void epilogue_in_registers2(const GemmParams& p, uint32_t t_lane, int h, int q, int lane, int n_real,
                                                        int64_t row, bool live, int rows_valid, int64_t blk_w,
@@ -741,7 +744,7 @@ __device__ __forceinline__ void epilogue_in_registers2(const GemmParams& p, uint
 // F16 = true : 3xFP16 (x and w scaled by powers of two into fp16 range and split hi/lo like above,
 //              16 K-elements per MMA at twice the TF32 rate; scales are undone in the epilogue).
 // PAIR = true: cta_group::2 -- see SmemLayoutT.
-template <bool F16, bool PAIR>
+template <bool F16, bool PAIR, bool EPI2 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                     const __grid_constant__ CUtensorMap map_wlo, const GemmParams p) {
@@ -1180,11 +1183,13 @@ gemm_softmax_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                                            chunk_ref, stg_r, acc_empty + buf, psum_scale, floor_err);
                 continue;
             }
-            if (!PAIR && n_chunks <= 4 && p.ncc == 1 && p.mma_n <= 128 && !(p.debug_skip & 6)) {
-                float* stg_r = reinterpret_cast<float*>(smem + SmemLayout::xchg) + ew * (kStoreTileBytes / 4);
-                epilogue_in_registers2<F16>(p, t_lane, h, q, lane, n_real, row, live, rows_valid, blk_w, cscale_s, bias_s,
-                                            chunk_ref, stg_r, acc_empty + buf, psum_scale, floor_err);
-                continue;
+            if constexpr (EPI2) {                     // 65..128 classes (launch_gemm_kernel picks this instantiation for them)
+                if (n_chunks <= 4 && !(p.debug_skip & 6)) {
+                    float* stg_r = reinterpret_cast<float*>(smem + SmemLayout::xchg) + ew * (kStoreTileBytes / 4);
+                    epilogue_in_registers2<F16>(p, t_lane, h, q, lane, n_real, row, live, rows_valid, blk_w, cscale_s, bias_s,
+                                                chunk_ref, stg_r, acc_empty + buf, psum_scale, floor_err);
+                    continue;
+                }
             }
 
             // ---- pass 1: running maximum (first argmax) and sum of exp(z - running maximum) over my columns.
@@ -2673,10 +2678,14 @@ struct AsyncScratch {
 template <bool F16>
 cudaError_t launch_gemm_kernel(const cudaLaunchConfig_t& cfg, bool pair, const CUtensorMap& map_x,
                                const GemmPlan::Layout& L, const GemmParams& p) {
+    // 65..128 classes in one class slice: the instantiation whose epilogue keeps two chunks per warp in registers
+    const bool epi2 = !pair && p.ncc == 1 && p.nb == 1 && p.mma_n > 64 && p.mma_n <= 128;
     if constexpr (F16) {
+        if (epi2) return cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, false, true>, map_x, L.map_w16hi, L.map_w16lo, p);
         return pair ? cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, true>, map_x, L.map_w16hi, L.map_w16lo, p)
                     : cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<true, false>, map_x, L.map_w16hi, L.map_w16lo, p);
     } else {
+        if (epi2) return cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, false, true>, map_x, L.map_whi, L.map_wlo, p);
         return pair ? cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, true>, map_x, L.map_whi, L.map_wlo, p)
                     : cudaLaunchKernelEx(&cfg, gemm_softmax_kernel<false, false>, map_x, L.map_whi, L.map_wlo, p);
     }
@@ -2753,6 +2762,8 @@ int gemm_launch_aligned(const Model& m, const ScoreArgs& a, int d_eff, const flo
         const int s0 = SmemLayoutT<false>::total + 1024, s1 = SmemLayoutT<true>::total + 1024;
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
+        LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s0));
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s1));
         LRS_CUDA(cudaFuncSetAttribute(gemm_softmax_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s1));
         g->configured[dev] = true;
