@@ -132,7 +132,9 @@ int lr_model_take_fallback(lr_model* m, void* stream, uint64_t* n_rows_tf32);
  * make, and the one bench.py's `e2e` figure times.  Returns LR_ERR_NONFINITE (outputs still
  * written) when a row scored to NaN/inf.  A batch of a few KB whose X and outputs all live in
  * page-locked memory (lr_host_alloc / lr_host_register) is scored in place over PCIe instead: one
- * launch, no copies (not on the tensor-core path).
+ * launch, no copies (not on the tensor-core path).  Pageable buffers (an ordinary numpy array) of 8 MB and more
+ * are copied to and from pinned buffers of the library's by four host threads of its own, chunk by chunk, in step
+ * with the transfers (page-locked buffers go straight to the link and are ~2x faster still).
  */
 int lr_score_host(lr_model* m, const float* X_host, int64_t n_rows, int64_t ldx,
                   float* proba_host, float* decision_host, int32_t* label_host,

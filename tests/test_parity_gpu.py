@@ -429,6 +429,46 @@ def test_host_chunking_is_bit_identical(eng):
     px.free()
 
 
+@pytest.mark.parametrize("d,ns,n,chunk", [(32, 1, 300_000, 0), (40, 3, 120_001, 7_777), (256, 300, 12_000, 5_000)])
+def test_pageable_host_arrays_go_through_pinned_bounce_buffers(eng, d, ns, n, chunk):
+    """Ordinary numpy arrays of 8 MB and more: lr_score_host copies them chunk by chunk into pinned buffers of its
+    own with a few host threads (and the results back out) instead of letting cudaMemcpyAsync crawl through
+    pageable memory.  Same bits as the pinned route -- on every kernel family, with ragged last chunks, a row pitch
+    that is not the row length, and with only some of the buffers pageable."""
+    from mlapi_b200.estimator import PinnedArray
+    _, lib = eng
+    W, b = synth.make_model(d, ns, 31 + d)
+    clf = _model(eng, W, b)
+    rep = clf._replicas[0]
+    if chunk:
+        lib.check(rep.lib.lr_model_set_host_chunk_rows(rep.handle, chunk))
+    X = synth.make_X(n, d, 77)
+    assert X.nbytes >= 8 << 20
+    px = PinnedArray(X.shape)
+    px.array[...] = X
+    ref = clf.score_rows(px.array, **ALL)                    # pinned in (outputs are numpy arrays: pageable)
+    got = clf.score_rows(X, **ALL)                           # pageable in
+    for k in ref:
+        assert np.array_equal(ref[k], got[k]), k
+    z = orc.decision_function(X[:4000], W, b)
+    parity.assert_parity({k: v[:4000] for k, v in got.items()}, z if ns > 1 else z.ravel(), orc.predict_proba(X[:4000], W, b),
+                         orc.predict_index(X[:4000], W, b), f"pageable d={d} ns={ns}",
+                         z_atol=parity.Z_ATOL_TENSOR if ns > 16 else parity.Z_ATOL)
+    # straight through the C ABI: pageable X with a pitch wider than the row, everything pinned on the way out
+    L = lib.load()
+    wide = np.zeros((n, d + 5), np.float32)
+    wide[:, :d] = X
+    n_out = max(ns, 2)
+    pp = PinnedArray((n, n_out))
+    pl = PinnedArray((n,), np.int32)
+    lib.check(L.lr_score_host(rep.handle, wide.ctypes.data_as(C.c_void_p), n, d + 5, pp.array.ctypes.data_as(C.c_void_p), None,
+                              pl.array.ctypes.data_as(C.c_void_p), None))
+    assert np.array_equal(pp.array, ref["proba"]) and np.array_equal(pl.array, ref["label"])
+    for a in (px, pp, pl):
+        a.free()
+    clf.close()
+
+
 def test_request_sized_pinned_batches_are_scored_in_place(eng, golden):
     """lr_score_host with page-locked X and outputs of a few KB takes the zero-copy path; the results
     must be the bits the staged path produces, for every narrow/wide/generic shape class."""
