@@ -350,6 +350,24 @@ def score_workload(ctx, name, rows, steps, warmup, want, logit_scale, e2e_steps,
                                    "stream, all bytes counted",
                "host_cpus_bound_per_rank": ctx.numa_cpus,
                "matches_device_result": same}
+        # The same call on ordinary (pageable) numpy arrays, which is what a user of the reference hands to
+        # predict_proba: a bounded sample (<= 2 GB of X), rank 0 of a one-rank run only.
+        if world == 1:
+            n_p = max(1, min(n_e, (2 << 30) // (d * 4)))
+            xp = np.array(xh.array[:n_p])                 # a pageable copy
+            pp = np.empty((n_p, n_out), np.float32)
+
+            def pageable_step():
+                _lib.check(L.lr_score_host(rep.handle, xp.ctypes.data_as(C.c_void_p), n_p, d,
+                                           pp.ctypes.data_as(C.c_void_p), None, None, None))
+            pageable_step()
+            t0 = time.perf_counter()
+            for _ in range(2):
+                pageable_step()
+            dtp = (time.perf_counter() - t0) / 2
+            e2e["pageable"] = {"value": n_p / dtp, "unit": UNIT, "rows_per_step": n_p, "x_gbs": n_p * d * 4 / dtp / 1e9,
+                               "note": "X and P in pageable numpy arrays: lr_score_host's pinned bounce buffers + host copy threads"}
+            del xp, pp
         xh.free(); ph.free()
 
     rec = None
