@@ -140,6 +140,16 @@ int lr_score_host(lr_model* m, const float* X_host, int64_t n_rows, int64_t ldx,
                   float* proba_host, float* decision_host, int32_t* label_host,
                   float* maxprob_host);
 
+/*
+ * lr_score_host for float64 rows (what scikit-learn users hold: numpy's default dtype; the reference itself hands
+ * Python floats to predict, REF/main.py:20-22).  The rows are rounded to fp32 -- the engine's input type -- by the
+ * library's host threads on their way into its pinned buffers, so no fp32 copy of X is ever made in host memory;
+ * values beyond fp32's range become infinities, i.e. non-finite rows.  ldx in float64 elements.
+ */
+int lr_score_host_f64(lr_model* m, const double* X_host, int64_t n_rows, int64_t ldx,
+                      float* proba_host, float* decision_host, int32_t* label_host,
+                      float* maxprob_host);
+
 /* Rows per staging chunk used by lr_score_host (0 = default: about 32 MiB of X per chunk). */
 int lr_model_set_host_chunk_rows(lr_model* m, int64_t rows);
 

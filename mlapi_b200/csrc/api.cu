@@ -52,12 +52,28 @@ public:
         if ((size_t)rows * width < ((size_t)1 << 20) || th_.empty()) { slice(dst, dpitch, src, spitch, width, rows, 0, 1); return; }
         {
             std::lock_guard<std::mutex> l(mu_);
-            job_ = {static_cast<char*>(dst), static_cast<const char*>(src), dpitch, spitch, width, rows, parts};
+            job_ = {static_cast<char*>(dst), static_cast<const char*>(src), dpitch, spitch, width, rows, parts, false};
             left_ = (int)th_.size();
             ++gen_;
         }
         cv_.notify_all();
         slice(dst, dpitch, src, spitch, width, rows, parts - 1, parts);
+        std::unique_lock<std::mutex> l(mu_);
+        done_.wait(l, [this] { return left_ == 0; });
+    }
+    // rows of doubles -> rows of floats (pitches and width in ELEMENTS), the same way
+    void convert2d(float* dst, size_t dpitch, const double* src, size_t spitch, size_t width, int64_t rows) {
+        if (rows <= 0 || width == 0) return;
+        const int parts = (int)th_.size() + 1;
+        if ((size_t)rows * width < ((size_t)1 << 18) || th_.empty()) { cslice(dst, dpitch, src, spitch, width, rows, 0, 1); return; }
+        {
+            std::lock_guard<std::mutex> l(mu_);
+            job_ = {reinterpret_cast<char*>(dst), reinterpret_cast<const char*>(src), dpitch, spitch, width, rows, parts, true};
+            left_ = (int)th_.size();
+            ++gen_;
+        }
+        cv_.notify_all();
+        cslice(dst, dpitch, src, spitch, width, rows, parts - 1, parts);
         std::unique_lock<std::mutex> l(mu_);
         done_.wait(l, [this] { return left_ == 0; });
     }
@@ -68,7 +84,15 @@ public:
     }
 
 private:
-    struct Job { char* dst; const char* src; size_t dpitch, spitch, width; int64_t rows; int parts; };
+    struct Job { char* dst; const char* src; size_t dpitch, spitch, width; int64_t rows; int parts; bool convert; };
+    static void cslice(float* dst, size_t dpitch, const double* src, size_t spitch, size_t width, int64_t rows, int part, int parts) {
+        const int64_t lo = rows * part / parts, hi = rows * (part + 1) / parts;
+        for (int64_t r = lo; r < hi; ++r) {
+            float* d = dst + (size_t)r * dpitch;
+            const double* s = src + (size_t)r * spitch;
+            for (size_t k = 0; k < width; ++k) d[k] = (float)s[k];      // (values beyond float range become inf: a non-finite row)
+        }
+    }
     static void slice(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, int64_t rows, int part, int parts) {
         const int64_t lo = rows * part / parts, hi = rows * (part + 1) / parts;
         char* d = static_cast<char*>(dst) + (size_t)lo * dpitch;
@@ -87,7 +111,8 @@ private:
                 if (stop_) return;
                 j = job_;
             }
-            slice(j.dst, j.dpitch, j.src, j.spitch, j.width, j.rows, me, j.parts);
+            if (j.convert) cslice(reinterpret_cast<float*>(j.dst), j.dpitch, reinterpret_cast<const double*>(j.src), j.spitch, j.width, j.rows, me, j.parts);
+            else slice(j.dst, j.dpitch, j.src, j.spitch, j.width, j.rows, me, j.parts);
             { std::lock_guard<std::mutex> l(mu_); --left_; }
             done_.notify_one();
         }
@@ -414,10 +439,11 @@ static int stage_prepare(Model& m, HostStage& st) {
     return LR_OK;
 }
 
-int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
-                  float* decision_host, int32_t* label_host, float* maxprob_host) {
+// X_host (fp32) or X64 (float64, converted on its way into the pinned bounce buffers): exactly one is given
+static int score_host_impl(lr_model* h, const float* X_host, const double* X64, int64_t n_rows, int64_t ldx, float* proba_host,
+                           float* decision_host, int32_t* label_host, float* maxprob_host) {
     Model* m = reinterpret_cast<Model*>(h);
-    int rc = check_args(m, X_host, n_rows, ldx);
+    int rc = check_args(m, X64 ? static_cast<const void*>(X64) : static_cast<const void*>(X_host), n_rows, ldx);
     if (rc != LR_OK) return rc;
     if (n_rows == 0) return LR_OK;
     DeviceGuard guard(m->device);
@@ -430,7 +456,7 @@ int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx,
     // A request-sized batch in pinned buffers is scored in place over PCIe (zero-copy): one launch and
     // one synchronise instead of an H2D copy, a launch and up to four D2H copies.  Worth it while the
     // batch is a few KB (a micro-batch of /predict rows); bigger batches want HBM-resident staging.
-    if (n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
+    if (!X64 && n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
         void *xd, *pd, *dd, *ld, *md;
         const size_t nr = (size_t)n_rows;
         if (mapped_host(X_host, ((nr - 1) * (size_t)ldx + (size_t)d) * sizeof(float), &xd) &&
@@ -479,7 +505,7 @@ staged:
         return at.type == cudaMemoryTypeUnregistered;
     };
     const bool big = (size_t)n_rows * d * sizeof(float) >= ((size_t)8 << 20);
-    const bool bx = big && pageable(X_host);
+    const bool bx = X64 != nullptr || (big && pageable(X_host));
     const bool bp = big && pageable(proba_host), bd = big && pageable(decision_host), bl = big && pageable(label_host),
                bm = big && pageable(maxprob_host);
     if (bx || bp || bd || bl || bm) {
@@ -510,10 +536,11 @@ staged:
     for (int64_t r0 = 0; r0 < n_rows; r0 += st.chunk_rows, slot = (slot + 1) % HostStage::kSlots) {
         const int64_t rows = (n_rows - r0 < st.chunk_rows) ? (n_rows - r0) : st.chunk_rows;
         cudaStream_t s = st.stream[slot];
-        const float* src = X_host + r0 * ldx;
+        const float* src = X_host ? X_host + r0 * ldx : nullptr;
         LRS_STAGE(collect(slot));                 // (also: the slot's pinned X has left for the device)
         if (bx) {
-            st.pool->copy2d(st.hx[slot], st.pitch * sizeof(float), src, ldx * sizeof(float), d * sizeof(float), rows);
+            if (X64) st.pool->convert2d(st.hx[slot], (size_t)st.pitch, X64 + r0 * ldx, (size_t)ldx, (size_t)d, rows);
+            else st.pool->copy2d(st.hx[slot], st.pitch * sizeof(float), src, ldx * sizeof(float), d * sizeof(float), rows);
             LRS_STAGE(cudaMemcpyAsync(st.x[slot], st.hx[slot], ((rows - 1) * st.pitch + d) * sizeof(float), cudaMemcpyHostToDevice, s));
             pend[slot].active = true;             // (so that the next use of the slot waits for this copy)
         } else if (ldx == st.pitch) {
@@ -554,6 +581,16 @@ staged:
         return fail(LR_ERR_NONFINITE, std::to_string(bad) + " row(s) scored to NaN or infinity (non-finite input)");
     }
     return LR_OK;
+}
+
+int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
+                  float* decision_host, int32_t* label_host, float* maxprob_host) {
+    return score_host_impl(h, X_host, nullptr, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host);
+}
+
+int lr_score_host_f64(lr_model* h, const double* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
+                      float* decision_host, int32_t* label_host, float* maxprob_host) {
+    return score_host_impl(h, nullptr, X_host, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host);
 }
 
 int lr_host_alloc(void** ptr, uint64_t bytes) {

@@ -186,6 +186,11 @@ class B200LogisticRegression:
             raise ValueError(
                 f"X has {Xa.shape[1]} features, but LogisticRegression is expecting "
                 f"{self.n_features_in_} features as input.")
+        # float64 rows (numpy's default, what sklearn users hold) stay as they are: the library rounds them to fp32 on
+        # their way into its pinned staging buffers (lr_score_host_f64) -- an fp32 copy made here by numpy, on one
+        # thread, took ten times as long as scoring it
+        if Xa.dtype == np.float64:
+            return np.ascontiguousarray(Xa)
         return np.ascontiguousarray(Xa, dtype=np.float32)
 
     # ---- the one scoring call ----------------------------------------------------------------
@@ -206,9 +211,10 @@ class B200LogisticRegression:
 
         def run(rep: _Replica, lo: int, hi: int):
             sl = lambda a: None if a is None else a[lo:hi]  # noqa: E731
-            return rep.lib.lr_score_host(rep.handle, _ptr(Xf[lo:hi]), hi - lo, d, _ptr(sl(out["proba"])),
-                                         _ptr(sl(out["decision"])), _ptr(sl(out["label"])),
-                                         _ptr(sl(out["maxprob"]))), _lib.last_error()
+            fn = rep.lib.lr_score_host_f64 if Xf.dtype == np.float64 else rep.lib.lr_score_host
+            return fn(rep.handle, _ptr(Xf[lo:hi]), hi - lo, d, _ptr(sl(out["proba"])),
+                      _ptr(sl(out["decision"])), _ptr(sl(out["label"])),
+                      _ptr(sl(out["maxprob"]))), _lib.last_error()
 
         with self._lock:
             G = len(self._replicas)

@@ -450,6 +450,12 @@ def test_pageable_host_arrays_go_through_pinned_bounce_buffers(eng, d, ns, n, ch
     got = clf.score_rows(X, **ALL)                           # pageable in
     for k in ref:
         assert np.array_equal(ref[k], got[k]), k
+    got64 = clf.score_rows(X.astype(np.float64), **ALL)      # float64 in: rounded to fp32 inside lr_score_host_f64
+    for k in ref:
+        assert np.array_equal(ref[k], got64[k]), k
+    few = clf.score_rows(X[:7].astype(np.float64), **ALL)    # ... and a handful of float64 rows
+    for k in ref:
+        assert np.array_equal(ref[k][:7], few[k]) or ns > 16, k      # (the tensor path scales each call from its own rows)
     z = orc.decision_function(X[:4000], W, b)
     parity.assert_parity({k: v[:4000] for k, v in got.items()}, z if ns > 1 else z.ravel(), orc.predict_proba(X[:4000], W, b),
                          orc.predict_index(X[:4000], W, b), f"pageable d={d} ns={ns}",
