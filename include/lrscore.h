@@ -150,6 +150,15 @@ int lr_score_host_f64(lr_model* m, const double* X_host, int64_t n_rows, int64_t
                       float* proba_host, float* decision_host, int32_t* label_host,
                       float* maxprob_host);
 
+/*
+ * The general form: X_host fp32 (x_is_f64 == 0) or float64; proba / decision / maxprob arrays of fp32
+ * (out_is_f64 == 0) or of float64 -- scikit-learn's output type -- widened from the engine's fp32 by the same host
+ * threads on their way out of the pinned buffers (numpy's astype of a 4 GB P matrix takes seconds on its one thread).
+ */
+int lr_score_host_ex(lr_model* m, const void* X_host, int x_is_f64, int64_t n_rows, int64_t ldx,
+                     void* proba_host, void* decision_host, int32_t* label_host, void* maxprob_host,
+                     int out_is_f64);
+
 /* Rows per staging chunk used by lr_score_host (0 = default: about 32 MiB of X per chunk). */
 int lr_model_set_host_chunk_rows(lr_model* m, int64_t rows);
 

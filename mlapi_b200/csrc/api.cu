@@ -77,6 +77,26 @@ public:
         std::unique_lock<std::mutex> l(mu_);
         done_.wait(l, [this] { return left_ == 0; });
     }
+    // floats -> doubles, contiguous (`count` elements), the same way
+    void widen1d(double* dst, const float* src, size_t count) {
+        const size_t blk = 16384, n = count / blk;               // 64 KB of floats per share
+        if (n >= 16 && !th_.empty()) {
+            const int parts = (int)th_.size() + 1;
+            {
+                std::lock_guard<std::mutex> l(mu_);
+                job_ = {reinterpret_cast<char*>(dst), reinterpret_cast<const char*>(src), blk, blk, blk, (int64_t)n, parts, false, true};
+                left_ = (int)th_.size();
+                ++gen_;
+            }
+            cv_.notify_all();
+            wslice(dst, src, blk, (int64_t)n, parts - 1, parts);
+            std::unique_lock<std::mutex> l(mu_);
+            done_.wait(l, [this] { return left_ == 0; });
+            for (size_t k = n * blk; k < count; ++k) dst[k] = (double)src[k];
+        } else {
+            for (size_t k = 0; k < count; ++k) dst[k] = (double)src[k];
+        }
+    }
     void copy1d(void* dst, const void* src, size_t bytes) {      // contiguous: shared out in 64 KB blocks
         const size_t blk = (size_t)64 << 10, n = bytes / blk;
         copy2d(dst, blk, src, blk, blk, (int64_t)n);
@@ -84,7 +104,11 @@ public:
     }
 
 private:
-    struct Job { char* dst; const char* src; size_t dpitch, spitch, width; int64_t rows; int parts; bool convert; };
+    struct Job { char* dst; const char* src; size_t dpitch, spitch, width; int64_t rows; int parts; bool convert; bool widen = false; };
+    static void wslice(double* dst, const float* src, size_t blk, int64_t blocks, int part, int parts) {
+        const size_t lo = (size_t)(blocks * part / parts) * blk, hi = (size_t)(blocks * (part + 1) / parts) * blk;
+        for (size_t k = lo; k < hi; ++k) dst[k] = (double)src[k];
+    }
     static void cslice(float* dst, size_t dpitch, const double* src, size_t spitch, size_t width, int64_t rows, int part, int parts) {
         const int64_t lo = rows * part / parts, hi = rows * (part + 1) / parts;
         for (int64_t r = lo; r < hi; ++r) {
@@ -111,7 +135,8 @@ private:
                 if (stop_) return;
                 j = job_;
             }
-            if (j.convert) cslice(reinterpret_cast<float*>(j.dst), j.dpitch, reinterpret_cast<const double*>(j.src), j.spitch, j.width, j.rows, me, j.parts);
+            if (j.widen) wslice(reinterpret_cast<double*>(j.dst), reinterpret_cast<const float*>(j.src), j.width, j.rows, me, j.parts);
+            else if (j.convert) cslice(reinterpret_cast<float*>(j.dst), j.dpitch, reinterpret_cast<const double*>(j.src), j.spitch, j.width, j.rows, me, j.parts);
             else slice(j.dst, j.dpitch, j.src, j.spitch, j.width, j.rows, me, j.parts);
             { std::lock_guard<std::mutex> l(mu_); --left_; }
             done_.notify_one();
@@ -440,8 +465,13 @@ static int stage_prepare(Model& m, HostStage& st) {
 }
 
 // X_host (fp32) or X64 (float64, converted on its way into the pinned bounce buffers): exactly one is given
-static int score_host_impl(lr_model* h, const float* X_host, const double* X64, int64_t n_rows, int64_t ldx, float* proba_host,
-                           float* decision_host, int32_t* label_host, float* maxprob_host) {
+// out64: proba / decision / maxprob are arrays of double (widened from the engine's fp32 on their way out of the pinned
+// buffers)
+static int score_host_impl(lr_model* h, const float* X_host, const double* X64, int64_t n_rows, int64_t ldx, void* proba_v,
+                           void* decision_v, int32_t* label_host, void* maxprob_v, bool out64) {
+    float* proba_host = static_cast<float*>(proba_v);           // (as fp32 arrays unless out64)
+    float* decision_host = static_cast<float*>(decision_v);
+    float* maxprob_host = static_cast<float*>(maxprob_v);
     Model* m = reinterpret_cast<Model*>(h);
     int rc = check_args(m, X64 ? static_cast<const void*>(X64) : static_cast<const void*>(X_host), n_rows, ldx);
     if (rc != LR_OK) return rc;
@@ -456,7 +486,7 @@ static int score_host_impl(lr_model* h, const float* X_host, const double* X64, 
     // A request-sized batch in pinned buffers is scored in place over PCIe (zero-copy): one launch and
     // one synchronise instead of an H2D copy, a launch and up to four D2H copies.  Worth it while the
     // batch is a few KB (a micro-batch of /predict rows); bigger batches want HBM-resident staging.
-    if (!X64 && n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
+    if (!X64 && !out64 && n_rows * d * (int64_t)sizeof(float) <= 64 * 1024 && (int64_t)n_rows * m->n_out <= 64 * 1024) {
         void *xd, *pd, *dd, *ld, *md;
         const size_t nr = (size_t)n_rows;
         if (mapped_host(X_host, ((nr - 1) * (size_t)ldx + (size_t)d) * sizeof(float), &xd) &&
@@ -506,8 +536,8 @@ staged:
     };
     const bool big = (size_t)n_rows * d * sizeof(float) >= ((size_t)8 << 20);
     const bool bx = X64 != nullptr || (big && pageable(X_host));
-    const bool bp = big && pageable(proba_host), bd = big && pageable(decision_host), bl = big && pageable(label_host),
-               bm = big && pageable(maxprob_host);
+    const bool bp = proba_host && (out64 || (big && pageable(proba_host))), bd = decision_host && (out64 || (big && pageable(decision_host))),
+               bl = big && pageable(label_host), bm = maxprob_host && (out64 || (big && pageable(maxprob_host)));
     if (bx || bp || bd || bl || bm) {
         if (!st.pool) st.pool = new CopyPool(getenv("LRS_HOST_COPY_THREADS") ? atoi(getenv("LRS_HOST_COPY_THREADS")) : 4);
         for (int i = 0; i < HostStage::kSlots; ++i) {
@@ -525,10 +555,16 @@ staged:
         const cudaError_t e = cudaStreamSynchronize(st.stream[sl]);
         if (e != cudaSuccess) return e;
         const int64_t r0 = pend[sl].r0, rows = pend[sl].rows;
-        if (bp) st.pool->copy1d(proba_host + r0 * m->n_out, st.hproba[sl], (size_t)rows * m->n_out * sizeof(float));
-        if (bd) st.pool->copy1d(decision_host + r0 * m->n_scores, st.hdecision[sl], (size_t)rows * m->n_scores * sizeof(float));
+        if (out64) {
+            if (bp) st.pool->widen1d(static_cast<double*>(proba_v) + r0 * m->n_out, st.hproba[sl], (size_t)rows * m->n_out);
+            if (bd) st.pool->widen1d(static_cast<double*>(decision_v) + r0 * m->n_scores, st.hdecision[sl], (size_t)rows * m->n_scores);
+            if (bm) st.pool->widen1d(static_cast<double*>(maxprob_v) + r0, st.hmaxprob[sl], (size_t)rows);
+        } else {
+            if (bp) st.pool->copy1d(proba_host + r0 * m->n_out, st.hproba[sl], (size_t)rows * m->n_out * sizeof(float));
+            if (bd) st.pool->copy1d(decision_host + r0 * m->n_scores, st.hdecision[sl], (size_t)rows * m->n_scores * sizeof(float));
+            if (bm) std::memcpy(maxprob_host + r0, st.hmaxprob[sl], (size_t)rows * sizeof(float));
+        }
         if (bl) std::memcpy(label_host + r0, st.hlabel[sl], (size_t)rows * sizeof(int32_t));
-        if (bm) std::memcpy(maxprob_host + r0, st.hmaxprob[sl], (size_t)rows * sizeof(float));
         pend[sl].active = false;
         return cudaSuccess;
     };
@@ -585,12 +621,19 @@ staged:
 
 int lr_score_host(lr_model* h, const float* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
                   float* decision_host, int32_t* label_host, float* maxprob_host) {
-    return score_host_impl(h, X_host, nullptr, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host);
+    return score_host_impl(h, X_host, nullptr, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host, false);
 }
 
 int lr_score_host_f64(lr_model* h, const double* X_host, int64_t n_rows, int64_t ldx, float* proba_host,
                       float* decision_host, int32_t* label_host, float* maxprob_host) {
-    return score_host_impl(h, nullptr, X_host, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host);
+    return score_host_impl(h, nullptr, X_host, n_rows, ldx, proba_host, decision_host, label_host, maxprob_host, false);
+}
+
+int lr_score_host_ex(lr_model* h, const void* X_host, int x_is_f64, int64_t n_rows, int64_t ldx, void* proba_host,
+                     void* decision_host, int32_t* label_host, void* maxprob_host, int out_is_f64) {
+    return score_host_impl(h, x_is_f64 ? nullptr : static_cast<const float*>(X_host),
+                           x_is_f64 ? static_cast<const double*>(X_host) : nullptr, n_rows, ldx, proba_host, decision_host,
+                           label_host, maxprob_host, out_is_f64 != 0);
 }
 
 int lr_host_alloc(void** ptr, uint64_t bytes) {

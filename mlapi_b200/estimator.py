@@ -194,27 +194,28 @@ class B200LogisticRegression:
         return np.ascontiguousarray(Xa, dtype=np.float32)
 
     # ---- the one scoring call ----------------------------------------------------------------
-    def score_rows(self, X, proba=False, decision=False, label=False, maxprob=False) -> dict:
-        """Single pass over X producing any subset of {proba, decision, label, maxprob}."""
+    def score_rows(self, X, proba=False, decision=False, label=False, maxprob=False, out_f64=False) -> dict:
+        """Single pass over X producing any subset of {proba, decision, label, maxprob}.  Host arrays: float32
+        results, or float64 ones (`out_f64`, scikit-learn's output type) widened by the library's own host threads."""
         if _is_torch_tensor(X) and X.is_cuda:
             return self._score_device(X, proba, decision, label, maxprob)
         Xf = self._validate_host(X)
         n = Xf.shape[0]
         ns = self.coef_.shape[0]
+        ft = np.float64 if out_f64 else np.float32
         out = {
-            "proba": np.empty((n, max(ns, 2)), np.float32) if proba else None,
-            "decision": np.empty((n,) if ns == 1 else (n, ns), np.float32) if decision else None,
+            "proba": np.empty((n, max(ns, 2)), ft) if proba else None,
+            "decision": np.empty((n,) if ns == 1 else (n, ns), ft) if decision else None,
             "label": np.empty((n,), np.int32) if label else None,
-            "maxprob": np.empty((n,), np.float32) if maxprob else None,
+            "maxprob": np.empty((n,), ft) if maxprob else None,
         }
         d = self.n_features_in_
 
         def run(rep: _Replica, lo: int, hi: int):
             sl = lambda a: None if a is None else a[lo:hi]  # noqa: E731
-            fn = rep.lib.lr_score_host_f64 if Xf.dtype == np.float64 else rep.lib.lr_score_host
-            return fn(rep.handle, _ptr(Xf[lo:hi]), hi - lo, d, _ptr(sl(out["proba"])),
-                      _ptr(sl(out["decision"])), _ptr(sl(out["label"])),
-                      _ptr(sl(out["maxprob"]))), _lib.last_error()
+            return rep.lib.lr_score_host_ex(rep.handle, _ptr(Xf[lo:hi]), int(Xf.dtype == np.float64), hi - lo, d,
+                                            _ptr(sl(out["proba"])), _ptr(sl(out["decision"])), _ptr(sl(out["label"])),
+                                            _ptr(sl(out["maxprob"])), int(out_f64)), _lib.last_error()
 
         with self._lock:
             G = len(self._replicas)
@@ -292,11 +293,11 @@ class B200LogisticRegression:
 
     def decision_function(self, X):
         """SK/linear_model/_base.py:366-396: (n,) for a binary model, (n, C) otherwise."""
-        return self._cast(self.score_rows(X, decision=True)["decision"])
+        return self._cast(self.score_rows(X, decision=True, out_f64=self.out_dtype == np.float64)["decision"])
 
     def predict_proba(self, X):
         """SK/linear_model/_logistic.py:1595-1625."""
-        return self._cast(self.score_rows(X, proba=True)["proba"])
+        return self._cast(self.score_rows(X, proba=True, out_f64=self.out_dtype == np.float64)["proba"])
 
     def predict_log_proba(self, X):
         """SK/linear_model/_logistic.py:1627-1650: log of predict_proba."""
@@ -313,7 +314,7 @@ class B200LogisticRegression:
     def predict_with_max_proba(self, X):
         """`predict(X)` and `predict_proba(X).max(axis=1)` -- the pair REF/main.py:21-22 computes
         with two passes -- from one pass over X."""
-        out = self.score_rows(X, label=True, maxprob=True)
+        out = self.score_rows(X, label=True, maxprob=True, out_f64=self.out_dtype == np.float64)
         if _is_torch_tensor(out["label"]):
             return out["label"], out["maxprob"]
         return self.classes_.take(out["label"], axis=0), self._cast(out["maxprob"])

@@ -453,6 +453,11 @@ def test_pageable_host_arrays_go_through_pinned_bounce_buffers(eng, d, ns, n, ch
     got64 = clf.score_rows(X.astype(np.float64), **ALL)      # float64 in: rounded to fp32 inside lr_score_host_f64
     for k in ref:
         assert np.array_equal(ref[k], got64[k]), k
+    wide64 = clf.score_rows(X, out_f64=True, **ALL)          # float64 results: the same fp32 values, widened
+    for k in ref:
+        assert wide64[k].dtype == (np.int32 if k == "label" else np.float64) and np.array_equal(ref[k].astype(wide64[k].dtype), wide64[k]), k
+    few64 = clf.score_rows(X[:3], out_f64=True, **ALL)
+    assert few64["proba"].dtype == np.float64 and (ns > 16 or np.array_equal(ref["proba"][:3].astype(np.float64), few64["proba"]))
     few = clf.score_rows(X[:7].astype(np.float64), **ALL)    # ... and a handful of float64 rows
     for k in ref:
         assert np.array_equal(ref[k][:7], few[k]) or ns > 16, k      # (the tensor path scales each call from its own rows)
