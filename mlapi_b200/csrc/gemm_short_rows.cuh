@@ -321,10 +321,8 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {                    // (128-bit broadcast loads: 16 instead of 64 per tile)
                 const float4 cs = *reinterpret_cast<const float4*>(cscale_s + i), bi = *reinterpret_cast<const float4*>(bias_s + i);
-                v[i] = fmaf(v[i], cs.x, bi.x);                   // padding carries -inf
-                v[i + 1] = fmaf(v[i + 1], cs.y, bi.y);
-                v[i + 2] = fmaf(v[i + 2], cs.z, bi.z);
-                v[i + 3] = fmaf(v[i + 3], cs.w, bi.w);
+                fma2(v[i], v[i + 1], cs.x, cs.y, bi.x, bi.y);    // padding carries -inf
+                fma2(v[i + 2], v[i + 3], cs.z, cs.w, bi.z, bi.w);
                 gm = fmaxf(fmaxf(gm, v[i]), fmaxf(v[i + 1], fmaxf(v[i + 2], v[i + 3])));
             }
             int garg = 31;
@@ -333,20 +331,24 @@ short_rows_kernel(const __grid_constant__ CUtensorMap map_whi, const __grid_cons
             if (p.decision) store_rows_coalesced(stage, v, C, lane, p.decision + row0 * C, rows_valid, z_al);
             const float ez = fmaxf(p.kappa * fmaxf(psum_scale, fabsf(gm)) + floor_err, 1e-30f);
             const float tau = gm - 2.0f * ez;
-            float gs = 0.0f;
+            float gs0 = 0.0f, gs1 = 0.0f;
             int gnear = 0;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                gnear += v[i] > tau ? 1 : 0;
-                v[i] = ex2((v[i] - gm) * kLog2e);                // (padding: exp(-inf) = 0)
-                gs += v[i];
+            for (int i = 0; i < 32; i += 2) {                    // two columns per multiply / add (packed fp32)
+                gnear += (v[i] > tau ? 1 : 0) + (v[i + 1] > tau ? 1 : 0);
+                sub2(v[i], v[i + 1], gm, gm);
+                mul2(v[i], v[i + 1], kLog2e, kLog2e);
+                v[i] = ex2(v[i]);                                // (padding: exp(-inf) = 0)
+                v[i + 1] = ex2(v[i + 1]);
+                add2(gs0, gs1, v[i], v[i + 1]);
             }
+            const float gs = gs0 + gs1;
             const float inv = __frcp_rn(gs);
             // |dp| ~ p (1 - p) |dz| is largest for the class nearest to one half, and that is always the top one
             // (p (1 - p) rises up to 1/2, and no class but the top one can pass it): its probability is `inv`
             const bool risk = p.need_prob && inv * (1.0f - inv) > 8e-6f / ez;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] *= inv;
+            for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], inv, inv);
             if (p.proba) store_rows_coalesced(stage, v, C, lane, p.proba + row0 * C, rows_valid, p_al);
             if (live) {
                 if (p.label) __stcs(p.label + row, garg);

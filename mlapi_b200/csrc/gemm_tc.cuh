@@ -337,6 +337,25 @@ __device__ __forceinline__ float ex2(float x) {
 }
 // Two scaled values -> packed fp16 (hi, hi) and packed fp16 residuals (lo, lo), with the packed
 // fp32x2 / f16x2 conversions of sm_100: 7 instructions per pair.
+// Packed fp32 arithmetic (two lanes of a 64-bit register pair per instruction; same IEEE results as the scalar forms):
+// an epilogue that is bound by its instruction count does its multiplies and adds two columns at a time.
+__device__ __forceinline__ void fma2(float& a0, float& a1, float b0, float b1, float c0, float c1) {   // a = a * b + c
+    asm("{\n\t.reg .b64 a, b, c;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tmov.b64 c, {%4, %5};\n\t"
+        "fma.rn.f32x2 a, a, b, c;\n\tmov.b64 {%0, %1}, a;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void mul2(float& a0, float& a1, float b0, float b1) {                        // a = a * b
+    asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tmul.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void sub2(float& a0, float& a1, float b0, float b1) {                        // a = a - b
+    asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tsub.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {                        // a = a + b
+    asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tadd.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
 __device__ __forceinline__ void split_pair(float a, float b, float sa, float sb, uint32_t& hi, uint32_t& lo) {
     asm("{\n\t"
         ".reg .b64 v, s, r;\n\t"
