@@ -747,7 +747,7 @@ int short_launch(const Model& m, const ScoreArgs& a) {
     // tile while the MMAs of its previous one are still on their way (measured: the hand-over, not the work, set the pace)
     p.op_stages = 2;             // four (rows of <= 32 floats leave the room) measured the same
     // measured (tools/shape_sweep.py): d=16, C=26 2.8 -> 3.9 TB/s with 1 + 3 sets, d=54, C=20 3.0 -> 3.9 with 2 + 2
-    p.conv_sets = d <= 32 ? 1 : 2;
+    p.conv_sets = d < 32 ? 1 : 2;                    // (d = 32, 20 classes: 3.70 TB/s with one set, 3.80 with two; d = 16, 26 classes: 3.74 against 3.04)
     if (const char* e = getenv("LRS_SHORT_CONV_SETS")) p.conv_sets = atoi(e) == 1 ? 1 : 2;
     const int room = 227 * 1024 - 1024 - SrSmem::op - p.op_stages * kSrOpBytes;
     p.raw_stages = room / p.stage_bytes < kSrMaxRaw ? room / p.stage_bytes : kSrMaxRaw;
