@@ -16,6 +16,8 @@ timeout 300 python tools/rescoring_rate.py > gpurun_out/r2_rescoring_rate.txt 2>
 timeout 300 python tools/gemm_kappa.py > gpurun_out/r2_gemm_accumulation_error.txt 2>&1
 timeout 300 python tools/gemm_kappa.py --short >> gpurun_out/r2_gemm_accumulation_error.txt 2>&1
 timeout 300 python tools/latency_single.py > gpurun_out/r2_latency_single.json 2>/dev/null
+timeout 300 python tools/output_patterns.py > gpurun_out/r2_output_patterns.md 2>&1
+python tools/sass_markers.py > gpurun_out/r2_sass_markers.txt 2>&1
 if [ "$1" != "skip-ncu" ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu"
   timeout 600 $CMD > gpurun_out/r2_plain.log 2>&1 &&
