@@ -51,7 +51,7 @@ typedef struct lr_model lr_model;
 const char* lr_last_error(void);
 
 /* Library ABI version (bumped on any signature change). */
-int lr_abi_version(void);
+int lr_abi_version(void);   /* 2 (round 2: additive over 1 -- lr_model_update, lr_grad_*, lr_score_host_f64 / _ex, ...) */
 
 /* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
 uint64_t lr_launch_count(void);

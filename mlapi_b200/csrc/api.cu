@@ -251,7 +251,7 @@ using namespace lrs;
 extern "C" {
 
 const char* lr_last_error(void) { return t_last_error.c_str(); }
-int lr_abi_version(void) { return 1; }
+int lr_abi_version(void) { return 2; }
 uint64_t lr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int lr_model_create(const double* coef, const double* intercept, int32_t n_scores,
